@@ -1,0 +1,495 @@
+"""epp_b200 — Python host side of the B200-native validity-check path.
+
+Thin ctypes binding over the C ABI of ``libepp_b200.so`` (``include/epp_c_api.h``) plus a
+``World`` class that mirrors the reference ``World`` (``include/World.h:16-127`` of
+Autonomous-Drone-Racing-Lab/Efficient-Path-Planner): same method names, argument meaning and
+error behaviour, with batched entry points added.  PyTorch is used only for device memory,
+streams and ``torch.distributed``; all checks run in the hand-written sm_100a kernels.  There
+is no CPU fallback: if the library is missing or no GPU is present the calls raise.
+
+The directory name contains a hyphen, so import it through the repo-root shim:
+``import epp_b200``.
+"""
+import ctypes as C
+import json
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libepp_b200.so")
+DEFAULT_CONFIG = os.path.join(_HERE, "config", "config.json")
+
+BP_AUTO, BP_BRUTE, BP_BITS, BP_GRID = 0, 1, 2, 3
+BP_NAMES = {BP_AUTO: "auto", BP_BRUTE: "brute", BP_BITS: "bits", BP_GRID: "grid"}
+
+
+class EppError(RuntimeError):
+    """Raised for every non-zero epp_status (message = epp_last_error())."""
+
+    def __init__(self, status, message):
+        super().__init__(message)
+        self.status = status
+
+
+class ObbDesc(C.Structure):
+    _fields_ = [("position", C.c_double * 3), ("size", C.c_double * 3), ("filling", C.c_int)]
+
+
+class Obb(C.Structure):
+    _fields_ = [("center", C.c_double * 3), ("half", C.c_double * 3), ("rot", C.c_double * 9),
+                ("aabb_min", C.c_double * 3), ("aabb_max", C.c_double * 3), ("inflate", C.c_double),
+                ("filling", C.c_int), ("is_gate", C.c_int), ("object_id", C.c_int),
+                ("obb_index", C.c_int)]
+
+
+_dp = C.POINTER(C.c_double)
+_up = C.POINTER(C.c_uint32)
+_vp = C.c_void_p
+
+# name -> (restype, argtypes); every symbol include/epp_c_api.h declares.
+SIGNATURES = {
+    "epp_last_error": (C.c_char_p, []),
+    "epp_version": (C.c_char_p, []),
+    "epp_device_count": (C.c_int, [C.POINTER(C.c_int)]),
+    "epp_world_create": (C.c_int, [C.c_double, C.c_double, C.POINTER(_vp)]),
+    "epp_world_destroy": (C.c_int, [_vp]),
+    "epp_world_set_gate_geometry": (C.c_int, [_vp, C.c_int, C.POINTER(ObbDesc), C.c_int]),
+    "epp_world_set_obstacle_geometry": (C.c_int, [_vp, C.POINTER(ObbDesc), C.c_int]),
+    "epp_world_reset": (C.c_int, [_vp]),
+    "epp_world_add_gate": (C.c_int, [_vp, C.c_int, _dp]),
+    "epp_world_update_gate": (C.c_int, [_vp, C.c_int, _dp]),
+    "epp_world_add_obstacle": (C.c_int, [_vp, C.c_int, _dp]),
+    "epp_world_parse_gates_and_obstacles": (C.c_int, [_vp, _dp, C.c_int, _dp, C.c_int]),
+    "epp_world_size": (C.c_int, [_vp, C.POINTER(C.c_int)]),
+    "epp_world_get_obb": (C.c_int, [_vp, C.c_int, C.POINTER(Obb)]),
+    "epp_world_set_broadphase": (C.c_int, [_vp, C.c_int]),
+    "epp_world_commit": (C.c_int, [_vp]),
+    "epp_world_epoch": (C.c_int, [_vp, C.POINTER(C.c_uint64)]),
+    "epp_world_active_broadphase": (C.c_int, [_vp, C.POINTER(C.c_int)]),
+    "epp_check_states": (C.c_int, [_vp, _vp, C.c_size_t, C.c_int, _vp]),
+    "epp_check_states_mindist": (C.c_int, [_vp, _vp, C.c_size_t, C.c_double, _vp]),
+    "epp_check_segments": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_int, _vp]),
+    "epp_is_valid": (C.c_int, [_vp, _dp, C.c_int, C.POINTER(C.c_int)]),
+    "epp_check_motion": (C.c_int, [_vp, _dp, _dp, C.c_int, C.POINTER(C.c_int)]),
+    "epp_check_trajectories": (C.c_int, [_vp, _vp, C.c_size_t, C.c_size_t, C.c_size_t, C.c_size_t,
+                                         C.c_int, C.c_double, _vp, _vp, _vp]),
+    "epp_check_poly_trajectories": (C.c_int, [_vp, _vp, _vp, _vp, C.c_size_t, C.c_int, C.c_int,
+                                              C.c_double, C.c_size_t, _vp, _vp, _vp, _vp]),
+    "epp_check_states_dev": (C.c_int, [_vp, _vp, C.c_size_t, C.c_int, _vp, _vp]),
+    "epp_check_states_mindist_dev": (C.c_int, [_vp, _vp, C.c_size_t, C.c_double, _vp, _vp]),
+    "epp_check_segments_dev": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_int, _vp, _vp]),
+    "epp_check_trajectories_dev": (C.c_int, [_vp, _vp, C.c_size_t, C.c_size_t, C.c_size_t,
+                                             C.c_size_t, C.c_int, C.c_double, _vp, _vp, _vp, _vp]),
+    "epp_check_poly_trajectories_dev": (C.c_int, [_vp, _vp, _vp, _vp, C.c_size_t, C.c_int, C.c_int,
+                                                  C.c_double, C.c_size_t, _vp, _vp, _vp, _vp, _vp]),
+    "epp_shard_range": (C.c_int, [C.c_size_t, C.c_int, C.c_int, C.c_size_t,
+                                  C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
+    "epp_mask_summary_dev": (C.c_int, [_vp, C.c_size_t, C.c_uint64, _vp, _vp]),
+    "epp_gen_states_dev": (C.c_int, [C.c_uint64, C.c_uint64, C.c_size_t, _dp, _dp, _vp, _vp]),
+    "epp_gen_segments_dev": (C.c_int, [C.c_uint64, C.c_uint64, C.c_size_t, _dp, _dp, C.c_double,
+                                       _vp, _vp, _vp]),
+    "epp_kernel_launch_count": (C.c_uint64, []),
+    "epp_set_tuning": (C.c_int, [C.c_char_p, C.c_int]),
+    "epp_get_tuning": (C.c_int, [C.c_char_p, C.POINTER(C.c_int)]),
+}
+
+_lib = None
+
+
+def lib():
+    """Load libepp_b200.so (built in-tree by __graft_entry__.build()).  No fallback."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise EppError(-1, "libepp_b200.so is not built (run `python __graft_entry__.py build` "
+                               "or `make -C efficient-path-planner_b200/csrc`); there is no CPU fallback")
+        L = C.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(L, name)
+            fn.restype = res
+            fn.argtypes = args
+        _lib = L
+    return _lib
+
+
+def _chk(status):
+    if status != 0:
+        raise EppError(status, lib().epp_last_error().decode())
+
+
+def device_count():
+    n = C.c_int(0)
+    _chk(lib().epp_device_count(C.byref(n)))
+    return n.value
+
+
+def kernel_launch_count():
+    return int(lib().epp_kernel_launch_count())
+
+
+def set_tuning(key, value):
+    _chk(lib().epp_set_tuning(key.encode(), int(value)))
+
+
+def get_tuning(key):
+    v = C.c_int(0)
+    _chk(lib().epp_get_tuning(key.encode(), C.byref(v)))
+    return v.value
+
+
+def shard_range(n, rank, world_size, align=1024):
+    """Contiguous unit range of `rank`: boundaries on whole mask words."""
+    b, e = C.c_size_t(0), C.c_size_t(0)
+    _chk(lib().epp_shard_range(n, rank, world_size, align, C.byref(b), C.byref(e)))
+    return b.value, e.value
+
+
+def _f64(a, shape=None):
+    a = np.ascontiguousarray(a, dtype=np.float64)
+    if shape is not None:
+        a = a.reshape(shape)
+    return a
+
+
+def _ptr(a):
+    return a.ctypes.data if a is not None else None
+
+
+def unpack_mask(mask, n):
+    """uint32 mask words -> bool[n] (bit i&31 of word i>>5)."""
+    bits = np.unpackbits(np.ascontiguousarray(mask, dtype="<u4").view(np.uint8), bitorder="little")
+    return bits[:n].astype(bool)
+
+
+def mask_words(n):
+    return (n + 31) // 32
+
+
+def descs_from_component(component):
+    """config component dict (file order, src/ConfigParserYAML.cpp:54-73) -> ObbDesc array."""
+    arr = (ObbDesc * len(component))()
+    for i, (_, o) in enumerate(component.items()):
+        arr[i].position[:] = [float(v) for v in o["position"]]
+        arr[i].size[:] = [float(v) for v in o["size"]]
+        arr[i].filling = 1 if o["type"] == "filling" else 0
+    return arr
+
+
+def load_config(path=None):
+    with open(path or DEFAULT_CONFIG) as f:
+        return json.load(f)
+
+
+class World:
+    """GPU-resident World.  Mirrors include/World.h of the reference.
+
+    ``World(config)`` takes the parsed config dict (or a path) where the reference takes a
+    ``ConfigParser``.  Mutators mark the world dirty; the next check commits a new device
+    epoch automatically (the reference mutates its R-tree in place).
+    """
+
+    def __init__(self, config=None, broadphase=BP_AUTO):
+        if config is None or isinstance(config, str):
+            config = load_config(config)
+        self.config = config
+        L = lib()
+        infl = config["world_properties"]["inflate_radius"]  # include/World.h:22-23
+        h = _vp()
+        _chk(L.epp_world_create(float(infl["gate"]), float(infl["obstacle"]), C.byref(h)))
+        self._h = h
+        for tid, name in config["gate_id_to_name_mapping"].items():
+            d = descs_from_component(config["component_geometry"][name])
+            _chk(L.epp_world_set_gate_geometry(self._h, int(tid), d, len(d)))
+        d = descs_from_component(config["component_geometry"]["obstacle"])
+        _chk(L.epp_world_set_obstacle_geometry(self._h, d, len(d)))
+        if broadphase != BP_AUTO:
+            self.set_broadphase(broadphase)
+        self._dirty = True
+
+    def __del__(self):
+        h = getattr(self, "_h", None)
+        if h:
+            try:
+                lib().epp_world_destroy(h)
+            except Exception:
+                pass
+            self._h = None
+
+    # -- reference World API (include/World.h:29-92) -------------------------------------
+    def resetWorld(self):
+        _chk(lib().epp_world_reset(self._h))
+        self._dirty = True
+
+    def addGate(self, gateId, coordinates):
+        c = _f64(coordinates, 7)
+        _chk(lib().epp_world_add_gate(self._h, int(gateId), c.ctypes.data_as(_dp)))
+        self._dirty = True
+
+    def updateGatePosition(self, gateId, coordinates):
+        c = _f64(coordinates, 7)
+        _chk(lib().epp_world_update_gate(self._h, int(gateId), c.ctypes.data_as(_dp)))
+        self._dirty = True
+
+    def addObstacle(self, obstacleId, coordinates):
+        c = _f64(coordinates, 6)
+        _chk(lib().epp_world_add_obstacle(self._h, int(obstacleId), c.ctypes.data_as(_dp)))
+        self._dirty = True
+
+    def checkPointValidity(self, point, arg=False):
+        """Both reference overloads: bool -> canPassGate, float -> minDistance
+        (src/World.cpp:80-128)."""
+        p = _f64(point, (1, 3))
+        if isinstance(arg, (bool, np.bool_)):
+            self._sync()
+            v = C.c_int(0)
+            _chk(lib().epp_is_valid(self._h, p.ctypes.data_as(_dp), int(arg), C.byref(v)))
+            return bool(v.value)
+        return bool(unpack_mask(self.check_states_mindist(p, float(arg)), 1)[0])
+
+    def checkRayValid(self, start, end, canPassGate=False):
+        self._sync()
+        a, b = _f64(start, 3), _f64(end, 3)
+        v = C.c_int(0)
+        _chk(lib().epp_check_motion(self._h, a.ctypes.data_as(_dp), b.ctypes.data_as(_dp),
+                                    int(canPassGate), C.byref(v)))
+        return bool(v.value)
+
+    # -- PathPlanner::parseGatesAndObstacles (src/PathPlanner.cpp:60-78) -----------------
+    def parse_gates_and_obstacles(self, gates, obstacles):
+        g = _f64(gates, (-1, 7)) if len(gates) else np.zeros((0, 7))
+        o = _f64(obstacles, (-1, 6)) if len(obstacles) else np.zeros((0, 6))
+        _chk(lib().epp_world_parse_gates_and_obstacles(self._h, g.ctypes.data_as(_dp), g.shape[0],
+                                                       o.ctypes.data_as(_dp), o.shape[0]))
+        self._dirty = False
+
+    # -- housekeeping ---------------------------------------------------------------------
+    def set_broadphase(self, mode):
+        _chk(lib().epp_world_set_broadphase(self._h, int(mode)))
+        self._dirty = True
+
+    def commit(self):
+        _chk(lib().epp_world_commit(self._h))
+        self._dirty = False
+
+    def _sync(self):
+        if self._dirty:
+            self.commit()
+
+    @property
+    def handle(self):
+        self._sync()
+        return self._h
+
+    def size(self):
+        n = C.c_int(0)
+        _chk(lib().epp_world_size(self._h, C.byref(n)))
+        return n.value
+
+    def epoch(self):
+        e = C.c_uint64(0)
+        _chk(lib().epp_world_epoch(self._h, C.byref(e)))
+        return e.value
+
+    def active_broadphase(self):
+        self._sync()
+        m = C.c_int(0)
+        _chk(lib().epp_world_active_broadphase(self._h, C.byref(m)))
+        return m.value
+
+    def obbs(self):
+        out = []
+        for i in range(self.size()):
+            o = Obb()
+            _chk(lib().epp_world_get_obb(self._h, i, C.byref(o)))
+            out.append(dict(center=list(o.center), half=list(o.half), rot=list(o.rot),
+                            aabb_min=list(o.aabb_min), aabb_max=list(o.aabb_max), inflate=o.inflate,
+                            filling=o.filling, is_gate=o.is_gate, object_id=o.object_id,
+                            obb_index=o.obb_index))
+        return out
+
+    # -- batched checks on host (numpy) buffers --------------------------------------------
+    def check_states(self, xyz, can_pass_gate=False):
+        """(n,3) float64 -> uint32 mask words (bit = valid)."""
+        self._sync()
+        xyz = _f64(xyz, (-1, 3))
+        n = xyz.shape[0]
+        mask = np.zeros(mask_words(n), dtype=np.uint32)
+        _chk(lib().epp_check_states(self._h, _ptr(xyz), n, int(can_pass_gate), _ptr(mask)))
+        return mask
+
+    def check_states_mindist(self, xyz, min_distance):
+        self._sync()
+        xyz = _f64(xyz, (-1, 3))
+        n = xyz.shape[0]
+        mask = np.zeros(mask_words(n), dtype=np.uint32)
+        _chk(lib().epp_check_states_mindist(self._h, _ptr(xyz), n, float(min_distance), _ptr(mask)))
+        return mask
+
+    def check_segments(self, a, b, can_pass_gate=False):
+        self._sync()
+        a, b = _f64(a, (-1, 3)), _f64(b, (-1, 3))
+        if a.shape != b.shape:
+            raise ValueError("start/end batches differ in shape")
+        n = a.shape[0]
+        mask = np.zeros(mask_words(n), dtype=np.uint32)
+        _chk(lib().epp_check_segments(self._h, _ptr(a), _ptr(b), n, int(can_pass_gate), _ptr(mask)))
+        return mask
+
+    def check_trajectories(self, trajs, min_distance, want_samples=True):
+        """trajs: (n_traj, rows, cols) array (each slice one trajectory matrix, evaluated as the
+        reference's column-major Eigen matrix) -> (traj_valid words, sample masks, first_invalid)."""
+        self._sync()
+        t = np.asarray(trajs, dtype=np.float64)
+        if t.ndim == 2:
+            t = t[None]
+        n_traj, rows, cols = t.shape
+        cm = np.ascontiguousarray(np.transpose(t, (0, 2, 1)))  # per trajectory: cols x rows = column-major
+        valid = np.zeros(mask_words(n_traj), dtype=np.uint32)
+        smask = np.zeros((n_traj, mask_words(rows)), dtype=np.uint32) if want_samples else None
+        first = np.zeros(n_traj, dtype=np.int64)
+        _chk(lib().epp_check_trajectories(self._h, _ptr(cm), n_traj, rows, rows, rows * cols, cols,
+                                          float(min_distance), _ptr(valid), _ptr(smask), _ptr(first)))
+        return valid, smask, first
+
+    def checkTrajectoryValidity(self, trajectory, minDistance):
+        """PathPlanner::checkTrajectoryValidity (src/PathPlanner.cpp:267-280)."""
+        valid, _, _ = self.check_trajectories(np.asarray(trajectory)[None], minDistance, False)
+        return bool(valid[0] & 1)
+
+    def check_poly_trajectories(self, coeffs, durations, dt, min_distance, max_samples=1024,
+                                want_samples=True):
+        """coeffs (n_traj, K, 3, N), durations (n_traj, K), dt scalar or (n_traj,)."""
+        self._sync()
+        c = _f64(coeffs)
+        d = _f64(durations)
+        if c.ndim == 3:
+            c, d = c[None], d[None]
+        n_traj, K, _, N = c.shape
+        dts = np.ascontiguousarray(np.broadcast_to(np.asarray(dt, dtype=np.float64), (n_traj,)))
+        max_samples = (int(max_samples) + 31) // 32 * 32
+        valid = np.zeros(mask_words(n_traj), dtype=np.uint32)
+        smask = np.zeros((n_traj, max_samples // 32), dtype=np.uint32) if want_samples else None
+        ns = np.zeros(n_traj, dtype=np.uint32)
+        first = np.zeros(n_traj, dtype=np.int64)
+        _chk(lib().epp_check_poly_trajectories(self._h, _ptr(c), _ptr(d), _ptr(dts), n_traj, K, N,
+                                               float(min_distance), max_samples, _ptr(valid),
+                                               _ptr(smask), _ptr(ns), _ptr(first)))
+        return valid, smask, ns, first
+
+    # -- batched checks on device (torch) buffers; asynchronous on the current stream -------
+    @staticmethod
+    def _stream():
+        import torch
+        return torch.cuda.current_stream().cuda_stream
+
+    def check_states_dev(self, xyz, mask=None, can_pass_gate=False, min_distance=None):
+        import torch
+        self._sync()
+        n = xyz.numel() // 3
+        if mask is None:
+            mask = torch.empty(mask_words(n), dtype=torch.int32, device=xyz.device)
+        if min_distance is None:
+            _chk(lib().epp_check_states_dev(self._h, xyz.data_ptr(), n, int(can_pass_gate),
+                                            mask.data_ptr(), self._stream()))
+        else:
+            _chk(lib().epp_check_states_mindist_dev(self._h, xyz.data_ptr(), n, float(min_distance),
+                                                    mask.data_ptr(), self._stream()))
+        return mask
+
+    def check_segments_dev(self, a, b, mask=None, can_pass_gate=False):
+        import torch
+        self._sync()
+        n = a.numel() // 3
+        if mask is None:
+            mask = torch.empty(mask_words(n), dtype=torch.int32, device=a.device)
+        _chk(lib().epp_check_segments_dev(self._h, a.data_ptr(), b.data_ptr(), n, int(can_pass_gate),
+                                          mask.data_ptr(), self._stream()))
+        return mask
+
+    def check_trajectories_dev(self, mats, n_traj, rows, ld, traj_stride, cols, min_distance,
+                               want_samples=True):
+        import torch
+        self._sync()
+        dev = mats.device
+        valid = torch.empty(mask_words(n_traj), dtype=torch.int32, device=dev)
+        smask = torch.empty((n_traj, mask_words(rows)), dtype=torch.int32, device=dev) if want_samples else None
+        first = torch.empty(n_traj, dtype=torch.int64, device=dev)
+        _chk(lib().epp_check_trajectories_dev(self._h, mats.data_ptr(), n_traj, rows, ld, traj_stride,
+                                              cols, float(min_distance), valid.data_ptr(),
+                                              smask.data_ptr() if want_samples else None,
+                                              first.data_ptr(), self._stream()))
+        return valid, smask, first
+
+    def check_poly_trajectories_dev(self, coeffs, durations, dt, min_distance, max_samples=1024,
+                                    want_samples=True):
+        import torch
+        self._sync()
+        n_traj, K, _, N = coeffs.shape
+        dev = coeffs.device
+        max_samples = (int(max_samples) + 31) // 32 * 32
+        valid = torch.empty(mask_words(n_traj), dtype=torch.int32, device=dev)
+        smask = torch.empty((n_traj, max_samples // 32), dtype=torch.int32, device=dev) if want_samples else None
+        ns = torch.empty(n_traj, dtype=torch.int32, device=dev)
+        first = torch.empty(n_traj, dtype=torch.int64, device=dev)
+        _chk(lib().epp_check_poly_trajectories_dev(self._h, coeffs.data_ptr(), durations.data_ptr(),
+                                                   dt.data_ptr(), n_traj, K, N, float(min_distance),
+                                                   max_samples, valid.data_ptr(),
+                                                   smask.data_ptr() if want_samples else None,
+                                                   ns.data_ptr(), first.data_ptr(), self._stream()))
+        return valid, smask, ns, first
+
+
+def gen_states_dev(seed, first, n, lo, hi, out=None, device="cuda"):
+    import torch
+    if out is None:
+        out = torch.empty((n, 3), dtype=torch.float64, device=device)
+    lo, hi = _f64(lo, 3), _f64(hi, 3)
+    _chk(lib().epp_gen_states_dev(seed, first, n, lo.ctypes.data_as(_dp), hi.ctypes.data_as(_dp),
+                                  out.data_ptr(), torch.cuda.current_stream().cuda_stream))
+    return out
+
+
+def gen_segments_dev(seed, first, n, lo, hi, max_len, device="cuda"):
+    import torch
+    a = torch.empty((n, 3), dtype=torch.float64, device=device)
+    b = torch.empty((n, 3), dtype=torch.float64, device=device)
+    lo, hi = _f64(lo, 3), _f64(hi, 3)
+    _chk(lib().epp_gen_segments_dev(seed, first, n, lo.ctypes.data_as(_dp), hi.ctypes.data_as(_dp),
+                                    float(max_len), a.data_ptr(), b.data_ptr(),
+                                    torch.cuda.current_stream().cuda_stream))
+    return a, b
+
+
+def mask_summary_dev(mask, first_word=0):
+    """(popcount, xor checksum) of a device mask; checksum is position dependent."""
+    import torch
+    out = torch.zeros(2, dtype=torch.int64, device=mask.device)
+    _chk(lib().epp_mask_summary_dev(mask.data_ptr(), mask.numel(), first_word, out.data_ptr(),
+                                    torch.cuda.current_stream().cuda_stream))
+    pop, x = out.cpu().numpy().view(np.uint64)
+    return int(pop), int(x)
+
+
+def _mix64(seed, counter):
+    """numpy restatement of the device mix64 (for host-side checksum comparison)."""
+    with np.errstate(over="ignore"):
+        z = np.uint64(seed) + np.uint64(0x9E3779B97F4A7C15) * (counter.astype(np.uint64) + np.uint64(1))
+        z ^= z >> np.uint64(30)
+        z *= np.uint64(0xBF58476D1CE4E5B9)
+        z ^= z >> np.uint64(27)
+        z *= np.uint64(0x94D049BB133111EB)
+        z ^= z >> np.uint64(31)
+    return z
+
+
+def mask_summary_host(mask, first_word=0):
+    m = np.ascontiguousarray(mask, dtype=np.uint32)
+    pop = int(np.unpackbits(m.view(np.uint8)).sum())
+    idx = np.arange(first_word, first_word + m.size, dtype=np.uint64)
+    h = _mix64(0x5EED, (idx << np.uint64(32)) | m.astype(np.uint64))
+    x = int(np.bitwise_xor.reduce(h)) if m.size else 0
+    return pop, x
+
+
+from . import worlds  # noqa: E402,F401  (synthetic world / input builders)

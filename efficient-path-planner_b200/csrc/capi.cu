@@ -1,0 +1,815 @@
+// capi.cu — the C ABI of libepp_b200.so (include/epp_c_api.h): world epochs on the device,
+// host-buffer staging, and dispatch into the kernels.  No CPU fallback exists anywhere in
+// this file: a missing device or CUDA failure is reported, never papered over.
+#include <cuda_runtime.h>
+
+#include <algorithm>
+#include <atomic>
+#include <cstring>
+#include <memory>
+#include <mutex>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/epp_c_api.h"
+#include "kernels.h"
+#include "world_host.h"
+
+using namespace epp;
+
+namespace {
+
+thread_local std::string tl_error;
+
+int fail(int status, const std::string &detail = std::string())
+{
+    tl_error = status_message(status);
+    if (!detail.empty()) tl_error += ": " + detail;
+    return status;
+}
+
+int cuda_fail(cudaError_t e, const char *what)
+{
+    if (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver)
+        return fail(EPP_ERR_NO_DEVICE, std::string(what) + ": " + cudaGetErrorString(e));
+    return fail(EPP_ERR_CUDA, std::string(what) + ": " + cudaGetErrorString(e));
+}
+
+#define EPP_CUDA(call)                                         \
+    do {                                                       \
+        cudaError_t e__ = (call);                              \
+        if (e__ != cudaSuccess) return cuda_fail(e__, #call);  \
+    } while (0)
+
+// Tuning knobs (epp_set_tuning).
+struct Tuning {
+    std::atomic<int> states_blocks_per_sm{8};
+    std::atomic<int> segments_blocks_per_sm{4};
+    std::atomic<int> states_variant{0};
+    std::atomic<int> bits_bins{0};          // 0: by world size
+    std::atomic<int> grid_max_cells{1 << 22};
+    std::atomic<int> bits_max_obbs{1024};
+} g_tuning;
+
+// One immutable committed world on one device.
+struct DeviceEpoch {
+    int device = -1;
+    int sm_count = 148;
+    uint64_t epoch = 0;
+    int bp = EPP_BP_BITS;
+    void *blob = nullptr;
+    WorldView view{};
+    ~DeviceEpoch()
+    {
+        if (blob) {
+            int prev = -1;
+            cudaGetDevice(&prev);
+            cudaSetDevice(device);
+            cudaFree(blob); // implicit device synchronisation: in-flight kernels finish first
+            if (prev >= 0) cudaSetDevice(prev);
+        }
+    }
+};
+
+} // namespace
+
+struct epp_world {
+    HostWorld host;
+    mutable std::mutex mu;
+    std::shared_ptr<DeviceEpoch> current;
+    bool dirty = true;
+    uint64_t epoch = 0;
+    int bp_request = EPP_BP_AUTO;
+    epp_world(double g, double o) : host(g, o) {}
+};
+
+namespace {
+
+// Per-thread, per-device staging: a stream, pinned host memory and device scratch.  Gives
+// the re-entrancy the reference's concurrent planner threads need without a global lock.
+struct Staging {
+    int device = -1;
+    cudaStream_t stream = nullptr;
+    unsigned char *h = nullptr;
+    size_t h_cap = 0;
+    unsigned char *d = nullptr;
+    size_t d_cap = 0;
+    ~Staging()
+    {
+        if (device < 0) return;
+        // Thread exit may happen after the primary context is gone; ignore errors.
+        if (stream) cudaStreamDestroy(stream);
+        if (h) cudaFreeHost(h);
+        if (d) cudaFree(d);
+    }
+};
+
+thread_local std::vector<std::unique_ptr<Staging>> tl_staging;
+
+int get_staging(int device, Staging **out)
+{
+    for (auto &s : tl_staging)
+        if (s->device == device) {
+            *out = s.get();
+            return EPP_OK;
+        }
+    std::unique_ptr<Staging> s(new Staging);
+    EPP_CUDA(cudaStreamCreateWithFlags(&s->stream, cudaStreamNonBlocking));
+    s->device = device;
+    *out = s.get();
+    tl_staging.push_back(std::move(s));
+    return EPP_OK;
+}
+
+int reserve_host(Staging *s, size_t bytes)
+{
+    if (bytes <= s->h_cap) return EPP_OK;
+    EPP_CUDA(cudaStreamSynchronize(s->stream));
+    if (s->h) cudaFreeHost(s->h);
+    s->h = nullptr;
+    s->h_cap = 0;
+    size_t cap = std::max<size_t>(bytes + bytes / 2, 1 << 16);
+    EPP_CUDA(cudaHostAlloc((void **)&s->h, cap, cudaHostAllocMapped));
+    s->h_cap = cap;
+    return EPP_OK;
+}
+
+int reserve_device(Staging *s, size_t bytes)
+{
+    if (bytes <= s->d_cap) return EPP_OK;
+    EPP_CUDA(cudaStreamSynchronize(s->stream));
+    if (s->d) cudaFree(s->d);
+    s->d = nullptr;
+    s->d_cap = 0;
+    size_t cap = std::max<size_t>(bytes + bytes / 2, 1 << 20);
+    EPP_CUDA(cudaMalloc((void **)&s->d, cap));
+    s->d_cap = cap;
+    return EPP_OK;
+}
+
+bool is_pinned(const void *p)
+{
+    cudaPointerAttributes a;
+    if (cudaPointerGetAttributes(&a, p) != cudaSuccess) {
+        cudaGetLastError();
+        return false;
+    }
+    return a.type == cudaMemoryTypeHost;
+}
+
+size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+
+constexpr size_t kChunk = 8u << 20; // staging chunk for pageable host memory
+
+// H2D from arbitrary host memory: pinned sources go straight to the copy engine, pageable
+// ones are bounced through two pinned chunks so memcpy overlaps the DMA.
+int upload(Staging *s, void *dst, const void *src, size_t bytes, size_t bounce_off)
+{
+    if (bytes == 0) return EPP_OK;
+    if (is_pinned(src)) {
+        EPP_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyHostToDevice, s->stream));
+        return EPP_OK;
+    }
+    EPP_CUDA(cudaStreamSynchronize(s->stream)); // bounce chunks may still feed an earlier copy
+    cudaEvent_t ev[2];
+    EPP_CUDA(cudaEventCreateWithFlags(&ev[0], cudaEventDisableTiming));
+    EPP_CUDA(cudaEventCreateWithFlags(&ev[1], cudaEventDisableTiming));
+    int rc = EPP_OK;
+    size_t off = 0;
+    for (int i = 0; off < bytes; ++i) {
+        const size_t len = std::min(kChunk, bytes - off);
+        unsigned char *b = s->h + bounce_off + (size_t)(i & 1) * kChunk;
+        if (i >= 2) cudaEventSynchronize(ev[i & 1]);
+        std::memcpy(b, (const unsigned char *)src + off, len);
+        cudaError_t e = cudaMemcpyAsync((unsigned char *)dst + off, b, len, cudaMemcpyHostToDevice, s->stream);
+        if (e == cudaSuccess) e = cudaEventRecord(ev[i & 1], s->stream);
+        if (e != cudaSuccess) {
+            rc = cuda_fail(e, "upload");
+            break;
+        }
+        off += len;
+    }
+    cudaEventDestroy(ev[0]);
+    cudaEventDestroy(ev[1]);
+    return rc;
+}
+
+int snapshot(epp_world *w, std::shared_ptr<DeviceEpoch> &ep)
+{
+    if (!w) return fail(EPP_ERR_INVALID_ARG, "null world");
+    std::lock_guard<std::mutex> lk(w->mu);
+    if (!w->current || w->dirty) return fail(EPP_ERR_NOT_COMMITTED);
+    ep = w->current;
+    return EPP_OK;
+}
+
+LaunchCfg launch_cfg(const DeviceEpoch &ep)
+{
+    LaunchCfg c;
+    c.sm_count = ep.sm_count;
+    c.states_blocks_per_sm = g_tuning.states_blocks_per_sm.load();
+    c.segments_blocks_per_sm = g_tuning.segments_blocks_per_sm.load();
+    c.states_variant = g_tuning.states_variant.load();
+    return c;
+}
+
+// RAII: run on the epoch's device, restore the caller's device afterwards.
+struct DeviceGuard {
+    int prev = -1;
+    bool switched = false;
+    cudaError_t enter(int device)
+    {
+        cudaError_t e = cudaGetDevice(&prev);
+        if (e != cudaSuccess) return e;
+        if (prev != device) {
+            e = cudaSetDevice(device);
+            switched = (e == cudaSuccess);
+        }
+        return e;
+    }
+    ~DeviceGuard()
+    {
+        if (switched) cudaSetDevice(prev);
+    }
+};
+
+size_t mask_words(size_t n) { return (n + 31) / 32; }
+
+// Common body of the host-buffer point/segment checks.
+int check_host(epp_world *w, const double *a, const double *b, size_t n, int kind /*0 point,1 ray*/, int mode,
+               int can_pass_gate, double min_distance, uint32_t *mask)
+{
+    std::shared_ptr<DeviceEpoch> ep;
+    int rc = snapshot(w, ep);
+    if (rc) return rc;
+    if (n == 0) return EPP_OK;
+    if (!a || !mask || (kind == 1 && !b)) return fail(EPP_ERR_INVALID_ARG, "null buffer");
+    DeviceGuard guard;
+    EPP_CUDA(guard.enter(ep->device));
+    Staging *s;
+    rc = get_staging(ep->device, &s);
+    if (rc) return rc;
+
+    const size_t in_bytes = n * 3 * sizeof(double);
+    const size_t words = mask_words(n);
+    const size_t off_b = align_up(in_bytes, 256);
+    const size_t off_mask = kind == 1 ? off_b + align_up(in_bytes, 256) : off_b;
+    rc = reserve_device(s, off_mask + words * 4);
+    if (rc) return rc;
+    const bool mask_pinned = is_pinned(mask);
+    // pinned layout: [bounce 2 x kChunk][mask]
+    rc = reserve_host(s, 2 * kChunk + (mask_pinned ? 0 : words * 4));
+    if (rc) return rc;
+
+    rc = upload(s, s->d, a, in_bytes, 0);
+    if (rc) return rc;
+    if (kind == 1) {
+        rc = upload(s, s->d + off_b, b, in_bytes, 0);
+        if (rc) return rc;
+    }
+    uint32_t *d_mask = (uint32_t *)(s->d + off_mask);
+    const LaunchCfg cfg = launch_cfg(*ep);
+    cudaError_t e;
+    if (kind == 0)
+        e = launch_states(cfg, ep->view, ep->bp, (const double *)s->d, n, mode, can_pass_gate, min_distance, d_mask,
+                          s->stream);
+    else
+        e = launch_segments(cfg, ep->view, ep->bp, (const double *)s->d, (const double *)(s->d + off_b), n,
+                            can_pass_gate, d_mask, s->stream);
+    if (e != cudaSuccess) return cuda_fail(e, "kernel launch");
+    uint32_t *h_mask = mask_pinned ? mask : (uint32_t *)(s->h + 2 * kChunk);
+    EPP_CUDA(cudaMemcpyAsync(h_mask, d_mask, words * 4, cudaMemcpyDeviceToHost, s->stream));
+    EPP_CUDA(cudaStreamSynchronize(s->stream));
+    if (!mask_pinned) std::memcpy(mask, h_mask, words * 4);
+    return EPP_OK;
+}
+
+// One unit through mapped pinned memory: a single launch + synchronise, no copies.
+int check_single(epp_world *w, const double *a, const double *b, int can_pass_gate, int *valid)
+{
+    std::shared_ptr<DeviceEpoch> ep;
+    int rc = snapshot(w, ep);
+    if (rc) return rc;
+    if (!a || !valid) return fail(EPP_ERR_INVALID_ARG, "null buffer");
+    DeviceGuard guard;
+    EPP_CUDA(guard.enter(ep->device));
+    Staging *s;
+    rc = get_staging(ep->device, &s);
+    if (rc) return rc;
+    rc = reserve_host(s, 256);
+    if (rc) return rc;
+    double *slot = (double *)s->h;
+    uint32_t *out = (uint32_t *)(s->h + 64);
+    std::memcpy(slot, a, 3 * sizeof(double));
+    if (b) std::memcpy(slot + 3, b, 3 * sizeof(double));
+    const LaunchCfg cfg = launch_cfg(*ep);
+    cudaError_t e;
+    if (!b)
+        e = launch_states(cfg, ep->view, ep->bp, slot, 1, kModeBool, can_pass_gate, 0.0, out, s->stream);
+    else
+        e = launch_segments(cfg, ep->view, ep->bp, slot, slot + 3, 1, can_pass_gate, out, s->stream);
+    if (e != cudaSuccess) return cuda_fail(e, "kernel launch");
+    EPP_CUDA(cudaStreamSynchronize(s->stream));
+    *valid = (int)(*out & 1u);
+    return EPP_OK;
+}
+
+} // namespace
+
+// ---- misc -----------------------------------------------------------------------------------
+
+extern "C" const char *epp_last_error(void) { return tl_error.c_str(); }
+
+extern "C" const char *epp_version(void) { return "epp_b200 0.1 (sm_100a)"; }
+
+extern "C" int epp_device_count(int *count)
+{
+    if (!count) return fail(EPP_ERR_INVALID_ARG);
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess) {
+        *count = 0;
+        return cuda_fail(e, "cudaGetDeviceCount");
+    }
+    *count = n;
+    return EPP_OK;
+}
+
+extern "C" uint64_t epp_kernel_launch_count(void) { return g_launches.load(); }
+
+extern "C" int epp_set_tuning(const char *key, int value)
+{
+    if (!key) return fail(EPP_ERR_INVALID_ARG);
+    const std::string k(key);
+    if (k == "states_blocks_per_sm") g_tuning.states_blocks_per_sm = value;
+    else if (k == "segments_blocks_per_sm") g_tuning.segments_blocks_per_sm = value;
+    else if (k == "states_variant") g_tuning.states_variant = value;
+    else if (k == "bits_bins") g_tuning.bits_bins = value;
+    else if (k == "grid_max_cells") g_tuning.grid_max_cells = value;
+    else if (k == "bits_max_obbs") g_tuning.bits_max_obbs = value;
+    else return fail(EPP_ERR_INVALID_ARG, "unknown tuning key " + k);
+    return EPP_OK;
+}
+
+extern "C" int epp_get_tuning(const char *key, int *value)
+{
+    if (!key || !value) return fail(EPP_ERR_INVALID_ARG);
+    const std::string k(key);
+    if (k == "states_blocks_per_sm") *value = g_tuning.states_blocks_per_sm;
+    else if (k == "segments_blocks_per_sm") *value = g_tuning.segments_blocks_per_sm;
+    else if (k == "states_variant") *value = g_tuning.states_variant;
+    else if (k == "bits_bins") *value = g_tuning.bits_bins;
+    else if (k == "grid_max_cells") *value = g_tuning.grid_max_cells;
+    else if (k == "bits_max_obbs") *value = g_tuning.bits_max_obbs;
+    else return fail(EPP_ERR_INVALID_ARG, "unknown tuning key " + k);
+    return EPP_OK;
+}
+
+// ---- world lifecycle ----------------------------------------------------------------------------
+
+extern "C" int epp_world_create(double inflate_gate, double inflate_obstacle, epp_world **out)
+{
+    if (!out) return fail(EPP_ERR_INVALID_ARG);
+    *out = new (std::nothrow) epp_world(inflate_gate, inflate_obstacle);
+    return *out ? EPP_OK : fail(EPP_ERR_INVALID_ARG, "out of memory");
+}
+
+extern "C" int epp_world_destroy(epp_world *w)
+{
+    delete w;
+    return EPP_OK;
+}
+
+#define EPP_MUTATE(expr)                              \
+    if (!w) return fail(EPP_ERR_INVALID_ARG, "null world"); \
+    std::lock_guard<std::mutex> lk(w->mu);            \
+    int rc = (expr);                                  \
+    if (rc == EPP_OK) w->dirty = true;                \
+    return rc == EPP_OK ? EPP_OK : fail(rc)
+
+extern "C" int epp_world_set_gate_geometry(epp_world *w, int type_id, const epp_obb_desc *d, int n)
+{
+    EPP_MUTATE(w->host.set_gate_geometry(type_id, d, n));
+}
+
+extern "C" int epp_world_set_obstacle_geometry(epp_world *w, const epp_obb_desc *d, int n)
+{
+    EPP_MUTATE(w->host.set_obstacle_geometry(d, n));
+}
+
+extern "C" int epp_world_reset(epp_world *w) { EPP_MUTATE((w->host.reset(), EPP_OK)); }
+
+extern "C" int epp_world_add_gate(epp_world *w, int gate_id, const double pose7[7])
+{
+    if (!pose7) return fail(EPP_ERR_INVALID_ARG);
+    EPP_MUTATE(w->host.add_gate(gate_id, pose7, false));
+}
+
+extern "C" int epp_world_update_gate(epp_world *w, int gate_id, const double pose7[7])
+{
+    if (!pose7) return fail(EPP_ERR_INVALID_ARG);
+    EPP_MUTATE(w->host.add_gate(gate_id, pose7, true));
+}
+
+extern "C" int epp_world_add_obstacle(epp_world *w, int obstacle_id, const double pose6[6])
+{
+    if (!pose6) return fail(EPP_ERR_INVALID_ARG);
+    EPP_MUTATE(w->host.add_obstacle(obstacle_id, pose6));
+}
+
+extern "C" int epp_world_set_broadphase(epp_world *w, epp_broadphase mode)
+{
+    if (mode < EPP_BP_AUTO || mode > EPP_BP_GRID) return fail(EPP_ERR_INVALID_ARG, "broadphase");
+    EPP_MUTATE((w->bp_request = mode, EPP_OK));
+}
+
+extern "C" int epp_world_size(const epp_world *w, int *n)
+{
+    if (!w || !n) return fail(EPP_ERR_INVALID_ARG);
+    std::lock_guard<std::mutex> lk(w->mu);
+    *n = w->host.size();
+    return EPP_OK;
+}
+
+extern "C" int epp_world_get_obb(const epp_world *w, int index, epp_obb *out)
+{
+    if (!w || !out) return fail(EPP_ERR_INVALID_ARG);
+    std::lock_guard<std::mutex> lk(w->mu);
+    int rc = w->host.get(index, out);
+    return rc == EPP_OK ? EPP_OK : fail(rc);
+}
+
+extern "C" int epp_world_epoch(const epp_world *w, uint64_t *epoch)
+{
+    if (!w || !epoch) return fail(EPP_ERR_INVALID_ARG);
+    std::lock_guard<std::mutex> lk(w->mu);
+    *epoch = w->epoch;
+    return EPP_OK;
+}
+
+extern "C" int epp_world_active_broadphase(const epp_world *w, int *mode)
+{
+    if (!w || !mode) return fail(EPP_ERR_INVALID_ARG);
+    std::lock_guard<std::mutex> lk(w->mu);
+    if (!w->current) return fail(EPP_ERR_NOT_COMMITTED);
+    *mode = w->current->bp;
+    return EPP_OK;
+}
+
+extern "C" int epp_world_commit(epp_world *w)
+{
+    if (!w) return fail(EPP_ERR_INVALID_ARG, "null world");
+    std::lock_guard<std::mutex> lk(w->mu);
+
+    int device = 0;
+    EPP_CUDA(cudaGetDevice(&device));
+    std::vector<AabbRec> aabbs;
+    std::vector<ObbRec> obbs;
+    int rc = w->host.flatten(aabbs, obbs);
+    if (rc) return fail(rc);
+    const int M = (int)aabbs.size();
+
+    int bp = w->bp_request;
+    const int bits_max = g_tuning.bits_max_obbs.load();
+    if (bp == EPP_BP_AUTO) bp = (M <= bits_max) ? EPP_BP_BITS : EPP_BP_GRID;
+    if (bp == EPP_BP_BITS && M > 4096) return fail(EPP_ERR_INVALID_ARG, "EPP_BP_BITS supports at most 4096 OBBs");
+
+    BitsTables bits;
+    GridTables grid;
+    if (bp == EPP_BP_BITS) {
+        int nb = g_tuning.bits_bins.load();
+        const int W = std::max(1, (M + 31) / 32);
+        if (nb <= 0) nb = W == 1 ? 256 : (W <= 8 ? 128 : (W <= 32 ? 64 : 32));
+        build_bits(aabbs, nb, bits);
+    }
+    if (bp == EPP_BP_GRID) build_grid(aabbs, obbs, g_tuning.grid_max_cells.load(), grid);
+
+    // One blob: [aabb][obb][bits inside|min_le|max_ge][cell_start][cell_items], 256 B aligned parts.
+    struct Part {
+        const void *src;
+        size_t bytes;
+        size_t off;
+    };
+    std::vector<Part> parts = {
+        {aabbs.data(), aabbs.size() * sizeof(AabbRec), 0},      {obbs.data(), obbs.size() * sizeof(ObbRec), 0},
+        {bits.inside.data(), bits.inside.size() * 4, 0},        {bits.min_le.data(), bits.min_le.size() * 4, 0},
+        {bits.max_ge.data(), bits.max_ge.size() * 4, 0},        {grid.cell_start.data(), grid.cell_start.size() * 4, 0},
+        {grid.cell_items.data(), grid.cell_items.size() * 4, 0}};
+    size_t total = 0;
+    for (Part &p : parts) {
+        p.off = total;
+        total += align_up(std::max<size_t>(p.bytes, 16), 256);
+    }
+    std::shared_ptr<DeviceEpoch> ep(new DeviceEpoch);
+    ep->device = device;
+    EPP_CUDA(cudaMalloc(&ep->blob, total));
+    EPP_CUDA(cudaMemset(ep->blob, 0, total));
+    for (const Part &p : parts)
+        if (p.bytes) EPP_CUDA(cudaMemcpy((unsigned char *)ep->blob + p.off, p.src, p.bytes, cudaMemcpyHostToDevice));
+    EPP_CUDA(cudaDeviceGetAttribute(&ep->sm_count, cudaDevAttrMultiProcessorCount, device));
+
+    unsigned char *base = (unsigned char *)ep->blob;
+    WorldView &v = ep->view;
+    v.aabb = (const AabbRec *)(base + parts[0].off);
+    v.obb = (const ObbRec *)(base + parts[1].off);
+    v.M = M;
+    v.bits_inside = (const uint32_t *)(base + parts[2].off);
+    v.bits_min_le = (const uint32_t *)(base + parts[3].off);
+    v.bits_max_ge = (const uint32_t *)(base + parts[4].off);
+    v.nb = bits.nb;
+    v.W = bits.W;
+    v.bbins = bits.bins;
+    v.cell_start = (const uint32_t *)(base + parts[5].off);
+    v.cell_items = (const uint32_t *)(base + parts[6].off);
+    v.gbins = grid.bins;
+    ep->bp = bp;
+    ep->epoch = ++w->epoch;
+    w->current = ep; // the previous epoch is released when its last in-flight user drops it
+    w->dirty = false;
+    return EPP_OK;
+}
+
+extern "C" int epp_world_parse_gates_and_obstacles(epp_world *w, const double *gates7, int n_gates,
+                                                   const double *obstacles6, int n_obstacles)
+{
+    if (!w || n_gates < 0 || n_obstacles < 0 || (n_gates && !gates7) || (n_obstacles && !obstacles6))
+        return fail(EPP_ERR_INVALID_ARG);
+    {
+        std::lock_guard<std::mutex> lk(w->mu);
+        w->host.reset(); // src/PathPlanner.cpp:63
+        w->dirty = true;
+        for (int i = 0; i < n_gates; ++i) {
+            double g[7];
+            std::memcpy(g, gates7 + 7 * i, sizeof g);
+            g[2] = 0.0; // src/PathPlanner.cpp:68
+            int rc = w->host.add_gate(i, g, false);
+            if (rc) return fail(rc);
+        }
+        for (int i = 0; i < n_obstacles; ++i) {
+            int rc = w->host.add_obstacle(i, obstacles6 + 6 * i);
+            if (rc) return fail(rc);
+        }
+    }
+    return epp_world_commit(w);
+}
+
+// ---- host-buffer checks ----------------------------------------------------------------------------
+
+extern "C" int epp_check_states(epp_world *w, const double *xyz, size_t n, int can_pass_gate, uint32_t *mask)
+{
+    return check_host(w, xyz, nullptr, n, 0, kModeBool, can_pass_gate, 0.0, mask);
+}
+
+extern "C" int epp_check_states_mindist(epp_world *w, const double *xyz, size_t n, double min_distance,
+                                        uint32_t *mask)
+{
+    return check_host(w, xyz, nullptr, n, 0, kModeMinDist, 0, min_distance, mask);
+}
+
+extern "C" int epp_check_segments(epp_world *w, const double *a, const double *b, size_t n, int can_pass_gate,
+                                  uint32_t *mask)
+{
+    return check_host(w, a, b, n, 1, kModeBool, can_pass_gate, 0.0, mask);
+}
+
+extern "C" int epp_is_valid(epp_world *w, const double p[3], int can_pass_gate, int *valid)
+{
+    return check_single(w, p, nullptr, can_pass_gate, valid);
+}
+
+extern "C" int epp_check_motion(epp_world *w, const double a[3], const double b[3], int can_pass_gate, int *valid)
+{
+    if (!b) return fail(EPP_ERR_INVALID_ARG, "null buffer");
+    return check_single(w, a, b, can_pass_gate, valid);
+}
+
+extern "C" int epp_check_trajectories(epp_world *w, const double *col_major, size_t n_traj, size_t rows, size_t ld,
+                                      size_t traj_stride, int cols, double min_distance, uint32_t *traj_valid,
+                                      uint32_t *sample_mask, int64_t *first_invalid)
+{
+    std::shared_ptr<DeviceEpoch> ep;
+    int rc = snapshot(w, ep);
+    if (rc) return rc;
+    if (n_traj == 0) return EPP_OK;
+    if (!col_major || !traj_valid || cols < 7 || ld < rows || (n_traj > 1 && traj_stride < ld * (size_t)cols))
+        return fail(EPP_ERR_INVALID_ARG, "trajectory matrix shape");
+    DeviceGuard guard;
+    EPP_CUDA(guard.enter(ep->device));
+    Staging *s;
+    rc = get_staging(ep->device, &s);
+    if (rc) return rc;
+
+    // Only the columns up to 6 of every matrix are needed on the device.
+    const size_t span = (n_traj - 1) * traj_stride + 6 * ld + rows;
+    const size_t in_bytes = span * sizeof(double);
+    const size_t wpt = mask_words(rows);
+    const size_t off_valid = align_up(in_bytes, 256);
+    const size_t off_first = off_valid + align_up(mask_words(n_traj) * 4, 256);
+    const size_t off_scratch = off_first + align_up(n_traj * 8, 256);
+    const size_t off_smask = off_scratch + align_up(n_traj * 8, 256);
+    const size_t smask_bytes = sample_mask ? n_traj * wpt * 4 : 0;
+    rc = reserve_device(s, off_smask + smask_bytes);
+    if (rc) return rc;
+    const size_t out_bytes = mask_words(n_traj) * 4 + n_traj * 8 + smask_bytes;
+    rc = reserve_host(s, 2 * kChunk + out_bytes + 512);
+    if (rc) return rc;
+    rc = upload(s, s->d, col_major, in_bytes, 0);
+    if (rc) return rc;
+    cudaError_t e = launch_trajectories(launch_cfg(*ep), ep->view, ep->bp, (const double *)s->d, n_traj, rows, ld,
+                                        traj_stride, min_distance, (uint32_t *)(s->d + off_valid),
+                                        sample_mask ? (uint32_t *)(s->d + off_smask) : nullptr,
+                                        (int64_t *)(s->d + off_first), (long long *)(s->d + off_scratch), s->stream);
+    if (e != cudaSuccess) return cuda_fail(e, "kernel launch");
+    unsigned char *hb = s->h + 2 * kChunk;
+    const size_t h_first = align_up(mask_words(n_traj) * 4, 8);
+    const size_t h_smask = h_first + n_traj * 8;
+    EPP_CUDA(cudaMemcpyAsync(hb, s->d + off_valid, mask_words(n_traj) * 4, cudaMemcpyDeviceToHost, s->stream));
+    if (first_invalid)
+        EPP_CUDA(cudaMemcpyAsync(hb + h_first, s->d + off_first, n_traj * 8, cudaMemcpyDeviceToHost, s->stream));
+    if (sample_mask)
+        EPP_CUDA(cudaMemcpyAsync(hb + h_smask, s->d + off_smask, smask_bytes, cudaMemcpyDeviceToHost, s->stream));
+    EPP_CUDA(cudaStreamSynchronize(s->stream));
+    std::memcpy(traj_valid, hb, mask_words(n_traj) * 4);
+    if (first_invalid) std::memcpy(first_invalid, hb + h_first, n_traj * 8);
+    if (sample_mask) std::memcpy(sample_mask, hb + h_smask, smask_bytes);
+    return EPP_OK;
+}
+
+extern "C" int epp_check_poly_trajectories(epp_world *w, const double *coeffs, const double *durations,
+                                           const double *dt, size_t n_traj, int n_segments, int n_coeffs,
+                                           double min_distance, size_t max_samples, uint32_t *traj_valid,
+                                           uint32_t *sample_mask, uint32_t *n_samples, int64_t *first_invalid)
+{
+    std::shared_ptr<DeviceEpoch> ep;
+    int rc = snapshot(w, ep);
+    if (rc) return rc;
+    if (n_traj == 0) return EPP_OK;
+    if (!coeffs || !durations || !dt || !traj_valid || n_segments <= 0 || n_segments > 65535 || n_coeffs <= 0 ||
+        max_samples == 0 || max_samples % 32)
+        return fail(EPP_ERR_INVALID_ARG, "polynomial trajectory batch shape");
+    DeviceGuard guard;
+    EPP_CUDA(guard.enter(ep->device));
+    Staging *s;
+    rc = get_staging(ep->device, &s);
+    if (rc) return rc;
+
+    const size_t c_bytes = n_traj * (size_t)n_segments * 3 * (size_t)n_coeffs * 8;
+    const size_t d_bytes = n_traj * (size_t)n_segments * 8;
+    const size_t t_bytes = n_traj * 8;
+    const size_t wpt = max_samples / 32;
+    const size_t off_d = align_up(c_bytes, 256);
+    const size_t off_t = off_d + align_up(d_bytes, 256);
+    const size_t off_valid = off_t + align_up(t_bytes, 256);
+    const size_t off_first = off_valid + align_up(mask_words(n_traj) * 4, 256);
+    const size_t off_scratch = off_first + align_up(n_traj * 8, 256);
+    const size_t off_ns = off_scratch + align_up(n_traj * 8, 256);
+    const size_t off_smask = off_ns + align_up(n_traj * 4, 256);
+    const size_t smask_bytes = sample_mask ? n_traj * wpt * 4 : 0;
+    rc = reserve_device(s, off_smask + smask_bytes);
+    if (rc) return rc;
+    const size_t out_bytes = mask_words(n_traj) * 4 + n_traj * 12 + smask_bytes;
+    rc = reserve_host(s, 2 * kChunk + out_bytes + 512);
+    if (rc) return rc;
+    if ((rc = upload(s, s->d, coeffs, c_bytes, 0))) return rc;
+    if ((rc = upload(s, s->d + off_d, durations, d_bytes, 0))) return rc;
+    if ((rc = upload(s, s->d + off_t, dt, t_bytes, 0))) return rc;
+    cudaError_t e = launch_poly_trajectories(
+        launch_cfg(*ep), ep->view, ep->bp, (const double *)s->d, (const double *)(s->d + off_d),
+        (const double *)(s->d + off_t), n_traj, n_segments, n_coeffs, min_distance, max_samples,
+        (uint32_t *)(s->d + off_valid), sample_mask ? (uint32_t *)(s->d + off_smask) : nullptr,
+        (uint32_t *)(s->d + off_ns), (int64_t *)(s->d + off_first), (long long *)(s->d + off_scratch), s->stream);
+    if (e != cudaSuccess) return cuda_fail(e, "kernel launch");
+    unsigned char *hb = s->h + 2 * kChunk;
+    const size_t h_first = align_up(mask_words(n_traj) * 4, 8);
+    const size_t h_ns = h_first + n_traj * 8;
+    const size_t h_smask = h_ns + align_up(n_traj * 4, 8);
+    EPP_CUDA(cudaMemcpyAsync(hb, s->d + off_valid, mask_words(n_traj) * 4, cudaMemcpyDeviceToHost, s->stream));
+    EPP_CUDA(cudaMemcpyAsync(hb + h_first, s->d + off_first, n_traj * 8, cudaMemcpyDeviceToHost, s->stream));
+    EPP_CUDA(cudaMemcpyAsync(hb + h_ns, s->d + off_ns, n_traj * 4, cudaMemcpyDeviceToHost, s->stream));
+    if (sample_mask)
+        EPP_CUDA(cudaMemcpyAsync(hb + h_smask, s->d + off_smask, smask_bytes, cudaMemcpyDeviceToHost, s->stream));
+    EPP_CUDA(cudaStreamSynchronize(s->stream));
+    std::memcpy(traj_valid, hb, mask_words(n_traj) * 4);
+    if (first_invalid) std::memcpy(first_invalid, hb + h_first, n_traj * 8);
+    if (n_samples) std::memcpy(n_samples, hb + h_ns, n_traj * 4);
+    if (sample_mask) std::memcpy(sample_mask, hb + h_smask, smask_bytes);
+    return EPP_OK;
+}
+
+// ---- device-buffer checks (asynchronous, capture-safe: launches only) ---------------------------------
+
+extern "C" int epp_check_states_dev(epp_world *w, const double *d_xyz, size_t n, int can_pass_gate, uint32_t *d_mask,
+                                    void *stream)
+{
+    std::shared_ptr<DeviceEpoch> ep;
+    int rc = snapshot(w, ep);
+    if (rc) return rc;
+    if (n && (!d_xyz || !d_mask)) return fail(EPP_ERR_INVALID_ARG, "null buffer");
+    cudaError_t e = launch_states(launch_cfg(*ep), ep->view, ep->bp, d_xyz, n, kModeBool, can_pass_gate, 0.0, d_mask,
+                                  (cudaStream_t)stream);
+    return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
+}
+
+extern "C" int epp_check_states_mindist_dev(epp_world *w, const double *d_xyz, size_t n, double min_distance,
+                                            uint32_t *d_mask, void *stream)
+{
+    std::shared_ptr<DeviceEpoch> ep;
+    int rc = snapshot(w, ep);
+    if (rc) return rc;
+    if (n && (!d_xyz || !d_mask)) return fail(EPP_ERR_INVALID_ARG, "null buffer");
+    cudaError_t e = launch_states(launch_cfg(*ep), ep->view, ep->bp, d_xyz, n, kModeMinDist, 0, min_distance, d_mask,
+                                  (cudaStream_t)stream);
+    return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
+}
+
+extern "C" int epp_check_segments_dev(epp_world *w, const double *d_a, const double *d_b, size_t n, int can_pass_gate,
+                                      uint32_t *d_mask, void *stream)
+{
+    std::shared_ptr<DeviceEpoch> ep;
+    int rc = snapshot(w, ep);
+    if (rc) return rc;
+    if (n && (!d_a || !d_b || !d_mask)) return fail(EPP_ERR_INVALID_ARG, "null buffer");
+    cudaError_t e = launch_segments(launch_cfg(*ep), ep->view, ep->bp, d_a, d_b, n, can_pass_gate, d_mask,
+                                    (cudaStream_t)stream);
+    return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
+}
+
+extern "C" int epp_check_trajectories_dev(epp_world *w, const double *d_col_major, size_t n_traj, size_t rows,
+                                          size_t ld, size_t traj_stride, int cols, double min_distance,
+                                          uint32_t *d_traj_valid, uint32_t *d_sample_mask, int64_t *d_first_invalid,
+                                          void *stream)
+{
+    std::shared_ptr<DeviceEpoch> ep;
+    int rc = snapshot(w, ep);
+    if (rc) return rc;
+    if (n_traj == 0) return EPP_OK;
+    if (!d_col_major || !d_traj_valid || !d_first_invalid || cols < 7 || ld < rows)
+        return fail(EPP_ERR_INVALID_ARG, "trajectory matrix shape (d_first_invalid is required on the device path)");
+    // d_first_invalid doubles as the atomicMin scratch (same width), finalised in place.
+    cudaError_t e = launch_trajectories(launch_cfg(*ep), ep->view, ep->bp, d_col_major, n_traj, rows, ld, traj_stride,
+                                        min_distance, d_traj_valid, d_sample_mask, d_first_invalid,
+                                        (long long *)d_first_invalid, (cudaStream_t)stream);
+    return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
+}
+
+extern "C" int epp_check_poly_trajectories_dev(epp_world *w, const double *d_coeffs, const double *d_durations,
+                                               const double *d_dt, size_t n_traj, int n_segments, int n_coeffs,
+                                               double min_distance, size_t max_samples, uint32_t *d_traj_valid,
+                                               uint32_t *d_sample_mask, uint32_t *d_n_samples,
+                                               int64_t *d_first_invalid, void *stream)
+{
+    std::shared_ptr<DeviceEpoch> ep;
+    int rc = snapshot(w, ep);
+    if (rc) return rc;
+    if (n_traj == 0) return EPP_OK;
+    if (!d_coeffs || !d_durations || !d_dt || !d_traj_valid || !d_first_invalid || n_segments <= 0 ||
+        n_segments > 65535 || n_coeffs <= 0 || max_samples == 0 || max_samples % 32)
+        return fail(EPP_ERR_INVALID_ARG, "polynomial trajectory batch shape");
+    cudaError_t e = launch_poly_trajectories(launch_cfg(*ep), ep->view, ep->bp, d_coeffs, d_durations, d_dt, n_traj,
+                                             n_segments, n_coeffs, min_distance, max_samples, d_traj_valid,
+                                             d_sample_mask, d_n_samples, d_first_invalid, (long long *)d_first_invalid,
+                                             (cudaStream_t)stream);
+    return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
+}
+
+// ---- multi-GPU helpers, generators ---------------------------------------------------------------------
+
+extern "C" int epp_shard_range(size_t n, int rank, int world_size, size_t align, size_t *begin, size_t *end)
+{
+    if (!begin || !end || world_size <= 0 || rank < 0 || rank >= world_size || align == 0 || align % 32)
+        return fail(EPP_ERR_INVALID_ARG, "shard range");
+    const size_t blocks = (n + align - 1) / align;
+    const size_t per = (blocks + (size_t)world_size - 1) / (size_t)world_size * align;
+    *begin = std::min(n, per * (size_t)rank);
+    *end = std::min(n, *begin + per);
+    return EPP_OK;
+}
+
+extern "C" int epp_mask_summary_dev(const uint32_t *d_mask, size_t n_words, uint64_t first_word,
+                                    uint64_t *d_popcount_xor, void *stream)
+{
+    if (!d_popcount_xor || (n_words && !d_mask)) return fail(EPP_ERR_INVALID_ARG, "null buffer");
+    LaunchCfg cfg;
+    int device = 0;
+    EPP_CUDA(cudaGetDevice(&device));
+    EPP_CUDA(cudaDeviceGetAttribute(&cfg.sm_count, cudaDevAttrMultiProcessorCount, device));
+    cudaError_t e = launch_mask_summary(cfg, d_mask, n_words, first_word, d_popcount_xor, (cudaStream_t)stream);
+    return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
+}
+
+extern "C" int epp_gen_states_dev(uint64_t seed, uint64_t first, size_t n, const double lo[3], const double hi[3],
+                                  double *d_xyz, void *stream)
+{
+    if (!lo || !hi || (n && !d_xyz)) return fail(EPP_ERR_INVALID_ARG, "null buffer");
+    cudaError_t e = launch_gen_states(seed, first, n, lo, hi, d_xyz, (cudaStream_t)stream);
+    return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
+}
+
+extern "C" int epp_gen_segments_dev(uint64_t seed, uint64_t first, size_t n, const double lo[3], const double hi[3],
+                                    double max_len, double *d_a, double *d_b, void *stream)
+{
+    if (!lo || !hi || (n && (!d_a || !d_b))) return fail(EPP_ERR_INVALID_ARG, "null buffer");
+    cudaError_t e = launch_gen_segments(seed, first, n, lo, hi, max_len, d_a, d_b, (cudaStream_t)stream);
+    return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
+}

@@ -1,0 +1,730 @@
+// kernels.cu — sm_100a kernels of the validity-check hot path and their launchers.
+//
+// K1  k_states        World::checkPointValidity (both overloads) over an n x 3 AoS batch
+// K2  k_segments      World::checkRayValid over two n x 3 AoS batches
+// K3a k_traj_samples  PathPlanner::checkTrajectoryValidity over column-major matrices
+// K3b k_poly_traj     evaluateRange + Horner + checkTrajectoryValidity fused
+// plus generators / reductions used by the multi-GPU and benchmark plumbing.
+//
+// One thread per unit; a warp's 32 verdicts are packed with __ballot_sync into one mask
+// word.  Broad phase is a template parameter (brute / per-axis bitmasks / grid); all three
+// produce identical masks because every candidate still takes the reference's exact
+// stored-AABB test before the OBB test (DESIGN.md "Broad phase").
+#include <cuda_runtime.h>
+
+#include <climits>
+#include <cstdint>
+
+#include "device_checks.cuh"
+#include "kernels.h"
+
+namespace epp {
+
+namespace {
+
+constexpr int kBlock = 256;
+constexpr int kWarpsPerBlock = kBlock / 32;
+
+extern __shared__ __align__(16) unsigned char g_smem[];
+
+__device__ __forceinline__ void block_copy_words(uint32_t *dst, const uint32_t *__restrict__ src, int words)
+{
+    for (int i = threadIdx.x; i < words; i += blockDim.x) dst[i] = __ldg(src + i);
+}
+
+// ---- point queries -----------------------------------------------------------------------
+
+template <int BP>
+struct PointWorld;
+
+// Brute force: stored AABBs staged in shared memory when they fit (smem_aabb != nullptr).
+template <>
+struct PointWorld<EPP_BP_BRUTE> {
+    const AabbRec *aabb;
+    __device__ void init(const WorldView &wv, bool aabb_in_smem)
+    {
+        aabb = wv.aabb;
+        if (aabb_in_smem) {
+            uint32_t *dst = reinterpret_cast<uint32_t *>(g_smem);
+            block_copy_words(dst, reinterpret_cast<const uint32_t *>(wv.aabb), wv.M * (int)(sizeof(AabbRec) / 4));
+            __syncthreads();
+            aabb = reinterpret_cast<const AabbRec *>(g_smem);
+        }
+    }
+    __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &p, int mode, bool cpg, double md) const
+    {
+        for (int k = 0; k < wv.M; ++k) {
+            if (!within_strict(aabb + k, p)) continue;
+            if (point_candidate_invalid(wv.aabb, wv.obb, k, p, mode, cpg, md)) return true;
+        }
+        return false;
+    }
+};
+
+// Per-axis bin bitmasks: candidates = inside_x[bin(x)] & inside_y[bin(y)] & inside_z[bin(z)].
+template <>
+struct PointWorld<EPP_BP_BITS> {
+    const uint32_t *inside;
+    __device__ void init(const WorldView &wv, bool)
+    {
+        uint32_t *dst = reinterpret_cast<uint32_t *>(g_smem);
+        block_copy_words(dst, wv.bits_inside, 3 * wv.nb * wv.W);
+        __syncthreads();
+        inside = dst;
+    }
+    __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &p, int mode, bool cpg, double md) const
+    {
+        const int nb = wv.nb, W = wv.W;
+        const uint32_t *tx = inside + dev_bin(p.x, wv.bbins.lo[0], wv.bbins.inv[0], nb) * W;
+        const uint32_t *ty = inside + (nb + dev_bin(p.y, wv.bbins.lo[1], wv.bbins.inv[1], nb)) * W;
+        const uint32_t *tz = inside + (2 * nb + dev_bin(p.z, wv.bbins.lo[2], wv.bbins.inv[2], nb)) * W;
+        for (int w = 0; w < W; ++w) {
+            uint32_t m = tx[w] & ty[w] & tz[w];
+            while (m) {
+                const int k = (w << 5) + __ffs(m) - 1;
+                m &= m - 1;
+                if (point_candidate_invalid(wv.aabb, wv.obb, k, p, mode, cpg, md)) return true;
+            }
+        }
+        return false;
+    }
+};
+
+// Uniform grid: candidates = CSR list of the cell holding p.
+template <>
+struct PointWorld<EPP_BP_GRID> {
+    __device__ void init(const WorldView &, bool) {}
+    __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &p, int mode, bool cpg, double md) const
+    {
+        const int bx = dev_bin(p.x, wv.gbins.lo[0], wv.gbins.inv[0], wv.gbins.n[0]);
+        const int by = dev_bin(p.y, wv.gbins.lo[1], wv.gbins.inv[1], wv.gbins.n[1]);
+        const int bz = dev_bin(p.z, wv.gbins.lo[2], wv.gbins.inv[2], wv.gbins.n[2]);
+        const size_t cell = ((size_t)bz * wv.gbins.n[1] + by) * wv.gbins.n[0] + bx;
+        const uint32_t s = __ldg(wv.cell_start + cell), e = __ldg(wv.cell_start + cell + 1);
+        for (uint32_t j = s; j < e; ++j) {
+            const int k = (int)__ldg(wv.cell_items + j);
+            if (point_candidate_invalid(wv.aabb, wv.obb, k, p, mode, cpg, md)) return true;
+        }
+        return false;
+    }
+};
+
+// ---- segment queries ---------------------------------------------------------------------
+
+template <int BP>
+struct RayWorld;
+
+template <>
+struct RayWorld<EPP_BP_BRUTE> {
+    const AabbRec *aabb;
+    __device__ void init(const WorldView &wv, bool aabb_in_smem)
+    {
+        aabb = wv.aabb;
+        if (aabb_in_smem) {
+            uint32_t *dst = reinterpret_cast<uint32_t *>(g_smem);
+            block_copy_words(dst, reinterpret_cast<const uint32_t *>(wv.aabb), wv.M * (int)(sizeof(AabbRec) / 4));
+            __syncthreads();
+            aabb = reinterpret_cast<const AabbRec *>(g_smem);
+        }
+    }
+    __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &a, const P3 &b, bool cpg) const
+    {
+        P3 mn, mx;
+        ray_box(a, b, mn, mx);
+        for (int k = 0; k < wv.M; ++k) {
+            if (!boxes_touch(aabb + k, mn, mx)) continue;
+            if (ray_candidate_invalid(wv.aabb, wv.obb, k, a, b, mn, mx, cpg)) return true;
+        }
+        return false;
+    }
+};
+
+// candidates = AND over axes of max_ge[bin(rayMin)] & min_le[bin(rayMax)].
+template <>
+struct RayWorld<EPP_BP_BITS> {
+    const uint32_t *min_le;
+    const uint32_t *max_ge;
+    __device__ void init(const WorldView &wv, bool)
+    {
+        const int words = 3 * wv.nb * wv.W;
+        uint32_t *dst = reinterpret_cast<uint32_t *>(g_smem);
+        block_copy_words(dst, wv.bits_min_le, words);
+        block_copy_words(dst + words, wv.bits_max_ge, words);
+        __syncthreads();
+        min_le = dst;
+        max_ge = dst + words;
+    }
+    __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &a, const P3 &b, bool cpg) const
+    {
+        P3 mn, mx;
+        ray_box(a, b, mn, mx);
+        const int nb = wv.nb, W = wv.W;
+        const uint32_t *gx = max_ge + dev_bin(mn.x, wv.bbins.lo[0], wv.bbins.inv[0], nb) * W;
+        const uint32_t *gy = max_ge + (nb + dev_bin(mn.y, wv.bbins.lo[1], wv.bbins.inv[1], nb)) * W;
+        const uint32_t *gz = max_ge + (2 * nb + dev_bin(mn.z, wv.bbins.lo[2], wv.bbins.inv[2], nb)) * W;
+        const uint32_t *lx = min_le + dev_bin(mx.x, wv.bbins.lo[0], wv.bbins.inv[0], nb) * W;
+        const uint32_t *ly = min_le + (nb + dev_bin(mx.y, wv.bbins.lo[1], wv.bbins.inv[1], nb)) * W;
+        const uint32_t *lz = min_le + (2 * nb + dev_bin(mx.z, wv.bbins.lo[2], wv.bbins.inv[2], nb)) * W;
+        for (int w = 0; w < W; ++w) {
+            uint32_t m = gx[w] & gy[w] & gz[w] & lx[w] & ly[w] & lz[w];
+            while (m) {
+                const int k = (w << 5) + __ffs(m) - 1;
+                m &= m - 1;
+                if (ray_candidate_invalid(wv.aabb, wv.obb, k, a, b, mn, mx, cpg)) return true;
+            }
+        }
+        return false;
+    }
+};
+
+// Cells overlapped by the ray box; a candidate listed in several of them is evaluated only
+// in the first cell of (ray cells) x (candidate cells).
+template <>
+struct RayWorld<EPP_BP_GRID> {
+    __device__ void init(const WorldView &, bool) {}
+    __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &a, const P3 &b, bool cpg) const
+    {
+        P3 mn, mx;
+        ray_box(a, b, mn, mx);
+        const AxisBins &g = wv.gbins;
+        const int x0 = dev_bin(mn.x, g.lo[0], g.inv[0], g.n[0]), x1 = dev_bin(mx.x, g.lo[0], g.inv[0], g.n[0]);
+        const int y0 = dev_bin(mn.y, g.lo[1], g.inv[1], g.n[1]), y1 = dev_bin(mx.y, g.lo[1], g.inv[1], g.n[1]);
+        const int z0 = dev_bin(mn.z, g.lo[2], g.inv[2], g.n[2]), z1 = dev_bin(mx.z, g.lo[2], g.inv[2], g.n[2]);
+        for (int z = z0; z <= z1; ++z)
+            for (int y = y0; y <= y1; ++y) {
+                const size_t row = ((size_t)z * g.n[1] + y) * g.n[0];
+                for (int x = x0; x <= x1; ++x) {
+                    const uint32_t s = __ldg(wv.cell_start + row + x), e = __ldg(wv.cell_start + row + x + 1);
+                    for (uint32_t j = s; j < e; ++j) {
+                        const int k = (int)__ldg(wv.cell_items + j);
+                        const uint64_t cm = wv.obb[k].cell_min;
+                        const int kx = (int)(cm & 0x1FFFFF), ky = (int)((cm >> 21) & 0x1FFFFF), kz = (int)(cm >> 42);
+                        if (x != (kx > x0 ? kx : x0) || y != (ky > y0 ? ky : y0) || z != (kz > z0 ? kz : z0)) continue;
+                        if (ray_candidate_invalid(wv.aabb, wv.obb, k, a, b, mn, mx, cpg)) return true;
+                    }
+                }
+            }
+        return false;
+    }
+};
+
+// ---- K1: states ----------------------------------------------------------------------------
+
+// Tile = kBlock consecutive states; block t, t + gridDim, ... ; the next tile's coordinates are
+// fetched before the current tile is evaluated so two tiles per thread are in flight.
+template <int BP>
+__global__ void __launch_bounds__(kBlock) k_states(WorldView wv, const double *__restrict__ xyz, size_t n, int mode,
+                                                   int can_pass_gate, double min_distance, int aabb_in_smem,
+                                                   uint32_t *__restrict__ mask)
+{
+    PointWorld<BP> world;
+    world.init(wv, aabb_in_smem != 0);
+    const size_t tiles = (n + kBlock - 1) / kBlock;
+    size_t tile = blockIdx.x;
+    if (tile >= tiles) return;
+
+    size_t i = tile * kBlock + threadIdx.x;
+    P3 cur = {0.0, 0.0, 0.0};
+    if (i < n) {
+        cur.x = __ldg(xyz + 3 * i);
+        cur.y = __ldg(xyz + 3 * i + 1);
+        cur.z = __ldg(xyz + 3 * i + 2);
+    }
+    for (;;) {
+        const size_t next_tile = tile + gridDim.x;
+        const size_t ni = next_tile * kBlock + threadIdx.x;
+        P3 nxt = {0.0, 0.0, 0.0};
+        if (next_tile < tiles && ni < n) {
+            nxt.x = __ldg(xyz + 3 * ni);
+            nxt.y = __ldg(xyz + 3 * ni + 1);
+            nxt.z = __ldg(xyz + 3 * ni + 2);
+        }
+        bool valid = false;
+        if (i < n) valid = !world.invalid(wv, cur, mode, can_pass_gate != 0, min_distance);
+        const uint32_t word = __ballot_sync(0xffffffffu, valid);
+        if ((threadIdx.x & 31) == 0 && i < n) mask[i >> 5] = word;
+        if (next_tile >= tiles) break;
+        tile = next_tile;
+        i = ni;
+        cur = nxt;
+    }
+}
+
+// ---- K2: segments --------------------------------------------------------------------------
+
+template <int BP>
+__global__ void __launch_bounds__(kBlock) k_segments(WorldView wv, const double *__restrict__ pa,
+                                                     const double *__restrict__ pb, size_t n, int can_pass_gate,
+                                                     int aabb_in_smem, uint32_t *__restrict__ mask)
+{
+    RayWorld<BP> world;
+    world.init(wv, aabb_in_smem != 0);
+    const size_t tiles = (n + kBlock - 1) / kBlock;
+    for (size_t tile = blockIdx.x; tile < tiles; tile += gridDim.x) {
+        const size_t i = tile * kBlock + threadIdx.x;
+        bool valid = false;
+        if (i < n) {
+            const P3 a = {__ldg(pa + 3 * i), __ldg(pa + 3 * i + 1), __ldg(pa + 3 * i + 2)};
+            const P3 b = {__ldg(pb + 3 * i), __ldg(pb + 3 * i + 1), __ldg(pb + 3 * i + 2)};
+            valid = !world.invalid(wv, a, b, can_pass_gate != 0);
+        }
+        const uint32_t word = __ballot_sync(0xffffffffu, valid);
+        if ((threadIdx.x & 31) == 0 && i < n) mask[i >> 5] = word;
+    }
+}
+
+// ---- K3a: pre-sampled trajectory matrices ----------------------------------------------------
+
+__global__ void k_fill_i64(int64_t *p, size_t n, int64_t v)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+// blockIdx.x = trajectory, blockIdx.y = tile of kBlock rows.  Position = columns 0, 3, 6
+// (src/PathPlanner.cpp:272-273).  first_row holds LLONG_MAX on entry.
+template <int BP>
+__global__ void __launch_bounds__(kBlock) k_traj_samples(WorldView wv, const double *__restrict__ mats, size_t rows,
+                                                         size_t ld, size_t traj_stride, double min_distance,
+                                                         int aabb_in_smem, uint32_t *__restrict__ sample_mask,
+                                                         long long *__restrict__ first_row)
+{
+    PointWorld<BP> world;
+    world.init(wv, aabb_in_smem != 0);
+    const size_t t = blockIdx.x;
+    const size_t r = (size_t)blockIdx.y * kBlock + threadIdx.x;
+    const double *m = mats + t * traj_stride;
+    bool valid = false;
+    if (r < rows) {
+        const P3 p = {__ldg(m + r), __ldg(m + 3 * ld + r), __ldg(m + 6 * ld + r)};
+        valid = !world.invalid(wv, p, kModeMinDist, false, min_distance);
+    }
+    const uint32_t word = __ballot_sync(0xffffffffu, valid);
+    const uint32_t active = __ballot_sync(0xffffffffu, r < rows);
+    if ((threadIdx.x & 31) == 0 && active) {
+        const size_t words_per_traj = (rows + 31) / 32;
+        if (sample_mask) sample_mask[t * words_per_traj + (r >> 5)] = word;
+        const uint32_t bad = active & ~word;
+        if (bad) atomicMin(first_row + t, (long long)(r + (size_t)(__ffs(bad) - 1)));
+    }
+}
+
+// first_row: LLONG_MAX -> -1 (valid); one validity bit per trajectory.
+__global__ void k_traj_finalize(long long *first_row, int64_t *first_out, size_t n_traj,
+                                uint32_t *__restrict__ traj_valid)
+{
+    const size_t t = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    bool valid = false;
+    if (t < n_traj) {
+        const long long f = first_row[t];
+        valid = (f == LLONG_MAX);
+        if (first_out) first_out[t] = valid ? -1 : (int64_t)f;
+    }
+    const uint32_t word = __ballot_sync(0xffffffffu, valid);
+    if ((threadIdx.x & 31) == 0 && (t - (threadIdx.x & 31)) < n_traj) traj_valid[t >> 5] = word;
+}
+
+// ---- K3b: fused polynomial sweep --------------------------------------------------------------
+
+constexpr int kPolyWarps = 4;
+constexpr int kPolyPitch = 33; // odd pitch: conflict-free column writes and row reads
+
+// Polynomial::evaluate(t, 0) (polynomial.h:136-150): Horner from the top coefficient.
+__device__ __forceinline__ double horner(const double *__restrict__ c, int n, double t)
+{
+    double r = __ldg(c + n - 1);
+    for (int j = n - 2; j >= 0; --j) r = dadd(dmul(r, t), __ldg(c + j));
+    return r;
+}
+
+// A warp owns 32 trajectories.  Phase 1: lane l advances the reference's sequential sampler
+// (trajectory.cpp:121-140: running sums, not k*dt) of ITS trajectory by up to 32 samples and
+// parks (segment, time_in_segment) in shared memory.  Phase 2: for each of the 32 trajectories
+// in turn, the 32 lanes evaluate its 32 parked samples (Horner x 3 + world check) and ballot
+// them into one mask word.
+template <int BP>
+__global__ void __launch_bounds__(kPolyWarps * 32) k_poly_traj(WorldView wv, const double *__restrict__ coeffs,
+                                                               const double *__restrict__ durations,
+                                                               const double *__restrict__ dts, size_t n_traj,
+                                                               int n_segments, int n_coeffs, double min_distance,
+                                                               size_t max_samples, int aabb_in_smem,
+                                                               uint32_t *__restrict__ sample_mask,
+                                                               uint32_t *__restrict__ n_samples_out,
+                                                               long long *__restrict__ first_row)
+{
+    __shared__ double s_t[kPolyWarps][32 * kPolyPitch];
+    __shared__ unsigned short s_seg[kPolyWarps][32 * kPolyPitch];
+    PointWorld<BP> world;
+    world.init(wv, aabb_in_smem != 0);
+
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const size_t traj0 = ((size_t)blockIdx.x * kPolyWarps + warp) * 32;
+    if (traj0 >= n_traj) return;
+    const size_t my = traj0 + lane;
+    const bool have = my < n_traj;
+    const size_t words_per_traj = max_samples / 32;
+
+    // Sampler state of my trajectory: evaluateRange(0, maxTime, dt), trajectory.cpp:95-119.
+    const double *dur = durations + my * n_segments;
+    double t_end = 0.0, dt = 0.0, acc = 0.0, tin = 0.0, seg_T = 0.0;
+    int seg = 0;
+    bool done = !have;
+    if (have) {
+        dt = __ldg(dts + my);
+        for (int k = 0; k < n_segments; ++k) t_end = dadd(t_end, __ldg(dur + k)); // trajectory.h:64-71
+        // start-segment search with t_start = 0 (:99-114)
+        double a = 0.0;
+        int k = 0;
+        for (k = 0; k < n_segments; ++k) {
+            a = dadd(a, __ldg(dur + k));
+            if (a > 0.0) break;
+        }
+        if (0.0 > a || k >= n_segments) {
+            done = true;
+        } else {
+            seg = k;
+            seg_T = __ldg(dur + seg);
+            acc = dsub(a, seg_T);      // :117
+            tin = dsub(0.0, acc);      // :118
+        }
+    }
+    uint32_t emitted_total = 0;
+
+    for (size_t chunk = 0; chunk < words_per_traj; ++chunk) {
+        // ---- phase 1: up to 32 samples of my trajectory
+        int cnt = 0;
+        while (!done && cnt < 32) {
+            if (!(acc < t_end)) { // :121
+                done = true;
+                break;
+            }
+            if (tin > seg_T) { // :122-130
+                tin = dsub(tin, seg_T);
+                ++seg;
+                if (seg >= n_segments) {
+                    done = true;
+                    break;
+                }
+                seg_T = __ldg(dur + seg);
+                continue;
+            }
+            s_t[warp][lane * kPolyPitch + cnt] = tin; // :132
+            s_seg[warp][lane * kPolyPitch + cnt] = (unsigned short)seg;
+            ++cnt;
+            tin = dadd(tin, dt); // :138-139
+            acc = dadd(acc, dt);
+        }
+        emitted_total += (uint32_t)cnt;
+        __syncwarp();
+        if (__ballot_sync(0xffffffffu, cnt > 0) == 0) break;
+
+        // ---- phase 2: evaluate trajectory j's parked samples, one per lane
+        for (int j = 0; j < 32; ++j) {
+            const int cj = __shfl_sync(0xffffffffu, cnt, j);
+            if (cj == 0) continue;
+            const size_t tj = traj0 + j;
+            bool valid = false;
+            if (lane < cj) {
+                const double t = s_t[warp][j * kPolyPitch + lane];
+                const int sg = s_seg[warp][j * kPolyPitch + lane];
+                const double *c = coeffs + ((tj * n_segments + sg) * 3) * (size_t)n_coeffs; // segment.cpp:51-58
+                const P3 p = {horner(c, n_coeffs, t), horner(c + n_coeffs, n_coeffs, t),
+                              horner(c + 2 * n_coeffs, n_coeffs, t)};
+                valid = !world.invalid(wv, p, kModeMinDist, false, min_distance);
+            }
+            const uint32_t word = __ballot_sync(0xffffffffu, valid);
+            if (lane == 0) {
+                if (sample_mask) sample_mask[tj * words_per_traj + chunk] = word;
+                const uint32_t active = cj >= 32 ? 0xffffffffu : ((1u << cj) - 1u);
+                const uint32_t bad = active & ~word;
+                if (bad) atomicMin(first_row + tj, (long long)(chunk * 32 + (size_t)(__ffs(bad) - 1)));
+            }
+        }
+        __syncwarp();
+    }
+    if (have && n_samples_out) n_samples_out[my] = emitted_total;
+}
+
+__global__ void k_fill_u32(uint32_t *p, size_t n, uint32_t v)
+{
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) p[i] = v;
+}
+
+// ---- generators (bit-identical to the oracle's host generators) ------------------------------
+
+__device__ __forceinline__ uint64_t mix64(uint64_t seed, uint64_t counter)
+{
+    uint64_t z = seed + 0x9E3779B97F4A7C15ull * (counter + 1);
+    z ^= z >> 30;
+    z *= 0xBF58476D1CE4E5B9ull;
+    z ^= z >> 27;
+    z *= 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    return z;
+}
+
+__device__ __forceinline__ double u01(uint64_t seed, uint64_t index, unsigned lane)
+{
+    return dmul((double)(mix64(seed, index * 8 + lane) >> 11), 0x1.0p-53);
+}
+
+struct Box3 {
+    double lo[3], hi[3];
+};
+
+__global__ void k_gen_states(uint64_t seed, uint64_t first, size_t n, Box3 box, double *__restrict__ xyz)
+{
+    const size_t e = (size_t)blockIdx.x * blockDim.x + threadIdx.x; // one thread per coordinate
+    if (e >= 3 * n) return;
+    const size_t k = e / 3;
+    const unsigned d = (unsigned)(e - 3 * k);
+    xyz[e] = dadd(box.lo[d], dmul(u01(seed, first + k, d), dsub(box.hi[d], box.lo[d])));
+}
+
+__global__ void k_gen_segments(uint64_t seed, uint64_t first, size_t n, Box3 box, double max_len,
+                               double *__restrict__ pa, double *__restrict__ pb)
+{
+    const size_t k = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (k >= n) return;
+    const uint64_t idx = first + k;
+    double a[3], v[3];
+    for (unsigned d = 0; d < 3; ++d) {
+        a[d] = dadd(box.lo[d], dmul(u01(seed, idx, d), dsub(box.hi[d], box.lo[d])));
+        v[d] = dsub(dmul(2.0, u01(seed, idx, 3 + d)), 1.0);
+    }
+    const double len2 = dadd(dadd(dmul(v[0], v[0]), dmul(v[1], v[1])), dmul(v[2], v[2]));
+    const double norm = __dsqrt_rn(len2);
+    const double L = dmul(max_len, dsub(1.0, u01(seed, idx, 6)));
+    for (unsigned d = 0; d < 3; ++d) {
+        const double u = norm > 0.0 ? __ddiv_rn(v[d], norm) : 0.0;
+        double e = dadd(a[d], dmul(L, u));
+        if (e < box.lo[d]) e = box.lo[d];
+        if (e > box.hi[d]) e = box.hi[d];
+        pa[3 * k + d] = a[d];
+        pb[3 * k + d] = e;
+    }
+}
+
+// out[0] += popcount, out[1] ^= XOR over words of mix64(0x5EED, (global word index << 32) | word).
+__global__ void k_mask_summary(const uint32_t *__restrict__ mask, size_t n_words, uint64_t first_word,
+                               unsigned long long *out)
+{
+    unsigned long long pop = 0, x = 0;
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n_words; i += (size_t)gridDim.x * blockDim.x) {
+        const uint32_t w = mask[i];
+        pop += (unsigned)__popc(w);
+        x ^= mix64(0x5EEDull, ((first_word + i) << 32) | w);
+    }
+    for (int o = 16; o; o >>= 1) {
+        pop += __shfl_xor_sync(0xffffffffu, pop, o);
+        x ^= __shfl_xor_sync(0xffffffffu, x, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(out, pop);
+        atomicXor(out + 1, x);
+    }
+}
+
+// Dynamic shared memory a kernel variant needs for this world.
+size_t point_smem_bytes(const WorldView &wv, int bp, bool &aabb_in_smem)
+{
+    aabb_in_smem = false;
+    if (bp == EPP_BP_BITS) return (size_t)3 * wv.nb * wv.W * 4;
+    if (bp == EPP_BP_BRUTE && wv.M <= 2048) {
+        aabb_in_smem = true;
+        return (size_t)wv.M * sizeof(AabbRec);
+    }
+    return 0;
+}
+
+size_t ray_smem_bytes(const WorldView &wv, int bp, bool &aabb_in_smem)
+{
+    aabb_in_smem = false;
+    if (bp == EPP_BP_BITS) return (size_t)6 * wv.nb * wv.W * 4;
+    if (bp == EPP_BP_BRUTE && wv.M <= 2048) {
+        aabb_in_smem = true;
+        return (size_t)wv.M * sizeof(AabbRec);
+    }
+    return 0;
+}
+
+// Opt in to more than 48 KB of (static + dynamic) shared memory per block when needed.
+template <typename K>
+cudaError_t ensure_smem(K kernel, size_t bytes, size_t static_bytes = 0)
+{
+    if (bytes + static_bytes <= 48 * 1024) return cudaSuccess;
+    return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+}
+
+unsigned persistent_grid(const LaunchCfg &cfg, size_t tiles, int blocks_per_sm)
+{
+    size_t cap = (size_t)cfg.sm_count * (size_t)blocks_per_sm;
+    size_t g = tiles < cap ? tiles : cap;
+    return (unsigned)(g ? g : 1);
+}
+
+} // namespace
+
+std::atomic<uint64_t> g_launches{0};
+
+#define EPP_DISPATCH_BP(bp, ...)                                                 \
+    switch (bp) {                                                                \
+    case EPP_BP_BRUTE: { constexpr int BP = EPP_BP_BRUTE; __VA_ARGS__; } break;  \
+    case EPP_BP_BITS: { constexpr int BP = EPP_BP_BITS; __VA_ARGS__; } break;    \
+    default: { constexpr int BP = EPP_BP_GRID; __VA_ARGS__; } break;             \
+    }
+
+cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_xyz, size_t n, int mode,
+                          int can_pass_gate, double min_distance, uint32_t *d_mask, cudaStream_t stream)
+{
+    if (n == 0) return cudaSuccess;
+    bool in_smem;
+    const size_t smem = point_smem_bytes(wv, bp, in_smem);
+    const size_t tiles = (n + kBlock - 1) / kBlock;
+    const unsigned grid = persistent_grid(cfg, tiles, cfg.states_blocks_per_sm);
+    cudaError_t err = cudaSuccess;
+    EPP_DISPATCH_BP(bp, {
+        err = ensure_smem(k_states<BP>, smem);
+        if (err == cudaSuccess) {
+            k_states<BP><<<grid, kBlock, smem, stream>>>(wv, d_xyz, n, mode, can_pass_gate, min_distance, in_smem ? 1 : 0, d_mask);
+            err = cudaGetLastError();
+        }
+    });
+    g_launches++;
+    return err;
+}
+
+cudaError_t launch_segments(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_a, const double *d_b,
+                            size_t n, int can_pass_gate, uint32_t *d_mask, cudaStream_t stream)
+{
+    if (n == 0) return cudaSuccess;
+    bool in_smem;
+    const size_t smem = ray_smem_bytes(wv, bp, in_smem);
+    const size_t tiles = (n + kBlock - 1) / kBlock;
+    const unsigned grid = persistent_grid(cfg, tiles, cfg.segments_blocks_per_sm);
+    cudaError_t err = cudaSuccess;
+    EPP_DISPATCH_BP(bp, {
+        err = ensure_smem(k_segments<BP>, smem);
+        if (err == cudaSuccess) {
+            k_segments<BP><<<grid, kBlock, smem, stream>>>(wv, d_a, d_b, n, can_pass_gate, in_smem ? 1 : 0, d_mask);
+            err = cudaGetLastError();
+        }
+    });
+    g_launches++;
+    return err;
+}
+
+cudaError_t launch_trajectories(const LaunchCfg &, const WorldView &wv, int bp, const double *d_mats, size_t n_traj,
+                                size_t rows, size_t ld, size_t traj_stride, double min_distance, uint32_t *d_traj_valid,
+                                uint32_t *d_sample_mask, int64_t *d_first_invalid, long long *d_first_scratch,
+                                cudaStream_t stream)
+{
+    if (n_traj == 0) return cudaSuccess;
+    k_fill_i64<<<(unsigned)((n_traj + 255) / 256), 256, 0, stream>>>((int64_t *)d_first_scratch, n_traj, LLONG_MAX);
+    g_launches++;
+    cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess) return err;
+    if (rows > 0) {
+        bool in_smem;
+        const size_t smem = point_smem_bytes(wv, bp, in_smem);
+        const size_t row_tiles = (rows + kBlock - 1) / kBlock;
+        if (row_tiles > 65535 || n_traj > 0x7fffffffull) return cudaErrorInvalidValue;
+        dim3 grid((unsigned)n_traj, (unsigned)row_tiles);
+        EPP_DISPATCH_BP(bp, {
+            err = ensure_smem(k_traj_samples<BP>, smem);
+            if (err == cudaSuccess) {
+                k_traj_samples<BP><<<grid, kBlock, smem, stream>>>(wv, d_mats, rows, ld, traj_stride, min_distance,
+                                                                   in_smem ? 1 : 0, d_sample_mask, d_first_scratch);
+                err = cudaGetLastError();
+            }
+        });
+        g_launches++;
+        if (err != cudaSuccess) return err;
+    }
+    k_traj_finalize<<<(unsigned)((n_traj + 255) / 256), 256, 0, stream>>>(d_first_scratch, d_first_invalid, n_traj,
+                                                                         d_traj_valid);
+    g_launches++;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_poly_trajectories(const LaunchCfg &, const WorldView &wv, int bp, const double *d_coeffs,
+                                     const double *d_durations, const double *d_dt, size_t n_traj, int n_segments,
+                                     int n_coeffs, double min_distance, size_t max_samples, uint32_t *d_traj_valid,
+                                     uint32_t *d_sample_mask, uint32_t *d_n_samples, int64_t *d_first_invalid,
+                                     long long *d_first_scratch, cudaStream_t stream)
+{
+    if (n_traj == 0) return cudaSuccess;
+    k_fill_i64<<<(unsigned)((n_traj + 255) / 256), 256, 0, stream>>>((int64_t *)d_first_scratch, n_traj, LLONG_MAX);
+    g_launches++;
+    cudaError_t err = cudaGetLastError();
+    if (err != cudaSuccess) return err;
+    if (d_sample_mask) {
+        const size_t words = n_traj * (max_samples / 32);
+        k_fill_u32<<<(unsigned)((words + 255) / 256), 256, 0, stream>>>(d_sample_mask, words, 0u);
+        g_launches++;
+    }
+    bool in_smem;
+    const size_t smem = point_smem_bytes(wv, bp, in_smem);
+    const size_t per_block = (size_t)kPolyWarps * 32;
+    const unsigned grid = (unsigned)((n_traj + per_block - 1) / per_block);
+    EPP_DISPATCH_BP(bp, {
+        err = ensure_smem(k_poly_traj<BP>, smem, sizeof(double) * kPolyWarps * 32 * kPolyPitch + 2 * kPolyWarps * 32 * kPolyPitch);
+        if (err == cudaSuccess) {
+            k_poly_traj<BP><<<grid, kPolyWarps * 32, smem, stream>>>(wv, d_coeffs, d_durations, d_dt, n_traj, n_segments,
+                                                                     n_coeffs, min_distance, max_samples, in_smem ? 1 : 0,
+                                                                     d_sample_mask, d_n_samples, d_first_scratch);
+            err = cudaGetLastError();
+        }
+    });
+    g_launches++;
+    if (err != cudaSuccess) return err;
+    k_traj_finalize<<<(unsigned)((n_traj + 255) / 256), 256, 0, stream>>>(d_first_scratch, d_first_invalid, n_traj,
+                                                                         d_traj_valid);
+    g_launches++;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_gen_states(uint64_t seed, uint64_t first, size_t n, const double lo[3], const double hi[3],
+                              double *d_xyz, cudaStream_t stream)
+{
+    if (n == 0) return cudaSuccess;
+    Box3 box;
+    for (int d = 0; d < 3; ++d) {
+        box.lo[d] = lo[d];
+        box.hi[d] = hi[d];
+    }
+    const size_t elems = 3 * n;
+    k_gen_states<<<(unsigned)((elems + 255) / 256), 256, 0, stream>>>(seed, first, n, box, d_xyz);
+    g_launches++;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_gen_segments(uint64_t seed, uint64_t first, size_t n, const double lo[3], const double hi[3],
+                                double max_len, double *d_a, double *d_b, cudaStream_t stream)
+{
+    if (n == 0) return cudaSuccess;
+    Box3 box;
+    for (int d = 0; d < 3; ++d) {
+        box.lo[d] = lo[d];
+        box.hi[d] = hi[d];
+    }
+    k_gen_segments<<<(unsigned)((n + 255) / 256), 256, 0, stream>>>(seed, first, n, box, max_len, d_a, d_b);
+    g_launches++;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_mask_summary(const LaunchCfg &cfg, const uint32_t *d_mask, size_t n_words, uint64_t first_word,
+                                uint64_t *d_out, cudaStream_t stream)
+{
+    cudaError_t err = cudaMemsetAsync(d_out, 0, 2 * sizeof(uint64_t), stream);
+    if (err != cudaSuccess || n_words == 0) return err;
+    size_t blocks = (n_words + 255) / 256;
+    const size_t cap = (size_t)cfg.sm_count * 8;
+    if (blocks > cap) blocks = cap;
+    k_mask_summary<<<(unsigned)blocks, 256, 0, stream>>>(d_mask, n_words, first_word, (unsigned long long *)d_out);
+    g_launches++;
+    return cudaGetLastError();
+}
+
+} // namespace epp

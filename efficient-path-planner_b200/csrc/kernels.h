@@ -1,0 +1,42 @@
+// kernels.h — launcher interface between the C-ABI layer (capi.cu) and the kernels (kernels.cu).
+#pragma once
+
+#include <cuda_runtime.h>
+
+#include <atomic>
+#include <cstdint>
+
+#include "device_checks.cuh"
+
+namespace epp {
+
+struct LaunchCfg {
+    int sm_count = 148;
+    int states_blocks_per_sm = 8;   // 0: one block per tile (non-persistent)
+    int segments_blocks_per_sm = 4; // 0: one block per tile
+    int states_variant = 0;         // 0: direct loads, 1: TMA bulk pipeline
+};
+
+extern std::atomic<uint64_t> g_launches;
+
+cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_xyz, size_t n, int mode,
+                          int can_pass_gate, double min_distance, uint32_t *d_mask, cudaStream_t stream);
+cudaError_t launch_segments(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_a, const double *d_b,
+                            size_t n, int can_pass_gate, uint32_t *d_mask, cudaStream_t stream);
+cudaError_t launch_trajectories(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_mats, size_t n_traj,
+                                size_t rows, size_t ld, size_t traj_stride, double min_distance, uint32_t *d_traj_valid,
+                                uint32_t *d_sample_mask, int64_t *d_first_invalid, long long *d_first_scratch,
+                                cudaStream_t stream);
+cudaError_t launch_poly_trajectories(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_coeffs,
+                                     const double *d_durations, const double *d_dt, size_t n_traj, int n_segments,
+                                     int n_coeffs, double min_distance, size_t max_samples, uint32_t *d_traj_valid,
+                                     uint32_t *d_sample_mask, uint32_t *d_n_samples, int64_t *d_first_invalid,
+                                     long long *d_first_scratch, cudaStream_t stream);
+cudaError_t launch_gen_states(uint64_t seed, uint64_t first, size_t n, const double lo[3], const double hi[3],
+                              double *d_xyz, cudaStream_t stream);
+cudaError_t launch_gen_segments(uint64_t seed, uint64_t first, size_t n, const double lo[3], const double hi[3],
+                                double max_len, double *d_a, double *d_b, cudaStream_t stream);
+cudaError_t launch_mask_summary(const LaunchCfg &cfg, const uint32_t *d_mask, size_t n_words, uint64_t first_word,
+                                uint64_t *d_out, cudaStream_t stream);
+
+} // namespace epp

@@ -1,0 +1,390 @@
+// world_host.cpp — host-side World construction and broad-phase tables (product code).
+// Compiled with -ffp-contract=off: every operation is an individually rounded binary64 op,
+// 3-term dot products are summed left to right (SURVEY.md §8a note E).
+#include "world_host.h"
+
+#include <algorithm>
+#include <cmath>
+#include <cstring>
+
+namespace epp {
+
+namespace {
+
+struct V3 {
+    double v[3];
+};
+
+// Eigen fixed-size product M * v, coefficient based: out_r = (M(r,0) v0 + M(r,1) v1) + M(r,2) v2.
+V3 mul(const double m[9], const V3 &x)
+{
+    V3 o;
+    for (int r = 0; r < 3; ++r) {
+        double s = m[3 * r] * x.v[0];
+        s = s + m[3 * r + 1] * x.v[1];
+        s = s + m[3 * r + 2] * x.v[2];
+        o.v[r] = s;
+    }
+    return o;
+}
+
+void mul33(const double a[9], const double b[9], double out[9])
+{
+    double t[9];
+    for (int r = 0; r < 3; ++r)
+        for (int c = 0; c < 3; ++c) {
+            double s = a[3 * r] * b[c];
+            s = s + a[3 * r + 1] * b[3 + c];
+            s = s + a[3 * r + 2] * b[6 + c];
+            t[3 * r + c] = s;
+        }
+    std::memcpy(out, t, sizeof t);
+}
+
+} // namespace
+
+const char *status_message(int status)
+{
+    switch (status) {
+    case EPP_OK: return "ok";
+    case EPP_ERR_ROT_X: return "Rotation around x axis is not supported";   // src/Object.cpp:41
+    case EPP_ERR_ROT_Y: return "Rotation around y axis is not supported";   // src/Object.cpp:46
+    case EPP_ERR_CENTER_Z: return "Center z position must be zero";         // src/Object.cpp:19
+    case EPP_ERR_NO_GEOMETRY: return "no geometry registered for this component / gate type";
+    case EPP_ERR_NO_SUCH_OBB: return "map::at";                             // src/World.cpp:74
+    case EPP_ERR_INVALID_ARG: return "invalid argument";
+    case EPP_ERR_NOT_COMMITTED: return "world has uncommitted changes or was never committed";
+    case EPP_ERR_CUDA: return "CUDA error";
+    case EPP_ERR_NO_DEVICE: return "no CUDA device available (there is no CPU fallback)";
+    default: return "unknown status";
+    }
+}
+
+int HostWorld::set_gate_geometry(int type_id, const epp_obb_desc *d, int n)
+{
+    if (n < 0 || (n > 0 && !d)) return EPP_ERR_INVALID_ARG;
+    gate_geom_[type_id].assign(d, d + n);
+    return EPP_OK;
+}
+
+int HostWorld::set_obstacle_geometry(const epp_obb_desc *d, int n)
+{
+    if (n < 0 || (n > 0 && !d)) return EPP_ERR_INVALID_ARG;
+    obstacle_geom_.assign(d, d + n);
+    return EPP_OK;
+}
+
+void HostWorld::reset() // include/World.h:29-33
+{
+    index_.clear();
+    obbs_.clear();
+}
+
+// Object::createFromDescription -> Object::Object -> translate -> rotateZ (src/Object.cpp:11-85).
+int HostWorld::build_object(const std::vector<epp_obb_desc> &g, const double pos[3],
+                            const double rot[3], std::vector<HostObb> &out) const
+{
+    if (std::fabs(rot[0]) > 1e-6) return EPP_ERR_ROT_X;
+    if (std::fabs(rot[1]) > 1e-6) return EPP_ERR_ROT_Y;
+    if (pos[2] > 1e-6) return EPP_ERR_CENTER_Z;
+
+    V3 global_center{{0.0, 0.0, 0.0}};
+    for (int r = 0; r < 3; ++r) global_center.v[r] += pos[r];
+
+    const double c = std::cos(rot[2]);
+    const double s = std::sin(rot[2]);
+    const double rz[9] = {c, -s, 0.0, s, c, 0.0, 0.0, 0.0, 1.0};
+
+    out.clear();
+    out.reserve(g.size());
+    for (const epp_obb_desc &d : g) {
+        HostObb o;
+        for (int r = 0; r < 3; ++r) {
+            o.center[r] = d.position[r];
+            o.half[r] = d.size[r] / 2; // src/ConfigParserYAML.cpp:63
+        }
+        const double ident[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1}; // include/OBB.h:49
+        std::memcpy(o.rot, ident, sizeof ident);
+        o.filling = d.filling != 0;
+
+        for (int r = 0; r < 3; ++r) o.center[r] += pos[r];
+        V3 rel;
+        for (int r = 0; r < 3; ++r) rel.v[r] = o.center[r] - global_center.v[r];
+        V3 turned = mul(rz, rel);
+        for (int r = 0; r < 3; ++r) o.center[r] = turned.v[r] + global_center.v[r];
+        mul33(rz, o.rot, o.rot);
+        out.push_back(o);
+    }
+    return EPP_OK;
+}
+
+// OBB::getAABB (src/OBB.cpp:93-124): extent of the 8 rotated corners of the UN-inflated box,
+// then +- inflate for collision boxes only.
+void obb_aabb(const HostObb &o, double inflate, double mn[3], double mx[3])
+{
+    for (int c = 0; c < 8; ++c) {
+        const double sx = ((c & 3) == 1 || (c & 3) == 2) ? 1.0 : -1.0; // -1 1 1 -1 | -1 1 1 -1
+        const double sy = (c & 2) ? 1.0 : -1.0;                         // -1 -1 1 1 | ...
+        const double sz = (c & 4) ? 1.0 : -1.0;
+        V3 corner{{sx * o.half[0], sy * o.half[1], sz * o.half[2]}};
+        V3 g = mul(o.rot, corner);
+        for (int r = 0; r < 3; ++r) {
+            const double v = g.v[r] + o.center[r];
+            if (c == 0) {
+                mn[r] = v;
+                mx[r] = v;
+            } else {
+                mn[r] = std::min(mn[r], v);
+                mx[r] = std::max(mx[r], v);
+            }
+        }
+    }
+    if (!o.filling) {
+        for (int r = 0; r < 3; ++r) {
+            mn[r] -= inflate;
+            mx[r] += inflate;
+        }
+    }
+}
+
+// World::addObject (src/World.cpp:57-67): map::insert keeps an existing key's OBB, the
+// R-tree always receives the new (aabb, key) value.
+void HostWorld::add_object(const std::vector<HostObb> &objs, int id, bool is_gate, double inflate)
+{
+    for (size_t i = 0; i < objs.size(); ++i) {
+        TreeValue tv;
+        obb_aabb(objs[i], inflate, tv.mn, tv.mx);
+        tv.key = ObbKey(is_gate ? 1 : 0, id, static_cast<int>(i));
+        obbs_.insert({tv.key, objs[i]});
+        index_.push_back(tv);
+    }
+}
+
+// World::removeObject (src/World.cpp:69-78).
+int HostWorld::remove_object(int id, bool is_gate, int n_obbs, double inflate)
+{
+    for (int i = 0; i < n_obbs; ++i) {
+        ObbKey key(is_gate ? 1 : 0, id, i);
+        auto it = obbs_.find(key);
+        if (it == obbs_.end()) return EPP_ERR_NO_SUCH_OBB;
+        double mn[3], mx[3];
+        obb_aabb(it->second, inflate, mn, mx);
+        for (size_t t = 0; t < index_.size(); ++t) {
+            const TreeValue &tv = index_[t];
+            if (tv.key == key && std::equal(mn, mn + 3, tv.mn) && std::equal(mx, mx + 3, tv.mx)) {
+                index_.erase(index_.begin() + static_cast<long>(t));
+                break;
+            }
+        }
+        obbs_.erase(it);
+    }
+    return EPP_OK;
+}
+
+// World::addGatePrivateOperation (src/World.cpp:13-35).
+int HostWorld::add_gate(int gate_id, const double pose7[7], bool is_update)
+{
+    const double pos[3] = {pose7[0], pose7[1], 0.0};
+    const double rot[3] = {pose7[3], pose7[4], pose7[5]};
+    const int type = static_cast<int>(pose7[6]);
+    auto g = gate_geom_.find(type);
+    if (g == gate_geom_.end() || g->second.empty()) return EPP_ERR_NO_GEOMETRY;
+    std::vector<HostObb> objs;
+    int rc = build_object(g->second, pos, rot, objs);
+    if (rc != EPP_OK) return rc;
+    if (is_update) {
+        rc = remove_object(gate_id, true, static_cast<int>(objs.size()), inflate_gate_);
+        if (rc != EPP_OK) return rc;
+    }
+    add_object(objs, gate_id, true, inflate_gate_);
+    return EPP_OK;
+}
+
+// World::addObstacle (src/World.cpp:47-55).
+int HostWorld::add_obstacle(int obstacle_id, const double pose6[6])
+{
+    const double pos[3] = {pose6[0], pose6[1], pose6[2]};
+    const double rot[3] = {pose6[3], pose6[4], pose6[5]};
+    if (obstacle_geom_.empty()) return EPP_ERR_NO_GEOMETRY;
+    std::vector<HostObb> objs;
+    int rc = build_object(obstacle_geom_, pos, rot, objs);
+    if (rc != EPP_OK) return rc;
+    add_object(objs, obstacle_id, false, inflate_obstacle_);
+    return EPP_OK;
+}
+
+int HostWorld::get(int i, epp_obb *out) const
+{
+    if (i < 0 || i >= size() || !out) return EPP_ERR_INVALID_ARG;
+    const TreeValue &tv = index_[static_cast<size_t>(i)];
+    auto it = obbs_.find(tv.key);
+    if (it == obbs_.end()) return EPP_ERR_NO_SUCH_OBB;
+    const HostObb &o = it->second;
+    std::memcpy(out->center, o.center, sizeof o.center);
+    std::memcpy(out->half, o.half, sizeof o.half);
+    std::memcpy(out->rot, o.rot, sizeof o.rot);
+    std::memcpy(out->aabb_min, tv.mn, sizeof tv.mn);
+    std::memcpy(out->aabb_max, tv.mx, sizeof tv.mx);
+    out->is_gate = std::get<0>(tv.key);
+    out->object_id = std::get<1>(tv.key);
+    out->obb_index = std::get<2>(tv.key);
+    out->inflate = out->is_gate ? inflate_gate_ : inflate_obstacle_;
+    out->filling = o.filling ? 1 : 0;
+    return EPP_OK;
+}
+
+int HostWorld::flatten(std::vector<AabbRec> &aabbs, std::vector<ObbRec> &obbs) const
+{
+    aabbs.resize(index_.size());
+    obbs.resize(index_.size());
+    for (size_t i = 0; i < index_.size(); ++i) {
+        epp_obb o;
+        int rc = get(static_cast<int>(i), &o);
+        if (rc != EPP_OK) return rc;
+        std::memcpy(aabbs[i].mn, o.aabb_min, sizeof o.aabb_min);
+        std::memcpy(aabbs[i].mx, o.aabb_max, sizeof o.aabb_max);
+        ObbRec &r = obbs[i];
+        std::memcpy(r.center, o.center, sizeof o.center);
+        std::memcpy(r.rot, o.rot, sizeof o.rot);
+        std::memcpy(r.half, o.half, sizeof o.half);
+        r.inflate = o.inflate;
+        r.flags = (o.filling ? kFlagFilling : 0u) | (o.is_gate ? kFlagGate : 0u);
+        r.pad = 0;
+        r.cell_min = 0;
+    }
+    return EPP_OK;
+}
+
+// ---- broad phase -----------------------------------------------------------------------
+
+int host_bin(double x, double lo, double inv, int n)
+{
+    const double d = x - lo;
+    const double t = d * inv;
+    const double f = std::floor(t);
+    if (!(f > 0.0)) return 0; // negative, zero and NaN
+    if (f >= static_cast<double>(n - 1)) return n - 1;
+    return static_cast<int>(f);
+}
+
+namespace {
+
+void world_extent(const std::vector<AabbRec> &aabbs, double lo[3], double hi[3])
+{
+    for (int a = 0; a < 3; ++a) {
+        lo[a] = 0.0;
+        hi[a] = 1.0;
+    }
+    for (size_t k = 0; k < aabbs.size(); ++k)
+        for (int a = 0; a < 3; ++a) {
+            if (k == 0 || aabbs[k].mn[a] < lo[a]) lo[a] = aabbs[k].mn[a];
+            if (k == 0 || aabbs[k].mx[a] > hi[a]) hi[a] = aabbs[k].mx[a];
+        }
+}
+
+// n bins: bin 0 = (-inf, lo), bins 1..n-2 tile [lo, hi], bin n-1 = beyond hi.
+void make_axis(double lo, double hi, int n, double &out_lo, double &out_inv)
+{
+    double span = hi - lo;
+    if (!(span > 0.0) || !std::isfinite(span)) span = 1.0;
+    const int inner = std::max(1, n - 2);
+    const double h = span / inner;
+    out_lo = lo - h;
+    out_inv = 1.0 / h;
+}
+
+} // namespace
+
+void build_bits(const std::vector<AabbRec> &aabbs, int bins_per_axis, BitsTables &out)
+{
+    const int M = static_cast<int>(aabbs.size());
+    out.nb = std::max(3, bins_per_axis);
+    out.W = std::max(1, (M + 31) / 32);
+    double lo[3], hi[3];
+    world_extent(aabbs, lo, hi);
+    for (int a = 0; a < 3; ++a) {
+        make_axis(lo[a], hi[a], out.nb, out.bins.lo[a], out.bins.inv[a]);
+        out.bins.n[a] = out.nb;
+    }
+    const size_t words = static_cast<size_t>(3) * out.nb * out.W;
+    out.inside.assign(words, 0u);
+    out.min_le.assign(words, 0u);
+    out.max_ge.assign(words, 0u);
+    for (int k = 0; k < M; ++k)
+        for (int a = 0; a < 3; ++a) {
+            const int b0 = host_bin(aabbs[k].mn[a], out.bins.lo[a], out.bins.inv[a], out.nb);
+            const int b1 = host_bin(aabbs[k].mx[a], out.bins.lo[a], out.bins.inv[a], out.nb);
+            const uint32_t bit = 1u << (k & 31);
+            const size_t w = static_cast<size_t>(k >> 5);
+            for (int b = 0; b < out.nb; ++b) {
+                const size_t at = (static_cast<size_t>(a) * out.nb + b) * out.W + w;
+                if (b0 <= b && b <= b1) out.inside[at] |= bit;
+                if (b0 <= b) out.min_le[at] |= bit;
+                if (b1 >= b) out.max_ge[at] |= bit;
+            }
+        }
+}
+
+void build_grid(const std::vector<AabbRec> &aabbs, std::vector<ObbRec> &obbs, long max_cells,
+                GridTables &out)
+{
+    const size_t M = aabbs.size();
+    double lo[3], hi[3];
+    world_extent(aabbs, lo, hi);
+
+    // Cell edge ~ the mean stored-AABB extent (largest axis mean), so a box spans ~2 cells/axis.
+    double mean_ext[3] = {0, 0, 0};
+    for (size_t k = 0; k < M; ++k)
+        for (int a = 0; a < 3; ++a) mean_ext[a] += aabbs[k].mx[a] - aabbs[k].mn[a];
+    double edge = 0.0;
+    for (int a = 0; a < 3; ++a) edge = std::max(edge, M ? mean_ext[a] / static_cast<double>(M) : 1.0);
+    if (!(edge > 0.0) || !std::isfinite(edge)) edge = 1.0;
+
+    int n[3];
+    for (;;) {
+        double cells = 1.0;
+        for (int a = 0; a < 3; ++a) {
+            double span = hi[a] - lo[a];
+            if (!(span > 0.0) || !std::isfinite(span)) span = edge;
+            double inner = std::ceil(span / edge);
+            inner = std::min(std::max(inner, 1.0), 1048574.0);
+            n[a] = static_cast<int>(inner) + 2;
+            cells *= n[a];
+        }
+        if (cells <= static_cast<double>(max_cells)) break;
+        edge *= 1.26; // ~ halves the cell count per step
+    }
+    for (int a = 0; a < 3; ++a) {
+        make_axis(lo[a], hi[a], n[a], out.bins.lo[a], out.bins.inv[a]);
+        out.bins.n[a] = n[a];
+    }
+    const size_t ncell = static_cast<size_t>(n[0]) * n[1] * n[2];
+    out.cell_start.assign(ncell + 1, 0u);
+
+    std::vector<int> b0(3 * M), b1(3 * M);
+    for (size_t k = 0; k < M; ++k) {
+        for (int a = 0; a < 3; ++a) {
+            b0[3 * k + a] = host_bin(aabbs[k].mn[a], out.bins.lo[a], out.bins.inv[a], n[a]);
+            b1[3 * k + a] = host_bin(aabbs[k].mx[a], out.bins.lo[a], out.bins.inv[a], n[a]);
+        }
+        obbs[k].cell_min = static_cast<uint64_t>(b0[3 * k]) | (static_cast<uint64_t>(b0[3 * k + 1]) << 21) |
+                           (static_cast<uint64_t>(b0[3 * k + 2]) << 42);
+    }
+    auto cell_id = [&](int x, int y, int z) {
+        return (static_cast<size_t>(z) * n[1] + y) * n[0] + x;
+    };
+    for (size_t k = 0; k < M; ++k)
+        for (int z = b0[3 * k + 2]; z <= b1[3 * k + 2]; ++z)
+            for (int y = b0[3 * k + 1]; y <= b1[3 * k + 1]; ++y)
+                for (int x = b0[3 * k]; x <= b1[3 * k]; ++x) out.cell_start[cell_id(x, y, z) + 1]++;
+    for (size_t c = 0; c < ncell; ++c) out.cell_start[c + 1] += out.cell_start[c];
+    out.cell_items.assign(out.cell_start[ncell], 0u);
+    std::vector<uint32_t> cursor(out.cell_start.begin(), out.cell_start.end() - 1);
+    for (size_t k = 0; k < M; ++k)
+        for (int z = b0[3 * k + 2]; z <= b1[3 * k + 2]; ++z)
+            for (int y = b0[3 * k + 1]; y <= b1[3 * k + 1]; ++y)
+                for (int x = b0[3 * k]; x <= b1[3 * k]; ++x)
+                    out.cell_items[cursor[cell_id(x, y, z)]++] = static_cast<uint32_t>(k);
+}
+
+} // namespace epp

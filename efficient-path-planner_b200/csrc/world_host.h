@@ -1,0 +1,129 @@
+// world_host.h — host side of the World: geometry registry, OBB records, broad-phase tables.
+// Product code (no oracle dependency).  Mirrors the reference World's construction path:
+//   include/World.h:20-33, src/World.cpp:13-78, src/Object.cpp:11-85, src/OBB.cpp:93-124.
+#pragma once
+
+#include <cstdint>
+#include <map>
+#include <string>
+#include <tuple>
+#include <vector>
+
+#include "../../include/epp_c_api.h"
+
+namespace epp {
+
+// ---- device-visible layouts ------------------------------------------------------------
+
+// Stored AABB of one R-tree value (src/World.cpp:60-65): 6 doubles, 48 B.
+struct AabbRec {
+    double mn[3];
+    double mx[3];
+};
+
+// Narrow-phase record, 18 doubles = 144 B.
+struct ObbRec {
+    double center[3];
+    double rot[9];  // row-major R(r,c)
+    double half[3];
+    double inflate; // radius of the owning kind (gate / obstacle), src/World.cpp:89-90
+    uint32_t flags; // bit0 filling, bit1 gate
+    uint32_t pad;
+    uint64_t cell_min; // grid broad phase: 21-bit cell index per axis of aabb min (x | y<<21 | z<<42)
+};
+static_assert(sizeof(AabbRec) == 48, "AabbRec layout");
+static_assert(sizeof(ObbRec) == 144, "ObbRec layout");
+
+constexpr uint32_t kFlagFilling = 1u;
+constexpr uint32_t kFlagGate = 2u;
+
+// Monotone binning shared by host table construction and device queries.  Monotonicity in x
+// (rounded subtract, multiply by a positive constant, floor, clamp) is what makes the broad
+// phases conservative: aabb_min < p < aabb_max  =>  bin(aabb_min) <= bin(p) <= bin(aabb_max).
+struct AxisBins {
+    double lo[3];
+    double inv[3];
+    int n[3];
+};
+
+int host_bin(double x, double lo, double inv, int n);
+
+// Per-axis bin bitmasks (EPP_BP_BITS).  Word w of bin b of axis a at [(a * nb + b) * W + w].
+struct BitsTables {
+    int nb = 0; // bins per axis
+    int W = 0;  // 32-bit words per bin = ceil(M / 32)
+    AxisBins bins{};
+    std::vector<uint32_t> inside; // k set iff bin(min_k) <= b <= bin(max_k)
+    std::vector<uint32_t> min_le; // k set iff bin(min_k) <= b
+    std::vector<uint32_t> max_ge; // k set iff bin(max_k) >= b
+};
+
+// Uniform grid with CSR candidate lists (EPP_BP_GRID).
+struct GridTables {
+    AxisBins bins{};
+    std::vector<uint32_t> cell_start; // ncell + 1
+    std::vector<uint32_t> cell_items;
+};
+
+// ---- host world ------------------------------------------------------------------------
+
+struct HostObb {
+    double center[3];
+    double half[3];
+    double rot[9];
+    bool filling;
+};
+
+// Key "{gate|obstacle}_{id}_obb_{i}" of src/World.cpp:63 as a tuple.
+using ObbKey = std::tuple<int /*is_gate*/, int /*id*/, int /*obb index*/>;
+
+struct TreeValue { // pair<box, string>, include/Types.h:13-16
+    double mn[3];
+    double mx[3];
+    ObbKey key;
+};
+
+class HostWorld {
+public:
+    HostWorld(double inflate_gate, double inflate_obstacle)
+        : inflate_gate_(inflate_gate), inflate_obstacle_(inflate_obstacle) {}
+
+    int set_gate_geometry(int type_id, const epp_obb_desc *d, int n);
+    int set_obstacle_geometry(const epp_obb_desc *d, int n);
+    void reset();
+    int add_gate(int gate_id, const double pose7[7], bool is_update);
+    int add_obstacle(int obstacle_id, const double pose6[6]);
+
+    int size() const { return static_cast<int>(index_.size()); }
+    int get(int i, epp_obb *out) const;
+
+    // Flatten the R-tree values (each resolved through the key map, src/World.cpp:87) into
+    // device records.
+    int flatten(std::vector<AabbRec> &aabbs, std::vector<ObbRec> &obbs) const;
+
+    double inflate_gate() const { return inflate_gate_; }
+    double inflate_obstacle() const { return inflate_obstacle_; }
+
+private:
+    int build_object(const std::vector<epp_obb_desc> &g, const double pos[3], const double rot[3],
+                     std::vector<HostObb> &out) const;
+    void add_object(const std::vector<HostObb> &objs, int id, bool is_gate, double inflate);
+    int remove_object(int id, bool is_gate, int n_obbs, double inflate);
+
+    double inflate_gate_, inflate_obstacle_;
+    std::map<int, std::vector<epp_obb_desc>> gate_geom_;
+    std::vector<epp_obb_desc> obstacle_geom_;
+    std::map<ObbKey, HostObb> obbs_;  // std::map<std::string, OBB> obbs, include/World.h:112
+    std::vector<TreeValue> index_;    // rtree index, include/World.h:109
+};
+
+void obb_aabb(const HostObb &o, double inflate, double mn[3], double mx[3]);
+
+// Broad-phase construction over flattened records.
+void build_bits(const std::vector<AabbRec> &aabbs, int bins_per_axis, BitsTables &out);
+void build_grid(const std::vector<AabbRec> &aabbs, std::vector<ObbRec> &obbs, long max_cells,
+                GridTables &out);
+
+const char *status_message(int status);
+
+} // namespace epp

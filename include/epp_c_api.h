@@ -1,0 +1,197 @@
+/*
+ * epp_c_api.h — C ABI of libepp_b200.so, the B200-native (sm_100a) replacement for the
+ * validity-check hot path of Autonomous-Drone-Racing-Lab/Efficient-Path-Planner.
+ *
+ * Every entry point names the reference interface it replaces (paths relative to the
+ * reference repository root).  Plain pointers and sizes only; no C++/torch types cross
+ * this boundary.  All functions return an epp_status (0 = ok); the message of the last
+ * failure on the calling thread is available from epp_last_error().  There is no CPU
+ * fallback: every check runs on the GPU and fails with EPP_ERR_NO_DEVICE / EPP_ERR_CUDA
+ * when it cannot.
+ *
+ * Mask convention (all batched checks): bit (i & 31) of word (i >> 5) is 1 iff unit i is
+ * VALID (collision free); tail bits of the last word are 0.  A batch of n units needs
+ * (n + 31) / 32 uint32 words.
+ *
+ * Threading: check calls are re-entrant and may be issued concurrently from several host
+ * threads on one world (the reference runs two planner threads on one World,
+ * src/OnlineTrajGenerator.cpp:324-340).  World mutation (reset/add/update/commit) must be
+ * externally serialised against other mutations; checks in flight keep using the epoch
+ * they started with.
+ */
+#ifndef EPP_C_API_H
+#define EPP_C_API_H
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct epp_world epp_world;
+
+typedef enum {
+    EPP_OK = 0,
+    EPP_ERR_ROT_X = 1,       /* "Rotation around x axis is not supported"  src/Object.cpp:38-42 */
+    EPP_ERR_ROT_Y = 2,       /* "Rotation around y axis is not supported"  src/Object.cpp:43-47 */
+    EPP_ERR_CENTER_Z = 3,    /* "Center z position must be zero"           src/Object.cpp:16-20 */
+    EPP_ERR_NO_GEOMETRY = 4, /* unknown gate type / component              src/ConfigParserYAML.cpp:21-37 */
+    EPP_ERR_NO_SUCH_OBB = 5, /* std::out_of_range from obbs.at()           src/World.cpp:74,87 */
+    EPP_ERR_INVALID_ARG = 6,
+    EPP_ERR_NOT_COMMITTED = 7, /* check issued before epp_world_commit */
+    EPP_ERR_CUDA = 8,
+    EPP_ERR_NO_DEVICE = 9
+} epp_status;
+
+/* One box of a component description: config component_geometry.<comp>.<obb>
+ * (include/Types.h:22-28 OBBDescription; halfSize = size / 2, src/ConfigParserYAML.cpp:63). */
+typedef struct {
+    double position[3];
+    double size[3];
+    int filling; /* 1: type "filling", 0: type "collision" (include/OBB.h:54-57) */
+} epp_obb_desc;
+
+/* Host copy of one world record (include/OBB.h:47-57 + its R-tree value, src/World.cpp:57-67). */
+typedef struct {
+    double center[3];
+    double half[3];
+    double rot[9]; /* row-major */
+    double aabb_min[3];
+    double aabb_max[3];
+    double inflate;
+    int filling;
+    int is_gate;
+    int object_id;
+    int obb_index;
+} epp_obb;
+
+/* Broad-phase selection (DESIGN.md "Broad phase").  Results are identical for all modes. */
+typedef enum {
+    EPP_BP_AUTO = 0,
+    EPP_BP_BRUTE = 1, /* every OBB's stored AABB tested per unit */
+    EPP_BP_BITS = 2,  /* per-axis bin bitmasks, M <= 1024 */
+    EPP_BP_GRID = 3   /* uniform 3-D grid with per-cell candidate lists, any M */
+} epp_broadphase;
+
+const char *epp_last_error(void);
+const char *epp_version(void);
+int epp_device_count(int *count);
+
+/* ---- World lifecycle ---------------------------------------------------------------- */
+
+/* World::World(configParser): inflate radii per kind (include/World.h:20-24). */
+int epp_world_create(double inflate_gate, double inflate_obstacle, epp_world **out);
+int epp_world_destroy(epp_world *w);
+/* ConfigParser::getGateGeometryByTypeId / getObstacleGeometry (src/ConfigParserYAML.cpp:21-37). */
+int epp_world_set_gate_geometry(epp_world *w, int type_id, const epp_obb_desc *descs, int n);
+int epp_world_set_obstacle_geometry(epp_world *w, const epp_obb_desc *descs, int n);
+/* World::resetWorld (include/World.h:29-33). */
+int epp_world_reset(epp_world *w);
+/* World::addGate(gateId, [x,y,z,roll,pitch,yaw,type]) (src/World.cpp:13-40). */
+int epp_world_add_gate(epp_world *w, int gate_id, const double pose7[7]);
+/* World::updateGatePosition (src/World.cpp:42-45, removeObject :69-78). */
+int epp_world_update_gate(epp_world *w, int gate_id, const double pose7[7]);
+/* World::addObstacle(obstacleId, [x,y,z,roll,pitch,yaw]) (src/World.cpp:47-55). */
+int epp_world_add_obstacle(epp_world *w, int obstacle_id, const double pose6[6]);
+/* PathPlanner::parseGatesAndObstacles (src/PathPlanner.cpp:60-78): reset, gates (z forced
+ * to 0) then obstacles, row-major n x 7 / n x 6, followed by a commit. */
+int epp_world_parse_gates_and_obstacles(epp_world *w, const double *gates7, int n_gates,
+                                        const double *obstacles6, int n_obstacles);
+int epp_world_size(const epp_world *w, int *n_obbs);
+int epp_world_get_obb(const epp_world *w, int index, epp_obb *out);
+int epp_world_set_broadphase(epp_world *w, epp_broadphase mode);
+/* Publishes the current host world as a new immutable device epoch on the calling
+ * thread's current CUDA device (replaces the reference's in-place R-tree mutation,
+ * src/World.cpp:57-78).  Must follow any reset/add/update before the next check. */
+int epp_world_commit(epp_world *w);
+int epp_world_epoch(const epp_world *w, uint64_t *epoch);
+/* Broad phase actually in use for the committed epoch (an epp_broadphase, never AUTO). */
+int epp_world_active_broadphase(const epp_world *w, int *mode);
+
+/* ---- Checks on HOST buffers (H2D copy, kernel, D2H copy; synchronous) ----------------- */
+
+/* World::checkPointValidity(point, bool canPassGate) over n points (src/World.cpp:80-104);
+ * xyz is n x 3 row-major. */
+int epp_check_states(epp_world *w, const double *xyz, size_t n, int can_pass_gate, uint32_t *mask);
+/* World::checkPointValidity(point, double minDistance) over n points (src/World.cpp:106-128). */
+int epp_check_states_mindist(epp_world *w, const double *xyz, size_t n, double min_distance,
+                             uint32_t *mask);
+/* World::checkRayValid(start, end, canPassGate) over n segments (src/World.cpp:130-163). */
+int epp_check_segments(epp_world *w, const double *a, const double *b, size_t n, int can_pass_gate,
+                       uint32_t *mask);
+/* StateValidator::isValid for one state (src/StateValidator.cpp:7-13). */
+int epp_is_valid(epp_world *w, const double p[3], int can_pass_gate, int *valid);
+/* MotionValidator::checkMotion(s1, s2) for one edge (src/MotionValidator.cpp:8-17). */
+int epp_check_motion(epp_world *w, const double a[3], const double b[3], int can_pass_gate,
+                     int *valid);
+/* PathPlanner::checkTrajectoryValidity(trajectory, minDistance) (src/PathPlanner.cpp:267-280)
+ * for n_traj column-major matrices of `rows` rows and leading dimension `ld`, consecutive
+ * matrices `traj_stride` doubles apart; position = columns 0, 3, 6 (so cols >= 7).
+ * traj_valid: one bit per trajectory.  sample_mask (nullable): per trajectory
+ * (rows + 31) / 32 words, one bit per row (no early exit).  first_invalid (nullable): per
+ * trajectory the first invalid row or -1. */
+int epp_check_trajectories(epp_world *w, const double *col_major, size_t n_traj, size_t rows,
+                           size_t ld, size_t traj_stride, int cols, double min_distance,
+                           uint32_t *traj_valid, uint32_t *sample_mask, int64_t *first_invalid);
+/* Fused sweep: Trajectory::evaluateRange(0, maxTime, dt) (external/poly_traj/src/trajectory.cpp:
+ * 81-141) + Segment::evaluate (external/poly_traj/src/segment.cpp:51-58) + Polynomial::evaluate
+ * (external/poly_traj/include/mav_trajectory_generation/polynomial.h:136-150) feeding
+ * checkTrajectoryValidity, for n_traj trajectories of n_segments segments each.
+ * coeffs[((t * n_segments + k) * 3 + d) * n_coeffs + j], durations[t * n_segments + k],
+ * dt[t] (per-trajectory sampling interval).  max_samples bounds the samples per trajectory
+ * (multiple of 32); n_samples (nullable) returns the count the sampler produced. */
+int epp_check_poly_trajectories(epp_world *w, const double *coeffs, const double *durations,
+                                const double *dt, size_t n_traj, int n_segments, int n_coeffs,
+                                double min_distance, size_t max_samples, uint32_t *traj_valid,
+                                uint32_t *sample_mask, uint32_t *n_samples, int64_t *first_invalid);
+
+/* ---- Checks on DEVICE buffers (asynchronous on `stream`, a cudaStream_t; capture-safe) - */
+
+int epp_check_states_dev(epp_world *w, const double *d_xyz, size_t n, int can_pass_gate,
+                         uint32_t *d_mask, void *stream);
+int epp_check_states_mindist_dev(epp_world *w, const double *d_xyz, size_t n, double min_distance,
+                                 uint32_t *d_mask, void *stream);
+int epp_check_segments_dev(epp_world *w, const double *d_a, const double *d_b, size_t n,
+                           int can_pass_gate, uint32_t *d_mask, void *stream);
+/* d_first_invalid (nullable) is int64 per trajectory; d_traj_valid words must be zeroed by
+ * the callee (they are). */
+int epp_check_trajectories_dev(epp_world *w, const double *d_col_major, size_t n_traj, size_t rows,
+                               size_t ld, size_t traj_stride, int cols, double min_distance,
+                               uint32_t *d_traj_valid, uint32_t *d_sample_mask,
+                               int64_t *d_first_invalid, void *stream);
+int epp_check_poly_trajectories_dev(epp_world *w, const double *d_coeffs, const double *d_durations,
+                                    const double *d_dt, size_t n_traj, int n_segments, int n_coeffs,
+                                    double min_distance, size_t max_samples, uint32_t *d_traj_valid,
+                                    uint32_t *d_sample_mask, uint32_t *d_n_samples,
+                                    int64_t *d_first_invalid, void *stream);
+
+/* ---- Multi-GPU sharding helpers (host logic) --------------------------- */
+
+/* Contiguous range of units for `rank` of `world_size`, boundaries aligned to `align`
+ * units (a multiple of 32 so every rank owns whole mask words). */
+int epp_shard_range(size_t n, int rank, int world_size, size_t align, size_t *begin, size_t *end);
+/* popcount and 64-bit XOR-fold checksum of a device mask (words consecutive pairs). */
+int epp_mask_summary_dev(const uint32_t *d_mask, size_t n_words, uint64_t first_word, uint64_t *d_popcount_xor,
+                         void *stream);
+
+/* ---- Synthetic inputs generated on the device (counter based, bit-identical to the
+ *      oracle's host generators; DESIGN.md "Synthetic inputs") -------------------------- */
+
+int epp_gen_states_dev(uint64_t seed, uint64_t first, size_t n, const double lo[3],
+                       const double hi[3], double *d_xyz, void *stream);
+int epp_gen_segments_dev(uint64_t seed, uint64_t first, size_t n, const double lo[3],
+                         const double hi[3], double max_len, double *d_a, double *d_b, void *stream);
+
+/* ---- Introspection used by bench.py --------------------------------------------------- */
+
+/* Number of kernels this library has launched on the calling process so far. */
+uint64_t epp_kernel_launch_count(void);
+/* Tuning knobs (DESIGN.md "Tuning"); unknown keys return EPP_ERR_INVALID_ARG. */
+int epp_set_tuning(const char *key, int value);
+int epp_get_tuning(const char *key, int *value);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
