@@ -1,0 +1,503 @@
+#!/usr/bin/env python
+"""bench.py — validity checks per second of the B200 path (and of the CPU reference arm).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl b200|reference] [--workload ...]
+
+Default workload = BASELINE.json configs[1]: 1 M uniform random states isValid
+(World::checkPointValidity(point, canPassGate=false), src/World.cpp:80-104) against the
+config.json track world (4 gates + 4 obstacles = 24 OBBs).  A step = one pass of the hot path
+over one 1 M-state batch.  Batches rotate over a ring of distinct buffers whose total size
+exceeds the 126 MB L2, so every step streams its states from HBM.
+
+  value     device-resident inputs, K steps timed with CUDA events on the launching stream
+            (steps are replayed from a CUDA graph of one ring pass so the Python launch cost
+            does not hide the kernel), max over ranks.
+  e2e       the same batches through the host-buffer C-ABI call epp_check_states(): pinned host
+            states -> H2D -> kernel -> D2H mask -> host, every step, copies inside the region.
+  roofline  dominant kernel (k_states) algorithmic bytes / its mean launch duration vs the
+            measured HBM copy bandwidth in MEASURED_PEAKS.json.
+  cpu_baseline  the CPU oracle (restatement of the reference validators), all host cores, on a
+            bounded sample of the same workload.  Rank 0, N=1 only.
+
+--impl reference times the reference's CPU implementation of the same path on the host cores
+(oracle/_ref = the reference's own sources when built, else the oracle port).
+"""
+import argparse
+import json
+import os
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+for p in (ROOT, os.path.join(ROOT, "oracle")):
+    if p not in sys.path:
+        sys.path.insert(0, p)
+
+import numpy as np  # noqa: E402
+
+BATCH = 1 << 20           # "1M random states" (BASELINE.json configs[1])
+RING = 16                 # 16 x 24 MiB = 384 MiB of states > 126 MB L2
+BYTES_PER_STATE = 24.125  # 3 doubles read + 1 mask bit written
+BYTES_PER_SEGMENT = 48.125
+
+WORKLOADS = {
+    "states": "config2: 1M uniform states isValid (canPassGate=false) vs config.json track world, M=24 OBBs",
+    "segments": "config3: 1M segments checkMotion (exact slab test) vs synthetic 256-OBB world",
+}
+
+
+def parse_args():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=4000)
+    ap.add_argument("--warmup", type=int, default=64)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--workload", default="states", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true")
+    ap.add_argument("--no-graph", action="store_true")
+    return ap.parse_args()
+
+
+def measured_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as f:
+            return float(json.load(f)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+# ------------------------------------------------------------------------------ workloads
+
+def make_world_inputs(workload):
+    import epp_b200
+    from epp_b200 import worlds
+    config = epp_b200.load_config()
+    if workload == "states":
+        g, o, lo, hi = worlds.track_world(config)
+        seed = worlds.SEED_STATES
+    else:
+        g, o, lo, hi = worlds.world_256()
+        seed = worlds.SEED_SEGMENTS
+    return config, g, o, lo, hi, seed
+
+
+class ClockSampler(threading.Thread):
+    """Samples SM clock and throttle reasons through NVML while the timed regions run."""
+
+    def __init__(self, index, period=0.01):
+        super().__init__(daemon=True)
+        self.index, self.period = index, period
+        self.samples, self.reasons, self.active = [], set(), False
+        self._stop_evt = threading.Event()
+        self.sm_max = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.sm_max = pynvml.nvmlDeviceGetMaxClockInfo(self.h, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def run(self):
+        if self.nv is None:
+            return
+        nv = self.nv
+        names = {
+            nv.nvmlClocksThrottleReasonHwSlowdown: "hw_slowdown",
+            nv.nvmlClocksThrottleReasonHwThermalSlowdown: "hw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwThermalSlowdown: "sw_thermal_slowdown",
+            nv.nvmlClocksThrottleReasonSwPowerCap: "sw_power_cap",
+            nv.nvmlClocksThrottleReasonHwPowerBrakeSlowdown: "hw_power_brake",
+        }
+        while not self._stop_evt.is_set():
+            if self.active:
+                try:
+                    self.samples.append(nv.nvmlDeviceGetClockInfo(self.h, nv.NVML_CLOCK_SM))
+                    r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.h)
+                    for bit, name in names.items():
+                        if r & bit:
+                            self.reasons.add(name)
+                except Exception:
+                    pass
+            time.sleep(self.period)
+
+    def stop(self):
+        self._stop_evt.set()
+
+    def summary(self):
+        s = sorted(self.samples)
+        return {"sm_mhz": (s[len(s) // 2] if s else None), "sm_max_mhz": self.sm_max,
+                "reasons": sorted(self.reasons), "samples": len(s)}
+
+
+# ------------------------------------------------------------------------------ B200 arm
+
+def dist_env():
+    return (int(os.environ.get("RANK", 0)), int(os.environ.get("WORLD_SIZE", 1)),
+            int(os.environ.get("LOCAL_RANK", 0)))
+
+
+def timed_events(torch, fn):
+    """Run fn() between two CUDA events on the current stream; returns milliseconds."""
+    s, e = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    s.record()
+    fn()
+    e.record()
+    torch.cuda.synchronize()
+    return s.elapsed_time(e)
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    import epp_b200
+
+    rank, world, local_rank = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl b200 needs a CUDA device: there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    L = epp_b200.lib()
+
+    config, g, o, lo, hi, seed = make_world_inputs(args.workload)
+    gw = epp_b200.World(config)
+    gw.parse_gates_and_obstacles(g, o)
+    segs = args.workload == "segments"
+    unit_bytes = BYTES_PER_SEGMENT if segs else BYTES_PER_STATE
+    words = BATCH // 32
+
+    # Ring of distinct batches.  Global unit index of (slot s, rank r, unit i) = (s*world + r)*BATCH + i:
+    # every rank owns a contiguous index range of each global batch.
+    ring = []
+    for s in range(RING):
+        first = (s * world + rank) * BATCH
+        if segs:
+            ring.append(epp_b200.gen_segments_dev(seed, first, BATCH, lo, hi, 1.0, device=dev))
+        else:
+            ring.append((epp_b200.gen_states_dev(seed, first, BATCH, lo, hi, device=dev),))
+    # Gathered masks, double buffered; rank r's kernel writes row r in place (in-place allgather).
+    gathered = [torch.zeros((world, words), dtype=torch.int32, device=dev) for _ in range(2)]
+    torch.cuda.synchronize()
+
+    def step_dev(s):
+        buf = gathered[s & 1]
+        mine = buf[rank]
+        if segs:
+            gw.check_segments_dev(ring[s % RING][0], ring[s % RING][1], mask=mine)
+        else:
+            gw.check_states_dev(ring[s % RING][0], mask=mine)
+        if world > 1:
+            dist.all_gather_into_tensor(buf.view(-1), mine)
+
+    K, W = args.steps, args.warmup
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+
+    # ---- value: device-resident inputs ------------------------------------------------------
+    use_graph = (world == 1) and not args.no_graph and K >= RING
+    for s in range(max(W, 3)):
+        step_dev(s)
+    torch.cuda.synchronize()
+    launches0 = epp_b200.kernel_launch_count()
+    graph = None
+    if use_graph:
+        graph = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(graph):
+            for s in range(RING):
+                step_dev(s)
+        graph.replay()  # warm the instantiated graph
+        torch.cuda.synchronize()
+    captured = epp_b200.kernel_launch_count() - launches0  # launches recorded into the graph
+    launches1 = epp_b200.kernel_launch_count()
+
+    def timed_region():
+        done = 0
+        if graph is not None:
+            for _ in range(K // RING):
+                graph.replay()
+            done = (K // RING) * RING
+        for s in range(done, K):
+            step_dev(s)
+
+    if world > 1:
+        dist.barrier()
+    sampler.active = True
+    ms = timed_events(torch, timed_region)
+    sampler.active = False
+    direct = epp_b200.kernel_launch_count() - launches1
+    gpu_launches = direct + (captured // RING) * ((K // RING) * RING if graph is not None else 0)
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    value = world * BATCH * K / (ms_total * 1e-3)
+    pop, xor = epp_b200.mask_summary_dev(gathered[0][rank])
+
+    # ---- e2e: host buffers through the C ABI, copies inside the timed region ------------------
+    e2e_steps = max(8, min(K, 64))
+    h_ring = [tuple(t_.cpu().pin_memory() for t_ in slot) for slot in ring]
+    h_mask = torch.zeros(words, dtype=torch.int32).pin_memory()
+
+    def step_host(s):
+        slot = h_ring[s % RING]
+        if segs:
+            rc = L.epp_check_segments(gw.handle, slot[0].data_ptr(), slot[1].data_ptr(), BATCH, 0, h_mask.data_ptr())
+        else:
+            rc = L.epp_check_states(gw.handle, slot[0].data_ptr(), BATCH, 0, h_mask.data_ptr())
+        if rc:
+            raise RuntimeError(L.epp_last_error().decode())
+
+    for s in range(3):
+        step_host(s)
+    e2e_pop = int(np.unpackbits(h_mask.numpy().view(np.uint8)).sum())
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    sampler.active = True
+    t0 = time.perf_counter()
+    for s in range(e2e_steps):
+        step_host(s)   # synchronous: returns after the mask is back in host memory
+    torch.cuda.synchronize()
+    e2e_s = time.perf_counter() - t0
+    sampler.active = False
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * BATCH * e2e_steps / float(t.item())
+    in_bytes = BATCH * (48 if segs else 24)
+
+    extras = None
+    if rank == 0 and world == 1 and not args.no_extras:
+        try:
+            extras = run_extras(torch, epp_b200, dev)
+        except Exception as ex:  # extras never take the headline down
+            extras = {"error": repr(ex)}
+    sampler.stop()
+
+    peak, peak_src = measured_peaks()
+    kernel_ms = ms_total / K
+    achieved = unit_bytes * BATCH / (kernel_ms * 1e-3) / 1e9
+    line = {
+        "metric": "OBB state+motion validity checks/sec",
+        "value": value, "unit": "checks/s", "n_gpus": world, "steps": K, "warmup": max(W, 3),
+        "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOADS[args.workload], "units_per_step_per_gpu": BATCH,
+                   "world_obbs": gw.size(), "broadphase": epp_b200.BP_NAMES[gw.active_broadphase()],
+                   "l2": "inputs rotate over a ring of %d distinct batches (%d MiB) > 126 MB L2" %
+                         (RING, RING * in_bytes >> 20),
+                   "launch": "cuda graph of one ring pass" if graph is not None else "direct launches",
+                   "sharding": "contiguous index range per rank; in-place NCCL allgather of mask words"
+                               if world > 1 else "single GPU",
+                   "mask_popcount_slot0": pop, "mask_xor_slot0": "%016x" % xor},
+        "e2e": {"value": e2e_value, "unit": "checks/s", "h2d_bytes_per_step": in_bytes,
+                "d2h_bytes_per_step": words * 4, "steps": e2e_steps,
+                "api": "epp_check_segments" if segs else "epp_check_states",
+                "mask_popcount": e2e_pop},
+        "gpu_launches": gpu_launches,
+        "clocks": sampler.summary(),
+        "roofline": {"bound": "hbm", "kernel": "k_segments" if segs else "k_states",
+                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                     "traffic": load_traffic("k_segments" if segs else "k_states"),
+                     "peak_source": peak_src, "bytes_per_launch": unit_bytes * BATCH,
+                     "launch_ms": kernel_ms},
+    }
+    if extras is not None:
+        line["extras"] = extras
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_baseline(args.workload, budget_s=8.0)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def load_traffic(kernel):
+    """dram bytes per launch from the committed ncu capture (profiles/traffic.json), else null."""
+    path = os.path.join(ROOT, "profiles", "traffic.json")
+    try:
+        with open(path) as f:
+            return json.load(f).get(kernel)
+    except Exception:
+        return None
+
+
+def run_extras(torch, epp_b200, dev):
+    """Kernel-only throughput of the other BASELINE configs (device-resident inputs, CUDA events).
+    Informational: the headline stays the workload named in `config`."""
+    from epp_b200 import worlds
+    config = epp_b200.load_config()
+    out = {}
+
+    def rate(fn, units, reps=20):
+        for _ in range(3):
+            fn()
+        ms = timed_events(torch, lambda: [fn() for _ in range(reps)])
+        return units * reps / (ms * 1e-3)
+
+    # config 3: 1M segments vs the 256-OBB world (ring of 4 x 48 MiB > L2)
+    g, o, lo, hi = worlds.world_256()
+    w3 = epp_b200.World(config)
+    w3.parse_gates_and_obstacles(g, o)
+    segs = [epp_b200.gen_segments_dev(worlds.SEED_SEGMENTS, s * BATCH, BATCH, lo, hi, 1.0, device=dev) for s in range(4)]
+    m = torch.empty(BATCH // 32, dtype=torch.int32, device=dev)
+    out["config3_segments_256obb_checks_per_s"] = rate(
+        lambda: [w3.check_segments_dev(a, b, mask=m) for a, b in segs], 4 * BATCH, reps=5)
+    pts = [epp_b200.gen_states_dev(worlds.SEED_SEGMENTS, s * BATCH, BATCH, lo, hi, device=dev) for s in range(8)]
+    out["states_256obb_checks_per_s"] = rate(lambda: [w3.check_states_dev(p, mask=m) for p in pts], 8 * BATCH, reps=5)
+    del segs, pts
+
+    # config 4: 10k trajectories x ~1k samples, fused and pre-sampled forms
+    n_traj = 10000
+    coeffs, T, dt = worlds.rest_to_rest_trajectories(n_traj, 8, lo, hi, n_samples=1000, max_hop=3.0)
+    d_c, d_T, d_dt = (torch.from_numpy(x).to(dev) for x in (coeffs, T, dt))
+    valid, smask, ns, first = w3.check_poly_trajectories_dev(d_c, d_T, d_dt, 0.1, max_samples=1024)
+    torch.cuda.synchronize()
+    samples = int(ns.sum().item())
+    out["config4_samples"] = samples
+    out["config4_fused_samples_per_s"] = rate(
+        lambda: w3.check_poly_trajectories_dev(d_c, d_T, d_dt, 0.1, max_samples=1024), samples, reps=5)
+    rows = 1000
+    mats = torch.zeros((n_traj, 10, rows), dtype=torch.float64, device=dev)  # column-major rows x 10 each
+    xyz = epp_b200.gen_states_dev(worlds.SEED_TRAJ, 0, n_traj * rows, lo, hi, device=dev).view(n_traj, rows, 3)
+    for c in range(3):
+        mats[:, 3 * c, :] = xyz[:, :, c]
+    out["config4_presampled_samples_per_s"] = rate(
+        lambda: w3.check_trajectories_dev(mats, n_traj, rows, rows, 10 * rows, 10, 0.1), n_traj * rows, reps=5)
+    del mats, xyz
+
+    # config 5 (single-GPU share): 10k-OBB world, grid broad phase, inputs generated on device
+    g, o, lo, hi = worlds.world_10k()
+    w5 = epp_b200.World(config)
+    w5.parse_gates_and_obstacles(g, o)
+    n5 = 1 << 24
+    pts = epp_b200.gen_states_dev(worlds.SEED_CLUTTER, 0, n5, lo, hi, device=dev)
+    m5 = torch.empty(n5 // 32, dtype=torch.int32, device=dev)
+    out["config5_states_10k_obb_checks_per_s"] = rate(lambda: w5.check_states_dev(pts, mask=m5), n5, reps=5)
+    a, b = epp_b200.gen_segments_dev(worlds.SEED_CLUTTER, 0, n5 // 4, lo, hi, 1.0, device=dev)
+    out["config5_segments_10k_obb_checks_per_s"] = rate(
+        lambda: w5.check_segments_dev(a, b, mask=m5), n5 // 4, reps=5)
+    out["config5_broadphase"] = epp_b200.BP_NAMES[w5.active_broadphase()]
+
+    # single-state latency through the OMPL-shaped entry point (epp_is_valid)
+    t0 = time.perf_counter()
+    for i in range(200):
+        w3.checkPointValidity([0.1 * i, 0.0, 1.0], False)
+    out["single_is_valid_latency_us"] = (time.perf_counter() - t0) / 200 * 1e6
+    return out
+
+
+# ------------------------------------------------------------------------------ CPU arms
+
+def cpu_world(workload):
+    """(kind, world object with check_states/check_segments(threads=...)) for the CPU arms:
+    oracle/_ref (the reference's own sources) when it was built, else the oracle port."""
+    import oracle_py
+    config, g, o, lo, hi, seed = make_world_inputs(workload)
+    kind = "port"
+    w = None
+    try:
+        import ref_py
+        if ref_py.available():
+            w = ref_py.RefWorld(config)
+            kind = "reference"
+    except ImportError:
+        pass
+    if w is None:
+        w = oracle_py.OracleWorld(config)
+    w.parse_gates_and_obstacles(g, o)
+    return kind, w, (lo, hi, seed)
+
+
+def cpu_inputs(workload, n, lo, hi, seed, first=0):
+    import oracle_py
+    if workload == "segments":
+        return oracle_py.gen_segments(seed, first, n, lo, hi, 1.0)
+    return (oracle_py.gen_states(seed, first, n, lo, hi),)
+
+
+def cpu_step(w, workload, inputs, threads):
+    if workload == "segments":
+        return w.check_segments(inputs[0], inputs[1], False, threads=threads)
+    return w.check_states(inputs[0], False, threads=threads)
+
+
+def cpu_baseline(workload, budget_s=8.0):
+    threads = os.cpu_count() or 1
+    kind, w, (lo, hi, seed) = cpu_world(workload)
+    inputs = cpu_inputs(workload, BATCH, lo, hi, seed)
+    cpu_step(w, workload, inputs, threads)  # warm-up
+    reps, t0 = 0, time.perf_counter()
+    while True:
+        cpu_step(w, workload, inputs, threads)
+        reps += 1
+        el = time.perf_counter() - t0
+        if el > budget_s or reps >= 200:
+            break
+    t1 = time.perf_counter()
+    cpu_step(w, workload, tuple(x[: BATCH // 8] for x in inputs), 1)
+    single = (BATCH // 8) / (time.perf_counter() - t1)
+    return {"value": BATCH * reps / el, "unit": "checks/s", "cores": threads, "kind": kind,
+            "sample": "%d passes over the step's own 1M-unit batch (%.1f s), %d threads over contiguous ranges"
+                      % (reps, el, threads),
+            "single_thread_value": single}
+
+
+def run_reference(args):
+    rank, world, _ = dist_env()
+    if rank != 0:
+        return
+    K, W = args.steps, max(args.warmup, 1)
+    threads = os.cpu_count() or 1
+    kind, w, (lo, hi, seed) = cpu_world(args.workload)
+    full = cpu_inputs(args.workload, BATCH, lo, hi, seed)
+    t0 = time.perf_counter()
+    cpu_step(w, args.workload, full, threads)
+    est = time.perf_counter() - t0
+    # Bound the run to ~100 s: a step is the first `n` units of the batch.
+    n = BATCH
+    while n > (1 << 15) and est * (n / BATCH) * (K + W) > 100.0:
+        n //= 2
+    if est * (n / BATCH) * (K + W) > 100.0:
+        K = max(1, int(100.0 / (est * n / BATCH)) - W)
+    inputs = tuple(x[:n] for x in full)
+    for _ in range(W):
+        cpu_step(w, args.workload, inputs, threads)
+    t0 = time.perf_counter()
+    for _ in range(K):
+        cpu_step(w, args.workload, inputs, threads)
+    el = time.perf_counter() - t0
+    value = n * K / el
+    segs = args.workload == "segments"
+    line = {
+        "impl": "reference", "metric": "OBB state+motion validity checks/sec", "value": value,
+        "unit": "checks/s", "n_gpus": args.gpus, "steps": K, "warmup": W, "ms_per_step": el / K * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
+        "data": "synthetic",
+        "config": {"workload": WORKLOADS[args.workload], "units_per_step": n,
+                   "note": "host CPU only; runs on rank 0 regardless of --gpus"},
+        "cpu_baseline": {"value": value, "unit": "checks/s", "cores": threads, "kind": kind,
+                         "sample": "first %d units of the 1M-unit batch per step, %d steps" % (n, K)},
+        "e2e": {"value": value, "unit": "checks/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    args = parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()

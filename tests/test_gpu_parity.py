@@ -1,0 +1,324 @@
+"""GPU parity tests: the CUDA path, called through the C ABI, against the CPU oracle on the same
+inputs.  Bit-exact masks are required everywhere (integer/bit outputs of FP64 predicates with FMA
+contraction disabled); the north star's 1e-9 m allowance is not used: the expected mismatch count
+is zero and the tests assert zero."""
+import os
+
+import numpy as np
+import pytest
+
+import epp_b200
+from epp_b200 import worlds
+from helpers import adversarial_points, adversarial_segments, build_pair, filling_config
+
+pytestmark = pytest.mark.gpu
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+BPS = [epp_b200.BP_BRUTE, epp_b200.BP_BITS, epp_b200.BP_GRID]
+BP_IDS = ["brute", "bits", "grid"]
+
+
+def mismatches(a, b):
+    return int(np.unpackbits((np.asarray(a, np.uint32) ^ np.asarray(b, np.uint32)).view(np.uint8)).sum())
+
+
+@pytest.fixture(scope="module")
+def track(oracle, config):
+    g, o, lo, hi = worlds.track_world(config)
+    return g, o, lo, hi
+
+
+@pytest.mark.parametrize("bp", BPS, ids=BP_IDS)
+def test_kat_through_c_abi(config, bp):
+    import json
+    kat = json.load(open(os.path.join(HERE, "golden", "kat_small_portal.json")))
+    w = epp_b200.World(config, broadphase=bp)
+    w.addGate(0, kat["gate"])
+    for p, want in kat["points"]:
+        assert w.checkPointValidity(p, False) is want, p
+    for a, b, want in kat["segments"]:
+        assert w.checkRayValid(a, b, False) is want, (a, b)
+    w.resetWorld()
+    w.addGate(0, kat["quirk"]["gate"])
+    assert w.checkPointValidity(kat["quirk"]["point"], False) is kat["quirk"]["valid"]
+    assert w.active_broadphase() == bp
+
+
+@pytest.mark.parametrize("bp", BPS, ids=BP_IDS)
+def test_config2_states_track(oracle, config, track, bp):
+    """BASELINE config 2 at a size the oracle finishes in seconds: uniform states + adversarial."""
+    g, o, lo, hi = track
+    ow, gw = build_pair(oracle, epp_b200, config, g, o, bp)
+    n = 1 << 18
+    xyz = worlds.gen_states(worlds.SEED_STATES, 0, n, lo, hi)
+    adv = adversarial_points(ow.obbs(), np.random.default_rng(2))
+    xyz = np.concatenate([xyz, adv])
+    for cpg in (False, True):
+        assert mismatches(gw.check_states(xyz, cpg), ow.check_states(xyz, cpg, threads=8)) == 0
+    for md in (0.05, 0.1, 0.2, 0.35):
+        assert mismatches(gw.check_states_mindist(xyz, md), ow.check_states_mindist(xyz, md, threads=8)) == 0
+
+
+@pytest.mark.parametrize("bp", BPS, ids=BP_IDS)
+def test_filling_boxes(oracle, config, track, bp):
+    g, o, lo, hi = track
+    cfg = filling_config(config)
+    ow, gw = build_pair(oracle, epp_b200, cfg, g, o, bp)
+    assert ow.size() == 28
+    xyz = np.concatenate([worlds.gen_states(11, 0, 50000, lo, hi),
+                          adversarial_points(ow.obbs(), np.random.default_rng(3))])
+    for cpg in (False, True):
+        assert mismatches(gw.check_states(xyz, cpg), ow.check_states(xyz, cpg, threads=8)) == 0
+    assert mismatches(gw.check_states_mindist(xyz, 0.1), ow.check_states_mindist(xyz, 0.1, threads=8)) == 0
+    a, b = worlds.gen_segments(12, 0, 50000, lo, hi, 1.0)
+    aa, ab = adversarial_segments(ow.obbs(), np.random.default_rng(4), lo, hi)
+    a, b = np.concatenate([a, aa]), np.concatenate([b, ab])
+    for cpg in (False, True):
+        assert mismatches(gw.check_segments(a, b, cpg), ow.check_segments(a, b, cpg, threads=8)) == 0
+
+
+@pytest.mark.parametrize("bp", BPS, ids=BP_IDS)
+def test_config3_segments_256(oracle, config, bp):
+    g, o, lo, hi = worlds.world_256()
+    ow, gw = build_pair(oracle, epp_b200, config, g, o, bp)
+    assert gw.size() == 256
+    n = 1 << 17
+    a, b = worlds.gen_segments(worlds.SEED_SEGMENTS, 0, n, lo, hi, 1.0)
+    aa, ab = adversarial_segments(ow.obbs(), np.random.default_rng(5), lo, hi, per_obb=8)
+    a, b = np.concatenate([a, aa]), np.concatenate([b, ab])
+    got, want = gw.check_segments(a, b, False), ow.check_segments(a, b, False, threads=8)
+    assert mismatches(got, want) == 0
+    frac = 1.0 - np.unpackbits(want.view(np.uint8)).sum() / a.shape[0]
+    assert frac > 0.001
+    # long segments spanning many bins / cells
+    la, _ = worlds.gen_segments(99, 0, 4096, lo, hi, 1.0)
+    lb = worlds.gen_states(98, 0, 4096, lo, hi)
+    assert mismatches(gw.check_segments(la, lb, True), ow.check_segments(la, lb, True, threads=8)) == 0
+    xyz = np.concatenate([worlds.gen_states(97, 0, 1 << 16, lo, hi),
+                          adversarial_points(ow.obbs(), np.random.default_rng(6), per_face=2)])
+    assert mismatches(gw.check_states(xyz, False), ow.check_states(xyz, False, threads=8)) == 0
+
+
+@pytest.mark.parametrize("n", [0, 1, 31, 32, 33, 255, 256, 257, 1000, 4097])
+def test_ragged_sizes(oracle, config, track, n):
+    g, o, lo, hi = track
+    ow, gw = build_pair(oracle, epp_b200, config, g, o)
+    xyz = worlds.gen_states(5, 0, n, lo, hi)
+    got = gw.check_states(xyz)
+    assert got.shape[0] == (n + 31) // 32
+    assert np.array_equal(got, ow.check_states(xyz))
+    a, b = worlds.gen_segments(6, 0, n, lo, hi, 1.0)
+    assert np.array_equal(gw.check_segments(a, b), ow.check_segments(a, b))
+    if n % 32:
+        assert got[-1] >> (n % 32) == 0        # tail bits are zero
+
+
+def test_outside_bounds_and_empty_world(oracle, config, track):
+    g, o, lo, hi = track
+    ow, gw = build_pair(oracle, epp_b200, config, g, o)
+    far = worlds.gen_states(8, 0, 10000, [-50, -50, -50], [50, 50, 50])
+    assert np.array_equal(gw.check_states(far), ow.check_states(far))
+    fa, fb = worlds.gen_segments(9, 0, 10000, [-50, -50, -50], [50, 50, 50], 80.0)
+    assert np.array_equal(gw.check_segments(fa, fb), ow.check_segments(fa, fb))
+    for bp in BPS:
+        e = epp_b200.World(config, broadphase=bp)
+        assert e.size() == 0
+        m = e.check_states(far[:100])
+        assert np.unpackbits(m.view(np.uint8)).sum() == 100       # everything valid in an empty world
+        assert np.unpackbits(e.check_segments(fa[:100], fb[:100]).view(np.uint8)).sum() == 100
+
+
+def test_golden_fixture(config):
+    """Committed oracle outputs (tests/golden/make_golden.py): guards the GPU path and the oracle
+    against drifting together."""
+    z = np.load(os.path.join(HERE, "golden", "track_golden.npz"))
+    g, o, lo, hi = worlds.track_world(config)
+    w = epp_b200.World(config)
+    w.parse_gates_and_obstacles(g, o)
+    assert np.array_equal(w.check_states(z["states"], False), z["states_mask"])
+    assert np.array_equal(w.check_states(z["states"], True), z["states_mask_cpg"])
+    assert np.array_equal(w.check_states_mindist(z["states"], 0.1), z["states_mask_md"])
+    assert np.array_equal(w.check_segments(z["seg_a"], z["seg_b"], False), z["seg_mask"])
+
+
+def test_world_update_epochs(oracle, config, track):
+    g, o, lo, hi = track
+    ow, gw = build_pair(oracle, epp_b200, config, g, o)
+    xyz = worlds.gen_states(21, 0, 40000, lo, hi)
+    assert np.array_equal(gw.check_states(xyz), ow.check_states(xyz))
+    e0 = gw.epoch()
+    new = [0.1, 0.2, 0, 0, 0, 1.0, 1]
+    ow.update_gate(2, new)
+    gw.updateGatePosition(2, new)
+    assert np.array_equal(gw.check_states(xyz), ow.check_states(xyz))
+    assert gw.epoch() == e0 + 1
+    g2 = g.copy()
+    g2[1, :2] += 0.3
+    ow.parse_gates_and_obstacles(g2, o)
+    gw.parse_gates_and_obstacles(g2, o)
+    assert np.array_equal(gw.check_states(xyz), ow.check_states(xyz))
+
+
+@pytest.mark.parametrize("bp", BPS, ids=BP_IDS)
+def test_presampled_trajectories(oracle, config, bp):
+    g, o, lo, hi = worlds.world_256()
+    ow, gw = build_pair(oracle, epp_b200, config, g, o, bp)
+    n_traj, rows = 37, 333
+    trajs = np.zeros((n_traj, rows, 10))
+    for t in range(n_traj):
+        xyz = worlds.gen_states(100 + t, 0, rows, lo, hi)
+        if t % 3 == 0:          # keep some trajectories collision free: fly high
+            xyz[:, 2] = 3.5
+        trajs[t] = worlds.traj_matrix_from_positions(xyz, np.arange(rows) * 0.1)
+    valid, smask, first = gw.check_trajectories(trajs, 0.1)
+    n_valid = 0
+    for t in range(n_traj):
+        ok, m, f = ow.check_trajectory(trajs[t], 0.1)
+        assert bool(valid[t >> 5] >> (t & 31) & 1) is ok
+        assert np.array_equal(smask[t], m)
+        assert first[t] == f
+        n_valid += ok
+    assert 0 < n_valid < n_traj
+    assert gw.checkTrajectoryValidity(trajs[0], 0.1) is ow.check_trajectory(trajs[0], 0.1)[0]
+    # N x 11 layout of the time-optimal back-end (position columns unchanged)
+    t11 = np.concatenate([trajs[:2], np.zeros((2, rows, 1))], axis=2)
+    v11, _, _ = gw.check_trajectories(t11, 0.1)
+    assert (v11[0] & 3) == (valid[0] & 3)
+
+
+@pytest.mark.parametrize("bp", BPS, ids=BP_IDS)
+def test_fused_polynomial_sweep(oracle, config, bp):
+    """Config 4 (fused form) at reduced size: coefficients -> sampler -> Horner -> world check."""
+    g, o, lo, hi = worlds.world_256()
+    ow, gw = build_pair(oracle, epp_b200, config, g, o, bp)
+    n_traj = 150
+    coeffs, T, dt = worlds.rest_to_rest_trajectories(n_traj, 8, lo, hi, n_samples=1000, max_hop=3.0)
+    valid, smask, ns, first = gw.check_poly_trajectories(coeffs, T, dt, 0.1, max_samples=1024)
+    n_valid = 0
+    for t in range(n_traj):
+        ok, m, n, f = ow.check_poly_traj(coeffs[t], T[t], dt[t], 0.1, max_samples=1024)
+        assert ns[t] == n, t
+        assert 990 <= n <= 1010
+        assert np.array_equal(smask[t], m), t
+        assert first[t] == f
+        assert bool(valid[t >> 5] >> (t & 31) & 1) is ok
+        n_valid += ok
+    assert 0 < n_valid < n_traj
+    # fused == pre-sampled on the oracle's own samples
+    xyz, times, n = oracle.traj_evaluate_range(coeffs[0], T[0], 0.0, oracle.traj_max_time(T[0]), dt[0])
+    mat = worlds.traj_matrix_from_positions(xyz, times)
+    v2, s2, _ = gw.check_trajectories(mat[None], 0.1)
+    assert np.array_equal(s2[0], smask[0][: s2.shape[1]])
+
+
+def test_polynomial_sweep_ragged(oracle, config, track):
+    """Different segment counts / sampling steps, dt not dividing the duration, tiny batches."""
+    g, o, lo, hi = track
+    ow, gw = build_pair(oracle, epp_b200, config, g, o)
+    for n_traj, K, ns in ((1, 1, 40), (33, 3, 100), (65, 5, 257)):
+        coeffs, T, dt = worlds.rest_to_rest_trajectories(n_traj, K, lo, hi, seed=77 + K, n_samples=ns)
+        dt = dt * (1.0 + 0.37 * np.arange(n_traj) / max(n_traj, 1))
+        valid, smask, cnt, first = gw.check_poly_trajectories(coeffs, T, dt, 0.15, max_samples=512)
+        for t in range(n_traj):
+            ok, m, n, f = ow.check_poly_traj(coeffs[t], T[t], dt[t], 0.15, max_samples=512)
+            assert cnt[t] == n and np.array_equal(smask[t], m) and first[t] == f
+            assert bool(valid[t >> 5] >> (t & 31) & 1) is ok
+
+
+def test_device_buffers_and_generators(oracle, config, track):
+    """_dev entry points on torch buffers + on-device generators bit-identical to the host twins."""
+    import torch
+    g, o, lo, hi = track
+    ow, gw = build_pair(oracle, epp_b200, config, g, o)
+    n = 100003
+    d_xyz = epp_b200.gen_states_dev(worlds.SEED_STATES, 12345, n, lo, hi)
+    h_xyz = oracle.gen_states(worlds.SEED_STATES, 12345, n, lo, hi)
+    assert np.array_equal(d_xyz.cpu().numpy(), h_xyz)
+    mask = gw.check_states_dev(d_xyz)
+    torch.cuda.synchronize()
+    want = ow.check_states(h_xyz, threads=8)
+    assert np.array_equal(mask.cpu().numpy().view(np.uint32), want)
+    d_a, d_b = epp_b200.gen_segments_dev(worlds.SEED_SEGMENTS, 777, n, lo, hi, 1.0)
+    h_a, h_b = oracle.gen_segments(worlds.SEED_SEGMENTS, 777, n, lo, hi, 1.0)
+    assert np.array_equal(d_a.cpu().numpy(), h_a) and np.array_equal(d_b.cpu().numpy(), h_b)
+    smask = gw.check_segments_dev(d_a, d_b)
+    wantseg = ow.check_segments(h_a, h_b, threads=8)
+    assert np.array_equal(smask.cpu().numpy().view(np.uint32), wantseg)
+    md = gw.check_states_dev(d_xyz, min_distance=0.1)
+    assert np.array_equal(md.cpu().numpy().view(np.uint32), ow.check_states_mindist(h_xyz, 0.1, threads=8))
+    # mask summary: device reduction == host restatement, shards combine
+    assert epp_b200.mask_summary_dev(mask) == epp_b200.mask_summary_host(want)
+    half = (mask.numel() // 2)
+    p0, x0 = epp_b200.mask_summary_dev(mask[:half], 0)
+    p1, x1 = epp_b200.mask_summary_dev(mask[half:], half)
+    assert (p0 + p1, x0 ^ x1) == epp_b200.mask_summary_host(want)
+    assert epp_b200.kernel_launch_count() > 0
+
+
+def test_pinned_host_buffers(oracle, config, track):
+    import torch
+    g, o, lo, hi = track
+    ow, gw = build_pair(oracle, epp_b200, config, g, o)
+    n = 1 << 16
+    h = torch.from_numpy(worlds.gen_states(31, 0, n, lo, hi)).pin_memory()
+    m = torch.zeros((n + 31) // 32, dtype=torch.int32).pin_memory()
+    epp_b200._chk(epp_b200.lib().epp_check_states(gw.handle, h.data_ptr(), n, 0, m.data_ptr()))
+    assert np.array_equal(m.numpy().view(np.uint32), ow.check_states(h.numpy()))
+
+
+def test_config5_cluttered_subsample(oracle, config):
+    """Config 5 at a size the oracle finishes in seconds: 10k-OBB world, grid broad phase, inputs
+    generated on device, parity on the same indices + checksum equality across shard counts."""
+    import torch
+    g, o, lo, hi = worlds.world_10k()
+    ow, gw = build_pair(oracle, epp_b200, config, g, o)
+    assert gw.size() == 10000 and gw.active_broadphase() == epp_b200.BP_GRID
+    n = 1 << 20
+    first = 123456789
+    d_xyz = epp_b200.gen_states_dev(worlds.SEED_CLUTTER, first, n, lo, hi)
+    mask = gw.check_states_dev(d_xyz)
+    want = ow.check_states(oracle.gen_states(worlds.SEED_CLUTTER, first, n, lo, hi), threads=8)
+    assert mismatches(mask.cpu().numpy().view(np.uint32), want) == 0
+    whole = epp_b200.mask_summary_dev(mask)
+    for shards in (2, 4, 8):
+        pop, x = 0, 0
+        for r in range(shards):
+            b, e = epp_b200.shard_range(n, r, shards, 1024)
+            part = gw.check_states_dev(d_xyz[b:e])
+            p, c = epp_b200.mask_summary_dev(part, b // 32)
+            pop, x = pop + p, x ^ c
+        assert (pop, x) == whole
+    ne = 1 << 17
+    d_a, d_b = epp_b200.gen_segments_dev(worlds.SEED_CLUTTER, first, ne, lo, hi, 1.0)
+    got = gw.check_segments_dev(d_a, d_b).cpu().numpy().view(np.uint32)
+    h_a, h_b = oracle.gen_segments(worlds.SEED_CLUTTER, first, ne, lo, hi, 1.0)
+    assert mismatches(got, ow.check_segments(h_a, h_b, threads=8)) == 0
+    # grid vs bits vs brute on the same world (bits allowed up to 4096 OBBs only -> brute here)
+    gb = epp_b200.World(config, broadphase=epp_b200.BP_BRUTE)
+    gb.parse_gates_and_obstacles(g, o)
+    gb.set_broadphase(epp_b200.BP_BRUTE)
+    sub = d_xyz[: 1 << 16]
+    assert torch.equal(gb.check_states_dev(sub), gw.check_states_dev(sub))
+
+
+def test_concurrent_host_threads(oracle, config, track):
+    """Two planner threads on one World (src/OnlineTrajGenerator.cpp:324-340)."""
+    import threading
+    g, o, lo, hi = track
+    ow, gw = build_pair(oracle, epp_b200, config, g, o)
+    gw.commit()
+    out = {}
+
+    def work(tid):
+        xyz = worlds.gen_states(1000 + tid, 0, 30000, lo, hi)
+        res = [gw.check_states(xyz) for _ in range(5)]
+        singles = [gw.checkPointValidity(p, False) for p in xyz[:50]]
+        out[tid] = (xyz, res, singles)
+
+    ts = [threading.Thread(target=work, args=(i,)) for i in range(4)]
+    [t.start() for t in ts]
+    [t.join() for t in ts]
+    for tid, (xyz, res, singles) in out.items():
+        want = ow.check_states(xyz)
+        assert all(np.array_equal(r, want) for r in res)
+        assert singles == [bool(want[i >> 5] >> (i & 31) & 1) for i in range(50)]
