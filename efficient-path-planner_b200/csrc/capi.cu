@@ -47,6 +47,10 @@ struct Tuning {
     std::atomic<int> states_blocks_per_sm{8};
     std::atomic<int> segments_blocks_per_sm{4};
     std::atomic<int> states_variant{0};
+    std::atomic<int> states_stages{2};
+    std::atomic<int> states_stream_blocks_per_sm{6};
+    std::atomic<int> states_per_thread{0};
+    std::atomic<int> states_queue_pairs{0};
     std::atomic<int> bits_bins{0};          // 0: by world size
     std::atomic<int> grid_max_cells{1 << 22};
     std::atomic<int> bits_max_obbs{1024};
@@ -211,6 +215,10 @@ LaunchCfg launch_cfg(const DeviceEpoch &ep)
     c.states_blocks_per_sm = g_tuning.states_blocks_per_sm.load();
     c.segments_blocks_per_sm = g_tuning.segments_blocks_per_sm.load();
     c.states_variant = g_tuning.states_variant.load();
+    c.states_stages = g_tuning.states_stages.load();
+    c.states_stream_blocks_per_sm = g_tuning.states_stream_blocks_per_sm.load();
+    c.states_per_thread = g_tuning.states_per_thread.load();
+    c.states_queue_pairs = g_tuning.states_queue_pairs.load();
     return c;
 }
 
@@ -345,6 +353,10 @@ extern "C" int epp_set_tuning(const char *key, int value)
     if (k == "states_blocks_per_sm") g_tuning.states_blocks_per_sm = value;
     else if (k == "segments_blocks_per_sm") g_tuning.segments_blocks_per_sm = value;
     else if (k == "states_variant") g_tuning.states_variant = value;
+    else if (k == "states_stages") g_tuning.states_stages = value;
+    else if (k == "states_stream_blocks_per_sm") g_tuning.states_stream_blocks_per_sm = value;
+    else if (k == "states_per_thread") g_tuning.states_per_thread = value;
+    else if (k == "states_queue_pairs") g_tuning.states_queue_pairs = value;
     else if (k == "bits_bins") g_tuning.bits_bins = value;
     else if (k == "grid_max_cells") g_tuning.grid_max_cells = value;
     else if (k == "bits_max_obbs") g_tuning.bits_max_obbs = value;
@@ -359,6 +371,10 @@ extern "C" int epp_get_tuning(const char *key, int *value)
     if (k == "states_blocks_per_sm") *value = g_tuning.states_blocks_per_sm;
     else if (k == "segments_blocks_per_sm") *value = g_tuning.segments_blocks_per_sm;
     else if (k == "states_variant") *value = g_tuning.states_variant;
+    else if (k == "states_stages") *value = g_tuning.states_stages;
+    else if (k == "states_stream_blocks_per_sm") *value = g_tuning.states_stream_blocks_per_sm;
+    else if (k == "states_per_thread") *value = g_tuning.states_per_thread;
+    else if (k == "states_queue_pairs") *value = g_tuning.states_queue_pairs;
     else if (k == "bits_bins") *value = g_tuning.bits_bins;
     else if (k == "grid_max_cells") *value = g_tuning.grid_max_cells;
     else if (k == "bits_max_obbs") *value = g_tuning.bits_max_obbs;

@@ -51,6 +51,16 @@ struct PointWorld<EPP_BP_BRUTE> {
             aabb = reinterpret_cast<const AabbRec *>(g_smem);
         }
     }
+    // Streaming form: the table arrives by bulk copy; table() names its source, bind() points at the copy.
+    __device__ static uint32_t table(const WorldView &wv, bool aabb_in_smem, const void *&src)
+    {
+        src = wv.aabb;
+        return aabb_in_smem ? (uint32_t)(wv.M * sizeof(AabbRec)) : 0u;
+    }
+    __device__ void bind(const WorldView &wv, bool aabb_in_smem)
+    {
+        aabb = aabb_in_smem ? reinterpret_cast<const AabbRec *>(g_smem) : wv.aabb;
+    }
     __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &p, int mode, bool cpg, double md) const
     {
         for (int k = 0; k < wv.M; ++k) {
@@ -72,6 +82,12 @@ struct PointWorld<EPP_BP_BITS> {
         __syncthreads();
         inside = dst;
     }
+    __device__ static uint32_t table(const WorldView &wv, bool, const void *&src)
+    {
+        src = wv.bits_inside;
+        return (uint32_t)(3 * wv.nb * wv.W * 4);
+    }
+    __device__ void bind(const WorldView &, bool) { inside = reinterpret_cast<const uint32_t *>(g_smem); }
     __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &p, int mode, bool cpg, double md) const
     {
         const int nb = wv.nb, W = wv.W;
@@ -94,6 +110,12 @@ struct PointWorld<EPP_BP_BITS> {
 template <>
 struct PointWorld<EPP_BP_GRID> {
     __device__ void init(const WorldView &, bool) {}
+    __device__ static uint32_t table(const WorldView &, bool, const void *&src)
+    {
+        src = nullptr;
+        return 0u;
+    }
+    __device__ void bind(const WorldView &, bool) {}
     __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &p, int mode, bool cpg, double md) const
     {
         const int bx = dev_bin(p.x, wv.gbins.lo[0], wv.gbins.inv[0], wv.gbins.n[0]);
@@ -247,6 +269,333 @@ __global__ void __launch_bounds__(kBlock) k_states(WorldView wv, const double *_
         tile = next_tile;
         i = ni;
         cur = nxt;
+    }
+}
+
+// ---- TMA bulk-copy plumbing (cp.async.bulk -> SASS UBLKCP, completion on an mbarrier) ------------
+
+__device__ __forceinline__ uint32_t smem_addr(const void *p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t *bar, uint32_t count)
+{
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
+}
+
+// Make freshly initialised barriers visible to the async (TMA) proxy.
+__device__ __forceinline__ void mbar_init_fence()
+{
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+}
+
+__device__ __forceinline__ void mbar_expect_tx(uint64_t *bar, uint32_t bytes)
+{
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes)
+                 : "memory");
+}
+
+__device__ __forceinline__ bool mbar_try_wait(uint64_t *bar, uint32_t parity)
+{
+    uint32_t ok;
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n\t"
+        "selp.u32 %0, 1, 0, p;\n\t}"
+        : "=r"(ok)
+        : "r"(smem_addr(bar)), "r"(parity)
+        : "memory");
+    return ok != 0;
+}
+
+__device__ __forceinline__ void mbar_wait(uint64_t *bar, uint32_t parity)
+{
+    while (!mbar_try_wait(bar, parity)) {
+    }
+}
+
+// global -> shared bulk copy; dst, src and bytes must be multiples of 16.
+__device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t bytes, uint64_t *bar)
+{
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                     smem_addr(dst)),
+                 "l"(src), "r"(bytes), "r"(smem_addr(bar))
+                 : "memory");
+}
+
+constexpr int kMaxStages = 8;
+
+// ---- K1 (streaming form): TMA bulk-copy ring + block-wide candidate compaction -----------------------
+//
+// Persistent blocks; tile = S * kBlock consecutive states = one contiguous span of the AoS batch that
+// thread 0 fetches with cp.async.bulk into a ring of `stages` shared-memory slots.
+//
+// The direct kernel above lets every lane walk its own candidate list, so a warp pays the full exact test
+// whenever ANY lane has a candidate, at ~50 % lane utilisation and with one dependent chain per warp.
+// Here a tile is handled in two dense phases:
+//   phase 1  every thread locates the candidates of its S states (independent chains -> ILP) and appends
+//            (state, OBB) pairs to a block-wide queue; one shared-memory atomic per warp reserves the space;
+//   phase 2  the block walks the queue with all lanes busy, running the reference's exact per-candidate
+//            test (strict stored-AABB test, type rule, OBB test) and OR-ing hits into an invalid bitmap.
+// The verdict of a state is an OR over its candidates, so neither the order of the queue nor the loss of the
+// early exit changes a single bit.  Pairs that do not fit the queue are tested in place by their lane.
+constexpr uint32_t kPairSentinel = 0xffffffffu;
+constexpr int kPairUnitShift = 22; // pair = unit << 22 | obb index (M < 2^22)
+
+template <int BP>
+struct PointCand;
+template <>
+struct PointCand<EPP_BP_BRUTE> {};
+template <>
+struct PointCand<EPP_BP_BITS> {
+    int ox, oy, oz; // row offsets (in words) of the three bin rows
+    uint32_t m;     // W == 1: the candidate word itself
+};
+template <>
+struct PointCand<EPP_BP_GRID> {
+    uint32_t s, e;
+};
+
+template <int BP>
+struct PointEnum;
+
+template <>
+struct PointEnum<EPP_BP_BRUTE> {
+    __device__ __forceinline__ static int locate(const PointWorld<EPP_BP_BRUTE> &w, const WorldView &wv, const P3 &p,
+                                                 PointCand<EPP_BP_BRUTE> &)
+    {
+        int c = 0;
+        for (int k = 0; k < wv.M; ++k) c += within_strict(w.aabb + k, p) ? 1 : 0;
+        return c;
+    }
+    template <class F>
+    __device__ __forceinline__ static void each(const PointWorld<EPP_BP_BRUTE> &w, const WorldView &wv, const P3 &p,
+                                                const PointCand<EPP_BP_BRUTE> &, F f)
+    {
+        for (int k = 0; k < wv.M; ++k)
+            if (within_strict(w.aabb + k, p)) f(k);
+    }
+};
+
+template <>
+struct PointEnum<EPP_BP_BITS> {
+    __device__ __forceinline__ static int locate(const PointWorld<EPP_BP_BITS> &w, const WorldView &wv, const P3 &p,
+                                                 PointCand<EPP_BP_BITS> &c)
+    {
+        const int nb = wv.nb, W = wv.W;
+        const int bx = dev_bin(p.x, wv.bbins.lo[0], wv.bbins.inv[0], nb);
+        const int by = nb + dev_bin(p.y, wv.bbins.lo[1], wv.bbins.inv[1], nb);
+        const int bz = 2 * nb + dev_bin(p.z, wv.bbins.lo[2], wv.bbins.inv[2], nb);
+        if (W == 1) { // worlds of up to 32 OBBs (the race track): one word per bin, no loops
+            c.m = w.inside[bx] & w.inside[by] & w.inside[bz];
+            return __popc(c.m);
+        }
+        c.ox = bx * W;
+        c.oy = by * W;
+        c.oz = bz * W;
+        int n = 0;
+        for (int i = 0; i < W; ++i) n += __popc(w.inside[c.ox + i] & w.inside[c.oy + i] & w.inside[c.oz + i]);
+        return n;
+    }
+    template <class F>
+    __device__ __forceinline__ static void each(const PointWorld<EPP_BP_BITS> &w, const WorldView &wv, const P3 &,
+                                                const PointCand<EPP_BP_BITS> &c, F f)
+    {
+        if (wv.W == 1) {
+            uint32_t m = c.m;
+            while (m) {
+                f(__ffs(m) - 1);
+                m &= m - 1;
+            }
+            return;
+        }
+        for (int i = 0; i < wv.W; ++i) {
+            uint32_t m = w.inside[c.ox + i] & w.inside[c.oy + i] & w.inside[c.oz + i];
+            while (m) {
+                f((i << 5) + __ffs(m) - 1);
+                m &= m - 1;
+            }
+        }
+    }
+};
+
+template <>
+struct PointEnum<EPP_BP_GRID> {
+    __device__ __forceinline__ static int locate(const PointWorld<EPP_BP_GRID> &, const WorldView &wv, const P3 &p,
+                                                 PointCand<EPP_BP_GRID> &c)
+    {
+        const int bx = dev_bin(p.x, wv.gbins.lo[0], wv.gbins.inv[0], wv.gbins.n[0]);
+        const int by = dev_bin(p.y, wv.gbins.lo[1], wv.gbins.inv[1], wv.gbins.n[1]);
+        const int bz = dev_bin(p.z, wv.gbins.lo[2], wv.gbins.inv[2], wv.gbins.n[2]);
+        const size_t cell = ((size_t)bz * wv.gbins.n[1] + by) * wv.gbins.n[0] + bx;
+        c.s = __ldg(wv.cell_start + cell);
+        c.e = __ldg(wv.cell_start + cell + 1);
+        return (int)(c.e - c.s);
+    }
+    template <class F>
+    __device__ __forceinline__ static void each(const PointWorld<EPP_BP_GRID> &, const WorldView &wv, const P3 &,
+                                                const PointCand<EPP_BP_GRID> &c, F f)
+    {
+        for (uint32_t j = c.s; j < c.e; ++j) f((int)__ldg(wv.cell_items + j));
+    }
+};
+
+// Shared-memory bookkeeping of the compaction, double buffered by tile parity.
+template <int UNITS>
+struct PairState {
+    int count[2];
+    uint32_t inv[2][UNITS / 32];
+};
+
+// One tile: `units` (<= S*kBlock) states at `pts` (AoS doubles in shared memory).  Ends with the block's
+// mask words written; contains two __syncthreads.  buf alternates 0/1 per call.
+template <int BP, int S>
+__device__ __forceinline__ void states_tile(const PointWorld<BP> &world, const WorldView &wv, const double *pts,
+                                            int units, int mode, bool cpg, double md, uint32_t *queue, int qcap,
+                                            PairState<S * kBlock> &ps, int buf, uint32_t *__restrict__ mask_out)
+{
+    // ---- phase 1
+    P3 p[S];
+    PointCand<BP> cand[S];
+    int cnt[S];
+    int total = 0;
+#pragma unroll
+    for (int u = 0; u < S; ++u) {
+        const int unit = u * kBlock + threadIdx.x;
+        cnt[u] = 0;
+        if (unit < units) {
+            p[u].x = pts[3 * unit];
+            p[u].y = pts[3 * unit + 1];
+            p[u].z = pts[3 * unit + 2];
+            cnt[u] = PointEnum<BP>::locate(world, wv, p[u], cand[u]);
+        }
+        total += cnt[u];
+    }
+    if (total != 0) {
+        // one shared-memory atomic per lane that has candidates (a minority of lanes in sparse worlds)
+        int base = atomicAdd(&ps.count[buf], total);
+        if (base + total <= qcap) {
+#pragma unroll
+            for (int u = 0; u < S; ++u) {
+                if (cnt[u] == 0) continue;
+                const uint32_t tag = (uint32_t)(u * kBlock + threadIdx.x) << kPairUnitShift;
+                PointEnum<BP>::each(world, wv, p[u], cand[u], [&](int k) { queue[base++] = tag | (uint32_t)k; });
+            }
+        } else { // queue full: blank my reserved slots and test in place
+            for (int j = base; j < qcap && j < base + total; ++j) queue[j] = kPairSentinel;
+#pragma unroll
+            for (int u = 0; u < S; ++u) {
+                if (cnt[u] == 0) continue;
+                bool hit = false;
+                PointEnum<BP>::each(world, wv, p[u], cand[u], [&](int k) {
+                    hit = hit || point_candidate_invalid(wv.aabb, wv.obb, k, p[u], mode, cpg, md);
+                });
+                const int unit = u * kBlock + threadIdx.x;
+                if (hit) atomicOr(&ps.inv[buf][unit >> 5], 1u << (unit & 31));
+            }
+        }
+    }
+    __syncthreads();
+    // ---- phase 2
+    const int pairs = ps.count[buf] < qcap ? ps.count[buf] : qcap;
+    for (int q = threadIdx.x; q < pairs; q += kBlock) {
+        const uint32_t pr = queue[q];
+        if (pr == kPairSentinel) continue;
+        const int unit = (int)(pr >> kPairUnitShift);
+        const int k = (int)(pr & ((1u << kPairUnitShift) - 1u));
+        const P3 q3 = {pts[3 * unit], pts[3 * unit + 1], pts[3 * unit + 2]};
+        if (point_candidate_invalid(wv.aabb, wv.obb, k, q3, mode, cpg, md))
+            atomicOr(&ps.inv[buf][unit >> 5], 1u << (unit & 31));
+    }
+    __syncthreads();
+    // ---- verdicts: bit = valid; bits of units beyond `units` stay 0
+    if (threadIdx.x < (units + 31) / 32) {
+        const int w = threadIdx.x;
+        const int live = units - 32 * w;
+        const uint32_t active = live >= 32 ? 0xffffffffu : ((1u << live) - 1u);
+        mask_out[w] = ~ps.inv[buf][w] & active;
+        ps.inv[buf][w] = 0u;
+    }
+    if (threadIdx.x == 0) ps.count[buf] = 0;
+}
+
+template <int BP, int S>
+__global__ void __launch_bounds__(kBlock, S == 2 ? 6 : 3) k_states_stream(WorldView wv, const double *__restrict__ xyz, size_t n, int mode,
+                                                          int can_pass_gate, double min_distance, int aabb_in_smem,
+                                                          int stages, uint32_t table_bytes, int qcap,
+                                                          uint32_t *__restrict__ mask)
+{
+    constexpr int kTile = S * kBlock;
+    constexpr uint32_t kTileBytes = kTile * 3 * sizeof(double);
+    __shared__ __align__(8) uint64_t s_full[kMaxStages];
+    __shared__ __align__(8) uint64_t s_table;
+    __shared__ PairState<kTile> s_ps;
+    unsigned char *ring = g_smem + table_bytes; // table_bytes is a multiple of 128
+    uint32_t *queue = reinterpret_cast<uint32_t *>(ring + (size_t)stages * kTileBytes);
+    const size_t full_tiles = n / kTile;
+    const size_t first = blockIdx.x;
+
+    if (threadIdx.x == 0) {
+        for (int s = 0; s < stages; ++s) mbar_init(&s_full[s], 1);
+        mbar_init(&s_table, 1);
+        mbar_init_fence();
+        // broad-phase table first (needed by every tile), then the first `stages` tiles
+        const void *tsrc;
+        const uint32_t tbytes = (PointWorld<BP>::table(wv, aabb_in_smem != 0, tsrc) + 15u) & ~15u; // blob parts are padded
+        if (tbytes) {
+            mbar_expect_tx(&s_table, tbytes);
+            bulk_g2s(g_smem, tsrc, tbytes, &s_table);
+        }
+        for (int s = 0; s < stages; ++s) {
+            const size_t tile = first + (size_t)s * gridDim.x;
+            if (tile < full_tiles) {
+                mbar_expect_tx(&s_full[s], kTileBytes);
+                bulk_g2s(ring + (size_t)s * kTileBytes, xyz + tile * (size_t)(3 * kTile), kTileBytes, &s_full[s]);
+            }
+        }
+        s_ps.count[0] = s_ps.count[1] = 0;
+    }
+    if (threadIdx.x < kTile / 32) s_ps.inv[0][threadIdx.x] = s_ps.inv[1][threadIdx.x] = 0u;
+    PointWorld<BP> world;
+    world.bind(wv, aabb_in_smem != 0);
+    __syncthreads(); // publishes the barriers and the zeroed bookkeeping
+    {
+        const void *tsrc;
+        if (PointWorld<BP>::table(wv, aabb_in_smem != 0, tsrc)) mbar_wait(&s_table, 0);
+    }
+
+    const bool cpg = can_pass_gate != 0;
+    int s = 0, buf = 0;
+    uint32_t parity = 0;
+    for (size_t tile = first; tile < full_tiles; tile += gridDim.x) {
+        mbar_wait(&s_full[s], parity);
+        const double *pts = reinterpret_cast<const double *>(ring + (size_t)s * kTileBytes);
+        states_tile<BP, S>(world, wv, pts, kTile, mode, cpg, min_distance, queue, qcap, s_ps, buf,
+                           mask + tile * (kTile / 32));
+        // every read of the slot happened before the second barrier inside states_tile
+        if (threadIdx.x == 0) {
+            const size_t nxt = tile + (size_t)stages * gridDim.x;
+            if (nxt < full_tiles) {
+                mbar_expect_tx(&s_full[s], kTileBytes);
+                bulk_g2s(ring + (size_t)s * kTileBytes, xyz + nxt * (size_t)(3 * kTile), kTileBytes, &s_full[s]);
+            }
+        }
+        buf ^= 1;
+        if (++s == stages) {
+            s = 0;
+            parity ^= 1u;
+        }
+    }
+
+    // ragged tail (n % kTile states): plain loads into slot 0, same tile routine
+    const size_t tail0 = full_tiles * kTile;
+    if (tail0 < n && blockIdx.x == (unsigned)(full_tiles % gridDim.x)) {
+        const int rem = (int)(n - tail0);
+        double *slot = reinterpret_cast<double *>(ring);
+        __syncthreads(); // phase 2 of another warp may still read slot 0 only before the barriers above; be explicit
+        for (int e = threadIdx.x; e < 3 * rem; e += kBlock) slot[e] = __ldg(xyz + 3 * tail0 + e);
+        __syncthreads();
+        states_tile<BP, S>(world, wv, slot, rem, mode, cpg, min_distance, queue, qcap, s_ps, buf,
+                           mask + tail0 / 32);
     }
 }
 
@@ -553,7 +902,7 @@ size_t ray_smem_bytes(const WorldView &wv, int bp, bool &aabb_in_smem)
 template <typename K>
 cudaError_t ensure_smem(K kernel, size_t bytes, size_t static_bytes = 0)
 {
-    if (bytes + static_bytes <= 48 * 1024) return cudaSuccess;
+    if (bytes + static_bytes <= 40 * 1024) return cudaSuccess;
     return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
 }
 
@@ -575,15 +924,57 @@ std::atomic<uint64_t> g_launches{0};
     default: { constexpr int BP = EPP_BP_GRID; __VA_ARGS__; } break;             \
     }
 
+template <int BP, int S>
+cudaError_t launch_states_stream(const LaunchCfg &cfg, const WorldView &wv, const double *d_xyz, size_t n, int mode,
+                                 int can_pass_gate, double min_distance, bool in_smem, size_t table_bytes, int stages,
+                                 uint32_t *d_mask, cudaStream_t stream, bool &launched)
+{
+    constexpr int kTile = S * kBlock;
+    const int qcap = cfg.states_queue_pairs > 0 ? cfg.states_queue_pairs : 2 * kTile;
+    const size_t smem = table_bytes + (size_t)stages * kTile * 24 + (size_t)qcap * 4;
+    launched = false;
+    if (smem > 200 * 1024) return cudaSuccess;
+    cudaError_t err = cudaFuncSetAttribute(k_states_stream<BP, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (err != cudaSuccess) return err;
+    const size_t tiles = (n + kTile - 1) / kTile;
+    const unsigned grid = persistent_grid(cfg, tiles, cfg.states_stream_blocks_per_sm);
+    k_states_stream<BP, S><<<grid, kBlock, smem, stream>>>(wv, d_xyz, n, mode, can_pass_gate, min_distance, in_smem ? 1 : 0,
+                                                           stages, (uint32_t)table_bytes, qcap, d_mask);
+    launched = true;
+    return cudaGetLastError();
+}
+
 cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_xyz, size_t n, int mode,
                           int can_pass_gate, double min_distance, uint32_t *d_mask, cudaStream_t stream)
 {
     if (n == 0) return cudaSuccess;
     bool in_smem;
     const size_t smem = point_smem_bytes(wv, bp, in_smem);
+    cudaError_t err = cudaSuccess;
+    // Streaming form: batches worth a ring, 16 B aligned (cp.async.bulk), obb index fits the pair encoding.
+    const bool stream_ok = (reinterpret_cast<uintptr_t>(d_xyz) & 15u) == 0 && wv.M < (1 << kPairUnitShift);
+    const bool want_stream = cfg.states_variant == 2 || (cfg.states_variant == 0 && n >= 8192);
+    if (stream_ok && want_stream) {
+        const size_t table_bytes = (smem + 127) / 128 * 128;
+        const int stages = cfg.states_stages < 2 ? 2 : (cfg.states_stages > kMaxStages ? kMaxStages : cfg.states_stages);
+        const int S = cfg.states_per_thread == 4 ? 4 : 2;
+        bool launched = false;
+        EPP_DISPATCH_BP(bp, {
+            if (S == 4)
+                err = launch_states_stream<BP, 4>(cfg, wv, d_xyz, n, mode, can_pass_gate, min_distance, in_smem, table_bytes,
+                                                  stages, d_mask, stream, launched);
+            else
+                err = launch_states_stream<BP, 2>(cfg, wv, d_xyz, n, mode, can_pass_gate, min_distance, in_smem, table_bytes,
+                                                  stages, d_mask, stream, launched);
+        });
+        if (err != cudaSuccess) return err;
+        if (launched) {
+            g_launches++;
+            return cudaSuccess;
+        }
+    }
     const size_t tiles = (n + kBlock - 1) / kBlock;
     const unsigned grid = persistent_grid(cfg, tiles, cfg.states_blocks_per_sm);
-    cudaError_t err = cudaSuccess;
     EPP_DISPATCH_BP(bp, {
         err = ensure_smem(k_states<BP>, smem);
         if (err == cudaSuccess) {

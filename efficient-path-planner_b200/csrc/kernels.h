@@ -14,7 +14,11 @@ struct LaunchCfg {
     int sm_count = 148;
     int states_blocks_per_sm = 8;   // 0: one block per tile (non-persistent)
     int segments_blocks_per_sm = 4; // 0: one block per tile
-    int states_variant = 0;         // 0: direct loads, 1: TMA bulk pipeline
+    int states_variant = 0;         // 0: auto (streaming form for large aligned batches), 1: direct, 2: streaming
+    int states_stages = 2;          // ring slots per block of the streaming form (2..8)
+    int states_stream_blocks_per_sm = 6;
+    int states_per_thread = 0;      // streaming form: 2 or 4 states per thread per tile; 0: by batch size
+    int states_queue_pairs = 0;     // pair-queue capacity per tile; 0: two pairs per state
 };
 
 extern std::atomic<uint64_t> g_launches;

@@ -322,3 +322,40 @@ def test_concurrent_host_threads(oracle, config, track):
         want = ow.check_states(xyz)
         assert all(np.array_equal(r, want) for r in res)
         assert singles == [bool(want[i >> 5] >> (i & 31) & 1) for i in range(50)]
+
+
+@pytest.mark.parametrize("bp", BPS, ids=BP_IDS)
+def test_states_streaming_form_equals_direct_form(oracle, config, bp):
+    """K1 has two forms (TMA bulk-copy ring + block-wide candidate compaction / direct loads with a
+    per-lane candidate walk).  Both must give the oracle's mask for whole tiles, ragged tails, batches
+    smaller than one tile, a pair queue that overflows, and 8 B-aligned (not 16 B) batches (which the
+    launcher routes to the direct form)."""
+    import torch
+    g, o, lo, hi = worlds.world_256()
+    ow, gw = build_pair(oracle, epp_b200, config, g, o, bp)
+    keys = ("states_variant", "states_stages", "states_stream_blocks_per_sm", "states_per_thread",
+            "states_queue_pairs")
+    saved = {k: epp_b200.get_tuning(k) for k in keys}
+    settings = [(1, 2, 4, 0, 0), (2, 2, 1, 2, 0), (2, 3, 4, 4, 0), (2, 8, 2, 2, 64), (2, 2, 4, 4, 1), (0, 2, 4, 0, 0)]
+    try:
+        for n in (1, 511, 512, 513, 1024, 1025, 8192 + 511, 100003, 1 << 19):
+            buf = torch.empty(3 * n + 1, dtype=torch.float64, device="cuda")
+            d_xyz = epp_b200.gen_states_dev(worlds.SEED_STATES, 7 * n, n, lo, hi, out=buf[: 3 * n].view(n, 3))
+            h_xyz = oracle.gen_states(worlds.SEED_STATES, 7 * n, n, lo, hi)
+            want = ow.check_states(h_xyz, threads=8)
+            want_md = ow.check_states_mindist(h_xyz, 0.1, threads=8)
+            for setting in settings:
+                for k, v in zip(keys, setting):
+                    epp_b200.set_tuning(k, v)
+                got = gw.check_states_dev(d_xyz).cpu().numpy().view(np.uint32)
+                assert np.array_equal(got, want), (n, setting)
+                md = gw.check_states_dev(d_xyz, min_distance=0.1).cpu().numpy().view(np.uint32)
+                assert np.array_equal(md, want_md), (n, setting)
+            # same states at an address that is only 8 B aligned
+            shifted = buf[1:].view(n, 3)
+            shifted.copy_(d_xyz.clone())
+            epp_b200.set_tuning("states_variant", 2)
+            assert np.array_equal(gw.check_states_dev(shifted).cpu().numpy().view(np.uint32), want), n
+    finally:
+        for k, v in saved.items():
+            epp_b200.set_tuning(k, v)
