@@ -48,7 +48,7 @@ struct Tuning {
     std::atomic<int> segments_blocks_per_sm{4};
     std::atomic<int> states_variant{0};
     std::atomic<int> states_stages{2};
-    std::atomic<int> states_stream_blocks_per_sm{6};
+    std::atomic<int> states_stream_blocks_per_sm{5};
     std::atomic<int> states_per_thread{0};
     std::atomic<int> states_queue_pairs{0};
     std::atomic<int> bits_bins{0};          // 0: by world size

@@ -519,7 +519,7 @@ __device__ __forceinline__ void states_tile(const PointWorld<BP> &world, const W
 }
 
 template <int BP, int S>
-__global__ void __launch_bounds__(kBlock, S == 2 ? 6 : 3) k_states_stream(WorldView wv, const double *__restrict__ xyz, size_t n, int mode,
+__global__ void __launch_bounds__(kBlock) k_states_stream(WorldView wv, const double *__restrict__ xyz, size_t n, int mode,
                                                           int can_pass_gate, double min_distance, int aabb_in_smem,
                                                           int stages, uint32_t table_bytes, int qcap,
                                                           uint32_t *__restrict__ mask)

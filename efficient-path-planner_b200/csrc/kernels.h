@@ -16,7 +16,7 @@ struct LaunchCfg {
     int segments_blocks_per_sm = 4; // 0: one block per tile
     int states_variant = 0;         // 0: auto (streaming form for large aligned batches), 1: direct, 2: streaming
     int states_stages = 2;          // ring slots per block of the streaming form (2..8)
-    int states_stream_blocks_per_sm = 6;
+    int states_stream_blocks_per_sm = 5;
     int states_per_thread = 0;      // streaming form: 2 or 4 states per thread per tile; 0: by batch size
     int states_queue_pairs = 0;     // pair-queue capacity per tile; 0: two pairs per state
 };
