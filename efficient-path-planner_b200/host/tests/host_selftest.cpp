@@ -162,8 +162,8 @@ static void gpu(const std::string &cfgPath)
         traj(i, 9) = 0.1 * i;
     }
     CHECK(planner.checkTrajectoryValidity(traj, 0.01) == true); // through the 5 cm slot with a 1 cm margin
-    for (int i = 0; i < 50; ++i) traj(i, 6) = 0.4;
-    CHECK(planner.checkTrajectoryValidity(traj, 0.01) == false); // through the bottom bar
+    for (int i = 0; i < 50; ++i) traj(i, 6) = 0.275;
+    CHECK(planner.checkTrajectoryValidity(traj, 0.01) == false); // through the bottom bar (z 0.25..0.30)
     CHECK(planner.checkTrajectoryValidity(epp::MatrixXd(0, 10), 0.1) == true);
     epp::MatrixXd high = traj;
     for (int i = 0; i < 50; ++i) high(i, 6) = 1.8;
