@@ -1,0 +1,2 @@
+#pragma once
+#include "../../../../../efficient-path-planner_b200/host/ompl_shim/ompl/base/SpaceInformation.h"
