@@ -51,6 +51,11 @@ struct Tuning {
     std::atomic<int> states_stream_blocks_per_sm{5};
     std::atomic<int> states_per_thread{0};
     std::atomic<int> states_queue_pairs{0};
+    std::atomic<int> states_warp_blocks_per_sm{3};
+    std::atomic<int> states_warp_min_n{4096};
+    std::atomic<int> states_rec_smem{1};
+    std::atomic<int> states_debug{0};
+    std::atomic<int> states_bits1{1};
     std::atomic<int> bits_bins{0};          // 0: by world size
     std::atomic<int> grid_max_cells{1 << 22};
     std::atomic<int> bits_max_obbs{1024};
@@ -219,6 +224,11 @@ LaunchCfg launch_cfg(const DeviceEpoch &ep)
     c.states_stream_blocks_per_sm = g_tuning.states_stream_blocks_per_sm.load();
     c.states_per_thread = g_tuning.states_per_thread.load();
     c.states_queue_pairs = g_tuning.states_queue_pairs.load();
+    c.states_warp_blocks_per_sm = g_tuning.states_warp_blocks_per_sm.load();
+    c.states_warp_min_n = g_tuning.states_warp_min_n.load();
+    c.states_rec_smem = g_tuning.states_rec_smem.load();
+    c.states_debug = g_tuning.states_debug.load();
+    c.states_bits1 = g_tuning.states_bits1.load();
     return c;
 }
 
@@ -357,6 +367,11 @@ extern "C" int epp_set_tuning(const char *key, int value)
     else if (k == "states_stream_blocks_per_sm") g_tuning.states_stream_blocks_per_sm = value;
     else if (k == "states_per_thread") g_tuning.states_per_thread = value;
     else if (k == "states_queue_pairs") g_tuning.states_queue_pairs = value;
+    else if (k == "states_warp_blocks_per_sm") g_tuning.states_warp_blocks_per_sm = value;
+    else if (k == "states_warp_min_n") g_tuning.states_warp_min_n = value;
+    else if (k == "states_rec_smem") g_tuning.states_rec_smem = value;
+    else if (k == "states_debug") g_tuning.states_debug = value;
+    else if (k == "states_bits1") g_tuning.states_bits1 = value;
     else if (k == "bits_bins") g_tuning.bits_bins = value;
     else if (k == "grid_max_cells") g_tuning.grid_max_cells = value;
     else if (k == "bits_max_obbs") g_tuning.bits_max_obbs = value;
@@ -375,6 +390,11 @@ extern "C" int epp_get_tuning(const char *key, int *value)
     else if (k == "states_stream_blocks_per_sm") *value = g_tuning.states_stream_blocks_per_sm;
     else if (k == "states_per_thread") *value = g_tuning.states_per_thread;
     else if (k == "states_queue_pairs") *value = g_tuning.states_queue_pairs;
+    else if (k == "states_warp_blocks_per_sm") *value = g_tuning.states_warp_blocks_per_sm;
+    else if (k == "states_warp_min_n") *value = g_tuning.states_warp_min_n;
+    else if (k == "states_rec_smem") *value = g_tuning.states_rec_smem;
+    else if (k == "states_debug") *value = g_tuning.states_debug;
+    else if (k == "states_bits1") *value = g_tuning.states_bits1;
     else if (k == "bits_bins") *value = g_tuning.bits_bins;
     else if (k == "grid_max_cells") *value = g_tuning.grid_max_cells;
     else if (k == "bits_max_obbs") *value = g_tuning.bits_max_obbs;
@@ -535,7 +555,10 @@ extern "C" int epp_world_commit(epp_world *w)
     v.bits_max_ge = (const uint32_t *)(base + parts[4].off);
     v.nb = bits.nb;
     v.W = bits.W;
-    v.bbins = bits.bins;
+    v.kb = bits.bins;
+    v.zrot = 1;
+    for (const ObbRec &o : obbs)
+        if (o.rot[2] != 0.0 || o.rot[5] != 0.0 || o.rot[6] != 0.0 || o.rot[7] != 0.0 || o.rot[8] != 1.0) v.zrot = 0;
     v.cell_start = (const uint32_t *)(base + parts[5].off);
     v.cell_items = (const uint32_t *)(base + parts[6].off);
     v.gbins = grid.bins;

@@ -28,7 +28,8 @@ struct WorldView {
     const uint32_t *bits_max_ge;
     int nb;
     int W;
-    AxisBins bbins;
+    KeyBins kb;
+    int zrot; // every OBB rotation is a rotation about z (rot[2,5,6,7] == 0, rot[8] == 1)
     // EPP_BP_GRID
     const uint32_t *cell_start;
     const uint32_t *cell_items;
@@ -48,6 +49,15 @@ __device__ __forceinline__ int dev_bin(double x, double lo, double inv, int n)
 {
     int b = __double2int_rd(dmul(dsub(x, lo), inv)); // saturating, NaN -> 0
     b = b < 0 ? 0 : b;
+    return b > n - 1 ? n - 1 : b;
+}
+
+// Same function as host_key_bin() in world_host.cpp: row of the per-axis bitmask tables for coordinate x.
+__device__ __forceinline__ int dev_key_bin(double x, double off, int h0, int shift, int n)
+{
+    int h = __double2hiint(dadd(x, off));
+    h = h < h0 ? h0 : h;
+    const int b = (h - h0) >> shift;
     return b > n - 1 ? n - 1 : b;
 }
 

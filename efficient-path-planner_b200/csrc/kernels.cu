@@ -61,13 +61,23 @@ struct PointWorld<EPP_BP_BRUTE> {
     {
         aabb = aabb_in_smem ? reinterpret_cast<const AabbRec *>(g_smem) : wv.aabb;
     }
-    __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &p, int mode, bool cpg, double md) const
+    // any(): true iff test(k) holds for some broad-phase candidate k of p (early exit).
+    template <class F>
+    __device__ __forceinline__ bool any(const WorldView &wv, const P3 &p, F test) const
     {
         for (int k = 0; k < wv.M; ++k) {
             if (!within_strict(aabb + k, p)) continue;
-            if (point_candidate_invalid(wv.aabb, wv.obb, k, p, mode, cpg, md)) return true;
+            if (test(k)) return true;
         }
         return false;
+    }
+    __device__ __forceinline__ bool has_candidates(const WorldView &wv, const P3 &p) const
+    {
+        return any(wv, p, [](int) { return true; });
+    }
+    __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &p, int mode, bool cpg, double md) const
+    {
+        return any(wv, p, [&](int k) { return point_candidate_invalid(wv.aabb, wv.obb, k, p, mode, cpg, md); });
     }
 };
 
@@ -88,21 +98,74 @@ struct PointWorld<EPP_BP_BITS> {
         return (uint32_t)(3 * wv.nb * wv.W * 4);
     }
     __device__ void bind(const WorldView &, bool) { inside = reinterpret_cast<const uint32_t *>(g_smem); }
-    __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &p, int mode, bool cpg, double md) const
+    template <class F>
+    __device__ __forceinline__ bool any(const WorldView &wv, const P3 &p, F test) const
     {
         const int nb = wv.nb, W = wv.W;
-        const uint32_t *tx = inside + dev_bin(p.x, wv.bbins.lo[0], wv.bbins.inv[0], nb) * W;
-        const uint32_t *ty = inside + (nb + dev_bin(p.y, wv.bbins.lo[1], wv.bbins.inv[1], nb)) * W;
-        const uint32_t *tz = inside + (2 * nb + dev_bin(p.z, wv.bbins.lo[2], wv.bbins.inv[2], nb)) * W;
+        const uint32_t *tx = inside + dev_key_bin(p.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb) * W;
+        const uint32_t *ty = inside + (nb + dev_key_bin(p.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb)) * W;
+        const uint32_t *tz = inside + (2 * nb + dev_key_bin(p.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb)) * W;
         for (int w = 0; w < W; ++w) {
             uint32_t m = tx[w] & ty[w] & tz[w];
             while (m) {
                 const int k = (w << 5) + __ffs(m) - 1;
                 m &= m - 1;
-                if (point_candidate_invalid(wv.aabb, wv.obb, k, p, mode, cpg, md)) return true;
+                if (test(k)) return true;
             }
         }
         return false;
+    }
+    __device__ __forceinline__ bool has_candidates(const WorldView &wv, const P3 &p) const
+    {
+        const int nb = wv.nb, W = wv.W;
+        const uint32_t *tx = inside + dev_key_bin(p.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb) * W;
+        const uint32_t *ty = inside + (nb + dev_key_bin(p.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb)) * W;
+        const uint32_t *tz = inside + (2 * nb + dev_key_bin(p.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb)) * W;
+        if (W == 1) return (tx[0] & ty[0] & tz[0]) != 0u;
+        uint32_t m = 0u;
+        for (int w = 0; w < W; ++w) m |= tx[w] & ty[w] & tz[w];
+        return m != 0u;
+    }
+    __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &p, int mode, bool cpg, double md) const
+    {
+        return any(wv, p, [&](int k) { return point_candidate_invalid(wv.aabb, wv.obb, k, p, mode, cpg, md); });
+    }
+};
+
+// EPP_BP_BITS for worlds of up to 32 OBBs (the race track): one word per bin, so the candidate set of a
+// point is a single 32-bit mask from three table reads; no loops over words.  Internal variant of the warp form.
+constexpr int kBpBits1 = 4;
+template <>
+struct PointWorld<kBpBits1> {
+    const uint32_t *inside;
+    __device__ static uint32_t table(const WorldView &wv, bool, const void *&src)
+    {
+        src = wv.bits_inside;
+        return (uint32_t)(3 * wv.nb * 4);
+    }
+    __device__ void bind(const WorldView &, bool) { inside = reinterpret_cast<const uint32_t *>(g_smem); }
+    __device__ __forceinline__ uint32_t candidates(const WorldView &wv, const P3 &p) const
+    {
+        const int nb = wv.nb;
+        const int bx = dev_key_bin(p.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb);
+        const int by = dev_key_bin(p.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb);
+        const int bz = dev_key_bin(p.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb);
+        return inside[bx] & inside[nb + by] & inside[2 * nb + bz];
+    }
+    template <class F>
+    __device__ __forceinline__ bool any(const WorldView &wv, const P3 &p, F test) const
+    {
+        uint32_t m = candidates(wv, p);
+        while (m) {
+            const int k = __ffs(m) - 1;
+            m &= m - 1;
+            if (test(k)) return true;
+        }
+        return false;
+    }
+    __device__ __forceinline__ bool has_candidates(const WorldView &wv, const P3 &p) const
+    {
+        return candidates(wv, p) != 0u;
     }
 };
 
@@ -116,18 +179,33 @@ struct PointWorld<EPP_BP_GRID> {
         return 0u;
     }
     __device__ void bind(const WorldView &, bool) {}
-    __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &p, int mode, bool cpg, double md) const
+    __device__ __forceinline__ static void cell_range(const WorldView &wv, const P3 &p, uint32_t &s, uint32_t &e)
     {
         const int bx = dev_bin(p.x, wv.gbins.lo[0], wv.gbins.inv[0], wv.gbins.n[0]);
         const int by = dev_bin(p.y, wv.gbins.lo[1], wv.gbins.inv[1], wv.gbins.n[1]);
         const int bz = dev_bin(p.z, wv.gbins.lo[2], wv.gbins.inv[2], wv.gbins.n[2]);
         const size_t cell = ((size_t)bz * wv.gbins.n[1] + by) * wv.gbins.n[0] + bx;
-        const uint32_t s = __ldg(wv.cell_start + cell), e = __ldg(wv.cell_start + cell + 1);
-        for (uint32_t j = s; j < e; ++j) {
-            const int k = (int)__ldg(wv.cell_items + j);
-            if (point_candidate_invalid(wv.aabb, wv.obb, k, p, mode, cpg, md)) return true;
-        }
+        s = __ldg(wv.cell_start + cell);
+        e = __ldg(wv.cell_start + cell + 1);
+    }
+    template <class F>
+    __device__ __forceinline__ bool any(const WorldView &wv, const P3 &p, F test) const
+    {
+        uint32_t s, e;
+        cell_range(wv, p, s, e);
+        for (uint32_t j = s; j < e; ++j)
+            if (test((int)__ldg(wv.cell_items + j))) return true;
         return false;
+    }
+    __device__ __forceinline__ bool has_candidates(const WorldView &wv, const P3 &p) const
+    {
+        uint32_t s, e;
+        cell_range(wv, p, s, e);
+        return e != s;
+    }
+    __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &p, int mode, bool cpg, double md) const
+    {
+        return any(wv, p, [&](int k) { return point_candidate_invalid(wv.aabb, wv.obb, k, p, mode, cpg, md); });
     }
 };
 
@@ -181,12 +259,12 @@ struct RayWorld<EPP_BP_BITS> {
         P3 mn, mx;
         ray_box(a, b, mn, mx);
         const int nb = wv.nb, W = wv.W;
-        const uint32_t *gx = max_ge + dev_bin(mn.x, wv.bbins.lo[0], wv.bbins.inv[0], nb) * W;
-        const uint32_t *gy = max_ge + (nb + dev_bin(mn.y, wv.bbins.lo[1], wv.bbins.inv[1], nb)) * W;
-        const uint32_t *gz = max_ge + (2 * nb + dev_bin(mn.z, wv.bbins.lo[2], wv.bbins.inv[2], nb)) * W;
-        const uint32_t *lx = min_le + dev_bin(mx.x, wv.bbins.lo[0], wv.bbins.inv[0], nb) * W;
-        const uint32_t *ly = min_le + (nb + dev_bin(mx.y, wv.bbins.lo[1], wv.bbins.inv[1], nb)) * W;
-        const uint32_t *lz = min_le + (2 * nb + dev_bin(mx.z, wv.bbins.lo[2], wv.bbins.inv[2], nb)) * W;
+        const uint32_t *gx = max_ge + dev_key_bin(mn.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb) * W;
+        const uint32_t *gy = max_ge + (nb + dev_key_bin(mn.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb)) * W;
+        const uint32_t *gz = max_ge + (2 * nb + dev_key_bin(mn.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb)) * W;
+        const uint32_t *lx = min_le + dev_key_bin(mx.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb) * W;
+        const uint32_t *ly = min_le + (nb + dev_key_bin(mx.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb)) * W;
+        const uint32_t *lz = min_le + (2 * nb + dev_key_bin(mx.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb)) * W;
         for (int w = 0; w < W; ++w) {
             uint32_t m = gx[w] & gy[w] & gz[w] & lx[w] & ly[w] & lz[w];
             while (m) {
@@ -382,9 +460,9 @@ struct PointEnum<EPP_BP_BITS> {
                                                  PointCand<EPP_BP_BITS> &c)
     {
         const int nb = wv.nb, W = wv.W;
-        const int bx = dev_bin(p.x, wv.bbins.lo[0], wv.bbins.inv[0], nb);
-        const int by = nb + dev_bin(p.y, wv.bbins.lo[1], wv.bbins.inv[1], nb);
-        const int bz = 2 * nb + dev_bin(p.z, wv.bbins.lo[2], wv.bbins.inv[2], nb);
+        const int bx = dev_key_bin(p.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb);
+        const int by = nb + dev_key_bin(p.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb);
+        const int bz = 2 * nb + dev_key_bin(p.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb);
         if (W == 1) { // worlds of up to 32 OBBs (the race track): one word per bin, no loops
             c.m = w.inside[bx] & w.inside[by] & w.inside[bz];
             return __popc(c.m);
@@ -596,6 +674,201 @@ __global__ void __launch_bounds__(kBlock) k_states_stream(WorldView wv, const do
         __syncthreads();
         states_tile<BP, S>(world, wv, slot, rem, mode, cpg, min_distance, queue, qcap, s_ps, buf,
                            mask + tail0 / 32);
+    }
+}
+
+// ---- K1 (warp-pipelined form): every warp streams its own contiguous range of states -----------------
+//
+// No block-wide barrier after the prologue.  Warp j of the grid owns a contiguous run of mask words and walks
+// it in steps of S words (S*32 states, lane l takes state l of each word).  Each warp runs its own
+// cp.async.bulk ring (`stages` slots of S*768 B, one mbarrier per slot, lane 0 issues), so a warp never waits
+// on another warp.  A step has two dense phases:
+//   phase 1  every lane bins its S states and asks the broad phase only WHETHER there is a candidate
+//            (~10 % of the states of the race track); states with candidates are compacted into a per-warp
+//            byte queue with one ballot per word, no atomics, no loops;
+//   phase 2  lanes take queued states one each and walk their candidates through the reference's exact
+//            test with early exit; hits are OR-ed into the warp's S-word invalid bitmap.
+// For worlds of up to kRecSmemMax OBBs the prologue folds the per-call rules of World::checkPointValidity
+// (src/World.cpp:92-97, :116-121) into one 22-double record per OBB in shared memory: stored AABB, centre,
+// rotation and the EFFECTIVE half sizes (half + inflate for collision boxes, half for filling boxes, -1 for
+// boxes the call skips, which no |local| can be <=).
+// Record = 17 doubles (odd stride: lanes reading the same field of different records hit different banks):
+// [0..2] aabb min, [3..5] aabb max, [6..8] centre, [9..12] R(0,0) R(0,1) R(1,0) R(1,1), [13..15] eff. half.
+// Only worlds whose rotations are all about z get records (WorldView::zrot; the only kind World::addGate /
+// addObstacle can build, src/Object.cpp:38-47).  There R(2,0) = R(2,1) = R(0,2) = R(1,2) = 0 and R(2,2) = 1, so the
+// reference's 3-term sums are (a + b) + (+-0) and (+-0 + +-0) + d2: dropping the zero terms changes at most
+// the sign of a zero, which fabs() and the comparisons cannot see.  The point is finite whenever the result
+// matters because it passed the strict stored-AABB test.
+constexpr int kRecDoubles = 17;
+constexpr int kRecSmemMax = 64;
+constexpr int kWordBytes = 32 * 3 * 8; // one mask word of states = 768 B of coordinates
+
+__device__ __forceinline__ bool rec_hit(const double *__restrict__ r, const P3 &p)
+{
+    const bool in = (p.x > r[0]) & (p.x < r[3]) & (p.y > r[1]) & (p.y < r[4]) & (p.z > r[2]) & (p.z < r[5]);
+    const double d0 = dsub(p.x, r[6]), d1 = dsub(p.y, r[7]), d2 = dsub(p.z, r[8]);
+    const double lx = dadd(dmul(r[9], d0), dmul(r[11], d1));  // R(0,0) d0 + R(1,0) d1   (src/OBB.cpp:66)
+    const double ly = dadd(dmul(r[10], d0), dmul(r[12], d1)); // R(0,1) d0 + R(1,1) d1
+    return in & (fabs(lx) <= r[13]) & (fabs(ly) <= r[14]) & (fabs(d2) <= r[15]);
+}
+
+template <int BP, int S, bool RS>
+__device__ __forceinline__ void warp_states_step(const PointWorld<BP> &world, const WorldView &wv,
+                                                 const double *__restrict__ rec, const double *__restrict__ pts,
+                                                 int units, int mode, bool cpg, double md, unsigned char *queue,
+                                                 uint32_t *inv, uint32_t *__restrict__ mask_out, int lane)
+{
+    // ---- phase 1: which of my S states have a broad-phase candidate at all
+    const uint32_t lt = (1u << lane) - 1u;
+    int queued = 0;
+    const int dbg = mode >> 8; // profiling only (epp_set_tuning states_debug): 1 skips phase 2, 2 also phase 1
+    mode &= 0xff;
+#pragma unroll
+    for (int u = 0; u < S; ++u) {
+        const int unit = u * 32 + lane;
+        bool has = false;
+        if (unit < units) {
+            const P3 p = {pts[3 * unit], pts[3 * unit + 1], pts[3 * unit + 2]};
+            has = dbg == 2 ? (p.x + p.y + p.z == 12345.0) : world.has_candidates(wv, p);
+        }
+        const uint32_t b = __ballot_sync(0xffffffffu, has);
+        if (has) queue[queued + __popc(b & lt)] = (unsigned char)unit;
+        queued += __popc(b);
+    }
+    if (queued != 0 && dbg == 0) {
+        __syncwarp();
+        // ---- phase 2: one queued state per lane, exact tests with early exit
+        for (int q = lane; q < queued; q += 32) {
+            const int unit = queue[q];
+            const P3 p = {pts[3 * unit], pts[3 * unit + 1], pts[3 * unit + 2]};
+            const bool hit = world.any(wv, p, [&](int k) -> bool {
+                if (RS) return rec_hit(rec + k * kRecDoubles, p);
+                return point_candidate_invalid(wv.aabb, wv.obb, k, p, mode, cpg, md);
+            });
+            if (hit) atomicOr(&inv[unit >> 5], 1u << (unit & 31));
+        }
+        __syncwarp();
+    }
+    // ---- verdicts: bit = valid; bits of units beyond `units` stay 0
+    if (lane < S && lane * 32 < units) {
+        const int live = units - 32 * lane;
+        const uint32_t active = live >= 32 ? 0xffffffffu : ((1u << live) - 1u);
+        mask_out[lane] = ~inv[lane] & active;
+        inv[lane] = 0u;
+    }
+    __syncwarp();
+}
+
+// Warp g (of gridDim.x * kWarpsPerBlock) owns words [g*wpw + min(g, rem), +wpw + (g < rem)); the host passes
+// wpw = words / warps and rem = words % warps so no thread divides.
+template <int BP, int S, bool RS>
+__global__ void __launch_bounds__(kBlock) k_states_warp(WorldView wv, const double *__restrict__ xyz, size_t n, int mode,
+                                                        int can_pass_gate, double min_distance, int aabb_in_smem,
+                                                        int stages, uint32_t table_bytes, uint32_t rec_bytes,
+                                                        uint32_t wpw, uint32_t rem, uint32_t *__restrict__ mask)
+{
+    __shared__ __align__(8) uint64_t s_full[kWarpsPerBlock][kMaxStages];
+    __shared__ __align__(8) uint64_t s_table;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const bool cpg = can_pass_gate != 0;
+    constexpr uint32_t kSlotBytes = S * kWordBytes;
+
+    // shared memory: [broad-phase table][records][per warp: ring | byte queue (S*32) | invalid words (32 B)]
+    double *rec = reinterpret_cast<double *>(g_smem + table_bytes);
+    const uint32_t ring_bytes = (uint32_t)stages * kSlotBytes;
+    const uint32_t warp_bytes = ring_bytes + S * 32u + 32u;
+    unsigned char *mine = g_smem + table_bytes + rec_bytes + (uint32_t)warp * warp_bytes;
+    unsigned char *queue = mine + ring_bytes;
+    uint32_t *inv = reinterpret_cast<uint32_t *>(queue + S * 32);
+
+    const uint32_t g = blockIdx.x * kWarpsPerBlock + warp;
+    const uint32_t w0 = g * wpw + (g < rem ? g : rem);
+    const uint32_t w1 = w0 + wpw + (g < rem ? 1u : 0u);
+    const uint32_t words_total = (uint32_t)((n + 31) / 32);
+    const bool aligned = (reinterpret_cast<uintptr_t>(xyz) & 15u) == 0;
+    // states in the chunk that starts at word cw (< w1)
+    auto chunk_units = [&](uint32_t cw) -> int {
+        const uint32_t sw = (w1 - cw) < (uint32_t)S ? (w1 - cw) : (uint32_t)S;
+        int units = (int)(sw * 32u);
+        if (cw + sw == words_total) units = (int)(n - (size_t)cw * 32u); // the batch's ragged last word
+        return units;
+    };
+    // cp.async.bulk moves multiples of 16 B from 16 B-aligned addresses: an odd number of states (only
+    // possible in the last chunk of the batch) or an 8 B-aligned batch is loaded by the lanes instead.
+    auto issue = [&](uint32_t cw, int slot) {
+        const uint32_t bytes = (uint32_t)chunk_units(cw) * 24u;
+        mbar_expect_tx(&s_full[warp][slot], bytes);
+        bulk_g2s(mine + (uint32_t)slot * kSlotBytes, xyz + (size_t)cw * 96, bytes, &s_full[warp][slot]);
+    };
+    auto by_tma = [&](uint32_t cw) -> bool { return aligned && (chunk_units(cw) & 1) == 0; };
+
+    if (lane == 0) {
+        for (int s = 0; s < stages; ++s) mbar_init(&s_full[warp][s], 1);
+        if (warp == 0) mbar_init(&s_table, 1);
+        mbar_init_fence();
+        if (warp == 0) {
+            const void *tsrc;
+            const uint32_t tbytes = (PointWorld<BP>::table(wv, aabb_in_smem != 0, tsrc) + 15u) & ~15u;
+            if (tbytes) {
+                mbar_expect_tx(&s_table, tbytes);
+                bulk_g2s(g_smem, tsrc, tbytes, &s_table);
+            }
+        }
+        uint32_t cw = w0;
+        for (int s = 0; s < stages && cw < w1; ++s, cw += S)
+            if (by_tma(cw)) issue(cw, s);
+    }
+    if (lane < 8) inv[lane] = 0u;
+    if (RS) {
+        for (int k = threadIdx.x; k < wv.M; k += kBlock) {
+            const AabbRec *a = wv.aabb + k;
+            const ObbRec *o = wv.obb + k;
+            double *r = rec + k * kRecDoubles;
+            for (int d = 0; d < 3; ++d) {
+                r[d] = a->mn[d];
+                r[3 + d] = a->mx[d];
+                r[6 + d] = o->center[d];
+            }
+            r[9] = o->rot[0];
+            r[10] = o->rot[1];
+            r[11] = o->rot[3];
+            r[12] = o->rot[4];
+            const bool filling = (o->flags & kFlagFilling) != 0;
+            const bool skip = (mode & 0xff) == kModeBool ? (filling && cpg) : filling; // src/World.cpp:92-95, :116-119
+            const double infl = (mode & 0xff) == kModeBool ? o->inflate : min_distance; // :97, :121
+            for (int d = 0; d < 3; ++d)
+                r[13 + d] = skip ? -1.0 : (filling ? o->half[d] : dadd(o->half[d], infl)); // src/OBB.cpp:67-72
+            r[16] = 0.0;
+        }
+    }
+    PointWorld<BP> world;
+    world.bind(wv, aabb_in_smem != 0);
+    __syncthreads(); // publishes s_table's init, the records and the zeroed bitmaps
+    {
+        const void *tsrc;
+        if (PointWorld<BP>::table(wv, aabb_in_smem != 0, tsrc)) mbar_wait(&s_table, 0);
+    }
+
+    int slot = 0;
+    uint32_t parity = 0;
+    for (uint32_t cw = w0; cw < w1; cw += S) {
+        const int units = chunk_units(cw);
+        double *pts = reinterpret_cast<double *>(mine + (uint32_t)slot * kSlotBytes);
+        if (by_tma(cw)) {
+            mbar_wait(&s_full[warp][slot], parity);
+        } else {
+            const double *src = xyz + (size_t)cw * 96;
+            for (int e = lane; e < 3 * units; e += 32) pts[e] = __ldg(src + e);
+            __syncwarp();
+        }
+        warp_states_step<BP, S, RS>(world, wv, rec, pts, units, mode, cpg, min_distance, queue, inv, mask + cw, lane);
+        // the step ended with __syncwarp: every lane's reads of the slot are done
+        const uint32_t nxt = cw + (uint32_t)stages * S;
+        if (lane == 0 && nxt < w1 && by_tma(nxt)) issue(nxt, slot);
+        if (++slot == stages) {
+            slot = 0;
+            parity ^= 1u;
+        }
     }
 }
 
@@ -944,6 +1217,36 @@ cudaError_t launch_states_stream(const LaunchCfg &cfg, const WorldView &wv, cons
     return cudaGetLastError();
 }
 
+template <int BP, int S, bool RS>
+cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const double *d_xyz, size_t n, int mode,
+                               int can_pass_gate, double min_distance, bool in_smem, size_t table_bytes, int stages,
+                               uint32_t *d_mask, cudaStream_t stream, bool &launched)
+{
+    const size_t rec_bytes = RS ? ((size_t)wv.M * kRecDoubles * 8 + 127) / 128 * 128 : 0;
+    const size_t warp_bytes = (size_t)stages * S * kWordBytes + S * 32 + 32;
+    const size_t smem = table_bytes + rec_bytes + kWarpsPerBlock * warp_bytes;
+    launched = false;
+    const size_t words = (n + 31) / 32;
+    if (smem > 200 * 1024 || words >= 0xfff00000ull) return cudaSuccess;
+    cudaError_t err = cudaFuncSetAttribute(k_states_warp<BP, S, RS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (err != cudaSuccess) return err;
+    // resident blocks per SM: the tuning value, limited by shared memory (228 KB per SM, 1 KB reserved per block)
+    int bps = cfg.states_warp_blocks_per_sm > 0 ? cfg.states_warp_blocks_per_sm : 3;
+    const int fit = (int)((228 * 1024) / (smem + 1024 + 768));
+    if (bps > fit) bps = fit;
+    if (bps < 1) bps = 1;
+    const size_t warps_needed = (words + S - 1) / S;
+    const size_t blocks_needed = (warps_needed + kWarpsPerBlock - 1) / kWarpsPerBlock;
+    const unsigned grid = persistent_grid(cfg, blocks_needed, bps);
+    const uint32_t warps = grid * kWarpsPerBlock;
+    k_states_warp<BP, S, RS><<<grid, kBlock, smem, stream>>>(wv, d_xyz, n, mode | (cfg.states_debug << 8), can_pass_gate, min_distance,
+                                                             in_smem ? 1 : 0, stages, (uint32_t)table_bytes,
+                                                             (uint32_t)rec_bytes, (uint32_t)(words / warps),
+                                                             (uint32_t)(words % warps), d_mask);
+    launched = true;
+    return cudaGetLastError();
+}
+
 cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_xyz, size_t n, int mode,
                           int can_pass_gate, double min_distance, uint32_t *d_mask, cudaStream_t stream)
 {
@@ -951,6 +1254,37 @@ cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, con
     bool in_smem;
     const size_t smem = point_smem_bytes(wv, bp, in_smem);
     cudaError_t err = cudaSuccess;
+    // Warp-pipelined form: any alignment, any n; worth its prologue from a few thousand states up.
+    if ((cfg.states_variant == 3 || (cfg.states_variant == 0 && n >= (size_t)cfg.states_warp_min_n)) &&
+        wv.M < (1 << kPairUnitShift)) {
+        const size_t table_bytes = (smem + 127) / 128 * 128;
+        const int stages = cfg.states_stages < 1 ? 1 : (cfg.states_stages > kMaxStages ? kMaxStages : cfg.states_stages);
+        const int S = cfg.states_per_thread == 4 ? 4 : 8;
+        const bool rs = wv.M <= kRecSmemMax && wv.zrot && cfg.states_rec_smem != 0;
+        const int wbp = (bp == EPP_BP_BITS && wv.W == 1 && cfg.states_bits1 != 0) ? kBpBits1 : bp;
+        bool launched = false;
+#define EPP_LAUNCH_WARP(S_, RS_)                                                                                       \
+    err = launch_states_warp<BP, S_, RS_>(cfg, wv, d_xyz, n, mode, can_pass_gate, min_distance, in_smem, table_bytes, \
+                                          stages, d_mask, stream, launched)
+#define EPP_LAUNCH_WARP_S()                      \
+    if (S == 4 && rs) EPP_LAUNCH_WARP(4, true);  \
+    else if (S == 4) EPP_LAUNCH_WARP(4, false);  \
+    else if (rs) EPP_LAUNCH_WARP(8, true);       \
+    else EPP_LAUNCH_WARP(8, false)
+        if (wbp == kBpBits1) {
+            constexpr int BP = kBpBits1;
+            EPP_LAUNCH_WARP_S();
+        } else {
+            EPP_DISPATCH_BP(bp, { EPP_LAUNCH_WARP_S(); });
+        }
+#undef EPP_LAUNCH_WARP_S
+#undef EPP_LAUNCH_WARP
+        if (err != cudaSuccess) return err;
+        if (launched) {
+            g_launches++;
+            return cudaSuccess;
+        }
+    }
     // Streaming form: batches worth a ring, 16 B aligned (cp.async.bulk), obb index fits the pair encoding.
     const bool stream_ok = (reinterpret_cast<uintptr_t>(d_xyz) & 15u) == 0 && wv.M < (1 << kPairUnitShift);
     const bool want_stream = cfg.states_variant == 2 || (cfg.states_variant == 0 && n >= 8192);

@@ -14,7 +14,12 @@ struct LaunchCfg {
     int sm_count = 148;
     int states_blocks_per_sm = 8;   // 0: one block per tile (non-persistent)
     int segments_blocks_per_sm = 4; // 0: one block per tile
-    int states_variant = 0;         // 0: auto (streaming form for large aligned batches), 1: direct, 2: streaming
+    int states_variant = 0;         // 0: auto, 1: direct, 2: block-streaming, 3: warp-pipelined
+    int states_warp_blocks_per_sm = 3;
+    int states_warp_min_n = 4096;   // auto: batches from this size up take the warp-pipelined form
+    int states_debug = 0;           // profiling only: 1 skips phase 2 of the warp form, 2 also phase 1 (wrong masks)
+    int states_bits1 = 1;           // warp form: single-word candidate masks for worlds of <= 32 OBBs
+    int states_rec_smem = 1;        // warp-pipelined form: fold the world records into shared memory (M <= 64)
     int states_stages = 2;          // ring slots per block of the streaming form (2..8)
     int states_stream_blocks_per_sm = 5;
     int states_per_thread = 0;      // streaming form: 2 or 4 states per thread per tile; 0: by batch size

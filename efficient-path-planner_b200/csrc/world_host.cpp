@@ -267,6 +267,17 @@ int host_bin(double x, double lo, double inv, int n)
     return static_cast<int>(f);
 }
 
+int host_key_bin(double x, double off, int32_t h0, int32_t shift, int32_t n)
+{
+    const double t = x + off;
+    uint64_t bits;
+    std::memcpy(&bits, &t, sizeof bits);
+    int32_t h = static_cast<int32_t>(bits >> 32);
+    if (h < h0) h = h0;
+    const int32_t b = (h - h0) >> shift;
+    return b > n - 1 ? n - 1 : b;
+}
+
 namespace {
 
 void world_extent(const std::vector<AabbRec> &aabbs, double lo[3], double hi[3])
@@ -293,27 +304,44 @@ void make_axis(double lo, double hi, int n, double &out_lo, double &out_inv)
     out_inv = 1.0 / h;
 }
 
+// Key binning of one axis: `inner` (power of two) bins over the binade that holds [lo, hi] after the shift.
+void make_key_axis(double lo, double hi, int inner, double &off, int32_t &h0, int32_t &shift, int32_t &n)
+{
+    double span = hi - lo;
+    if (!(span > 0.0) || !std::isfinite(span)) span = 1.0;
+    int ex = 0;
+    const double m = std::frexp(span, &ex); // span = m * 2^ex, m in [0.5, 1)
+    int e = (m == 0.5) ? ex - 1 : ex;       // smallest e with 2^e >= span
+    e = std::min(std::max(e, -200), 200);
+    if (!std::isfinite(lo)) lo = 0.0;
+    off = std::ldexp(1.0, e) - lo;
+    h0 = static_cast<int32_t>((1023 + e) << 20);
+    int lg = 0;
+    while ((1 << (lg + 1)) <= inner && lg < 19) ++lg;
+    shift = 20 - lg;
+    n = (1 << lg) + 1;
+}
+
 } // namespace
 
 void build_bits(const std::vector<AabbRec> &aabbs, int bins_per_axis, BitsTables &out)
 {
     const int M = static_cast<int>(aabbs.size());
-    out.nb = std::max(3, bins_per_axis);
     out.W = std::max(1, (M + 31) / 32);
     double lo[3], hi[3];
     world_extent(aabbs, lo, hi);
-    for (int a = 0; a < 3; ++a) {
-        make_axis(lo[a], hi[a], out.nb, out.bins.lo[a], out.bins.inv[a]);
-        out.bins.n[a] = out.nb;
-    }
+    for (int a = 0; a < 3; ++a)
+        make_key_axis(lo[a], hi[a], std::max(2, bins_per_axis), out.bins.off[a], out.bins.h0[a], out.bins.shift[a],
+                      out.bins.n[a]);
+    out.nb = out.bins.n[0]; // the same power of two + 1 on every axis
     const size_t words = static_cast<size_t>(3) * out.nb * out.W;
     out.inside.assign(words, 0u);
     out.min_le.assign(words, 0u);
     out.max_ge.assign(words, 0u);
     for (int k = 0; k < M; ++k)
         for (int a = 0; a < 3; ++a) {
-            const int b0 = host_bin(aabbs[k].mn[a], out.bins.lo[a], out.bins.inv[a], out.nb);
-            const int b1 = host_bin(aabbs[k].mx[a], out.bins.lo[a], out.bins.inv[a], out.nb);
+            const int b0 = host_key_bin(aabbs[k].mn[a], out.bins.off[a], out.bins.h0[a], out.bins.shift[a], out.nb);
+            const int b1 = host_key_bin(aabbs[k].mx[a], out.bins.off[a], out.bins.h0[a], out.bins.shift[a], out.nb);
             const uint32_t bit = 1u << (k & 31);
             const size_t w = static_cast<size_t>(k >> 5);
             for (int b = 0; b < out.nb; ++b) {

@@ -48,11 +48,24 @@ struct AxisBins {
 
 int host_bin(double x, double lo, double inv, int n);
 
+// Binning of the per-axis bitmask tables (EPP_BP_BITS): one rounded add moves the world's extent into a
+// single binade [2^e, 2^(e+1)), where the high word of the double grows linearly with x; the bin is that
+// word's offset from the binade's start, shifted down and clamped to [0, n-1].  Integer work after one
+// FP64 add, monotone in x for every double (negative sums and NaNs clamp), identical on host and device.
+struct KeyBins {
+    double off[3];  // t = x + off
+    int32_t h0[3];  // high word of 2^e
+    int32_t shift[3];
+    int32_t n[3];   // rows per axis = inner bins (a power of two) + 1 row beyond the binade
+};
+
+int host_key_bin(double x, double off, int32_t h0, int32_t shift, int32_t n);
+
 // Per-axis bin bitmasks (EPP_BP_BITS).  Word w of bin b of axis a at [(a * nb + b) * W + w].
 struct BitsTables {
     int nb = 0; // bins per axis
     int W = 0;  // 32-bit words per bin = ceil(M / 32)
-    AxisBins bins{};
+    KeyBins bins{};
     std::vector<uint32_t> inside; // k set iff bin(min_k) <= b <= bin(max_k)
     std::vector<uint32_t> min_le; // k set iff bin(min_k) <= b
     std::vector<uint32_t> max_ge; // k set iff bin(max_k) >= b

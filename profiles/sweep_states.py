@@ -33,7 +33,8 @@ def main():
     torch.cuda.synchronize()
     # (variant, stages, blocks/SM, states per thread)
     settings = [(1, 0, b, 0) for b in (4, 8)]
-    settings += [(2, st, b, spt) for spt in (2, 4) for st in (2, 3) for b in (2, 3, 4, 5, 6)]
+    settings += [(2, st, b, spt) for spt in (2, 4) for st in (2, 3) for b in (3, 5)]
+    settings += [(3, st, b, spt) for spt in (4, 8) for st in (1, 2, 3) for b in (1, 2, 3, 4, 5, 6)]
     print("workload %s batch %d ring %d world_obbs %d bp %s" % (workload, batch, ring_n, w.size(),
                                                               epp_b200.BP_NAMES[w.active_broadphase()]))
     for variant, stages, bps, spt in settings:
@@ -43,6 +44,7 @@ def main():
         else:
             epp_b200.set_tuning("states_stages", stages)
             epp_b200.set_tuning("states_stream_blocks_per_sm", bps)
+            epp_b200.set_tuning("states_warp_blocks_per_sm", bps)
             epp_b200.set_tuning("states_per_thread", spt)
         try:
             for x in ring[:3]:

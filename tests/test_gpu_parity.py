@@ -334,9 +334,13 @@ def test_states_streaming_form_equals_direct_form(oracle, config, bp):
     g, o, lo, hi = worlds.world_256()
     ow, gw = build_pair(oracle, epp_b200, config, g, o, bp)
     keys = ("states_variant", "states_stages", "states_stream_blocks_per_sm", "states_per_thread",
-            "states_queue_pairs")
+            "states_queue_pairs", "states_warp_blocks_per_sm", "states_rec_smem")
     saved = {k: epp_b200.get_tuning(k) for k in keys}
-    settings = [(1, 2, 4, 0, 0), (2, 2, 1, 2, 0), (2, 3, 4, 4, 0), (2, 8, 2, 2, 64), (2, 2, 4, 4, 1), (0, 2, 4, 0, 0)]
+    settings = [(1, 2, 4, 0, 0, 3, 1), (2, 2, 1, 2, 0, 3, 1), (2, 3, 4, 4, 0, 3, 1), (2, 8, 2, 2, 64, 3, 1),
+                (2, 2, 4, 4, 1, 3, 1), (0, 2, 4, 0, 0, 3, 1),
+                # warp-pipelined form: ring depth 1..4, 2 / 4 states per lane, tiny queue (overflow path),
+                # one block per SM (many steps per warp), records from global memory
+                (3, 2, 4, 4, 0, 3, 1), (3, 1, 4, 8, 0, 1, 1), (3, 4, 4, 8, 4, 2, 0), (3, 3, 4, 4, 8, 6, 1)]
     try:
         for n in (1, 511, 512, 513, 1024, 1025, 8192 + 511, 100003, 1 << 19):
             buf = torch.empty(3 * n + 1, dtype=torch.float64, device="cuda")
@@ -354,8 +358,50 @@ def test_states_streaming_form_equals_direct_form(oracle, config, bp):
             # same states at an address that is only 8 B aligned
             shifted = buf[1:].view(n, 3)
             shifted.copy_(d_xyz.clone())
-            epp_b200.set_tuning("states_variant", 2)
-            assert np.array_equal(gw.check_states_dev(shifted).cpu().numpy().view(np.uint32), want), n
+            for variant in (2, 3):
+                epp_b200.set_tuning("states_variant", variant)
+                assert np.array_equal(gw.check_states_dev(shifted).cpu().numpy().view(np.uint32), want), (n, variant)
+    finally:
+        for k, v in saved.items():
+            epp_b200.set_tuning(k, v)
+
+
+@pytest.mark.parametrize("bp", BPS, ids=BP_IDS)
+def test_states_warp_form_small_world_records_in_smem(oracle, config, track, bp):
+    """The warp-pipelined K1 folds canPassGate / minDistance / filling rules into per-OBB records in
+    shared memory for worlds of <= 64 OBBs.  Track + filling boxes (M=28), every call flavour, sizes
+    around the word / step boundaries, odd sizes (lane-loaded last chunk) and an 8 B-aligned batch."""
+    import torch
+    g, o, lo, hi = track
+    cfg = filling_config(config)
+    ow, gw = build_pair(oracle, epp_b200, cfg, g, o, bp)
+    keys = ("states_variant", "states_stages", "states_per_thread", "states_queue_pairs",
+            "states_warp_blocks_per_sm", "states_rec_smem")
+    saved = {k: epp_b200.get_tuning(k) for k in keys}
+    adv = adversarial_points(ow.obbs(), np.random.default_rng(8), per_face=2)
+    try:
+        for n in (1, 2, 31, 33, 127, 128, 129, 4095, 20001, 1 << 17):
+            h_xyz = np.array(oracle.gen_states(21, 3 * n, n, lo, hi))
+            if n > len(adv):
+                h_xyz[-len(adv):] = adv  # face-adjacent points at the end (covers the ragged last chunk)
+            buf = torch.empty(3 * n + 1, dtype=torch.float64, device="cuda")
+            d_xyz = buf[: 3 * n].view(n, 3)
+            d_xyz.copy_(torch.from_numpy(h_xyz))
+            shifted = buf[1:].view(n, 3)
+            want = {("b", c): ow.check_states(h_xyz, c, threads=8) for c in (False, True)}
+            want.update({("m", md): ow.check_states_mindist(h_xyz, md, threads=8) for md in (0.05, 0.3)})
+            for setting in [(3, 2, 4, 0, 3, 1), (3, 3, 8, 4, 1, 1), (3, 1, 8, 0, 8, 0)]:
+                for k, v in zip(keys, setting):
+                    epp_b200.set_tuning(k, v)
+                for src in (d_xyz, None):
+                    if src is None:
+                        shifted.copy_(d_xyz.clone())
+                        src = shifted
+                    for (kind, arg), w in want.items():
+                        got = gw.check_states_dev(src, can_pass_gate=arg) if kind == "b" else \
+                            gw.check_states_dev(src, min_distance=arg)
+                        assert np.array_equal(got.cpu().numpy().view(np.uint32), w), (n, setting, kind, arg)
+                    d_xyz.copy_(torch.from_numpy(h_xyz))
     finally:
         for k, v in saved.items():
             epp_b200.set_tuning(k, v)
