@@ -17,7 +17,7 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libepp_b200.so")
+LIB_PATH = os.environ.get("EPP_B200_LIB") or os.path.join(_HERE, "libepp_b200.so")  # override: profiling builds
 DEFAULT_CONFIG = os.path.join(_HERE, "config", "config.json")
 
 BP_AUTO, BP_BRUTE, BP_BITS, BP_GRID = 0, 1, 2, 3

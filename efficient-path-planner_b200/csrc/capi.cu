@@ -42,24 +42,37 @@ int cuda_fail(cudaError_t e, const char *what)
         if (e__ != cudaSuccess) return cuda_fail(e__, #call);  \
     } while (0)
 
-// Tuning knobs (epp_set_tuning).
-struct Tuning {
-    std::atomic<int> states_blocks_per_sm{8};
-    std::atomic<int> segments_blocks_per_sm{4};
-    std::atomic<int> states_variant{0};
-    std::atomic<int> states_stages{2};
-    std::atomic<int> states_stream_blocks_per_sm{5};
-    std::atomic<int> states_per_thread{0};
-    std::atomic<int> states_queue_pairs{0};
-    std::atomic<int> states_warp_blocks_per_sm{3};
-    std::atomic<int> states_warp_min_n{4096};
-    std::atomic<int> states_rec_smem{1};
-    std::atomic<int> states_debug{0};
-    std::atomic<int> states_bits1{1};
-    std::atomic<int> bits_bins{0};          // 0: by world size
-    std::atomic<int> grid_max_cells{1 << 22};
-    std::atomic<int> bits_max_obbs{1024};
-} g_tuning;
+// Tuning knobs (epp_set_tuning / epp_get_tuning): one table, looked up by name.
+struct Knob {
+    const char *name;
+    std::atomic<int> value;
+};
+Knob g_knobs[] = {
+    {"states_blocks_per_sm", {8}},       // direct form of K1: persistent blocks per SM
+    {"segments_blocks_per_sm", {4}},
+    {"states_variant", {0}},             // 0: auto, 1: direct, 3: warp-pipelined
+    {"states_per_thread", {0}},          // warp form: mask words per chunk (4 default, 8)
+    {"states_warp_blocks_per_sm", {1}},
+    {"states_warp_threads", {1024}},
+    {"states_warp_log2_slots", {0}},
+    {"states_warp_min_n", {4096}},
+    {"states_rec_smem", {1}},
+    {"states_bits1", {1}},
+    {"states_pdl", {1}},
+    {"states_debug", {0}},               // profiling builds only
+    {"bits_bins", {0}},                  // 0: by world size
+    {"grid_max_cells", {1 << 22}},
+    {"bits_max_obbs", {1024}},
+};
+
+std::atomic<int> *knob(const char *name)
+{
+    for (Knob &k : g_knobs)
+        if (std::strcmp(k.name, name) == 0) return &k.value;
+    return nullptr;
+}
+
+int knob_value(const char *name) { return knob(name)->load(); }
 
 // One immutable committed world on one device.
 struct DeviceEpoch {
@@ -217,18 +230,18 @@ LaunchCfg launch_cfg(const DeviceEpoch &ep)
 {
     LaunchCfg c;
     c.sm_count = ep.sm_count;
-    c.states_blocks_per_sm = g_tuning.states_blocks_per_sm.load();
-    c.segments_blocks_per_sm = g_tuning.segments_blocks_per_sm.load();
-    c.states_variant = g_tuning.states_variant.load();
-    c.states_stages = g_tuning.states_stages.load();
-    c.states_stream_blocks_per_sm = g_tuning.states_stream_blocks_per_sm.load();
-    c.states_per_thread = g_tuning.states_per_thread.load();
-    c.states_queue_pairs = g_tuning.states_queue_pairs.load();
-    c.states_warp_blocks_per_sm = g_tuning.states_warp_blocks_per_sm.load();
-    c.states_warp_min_n = g_tuning.states_warp_min_n.load();
-    c.states_rec_smem = g_tuning.states_rec_smem.load();
-    c.states_debug = g_tuning.states_debug.load();
-    c.states_bits1 = g_tuning.states_bits1.load();
+    c.states_blocks_per_sm = knob_value("states_blocks_per_sm");
+    c.segments_blocks_per_sm = knob_value("segments_blocks_per_sm");
+    c.states_variant = knob_value("states_variant");
+    c.states_per_thread = knob_value("states_per_thread");
+    c.states_warp_blocks_per_sm = knob_value("states_warp_blocks_per_sm");
+    c.states_warp_threads = knob_value("states_warp_threads");
+    c.states_warp_log2_slots = knob_value("states_warp_log2_slots");
+    c.states_warp_min_n = knob_value("states_warp_min_n");
+    c.states_rec_smem = knob_value("states_rec_smem");
+    c.states_bits1 = knob_value("states_bits1");
+    c.states_pdl = knob_value("states_pdl");
+    c.states_debug = knob_value("states_debug");
     return c;
 }
 
@@ -359,46 +372,18 @@ extern "C" uint64_t epp_kernel_launch_count(void) { return g_launches.load(); }
 extern "C" int epp_set_tuning(const char *key, int value)
 {
     if (!key) return fail(EPP_ERR_INVALID_ARG);
-    const std::string k(key);
-    if (k == "states_blocks_per_sm") g_tuning.states_blocks_per_sm = value;
-    else if (k == "segments_blocks_per_sm") g_tuning.segments_blocks_per_sm = value;
-    else if (k == "states_variant") g_tuning.states_variant = value;
-    else if (k == "states_stages") g_tuning.states_stages = value;
-    else if (k == "states_stream_blocks_per_sm") g_tuning.states_stream_blocks_per_sm = value;
-    else if (k == "states_per_thread") g_tuning.states_per_thread = value;
-    else if (k == "states_queue_pairs") g_tuning.states_queue_pairs = value;
-    else if (k == "states_warp_blocks_per_sm") g_tuning.states_warp_blocks_per_sm = value;
-    else if (k == "states_warp_min_n") g_tuning.states_warp_min_n = value;
-    else if (k == "states_rec_smem") g_tuning.states_rec_smem = value;
-    else if (k == "states_debug") g_tuning.states_debug = value;
-    else if (k == "states_bits1") g_tuning.states_bits1 = value;
-    else if (k == "bits_bins") g_tuning.bits_bins = value;
-    else if (k == "grid_max_cells") g_tuning.grid_max_cells = value;
-    else if (k == "bits_max_obbs") g_tuning.bits_max_obbs = value;
-    else return fail(EPP_ERR_INVALID_ARG, "unknown tuning key " + k);
+    std::atomic<int> *k = knob(key);
+    if (!k) return fail(EPP_ERR_INVALID_ARG, std::string("unknown tuning key ") + key);
+    k->store(value);
     return EPP_OK;
 }
 
 extern "C" int epp_get_tuning(const char *key, int *value)
 {
     if (!key || !value) return fail(EPP_ERR_INVALID_ARG);
-    const std::string k(key);
-    if (k == "states_blocks_per_sm") *value = g_tuning.states_blocks_per_sm;
-    else if (k == "segments_blocks_per_sm") *value = g_tuning.segments_blocks_per_sm;
-    else if (k == "states_variant") *value = g_tuning.states_variant;
-    else if (k == "states_stages") *value = g_tuning.states_stages;
-    else if (k == "states_stream_blocks_per_sm") *value = g_tuning.states_stream_blocks_per_sm;
-    else if (k == "states_per_thread") *value = g_tuning.states_per_thread;
-    else if (k == "states_queue_pairs") *value = g_tuning.states_queue_pairs;
-    else if (k == "states_warp_blocks_per_sm") *value = g_tuning.states_warp_blocks_per_sm;
-    else if (k == "states_warp_min_n") *value = g_tuning.states_warp_min_n;
-    else if (k == "states_rec_smem") *value = g_tuning.states_rec_smem;
-    else if (k == "states_debug") *value = g_tuning.states_debug;
-    else if (k == "states_bits1") *value = g_tuning.states_bits1;
-    else if (k == "bits_bins") *value = g_tuning.bits_bins;
-    else if (k == "grid_max_cells") *value = g_tuning.grid_max_cells;
-    else if (k == "bits_max_obbs") *value = g_tuning.bits_max_obbs;
-    else return fail(EPP_ERR_INVALID_ARG, "unknown tuning key " + k);
+    std::atomic<int> *k = knob(key);
+    if (!k) return fail(EPP_ERR_INVALID_ARG, std::string("unknown tuning key ") + key);
+    *value = k->load();
     return EPP_OK;
 }
 
@@ -507,19 +492,19 @@ extern "C" int epp_world_commit(epp_world *w)
     const int M = (int)aabbs.size();
 
     int bp = w->bp_request;
-    const int bits_max = g_tuning.bits_max_obbs.load();
+    const int bits_max = knob_value("bits_max_obbs");
     if (bp == EPP_BP_AUTO) bp = (M <= bits_max) ? EPP_BP_BITS : EPP_BP_GRID;
     if (bp == EPP_BP_BITS && M > 4096) return fail(EPP_ERR_INVALID_ARG, "EPP_BP_BITS supports at most 4096 OBBs");
 
     BitsTables bits;
     GridTables grid;
     if (bp == EPP_BP_BITS) {
-        int nb = g_tuning.bits_bins.load();
+        int nb = knob_value("bits_bins");
         const int W = std::max(1, (M + 31) / 32);
         if (nb <= 0) nb = W == 1 ? 256 : (W <= 8 ? 128 : (W <= 32 ? 64 : 32));
         build_bits(aabbs, nb, bits);
     }
-    if (bp == EPP_BP_GRID) build_grid(aabbs, obbs, g_tuning.grid_max_cells.load(), grid);
+    if (bp == EPP_BP_GRID) build_grid(aabbs, obbs, knob_value("grid_max_cells"), grid);
 
     // One blob: [aabb][obb][bits inside|min_le|max_ge][cell_start][cell_items], 256 B aligned parts.
     struct Part {

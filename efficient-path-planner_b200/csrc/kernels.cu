@@ -1,6 +1,6 @@
 // kernels.cu — sm_100a kernels of the validity-check hot path and their launchers.
 //
-// K1  k_states        World::checkPointValidity (both overloads) over an n x 3 AoS batch
+// K1  k_states_warp   World::checkPointValidity (both overloads) over an n x 3 AoS batch (k_states: small batches)
 // K2  k_segments      World::checkRayValid over two n x 3 AoS batches
 // K3a k_traj_samples  PathPlanner::checkTrajectoryValidity over column-major matrices
 // K3b k_poly_traj     evaluateRange + Horner + checkTrajectoryValidity fused
@@ -23,7 +23,7 @@ namespace epp {
 namespace {
 
 constexpr int kBlock = 256;
-constexpr int kWarpsPerBlock = kBlock / 32;
+constexpr int kWarpsPerBlock = kBlock / 32; // direct kernels
 
 extern __shared__ __align__(16) unsigned char g_smem[];
 
@@ -400,283 +400,6 @@ __device__ __forceinline__ void bulk_g2s(void *dst, const void *src, uint32_t by
                  : "memory");
 }
 
-constexpr int kMaxStages = 8;
-
-// ---- K1 (streaming form): TMA bulk-copy ring + block-wide candidate compaction -----------------------
-//
-// Persistent blocks; tile = S * kBlock consecutive states = one contiguous span of the AoS batch that
-// thread 0 fetches with cp.async.bulk into a ring of `stages` shared-memory slots.
-//
-// The direct kernel above lets every lane walk its own candidate list, so a warp pays the full exact test
-// whenever ANY lane has a candidate, at ~50 % lane utilisation and with one dependent chain per warp.
-// Here a tile is handled in two dense phases:
-//   phase 1  every thread locates the candidates of its S states (independent chains -> ILP) and appends
-//            (state, OBB) pairs to a block-wide queue; one shared-memory atomic per warp reserves the space;
-//   phase 2  the block walks the queue with all lanes busy, running the reference's exact per-candidate
-//            test (strict stored-AABB test, type rule, OBB test) and OR-ing hits into an invalid bitmap.
-// The verdict of a state is an OR over its candidates, so neither the order of the queue nor the loss of the
-// early exit changes a single bit.  Pairs that do not fit the queue are tested in place by their lane.
-constexpr uint32_t kPairSentinel = 0xffffffffu;
-constexpr int kPairUnitShift = 22; // pair = unit << 22 | obb index (M < 2^22)
-
-template <int BP>
-struct PointCand;
-template <>
-struct PointCand<EPP_BP_BRUTE> {};
-template <>
-struct PointCand<EPP_BP_BITS> {
-    int ox, oy, oz; // row offsets (in words) of the three bin rows
-    uint32_t m;     // W == 1: the candidate word itself
-};
-template <>
-struct PointCand<EPP_BP_GRID> {
-    uint32_t s, e;
-};
-
-template <int BP>
-struct PointEnum;
-
-template <>
-struct PointEnum<EPP_BP_BRUTE> {
-    __device__ __forceinline__ static int locate(const PointWorld<EPP_BP_BRUTE> &w, const WorldView &wv, const P3 &p,
-                                                 PointCand<EPP_BP_BRUTE> &)
-    {
-        int c = 0;
-        for (int k = 0; k < wv.M; ++k) c += within_strict(w.aabb + k, p) ? 1 : 0;
-        return c;
-    }
-    template <class F>
-    __device__ __forceinline__ static void each(const PointWorld<EPP_BP_BRUTE> &w, const WorldView &wv, const P3 &p,
-                                                const PointCand<EPP_BP_BRUTE> &, F f)
-    {
-        for (int k = 0; k < wv.M; ++k)
-            if (within_strict(w.aabb + k, p)) f(k);
-    }
-};
-
-template <>
-struct PointEnum<EPP_BP_BITS> {
-    __device__ __forceinline__ static int locate(const PointWorld<EPP_BP_BITS> &w, const WorldView &wv, const P3 &p,
-                                                 PointCand<EPP_BP_BITS> &c)
-    {
-        const int nb = wv.nb, W = wv.W;
-        const int bx = dev_key_bin(p.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb);
-        const int by = nb + dev_key_bin(p.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb);
-        const int bz = 2 * nb + dev_key_bin(p.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb);
-        if (W == 1) { // worlds of up to 32 OBBs (the race track): one word per bin, no loops
-            c.m = w.inside[bx] & w.inside[by] & w.inside[bz];
-            return __popc(c.m);
-        }
-        c.ox = bx * W;
-        c.oy = by * W;
-        c.oz = bz * W;
-        int n = 0;
-        for (int i = 0; i < W; ++i) n += __popc(w.inside[c.ox + i] & w.inside[c.oy + i] & w.inside[c.oz + i]);
-        return n;
-    }
-    template <class F>
-    __device__ __forceinline__ static void each(const PointWorld<EPP_BP_BITS> &w, const WorldView &wv, const P3 &,
-                                                const PointCand<EPP_BP_BITS> &c, F f)
-    {
-        if (wv.W == 1) {
-            uint32_t m = c.m;
-            while (m) {
-                f(__ffs(m) - 1);
-                m &= m - 1;
-            }
-            return;
-        }
-        for (int i = 0; i < wv.W; ++i) {
-            uint32_t m = w.inside[c.ox + i] & w.inside[c.oy + i] & w.inside[c.oz + i];
-            while (m) {
-                f((i << 5) + __ffs(m) - 1);
-                m &= m - 1;
-            }
-        }
-    }
-};
-
-template <>
-struct PointEnum<EPP_BP_GRID> {
-    __device__ __forceinline__ static int locate(const PointWorld<EPP_BP_GRID> &, const WorldView &wv, const P3 &p,
-                                                 PointCand<EPP_BP_GRID> &c)
-    {
-        const int bx = dev_bin(p.x, wv.gbins.lo[0], wv.gbins.inv[0], wv.gbins.n[0]);
-        const int by = dev_bin(p.y, wv.gbins.lo[1], wv.gbins.inv[1], wv.gbins.n[1]);
-        const int bz = dev_bin(p.z, wv.gbins.lo[2], wv.gbins.inv[2], wv.gbins.n[2]);
-        const size_t cell = ((size_t)bz * wv.gbins.n[1] + by) * wv.gbins.n[0] + bx;
-        c.s = __ldg(wv.cell_start + cell);
-        c.e = __ldg(wv.cell_start + cell + 1);
-        return (int)(c.e - c.s);
-    }
-    template <class F>
-    __device__ __forceinline__ static void each(const PointWorld<EPP_BP_GRID> &, const WorldView &wv, const P3 &,
-                                                const PointCand<EPP_BP_GRID> &c, F f)
-    {
-        for (uint32_t j = c.s; j < c.e; ++j) f((int)__ldg(wv.cell_items + j));
-    }
-};
-
-// Shared-memory bookkeeping of the compaction, double buffered by tile parity.
-template <int UNITS>
-struct PairState {
-    int count[2];
-    uint32_t inv[2][UNITS / 32];
-};
-
-// One tile: `units` (<= S*kBlock) states at `pts` (AoS doubles in shared memory).  Ends with the block's
-// mask words written; contains two __syncthreads.  buf alternates 0/1 per call.
-template <int BP, int S>
-__device__ __forceinline__ void states_tile(const PointWorld<BP> &world, const WorldView &wv, const double *pts,
-                                            int units, int mode, bool cpg, double md, uint32_t *queue, int qcap,
-                                            PairState<S * kBlock> &ps, int buf, uint32_t *__restrict__ mask_out)
-{
-    // ---- phase 1
-    P3 p[S];
-    PointCand<BP> cand[S];
-    int cnt[S];
-    int total = 0;
-#pragma unroll
-    for (int u = 0; u < S; ++u) {
-        const int unit = u * kBlock + threadIdx.x;
-        cnt[u] = 0;
-        if (unit < units) {
-            p[u].x = pts[3 * unit];
-            p[u].y = pts[3 * unit + 1];
-            p[u].z = pts[3 * unit + 2];
-            cnt[u] = PointEnum<BP>::locate(world, wv, p[u], cand[u]);
-        }
-        total += cnt[u];
-    }
-    if (total != 0) {
-        // one shared-memory atomic per lane that has candidates (a minority of lanes in sparse worlds)
-        int base = atomicAdd(&ps.count[buf], total);
-        if (base + total <= qcap) {
-#pragma unroll
-            for (int u = 0; u < S; ++u) {
-                if (cnt[u] == 0) continue;
-                const uint32_t tag = (uint32_t)(u * kBlock + threadIdx.x) << kPairUnitShift;
-                PointEnum<BP>::each(world, wv, p[u], cand[u], [&](int k) { queue[base++] = tag | (uint32_t)k; });
-            }
-        } else { // queue full: blank my reserved slots and test in place
-            for (int j = base; j < qcap && j < base + total; ++j) queue[j] = kPairSentinel;
-#pragma unroll
-            for (int u = 0; u < S; ++u) {
-                if (cnt[u] == 0) continue;
-                bool hit = false;
-                PointEnum<BP>::each(world, wv, p[u], cand[u], [&](int k) {
-                    hit = hit || point_candidate_invalid(wv.aabb, wv.obb, k, p[u], mode, cpg, md);
-                });
-                const int unit = u * kBlock + threadIdx.x;
-                if (hit) atomicOr(&ps.inv[buf][unit >> 5], 1u << (unit & 31));
-            }
-        }
-    }
-    __syncthreads();
-    // ---- phase 2
-    const int pairs = ps.count[buf] < qcap ? ps.count[buf] : qcap;
-    for (int q = threadIdx.x; q < pairs; q += kBlock) {
-        const uint32_t pr = queue[q];
-        if (pr == kPairSentinel) continue;
-        const int unit = (int)(pr >> kPairUnitShift);
-        const int k = (int)(pr & ((1u << kPairUnitShift) - 1u));
-        const P3 q3 = {pts[3 * unit], pts[3 * unit + 1], pts[3 * unit + 2]};
-        if (point_candidate_invalid(wv.aabb, wv.obb, k, q3, mode, cpg, md))
-            atomicOr(&ps.inv[buf][unit >> 5], 1u << (unit & 31));
-    }
-    __syncthreads();
-    // ---- verdicts: bit = valid; bits of units beyond `units` stay 0
-    if (threadIdx.x < (units + 31) / 32) {
-        const int w = threadIdx.x;
-        const int live = units - 32 * w;
-        const uint32_t active = live >= 32 ? 0xffffffffu : ((1u << live) - 1u);
-        mask_out[w] = ~ps.inv[buf][w] & active;
-        ps.inv[buf][w] = 0u;
-    }
-    if (threadIdx.x == 0) ps.count[buf] = 0;
-}
-
-template <int BP, int S>
-__global__ void __launch_bounds__(kBlock) k_states_stream(WorldView wv, const double *__restrict__ xyz, size_t n, int mode,
-                                                          int can_pass_gate, double min_distance, int aabb_in_smem,
-                                                          int stages, uint32_t table_bytes, int qcap,
-                                                          uint32_t *__restrict__ mask)
-{
-    constexpr int kTile = S * kBlock;
-    constexpr uint32_t kTileBytes = kTile * 3 * sizeof(double);
-    __shared__ __align__(8) uint64_t s_full[kMaxStages];
-    __shared__ __align__(8) uint64_t s_table;
-    __shared__ PairState<kTile> s_ps;
-    unsigned char *ring = g_smem + table_bytes; // table_bytes is a multiple of 128
-    uint32_t *queue = reinterpret_cast<uint32_t *>(ring + (size_t)stages * kTileBytes);
-    const size_t full_tiles = n / kTile;
-    const size_t first = blockIdx.x;
-
-    if (threadIdx.x == 0) {
-        for (int s = 0; s < stages; ++s) mbar_init(&s_full[s], 1);
-        mbar_init(&s_table, 1);
-        mbar_init_fence();
-        // broad-phase table first (needed by every tile), then the first `stages` tiles
-        const void *tsrc;
-        const uint32_t tbytes = (PointWorld<BP>::table(wv, aabb_in_smem != 0, tsrc) + 15u) & ~15u; // blob parts are padded
-        if (tbytes) {
-            mbar_expect_tx(&s_table, tbytes);
-            bulk_g2s(g_smem, tsrc, tbytes, &s_table);
-        }
-        for (int s = 0; s < stages; ++s) {
-            const size_t tile = first + (size_t)s * gridDim.x;
-            if (tile < full_tiles) {
-                mbar_expect_tx(&s_full[s], kTileBytes);
-                bulk_g2s(ring + (size_t)s * kTileBytes, xyz + tile * (size_t)(3 * kTile), kTileBytes, &s_full[s]);
-            }
-        }
-        s_ps.count[0] = s_ps.count[1] = 0;
-    }
-    if (threadIdx.x < kTile / 32) s_ps.inv[0][threadIdx.x] = s_ps.inv[1][threadIdx.x] = 0u;
-    PointWorld<BP> world;
-    world.bind(wv, aabb_in_smem != 0);
-    __syncthreads(); // publishes the barriers and the zeroed bookkeeping
-    {
-        const void *tsrc;
-        if (PointWorld<BP>::table(wv, aabb_in_smem != 0, tsrc)) mbar_wait(&s_table, 0);
-    }
-
-    const bool cpg = can_pass_gate != 0;
-    int s = 0, buf = 0;
-    uint32_t parity = 0;
-    for (size_t tile = first; tile < full_tiles; tile += gridDim.x) {
-        mbar_wait(&s_full[s], parity);
-        const double *pts = reinterpret_cast<const double *>(ring + (size_t)s * kTileBytes);
-        states_tile<BP, S>(world, wv, pts, kTile, mode, cpg, min_distance, queue, qcap, s_ps, buf,
-                           mask + tile * (kTile / 32));
-        // every read of the slot happened before the second barrier inside states_tile
-        if (threadIdx.x == 0) {
-            const size_t nxt = tile + (size_t)stages * gridDim.x;
-            if (nxt < full_tiles) {
-                mbar_expect_tx(&s_full[s], kTileBytes);
-                bulk_g2s(ring + (size_t)s * kTileBytes, xyz + nxt * (size_t)(3 * kTile), kTileBytes, &s_full[s]);
-            }
-        }
-        buf ^= 1;
-        if (++s == stages) {
-            s = 0;
-            parity ^= 1u;
-        }
-    }
-
-    // ragged tail (n % kTile states): plain loads into slot 0, same tile routine
-    const size_t tail0 = full_tiles * kTile;
-    if (tail0 < n && blockIdx.x == (unsigned)(full_tiles % gridDim.x)) {
-        const int rem = (int)(n - tail0);
-        double *slot = reinterpret_cast<double *>(ring);
-        __syncthreads(); // phase 2 of another warp may still read slot 0 only before the barriers above; be explicit
-        for (int e = threadIdx.x; e < 3 * rem; e += kBlock) slot[e] = __ldg(xyz + 3 * tail0 + e);
-        __syncthreads();
-        states_tile<BP, S>(world, wv, slot, rem, mode, cpg, min_distance, queue, qcap, s_ps, buf,
-                           mask + tail0 / 32);
-    }
-}
-
 // ---- K1 (warp-pipelined form): every warp streams its own contiguous range of states -----------------
 //
 // No block-wide barrier after the prologue.  Warp j of the grid owns a contiguous run of mask words and walks
@@ -699,6 +422,22 @@ __global__ void __launch_bounds__(kBlock) k_states_stream(WorldView wv, const do
 // reference's 3-term sums are (a + b) + (+-0) and (+-0 + +-0) + d2: dropping the zero terms changes at most
 // the sign of a zero, which fabs() and the comparisons cannot see.  The point is finite whenever the result
 // matters because it passed the strict stored-AABB test.
+#ifdef EPP_TRACE
+// Profiling build only (make trace): per-warp timeline of the warp form, 16 globaltimer stamps per warp.
+__device__ unsigned long long g_trace[1 << 20];
+__device__ uint32_t g_trace_base; // 0 or 1 << 19: which half of g_trace the running launch writes
+__device__ __forceinline__ void trace(uint32_t g, int ev)
+{
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+    if ((threadIdx.x & 31) == 0 && ev < 16 && g * 16 + ev < (1u << 19)) g_trace[g_trace_base + g * 16 + ev] = t;
+}
+__global__ void k_trace_base(uint32_t base) { g_trace_base = base; }
+#define EPP_TRACE_EV(g, ev) trace(g, ev)
+#else
+#define EPP_TRACE_EV(g, ev)
+#endif
+
 constexpr int kRecDoubles = 17;
 constexpr int kRecSmemMax = 64;
 constexpr int kWordBytes = 32 * 3 * 8; // one mask word of states = 768 B of coordinates
@@ -721,7 +460,11 @@ __device__ __forceinline__ void warp_states_step(const PointWorld<BP> &world, co
     // ---- phase 1: which of my S states have a broad-phase candidate at all
     const uint32_t lt = (1u << lane) - 1u;
     int queued = 0;
-    const int dbg = mode >> 8; // profiling only (epp_set_tuning states_debug): 1 skips phase 2, 2 also phase 1
+#ifdef EPP_TRACE
+    const int dbg = mode >> 8; // profiling build only (epp_set_tuning states_debug): 1 skips phase 2, 2 also phase 1
+#else
+    constexpr int dbg = 0;
+#endif
     mode &= 0xff;
 #pragma unroll
     for (int u = 0; u < S; ++u) {
@@ -759,117 +502,208 @@ __device__ __forceinline__ void warp_states_step(const PointWorld<BP> &world, co
     __syncwarp();
 }
 
-// Warp g (of gridDim.x * kWarpsPerBlock) owns words [g*wpw + min(g, rem), +wpw + (g < rem)); the host passes
-// wpw = words / warps and rem = words % warps so no thread divides.
-template <int BP, int S, bool RS>
-__global__ void __launch_bounds__(kBlock) k_states_warp(WorldView wv, const double *__restrict__ xyz, size_t n, int mode,
-                                                        int can_pass_gate, double min_distance, int aabb_in_smem,
-                                                        int stages, uint32_t table_bytes, uint32_t rec_bytes,
-                                                        uint32_t wpw, uint32_t rem, uint32_t *__restrict__ mask)
+// Block = 1 producer warp + up to 31 consumer warps, one block per SM by default.  Block b owns words
+// [b*wpb + min(b, rem), +wpb + (b < rem)) (the host passes wpb = words / blocks and rem = words % blocks, so no
+// thread divides) and cuts them into chunks of S words.  Chunks flow through a block-wide ring of 2^log2_slots
+// shared-memory slots:
+//   producer   lane l issues chunks l, l+32, ... in order (cp.async.bulk, `full` barrier of the slot), waiting
+//              on the slot's `empty` barrier once the ring has wrapped;
+//   consumers  take the next chunk number from a shared counter, wait for its `full` barrier, run the two
+//              phases of warp_states_step on it, write its S mask words and release the slot.
+// Why a producer warp: an SM's share of HBM bandwidth is ~44 GB/s and its bulk-copy queue is shallow, so
+// cp.async.bulk BLOCKS at issue once ~100 KB are queued (measured: a warp that issues two chunks up front
+// stalls for microseconds before it can touch the first).  Why a shared counter: chunks arrive over several
+// microseconds in issue order; with static per-warp ranges the warps whose data comes last start last and
+// finish last while the others idle.  The broad-phase table and the records are requested before the first
+// coordinate so they are not queued behind the coordinates.
+constexpr int kMaxWarps = 32;
+constexpr int kMaxSlots = 64;
+
+__device__ __forceinline__ void mbar_arrive(uint64_t *bar)
 {
-    __shared__ __align__(8) uint64_t s_full[kWarpsPerBlock][kMaxStages];
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_addr(bar)) : "memory");
+}
+
+template <int BP, int S, bool RS>
+__global__ void __launch_bounds__(1024) k_states_warp(WorldView wv, const double *__restrict__ xyz, size_t n, int mode,
+                                                      int can_pass_gate, double min_distance, int aabb_in_smem,
+                                                      int log2_slots, uint32_t table_bytes, uint32_t rec_bytes,
+                                                      uint32_t wpb, uint32_t rem, uint32_t *__restrict__ mask)
+{
+    __shared__ __align__(8) uint64_t s_full[kMaxSlots];
+    __shared__ __align__(8) uint64_t s_empty[kMaxSlots];
     __shared__ __align__(8) uint64_t s_table;
+    __shared__ uint32_t s_next;
+    __shared__ uint32_t s_rounds_done[kMaxSlots]; // per slot: how many rounds of it have been consumed
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t consumers = (blockDim.x >> 5) - 1u;
     const bool cpg = can_pass_gate != 0;
     constexpr uint32_t kSlotBytes = S * kWordBytes;
-
-    // shared memory: [broad-phase table][records][per warp: ring | byte queue (S*32) | invalid words (32 B)]
+    const uint32_t slots = 1u << log2_slots, slot_mask = slots - 1u;
+    // shared memory: [broad-phase table][records][ring][per consumer: byte queue (S*32) | invalid words (32 B)]
     double *rec = reinterpret_cast<double *>(g_smem + table_bytes);
-    const uint32_t ring_bytes = (uint32_t)stages * kSlotBytes;
-    const uint32_t warp_bytes = ring_bytes + S * 32u + 32u;
-    unsigned char *mine = g_smem + table_bytes + rec_bytes + (uint32_t)warp * warp_bytes;
-    unsigned char *queue = mine + ring_bytes;
-    uint32_t *inv = reinterpret_cast<uint32_t *>(queue + S * 32);
+    unsigned char *ring = g_smem + table_bytes + rec_bytes;
+    unsigned char *areas = ring + slots * kSlotBytes;
+    EPP_TRACE_EV(blockIdx.x * consumers + (warp == 0 ? 0 : warp - 1), warp == 0 ? 13 : 14);
 
-    const uint32_t g = blockIdx.x * kWarpsPerBlock + warp;
-    const uint32_t w0 = g * wpw + (g < rem ? g : rem);
-    const uint32_t w1 = w0 + wpw + (g < rem ? 1u : 0u);
+    const uint32_t b0 = blockIdx.x * wpb + (blockIdx.x < rem ? blockIdx.x : rem);
+    const uint32_t b1 = b0 + wpb + (blockIdx.x < rem ? 1u : 0u);
+    const uint32_t chunks = (b1 - b0 + S - 1) / S;
     const uint32_t words_total = (uint32_t)((n + 31) / 32);
     const bool aligned = (reinterpret_cast<uintptr_t>(xyz) & 15u) == 0;
-    // states in the chunk that starts at word cw (< w1)
-    auto chunk_units = [&](uint32_t cw) -> int {
-        const uint32_t sw = (w1 - cw) < (uint32_t)S ? (w1 - cw) : (uint32_t)S;
+    // states in chunk i of this block
+    auto chunk_units = [&](uint32_t i) -> int {
+        const uint32_t cw = b0 + i * S;
+        const uint32_t sw = (b1 - cw) < (uint32_t)S ? (b1 - cw) : (uint32_t)S;
         int units = (int)(sw * 32u);
         if (cw + sw == words_total) units = (int)(n - (size_t)cw * 32u); // the batch's ragged last word
         return units;
     };
     // cp.async.bulk moves multiples of 16 B from 16 B-aligned addresses: an odd number of states (only
-    // possible in the last chunk of the batch) or an 8 B-aligned batch is loaded by the lanes instead.
-    auto issue = [&](uint32_t cw, int slot) {
-        const uint32_t bytes = (uint32_t)chunk_units(cw) * 24u;
-        mbar_expect_tx(&s_full[warp][slot], bytes);
-        bulk_g2s(mine + (uint32_t)slot * kSlotBytes, xyz + (size_t)cw * 96, bytes, &s_full[warp][slot]);
-    };
-    auto by_tma = [&](uint32_t cw) -> bool { return aligned && (chunk_units(cw) & 1) == 0; };
+    // possible in the last chunk of the batch) or an 8 B-aligned batch is loaded by the consumer's lanes.
+    auto by_tma = [&](int units) -> bool { return aligned && (units & 1) == 0; };
 
-    if (lane == 0) {
-        for (int s = 0; s < stages; ++s) mbar_init(&s_full[warp][s], 1);
-        if (warp == 0) mbar_init(&s_table, 1);
-        mbar_init_fence();
-        if (warp == 0) {
-            const void *tsrc;
-            const uint32_t tbytes = (PointWorld<BP>::table(wv, aabb_in_smem != 0, tsrc) + 15u) & ~15u;
-            if (tbytes) {
-                mbar_expect_tx(&s_table, tbytes);
-                bulk_g2s(g_smem, tsrc, tbytes, &s_table);
-            }
+    // thread 0 requests the table while threads 32.. initialise the ring's barriers (one slot each)
+    if (threadIdx.x >= 32) {
+        for (uint32_t s = threadIdx.x - 32; s < slots; s += blockDim.x - 32) {
+            mbar_init(&s_full[s], 1);
+            mbar_init(&s_empty[s], 1);
+            s_rounds_done[s] = 0u;
         }
-        uint32_t cw = w0;
-        for (int s = 0; s < stages && cw < w1; ++s, cw += S)
-            if (by_tma(cw)) issue(cw, s);
+        if (threadIdx.x - 32 < slots) mbar_init_fence();
     }
-    if (lane < 8) inv[lane] = 0u;
-    if (RS) {
-        for (int k = threadIdx.x; k < wv.M; k += kBlock) {
-            const AabbRec *a = wv.aabb + k;
-            const ObbRec *o = wv.obb + k;
-            double *r = rec + k * kRecDoubles;
-            for (int d = 0; d < 3; ++d) {
-                r[d] = a->mn[d];
-                r[3 + d] = a->mx[d];
-                r[6 + d] = o->center[d];
-            }
-            r[9] = o->rot[0];
-            r[10] = o->rot[1];
-            r[11] = o->rot[3];
-            r[12] = o->rot[4];
-            const bool filling = (o->flags & kFlagFilling) != 0;
-            const bool skip = (mode & 0xff) == kModeBool ? (filling && cpg) : filling; // src/World.cpp:92-95, :116-119
-            const double infl = (mode & 0xff) == kModeBool ? o->inflate : min_distance; // :97, :121
-            for (int d = 0; d < 3; ++d)
-                r[13 + d] = skip ? -1.0 : (filling ? o->half[d] : dadd(o->half[d], infl)); // src/OBB.cpp:67-72
-            r[16] = 0.0;
+    if (threadIdx.x == 0) {
+        s_next = 0u;
+        mbar_init(&s_table, 1);
+        mbar_init_fence();
+        const void *tsrc;
+        const uint32_t tbytes = (PointWorld<BP>::table(wv, aabb_in_smem != 0, tsrc) + 15u) & ~15u;
+        if (tbytes) {
+            mbar_expect_tx(&s_table, tbytes);
+            bulk_g2s(g_smem, tsrc, tbytes, &s_table);
         }
+    }
+    EPP_TRACE_EV(blockIdx.x * consumers + (warp == 0 ? 0 : warp - 1), warp == 0 ? 11 : 12);
+    // record fields into registers (threads 32 .. 32+M-1, i.e. consumer warps) before any coordinate is requested
+    double rv[kRecDoubles];
+    const int rk = (int)threadIdx.x - 32;
+    const bool have_rec = RS && rk >= 0 && rk < wv.M;
+    uint32_t rec_flags = 0u;
+    if (have_rec) {
+        const AabbRec *a = wv.aabb + rk;
+        const ObbRec *o = wv.obb + rk;
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+            rv[d] = __ldg(&a->mn[d]);
+            rv[3 + d] = __ldg(&a->mx[d]);
+            rv[6 + d] = __ldg(&o->center[d]);
+            rv[13 + d] = __ldg(&o->half[d]);
+        }
+        rv[9] = __ldg(&o->rot[0]);
+        rv[10] = __ldg(&o->rot[1]);
+        rv[11] = __ldg(&o->rot[3]);
+        rv[12] = __ldg(&o->rot[4]);
+        rv[16] = __ldg(&o->inflate);
+        rec_flags = __ldg(&o->flags);
+    }
+    __syncthreads(); // barriers initialised; the world's requests are ahead of every coordinate request
+    // Programmatic dependent launch: everything above touched only this block's shared memory and the
+    // immutable world epoch, so it may overlap the tail of the previous kernel in the stream; the batch and
+    // the mask may not.  (Without the launch attribute both instructions are no-ops.)
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+
+    if (warp == 0) {
+        // ---- producer
+        // Waves of min(32, slots) chunks: a slot is armed by one lane per wave, in program order, so a lane
+        // never waits on a phase of `empty` that lies more than one behind the barrier's current phase.
+        const uint32_t wave = slots < 32u ? slots : 32u;
+        for (uint32_t base = 0; base < chunks; base += wave) {
+            const uint32_t i = base + (uint32_t)lane;
+            if ((uint32_t)lane >= wave || i >= chunks) continue;
+            const uint32_t slot = i & slot_mask, round = i >> log2_slots;
+            if (round > 0) mbar_wait(&s_empty[slot], (round - 1u) & 1u);
+            const int units = chunk_units(i);
+            if (by_tma(units)) {
+                mbar_expect_tx(&s_full[slot], (uint32_t)units * 24u);
+                bulk_g2s(ring + slot * kSlotBytes, xyz + (size_t)(b0 + i * S) * 96, (uint32_t)units * 24u, &s_full[slot]);
+            } else {
+                mbar_arrive(&s_full[slot]); // the consumer loads this chunk with its lanes
+            }
+        }
+        return;
+    }
+
+    // ---- consumers
+    const uint32_t c = (uint32_t)warp - 1u;
+#ifdef EPP_TRACE
+    const uint32_t g = blockIdx.x * consumers + c;
+    int tstep = 0;
+#endif
+    EPP_TRACE_EV(g, 0);
+    unsigned char *queue = areas + c * (S * 32u + 32u);
+    uint32_t *inv = reinterpret_cast<uint32_t *>(queue + S * 32);
+    if (lane < 8) inv[lane] = 0u;
+    // fold the call's rules into the records (src/World.cpp:92-97, :116-121; src/OBB.cpp:67-72)
+    if (have_rec) {
+        double *r = rec + rk * kRecDoubles;
+        const bool filling = (rec_flags & kFlagFilling) != 0;
+        const bool skip = (mode & 0xff) == kModeBool ? (filling && cpg) : filling;
+        const double infl = (mode & 0xff) == kModeBool ? rv[16] : min_distance;
+#pragma unroll
+        for (int d = 0; d < 13; ++d) r[d] = rv[d];
+#pragma unroll
+        for (int d = 0; d < 3; ++d) r[13 + d] = skip ? -1.0 : (filling ? rv[13 + d] : dadd(rv[13 + d], infl));
+        r[16] = 0.0;
     }
     PointWorld<BP> world;
     world.bind(wv, aabb_in_smem != 0);
-    __syncthreads(); // publishes s_table's init, the records and the zeroed bitmaps
+    EPP_TRACE_EV(g, 1);
+    asm volatile("bar.sync 1, %0;" ::"r"(consumers * 32u) : "memory"); // consumers only: publishes the records
+    EPP_TRACE_EV(g, 2);
     {
         const void *tsrc;
         if (PointWorld<BP>::table(wv, aabb_in_smem != 0, tsrc)) mbar_wait(&s_table, 0);
     }
+    EPP_TRACE_EV(g, 3);
 
-    int slot = 0;
-    uint32_t parity = 0;
-    for (uint32_t cw = w0; cw < w1; cw += S) {
-        const int units = chunk_units(cw);
-        double *pts = reinterpret_cast<double *>(mine + (uint32_t)slot * kSlotBytes);
-        if (by_tma(cw)) {
-            mbar_wait(&s_full[warp][slot], parity);
-        } else {
-            const double *src = xyz + (size_t)cw * 96;
+    for (;;) {
+        uint32_t i = 0;
+        if (lane == 0) i = atomicAdd(&s_next, 1u);
+        i = __shfl_sync(0xffffffffu, i, 0);
+        if (i >= chunks) break;
+        const uint32_t slot = i & slot_mask, round = i >> log2_slots;
+        const int units = chunk_units(i);
+        double *pts = reinterpret_cast<double *>(ring + slot * kSlotBytes);
+        // A parity wait is only meaningful while the barrier is in phase `round` or `round + 1`.  Chunk numbers
+        // are handed out in order but finish out of order, so a fast warp can be handed round r of a slot whose
+        // round r-1 is still being loaded or worked on; the explicit count closes that window.
+        if (round > 0) {
+            uint32_t done;
+            do {
+                asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(done) : "r"(smem_addr(&s_rounds_done[slot])) : "memory");
+            } while (done < round);
+        }
+        mbar_wait(&s_full[slot], round & 1u);
+        if (!by_tma(units)) {
+            const double *src = xyz + (size_t)(b0 + i * S) * 96;
             for (int e = lane; e < 3 * units; e += 32) pts[e] = __ldg(src + e);
             __syncwarp();
         }
-        warp_states_step<BP, S, RS>(world, wv, rec, pts, units, mode, cpg, min_distance, queue, inv, mask + cw, lane);
-        // the step ended with __syncwarp: every lane's reads of the slot are done
-        const uint32_t nxt = cw + (uint32_t)stages * S;
-        if (lane == 0 && nxt < w1 && by_tma(nxt)) issue(nxt, slot);
-        if (++slot == stages) {
-            slot = 0;
-            parity ^= 1u;
+        EPP_TRACE_EV(g, 4 + 2 * tstep);
+        warp_states_step<BP, S, RS>(world, wv, rec, pts, units, mode, cpg, min_distance, queue, inv, mask + b0 + i * S,
+                                    lane);
+        EPP_TRACE_EV(g, 5 + 2 * tstep);
+#ifdef EPP_TRACE
+        if (tstep < 3) ++tstep;
+#endif
+        // the step ended with __syncwarp: every lane's reads of the slot are done, the producer may refill it
+        if (lane == 0) {
+            mbar_arrive(&s_empty[slot]);
+            asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(smem_addr(&s_rounds_done[slot])), "r"(round + 1u) : "memory");
         }
     }
+    EPP_TRACE_EV(g, 15);
 }
 
 // ---- K2: segments --------------------------------------------------------------------------
@@ -1190,6 +1024,27 @@ unsigned persistent_grid(const LaunchCfg &cfg, size_t tiles, int blocks_per_sm)
 
 std::atomic<uint64_t> g_launches{0};
 
+#ifdef EPP_TRACE
+extern "C" int epp_debug_trace_base(unsigned base, void *stream)
+{
+    k_trace_base<<<1, 1, 0, (cudaStream_t)stream>>>(base);
+    return (int)cudaGetLastError();
+}
+
+extern "C" int epp_debug_trace_copy(unsigned long long *host, size_t n, int clear)
+{
+    cudaDeviceSynchronize();
+    if (n > (1u << 20)) n = 1u << 20;
+    cudaError_t e = cudaMemcpyFromSymbol(host, g_trace, n * 8);
+    if (e == cudaSuccess && clear) {
+        void *p;
+        cudaGetSymbolAddress(&p, g_trace);
+        cudaMemset(p, 0, sizeof(unsigned long long) << 20);
+    }
+    return (int)e;
+}
+#endif
+
 #define EPP_DISPATCH_BP(bp, ...)                                                 \
     switch (bp) {                                                                \
     case EPP_BP_BRUTE: { constexpr int BP = EPP_BP_BRUTE; __VA_ARGS__; } break;  \
@@ -1197,52 +1052,55 @@ std::atomic<uint64_t> g_launches{0};
     default: { constexpr int BP = EPP_BP_GRID; __VA_ARGS__; } break;             \
     }
 
-template <int BP, int S>
-cudaError_t launch_states_stream(const LaunchCfg &cfg, const WorldView &wv, const double *d_xyz, size_t n, int mode,
-                                 int can_pass_gate, double min_distance, bool in_smem, size_t table_bytes, int stages,
-                                 uint32_t *d_mask, cudaStream_t stream, bool &launched)
-{
-    constexpr int kTile = S * kBlock;
-    const int qcap = cfg.states_queue_pairs > 0 ? cfg.states_queue_pairs : 2 * kTile;
-    const size_t smem = table_bytes + (size_t)stages * kTile * 24 + (size_t)qcap * 4;
-    launched = false;
-    if (smem > 200 * 1024) return cudaSuccess;
-    cudaError_t err = cudaFuncSetAttribute(k_states_stream<BP, S>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (err != cudaSuccess) return err;
-    const size_t tiles = (n + kTile - 1) / kTile;
-    const unsigned grid = persistent_grid(cfg, tiles, cfg.states_stream_blocks_per_sm);
-    k_states_stream<BP, S><<<grid, kBlock, smem, stream>>>(wv, d_xyz, n, mode, can_pass_gate, min_distance, in_smem ? 1 : 0,
-                                                           stages, (uint32_t)table_bytes, qcap, d_mask);
-    launched = true;
-    return cudaGetLastError();
-}
-
 template <int BP, int S, bool RS>
 cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const double *d_xyz, size_t n, int mode,
                                int can_pass_gate, double min_distance, bool in_smem, size_t table_bytes, int stages,
                                uint32_t *d_mask, cudaStream_t stream, bool &launched)
 {
-    const size_t rec_bytes = RS ? ((size_t)wv.M * kRecDoubles * 8 + 127) / 128 * 128 : 0;
-    const size_t warp_bytes = (size_t)stages * S * kWordBytes + S * 32 + 32;
-    const size_t smem = table_bytes + rec_bytes + kWarpsPerBlock * warp_bytes;
     launched = false;
     const size_t words = (n + 31) / 32;
-    if (smem > 200 * 1024 || words >= 0xfff00000ull) return cudaSuccess;
+    if (words >= 0xfff00000ull) return cudaSuccess;
+    const size_t rec_bytes = RS ? ((size_t)wv.M * kRecDoubles * 8 + 127) / 128 * 128 : 0;
+    const size_t warp_bytes = S * 32 + 32, slot_bytes = (size_t)S * kWordBytes;
+    // resident blocks per SM (tuning, default 1) and the shared-memory budget of each
+    int bps = cfg.states_warp_blocks_per_sm > 0 ? cfg.states_warp_blocks_per_sm : 1;
+    bps = bps > 8 ? 8 : bps;
+    int cons = (cfg.states_warp_threads > 0 ? cfg.states_warp_threads / 32 : kMaxWarps) - 1;
+    cons = cons < 1 ? 1 : (cons > kMaxWarps - 1 ? kMaxWarps - 1 : cons);
+    if ((cons + 1) * 32 * bps > 2048) bps = 2048 / ((cons + 1) * 32);
+    const size_t chunks_total = (words + S - 1) / S;
+    const size_t blocks_cap = (size_t)cfg.sm_count * bps;
+    const size_t grid = chunks_total < blocks_cap ? chunks_total : blocks_cap;
+    const size_t chunks_per_block = (chunks_total + grid - 1) / grid;
+    if ((size_t)cons > chunks_per_block) cons = (int)chunks_per_block;
+    const size_t budget = (size_t)(228 * 1024) / bps - 1024 - 4096; // 1 KB reserved per block + static + slack
+    const size_t fixed = table_bytes + rec_bytes + cons * warp_bytes;
+    if (fixed + 2 * slot_bytes > budget) return cudaSuccess;
+    int log2_slots = 1;
+    while (log2_slots < 6 && fixed + (slot_bytes << (log2_slots + 1)) <= budget &&
+           ((size_t)1 << log2_slots) < chunks_per_block)
+        ++log2_slots;
+    if (cfg.states_warp_log2_slots > 0 && cfg.states_warp_log2_slots < log2_slots) log2_slots = cfg.states_warp_log2_slots;
+    // A consumer that takes chunk i waits on phase (i / slots) of the slot's `full` barrier; that is only
+    // well defined if chunk i - slots has been consumed, which in-order hand-out guarantees iff slots >= consumers.
+    if (cons > (1 << log2_slots)) cons = 1 << log2_slots;
+    const size_t smem = table_bytes + rec_bytes + cons * warp_bytes + (slot_bytes << log2_slots);
     cudaError_t err = cudaFuncSetAttribute(k_states_warp<BP, S, RS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
-    // resident blocks per SM: the tuning value, limited by shared memory (228 KB per SM, 1 KB reserved per block)
-    int bps = cfg.states_warp_blocks_per_sm > 0 ? cfg.states_warp_blocks_per_sm : 3;
-    const int fit = (int)((228 * 1024) / (smem + 1024 + 768));
-    if (bps > fit) bps = fit;
-    if (bps < 1) bps = 1;
-    const size_t warps_needed = (words + S - 1) / S;
-    const size_t blocks_needed = (warps_needed + kWarpsPerBlock - 1) / kWarpsPerBlock;
-    const unsigned grid = persistent_grid(cfg, blocks_needed, bps);
-    const uint32_t warps = grid * kWarpsPerBlock;
-    k_states_warp<BP, S, RS><<<grid, kBlock, smem, stream>>>(wv, d_xyz, n, mode | (cfg.states_debug << 8), can_pass_gate, min_distance,
-                                                             in_smem ? 1 : 0, stages, (uint32_t)table_bytes,
-                                                             (uint32_t)rec_bytes, (uint32_t)(words / warps),
-                                                             (uint32_t)(words % warps), d_mask);
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3((unsigned)grid);
+    lc.blockDim = dim3((unsigned)(cons + 1) * 32);
+    lc.dynamicSmemBytes = smem;
+    lc.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = attr;
+    lc.numAttrs = cfg.states_pdl ? 1 : 0;
+    err = cudaLaunchKernelEx(&lc, k_states_warp<BP, S, RS>, wv, d_xyz, n, mode | (cfg.states_debug << 8), can_pass_gate,
+                             min_distance, in_smem ? 1 : 0, log2_slots, (uint32_t)table_bytes, (uint32_t)rec_bytes,
+                             (uint32_t)(words / grid), (uint32_t)(words % grid), d_mask);
+    if (err != cudaSuccess) return err;
     launched = true;
     return cudaGetLastError();
 }
@@ -1255,11 +1113,10 @@ cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, con
     const size_t smem = point_smem_bytes(wv, bp, in_smem);
     cudaError_t err = cudaSuccess;
     // Warp-pipelined form: any alignment, any n; worth its prologue from a few thousand states up.
-    if ((cfg.states_variant == 3 || (cfg.states_variant == 0 && n >= (size_t)cfg.states_warp_min_n)) &&
-        wv.M < (1 << kPairUnitShift)) {
+    if ((cfg.states_variant == 3 || (cfg.states_variant == 0 && n >= (size_t)cfg.states_warp_min_n))) {
         const size_t table_bytes = (smem + 127) / 128 * 128;
-        const int stages = cfg.states_stages < 1 ? 1 : (cfg.states_stages > kMaxStages ? kMaxStages : cfg.states_stages);
-        const int S = cfg.states_per_thread == 4 ? 4 : 8;
+        const int stages = 0; // ring depth comes from the shared-memory budget
+        const int S = cfg.states_per_thread == 8 ? 8 : 4;
         const bool rs = wv.M <= kRecSmemMax && wv.zrot && cfg.states_rec_smem != 0;
         const int wbp = (bp == EPP_BP_BITS && wv.W == 1 && cfg.states_bits1 != 0) ? kBpBits1 : bp;
         bool launched = false;
@@ -1267,10 +1124,10 @@ cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, con
     err = launch_states_warp<BP, S_, RS_>(cfg, wv, d_xyz, n, mode, can_pass_gate, min_distance, in_smem, table_bytes, \
                                           stages, d_mask, stream, launched)
 #define EPP_LAUNCH_WARP_S()                      \
-    if (S == 4 && rs) EPP_LAUNCH_WARP(4, true);  \
-    else if (S == 4) EPP_LAUNCH_WARP(4, false);  \
-    else if (rs) EPP_LAUNCH_WARP(8, true);       \
-    else EPP_LAUNCH_WARP(8, false)
+    if (S == 8 && rs) EPP_LAUNCH_WARP(8, true);  \
+    else if (S == 8) EPP_LAUNCH_WARP(8, false);  \
+    else if (rs) EPP_LAUNCH_WARP(4, true);       \
+    else EPP_LAUNCH_WARP(4, false)
         if (wbp == kBpBits1) {
             constexpr int BP = kBpBits1;
             EPP_LAUNCH_WARP_S();
@@ -1279,28 +1136,6 @@ cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, con
         }
 #undef EPP_LAUNCH_WARP_S
 #undef EPP_LAUNCH_WARP
-        if (err != cudaSuccess) return err;
-        if (launched) {
-            g_launches++;
-            return cudaSuccess;
-        }
-    }
-    // Streaming form: batches worth a ring, 16 B aligned (cp.async.bulk), obb index fits the pair encoding.
-    const bool stream_ok = (reinterpret_cast<uintptr_t>(d_xyz) & 15u) == 0 && wv.M < (1 << kPairUnitShift);
-    const bool want_stream = cfg.states_variant == 2 || (cfg.states_variant == 0 && n >= 8192);
-    if (stream_ok && want_stream) {
-        const size_t table_bytes = (smem + 127) / 128 * 128;
-        const int stages = cfg.states_stages < 2 ? 2 : (cfg.states_stages > kMaxStages ? kMaxStages : cfg.states_stages);
-        const int S = cfg.states_per_thread == 4 ? 4 : 2;
-        bool launched = false;
-        EPP_DISPATCH_BP(bp, {
-            if (S == 4)
-                err = launch_states_stream<BP, 4>(cfg, wv, d_xyz, n, mode, can_pass_gate, min_distance, in_smem, table_bytes,
-                                                  stages, d_mask, stream, launched);
-            else
-                err = launch_states_stream<BP, 2>(cfg, wv, d_xyz, n, mode, can_pass_gate, min_distance, in_smem, table_bytes,
-                                                  stages, d_mask, stream, launched);
-        });
         if (err != cudaSuccess) return err;
         if (launched) {
             g_launches++;

@@ -14,16 +14,16 @@ struct LaunchCfg {
     int sm_count = 148;
     int states_blocks_per_sm = 8;   // 0: one block per tile (non-persistent)
     int segments_blocks_per_sm = 4; // 0: one block per tile
-    int states_variant = 0;         // 0: auto, 1: direct, 2: block-streaming, 3: warp-pipelined
-    int states_warp_blocks_per_sm = 3;
+    int states_variant = 0;         // 0: auto (warp-pipelined from states_warp_min_n states up), 1: direct, 3: warp-pipelined
+    int states_warp_blocks_per_sm = 1;
+    int states_warp_threads = 1024; // block size of the warp-pipelined form
+    int states_warp_log2_slots = 0; // cap on log2(ring slots per block); 0: as many as fit (<= 64)
     int states_warp_min_n = 4096;   // auto: batches from this size up take the warp-pipelined form
     int states_debug = 0;           // profiling only: 1 skips phase 2 of the warp form, 2 also phase 1 (wrong masks)
+    int states_pdl = 1;             // warp form: programmatic dependent launch (prologue overlaps the previous kernel's tail)
     int states_bits1 = 1;           // warp form: single-word candidate masks for worlds of <= 32 OBBs
     int states_rec_smem = 1;        // warp-pipelined form: fold the world records into shared memory (M <= 64)
-    int states_stages = 2;          // ring slots per block of the streaming form (2..8)
-    int states_stream_blocks_per_sm = 5;
-    int states_per_thread = 0;      // streaming form: 2 or 4 states per thread per tile; 0: by batch size
-    int states_queue_pairs = 0;     // pair-queue capacity per tile; 0: two pairs per state
+    int states_per_thread = 0;      // warp form: mask words (32 states) per chunk and warp step, 4 (default) or 8
 };
 
 extern std::atomic<uint64_t> g_launches;

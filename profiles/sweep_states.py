@@ -1,7 +1,7 @@
 #!/usr/bin/env python
-"""Tuning sweep of K1 (states) on a B200: load path x ring depth x blocks/SM, CUDA-event timed from
+"""Tuning sweep of K1 (states) on a B200: form x chunk size x block shape, CUDA-event timed from
 a CUDA graph of one pass over a ring of batches larger than L2.  Prints one line per setting:
-    variant stages blocks/SM  us/launch  GB/s(algorithmic)  frac of measured HBM peak
+    variant words/chunk blocks/SM threads pdl  us/launch  GB/s(algorithmic)  frac of measured HBM peak
 Usage: python profiles/sweep_states.py [workload=states|clutter] [batch_log2=20]"""
 import json
 import os
@@ -31,21 +31,21 @@ def main():
     ring = [epp_b200.gen_states_dev(worlds.SEED_STATES, s * batch, batch, lo, hi) for s in range(ring_n)]
     mask = torch.empty(batch // 32, dtype=torch.int32, device="cuda")
     torch.cuda.synchronize()
-    # (variant, stages, blocks/SM, states per thread)
-    settings = [(1, 0, b, 0) for b in (4, 8)]
-    settings += [(2, st, b, spt) for spt in (2, 4) for st in (2, 3) for b in (3, 5)]
-    settings += [(3, st, b, spt) for spt in (4, 8) for st in (1, 2, 3) for b in (1, 2, 3, 4, 5, 6)]
+    # (variant, words per chunk, blocks/SM, threads per block, programmatic dependent launch)
+    settings = [(1, 0, b, 0, 0) for b in (4, 8)]
+    settings += [(3, spt, b, thr, pdl) for pdl in (0, 1) for spt in (4, 8)
+                 for (b, thr) in ((1, 1024), (1, 768), (1, 512), (2, 512), (2, 1024), (4, 256))]
     print("workload %s batch %d ring %d world_obbs %d bp %s" % (workload, batch, ring_n, w.size(),
                                                               epp_b200.BP_NAMES[w.active_broadphase()]))
-    for variant, stages, bps, spt in settings:
+    for variant, spt, bps, thr, pdl in settings:
         epp_b200.set_tuning("states_variant", variant)
         if variant == 1:
             epp_b200.set_tuning("states_blocks_per_sm", bps)
         else:
-            epp_b200.set_tuning("states_stages", stages)
-            epp_b200.set_tuning("states_stream_blocks_per_sm", bps)
-            epp_b200.set_tuning("states_warp_blocks_per_sm", bps)
             epp_b200.set_tuning("states_per_thread", spt)
+            epp_b200.set_tuning("states_warp_blocks_per_sm", bps)
+            epp_b200.set_tuning("states_warp_threads", thr)
+            epp_b200.set_tuning("states_pdl", pdl)
         try:
             for x in ring[:3]:
                 w.check_states_dev(x, mask=mask)
@@ -65,10 +65,10 @@ def main():
             torch.cuda.synchronize()
             us = s.elapsed_time(e) * 1e3 / (reps * ring_n)
             gbs = batch * 24.125 / (us * 1e-6) / 1e9
-            print("variant %d stages %d blocks/SM %2d states/thread %d  %8.2f us  %8.1f GB/s  frac %.3f" %
-                  (variant, stages, bps, spt, us, gbs, gbs / peak), flush=True)
+            print("variant %d words/chunk %d blocks/SM %d threads %4d pdl %d  %8.2f us  %8.1f GB/s  frac %.3f" %
+                  (variant, spt, bps, thr, pdl, us, gbs, gbs / peak), flush=True)
         except Exception as ex:
-            print("variant %d stages %d blocks/SM %d spt %d failed: %r" % (variant, stages, bps, spt, ex), flush=True)
+            print("variant %d spt %d blocks/SM %d threads %d pdl %d failed: %r" % (variant, spt, bps, thr, pdl, ex), flush=True)
 
 
 if __name__ == "__main__":

@@ -325,24 +325,23 @@ def test_concurrent_host_threads(oracle, config, track):
 
 
 @pytest.mark.parametrize("bp", BPS, ids=BP_IDS)
-def test_states_streaming_form_equals_direct_form(oracle, config, bp):
-    """K1 has two forms (TMA bulk-copy ring + block-wide candidate compaction / direct loads with a
-    per-lane candidate walk).  Both must give the oracle's mask for whole tiles, ragged tails, batches
-    smaller than one tile, a pair queue that overflows, and 8 B-aligned (not 16 B) batches (which the
-    launcher routes to the direct form)."""
+def test_states_warp_form_equals_direct_form(oracle, config, bp):
+    """K1 has two forms: warp-pipelined (producer warp + cp.async.bulk ring + per-warp compaction of the
+    states that have candidates) and direct (per-lane loads and candidate walk, small batches).  Both must
+    give the oracle's mask for whole chunks, ragged tails, batches smaller than one chunk, rings that wrap
+    many times, every block shape, and 8 B-aligned (not 16 B) batches (loaded by the lanes instead of TMA)."""
     import torch
     g, o, lo, hi = worlds.world_256()
     ow, gw = build_pair(oracle, epp_b200, config, g, o, bp)
-    keys = ("states_variant", "states_stages", "states_stream_blocks_per_sm", "states_per_thread",
-            "states_queue_pairs", "states_warp_blocks_per_sm", "states_rec_smem")
+    keys = ("states_variant", "states_per_thread", "states_warp_blocks_per_sm", "states_rec_smem",
+            "states_warp_log2_slots", "states_warp_threads", "states_pdl")
     saved = {k: epp_b200.get_tuning(k) for k in keys}
-    settings = [(1, 2, 4, 0, 0, 3, 1), (2, 2, 1, 2, 0, 3, 1), (2, 3, 4, 4, 0, 3, 1), (2, 8, 2, 2, 64, 3, 1),
-                (2, 2, 4, 4, 1, 3, 1), (0, 2, 4, 0, 0, 3, 1),
-                # warp-pipelined form: ring depth 1..4, 2 / 4 states per lane, tiny queue (overflow path),
-                # one block per SM (many steps per warp), records from global memory
-                (3, 2, 4, 4, 0, 3, 1), (3, 1, 4, 8, 0, 1, 1), (3, 4, 4, 8, 4, 2, 0), (3, 3, 4, 4, 8, 6, 1)]
+    settings = [(1, 0, 1, 1, 0, 1024, 1), (0, 0, 1, 1, 0, 1024, 1),
+                # 4 / 8 words per chunk, ring of 2 slots (wraps many times) .. as many as fit, 1 .. 31 consumer
+                # warps, 1 .. 4 blocks per SM, with and without programmatic dependent launch
+                (3, 4, 1, 1, 0, 1024, 1), (3, 8, 1, 1, 1, 64, 0), (3, 8, 2, 0, 2, 512, 1), (3, 4, 4, 1, 3, 256, 0)]
     try:
-        for n in (1, 511, 512, 513, 1024, 1025, 8192 + 511, 100003, 1 << 19):
+        for n in (1, 127, 128, 129, 1024, 1025, 8192 + 511, 100003, 1 << 19):
             buf = torch.empty(3 * n + 1, dtype=torch.float64, device="cuda")
             d_xyz = epp_b200.gen_states_dev(worlds.SEED_STATES, 7 * n, n, lo, hi, out=buf[: 3 * n].view(n, 3))
             h_xyz = oracle.gen_states(worlds.SEED_STATES, 7 * n, n, lo, hi)
@@ -358,7 +357,7 @@ def test_states_streaming_form_equals_direct_form(oracle, config, bp):
             # same states at an address that is only 8 B aligned
             shifted = buf[1:].view(n, 3)
             shifted.copy_(d_xyz.clone())
-            for variant in (2, 3):
+            for variant in (1, 3):
                 epp_b200.set_tuning("states_variant", variant)
                 assert np.array_equal(gw.check_states_dev(shifted).cpu().numpy().view(np.uint32), want), (n, variant)
     finally:
@@ -375,7 +374,7 @@ def test_states_warp_form_small_world_records_in_smem(oracle, config, track, bp)
     g, o, lo, hi = track
     cfg = filling_config(config)
     ow, gw = build_pair(oracle, epp_b200, cfg, g, o, bp)
-    keys = ("states_variant", "states_stages", "states_per_thread", "states_queue_pairs",
+    keys = ("states_variant", "states_warp_log2_slots", "states_per_thread", "states_warp_threads",
             "states_warp_blocks_per_sm", "states_rec_smem")
     saved = {k: epp_b200.get_tuning(k) for k in keys}
     adv = adversarial_points(ow.obbs(), np.random.default_rng(8), per_face=2)
@@ -390,7 +389,7 @@ def test_states_warp_form_small_world_records_in_smem(oracle, config, track, bp)
             shifted = buf[1:].view(n, 3)
             want = {("b", c): ow.check_states(h_xyz, c, threads=8) for c in (False, True)}
             want.update({("m", md): ow.check_states_mindist(h_xyz, md, threads=8) for md in (0.05, 0.3)})
-            for setting in [(3, 2, 4, 0, 3, 1), (3, 3, 8, 4, 1, 1), (3, 1, 8, 0, 8, 0)]:
+            for setting in [(3, 0, 4, 1024, 1, 1), (3, 1, 8, 64, 1, 1), (3, 2, 8, 256, 4, 0)]:
                 for k, v in zip(keys, setting):
                     epp_b200.set_tuning(k, v)
                 for src in (d_xyz, None):
@@ -402,6 +401,37 @@ def test_states_warp_form_small_world_records_in_smem(oracle, config, track, bp)
                             gw.check_states_dev(src, min_distance=arg)
                         assert np.array_equal(got.cpu().numpy().view(np.uint32), w), (n, setting, kind, arg)
                     d_xyz.copy_(torch.from_numpy(h_xyz))
+    finally:
+        for k, v in saved.items():
+            epp_b200.set_tuning(k, v)
+
+
+def test_states_warp_form_ring_wrap_stress(oracle, config, track):
+    """Many launches of batches large enough for every block's ring to wrap dozens of times, with ring sizes
+    from 2 slots to as many as fit: the mask checksum must never change and must equal the direct form's
+    (chunk hand-out is dynamic, so a protocol hole shows up as a rare wrong word or a hang, not every run)."""
+    import torch
+    g, o, lo, hi = track
+    ow, gw = build_pair(oracle, epp_b200, config, g, o)
+    keys = ("states_variant", "states_warp_log2_slots", "states_warp_threads", "states_per_thread")
+    saved = {k: epp_b200.get_tuning(k) for k in keys}
+    n = 1 << 23
+    d_xyz = epp_b200.gen_states_dev(worlds.SEED_STATES, 123, n, lo, hi)
+    mask = torch.empty(n // 32, dtype=torch.int32, device="cuda")
+    try:
+        epp_b200.set_tuning("states_variant", 1)
+        gw.check_states_dev(d_xyz, mask=mask)
+        want = epp_b200.mask_summary_dev(mask)
+        sub = 1 << 18
+        assert np.array_equal(mask[: sub // 32].cpu().numpy().view(np.uint32),
+                              ow.check_states(d_xyz[:sub].cpu().numpy(), threads=8))
+        for setting in [(3, 0, 1024, 4), (3, 1, 1024, 4), (3, 3, 1024, 8), (3, 5, 512, 4), (3, 0, 256, 8)]:
+            for k, v in zip(keys, setting):
+                epp_b200.set_tuning(k, v)
+            for rep in range(60):
+                mask.zero_()
+                gw.check_states_dev(d_xyz, mask=mask)
+                assert epp_b200.mask_summary_dev(mask) == want, (setting, rep)
     finally:
         for k, v in saved.items():
             epp_b200.set_tuning(k, v)
