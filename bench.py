@@ -14,7 +14,7 @@ exceeds the 126 MB L2, so every step streams its states from HBM.
             does not hide the kernel), max over ranks.
   e2e       the same batches through the host-buffer C-ABI call epp_check_states(): pinned host
             states -> H2D -> kernel -> D2H mask -> host, every step, copies inside the region.
-  roofline  dominant kernel (k_states) algorithmic bytes / its mean launch duration vs the
+  roofline  dominant kernel (k_states_warp) algorithmic bytes / its mean launch duration vs the
             measured HBM copy bandwidth in MEASURED_PEAKS.json.
   cpu_baseline  the CPU oracle (restatement of the reference validators), all host cores, on a
             bounded sample of the same workload.  Rank 0, N=1 only.
@@ -302,9 +302,9 @@ def run_b200(args):
                 "mask_popcount": e2e_pop},
         "gpu_launches": gpu_launches,
         "clocks": sampler.summary(),
-        "roofline": {"bound": "hbm", "kernel": "k_segments" if segs else "k_states",
+        "roofline": {"bound": "hbm", "kernel": "k_segments" if segs else "k_states_warp",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
-                     "traffic": load_traffic("k_segments" if segs else "k_states"),
+                     "traffic": load_traffic("k_segments" if segs else "k_states_warp"),
                      "peak_source": peak_src, "bytes_per_launch": unit_bytes * BATCH,
                      "launch_ms": kernel_ms},
     }
