@@ -44,20 +44,31 @@ BYTES_PER_SEGMENT = 48.125
 WORKLOADS = {
     "states": "config2: 1M uniform states isValid (canPassGate=false) vs config.json track world, M=24 OBBs",
     "segments": "config3: 1M segments checkMotion (exact slab test) vs synthetic 256-OBB world",
+    "config5": "config5: 1B states isValid + 100M edges checkMotion vs synthetic 10k-OBB world, "
+               "index ranges sharded over the ranks, NCCL all-gather of the mask words",
 }
+C5_STATES = 1_000_000_000
+C5_EDGES = 100_000_000
 
 
 def parse_args():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=4000)
-    ap.add_argument("--warmup", type=int, default=64)
+    ap.add_argument("--steps", type=int, default=None, help="default 4000 (config5: 20)")
+    ap.add_argument("--warmup", type=int, default=None, help="default 64 (config5: 3)")
+    ap.add_argument("--c5-states", type=int, default=C5_STATES)
+    ap.add_argument("--c5-edges", type=int, default=C5_EDGES)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--workload", default="states", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
-    return ap.parse_args()
+    args = ap.parse_args()
+    if args.steps is None:
+        args.steps = 20 if args.workload == "config5" else 4000
+    if args.warmup is None:
+        args.warmup = 3 if args.workload == "config5" else 64
+    return args
 
 
 def measured_peaks():
@@ -77,6 +88,9 @@ def make_world_inputs(workload):
     if workload == "states":
         g, o, lo, hi = worlds.track_world(config)
         seed = worlds.SEED_STATES
+    elif workload == "config5":
+        g, o, lo, hi = worlds.world_10k()
+        seed = worlds.SEED_CLUTTER
     else:
         g, o, lo, hi = worlds.world_256()
         seed = worlds.SEED_SEGMENTS
@@ -319,6 +333,170 @@ def run_b200(args):
         dist.destroy_process_group()
 
 
+def run_b200_config5(args):
+    """BASELINE.json configs[4]: one step = the whole 1 B-state + 100 M-edge job against the 10 000-OBB
+    world, STRONG scaling: rank r owns the contiguous index range epp_shard_range(n, r, G, 1024) of the
+    states and of the edges (inputs generated on its device from the counter-based generator, resident
+    before the timed region), writes its mask words into row r of the gathered buffers and the ranks
+    exchange them with one in-place NCCL all-gather each."""
+    import torch
+    import torch.distributed as dist
+    import epp_b200
+    from epp_b200 import sharding
+
+    rank, world, local_rank = dist_env()
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py --impl b200 needs a CUDA device: there is no CPU fallback")
+    torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    L = epp_b200.lib()
+    config, g, o, lo, hi, seed = make_world_inputs("config5")
+    gw = epp_b200.World(config)
+    gw.parse_gates_and_obstacles(g, o)
+    gw.commit()
+
+    NS, NE = args.c5_states, args.c5_edges
+    sb, se = epp_b200.shard_range(NS, rank, world, 1024)
+    eb, ee = epp_b200.shard_range(NE, rank, world, 1024)
+    d_xyz = epp_b200.gen_states_dev(seed, sb, se - sb, lo, hi, device=dev)
+    d_a, d_b = epp_b200.gen_segments_dev(seed, eb, ee - eb, lo, hi, 1.0, device=dev)
+    sw_s, sw_e = sharding.slot_words(NS, world), sharding.slot_words(NE, world)
+    gs = torch.zeros((world, sw_s), dtype=torch.int32, device=dev)
+    ge = torch.zeros((world, sw_e), dtype=torch.int32, device=dev)
+    ws, we = (se - sb + 31) // 32, (ee - eb + 31) // 32
+    torch.cuda.synchronize()
+
+    def step():
+        if se > sb:
+            gw.check_states_dev(d_xyz, mask=gs[rank][:ws])
+        if world > 1:
+            dist.all_gather_into_tensor(gs.view(-1), gs[rank])
+        if ee > eb:
+            gw.check_segments_dev(d_a, d_b, mask=ge[rank][:we])
+        if world > 1:
+            dist.all_gather_into_tensor(ge.view(-1), ge[rank])
+
+    K, W = args.steps, max(args.warmup, 3)
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    for _ in range(W):
+        step()
+    torch.cuda.synchronize()
+    l0 = epp_b200.kernel_launch_count()
+    if world > 1:
+        dist.barrier()
+    sampler.active = True
+    ms = timed_events(torch, lambda: [step() for _ in range(K)])
+    sampler.active = False
+    gpu_launches = epp_b200.kernel_launch_count() - l0
+    t = torch.tensor([ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    ms_total = float(t.item())
+    value = (NS + NE) * K / (ms_total * 1e-3)
+
+    # states-only kernel time on this rank (dominant kernel of the step) for the roofline
+    ms_states = timed_events(torch, lambda: [gw.check_states_dev(d_xyz, mask=gs[rank][:ws]) for _ in range(5)]) / 5
+    ms_edges = timed_events(torch, lambda: [gw.check_segments_dev(d_a, d_b, mask=ge[rank][:we]) for _ in range(5)]) / 5
+
+    # Checksums of the WHOLE gathered masks: must not depend on the number of ranks.
+    full_s = torch.from_numpy(sharding.assemble(gs, NS).view(np.int32)).to(dev)
+    full_e = torch.from_numpy(sharding.assemble(ge, NE).view(np.int32)).to(dev)
+    sum_s, sum_e = epp_b200.mask_summary_dev(full_s), epp_b200.mask_summary_dev(full_e)
+
+    # e2e: host buffers through the C ABI on a bounded slice of the rank's range (the full 24 GB of
+    # states would not fit a pinned host allocation on every box); copies inside the timed region.
+    n_s, n_e = min(se - sb, 1 << 24), min(ee - eb, 1 << 22) // 32 * 32
+    n_s = n_s // 32 * 32
+    h_xyz = d_xyz[:n_s].cpu().pin_memory()
+    h_a, h_b = d_a[:n_e].cpu().pin_memory(), d_b[:n_e].cpu().pin_memory()
+    h_ms = torch.zeros(max(n_s // 32, 1), dtype=torch.int32).pin_memory()
+    h_me = torch.zeros(max(n_e // 32, 1), dtype=torch.int32).pin_memory()
+
+    def step_host():
+        rc = L.epp_check_states(gw.handle, h_xyz.data_ptr(), n_s, 0, h_ms.data_ptr())
+        rc = rc or L.epp_check_segments(gw.handle, h_a.data_ptr(), h_b.data_ptr(), n_e, 0, h_me.data_ptr())
+        if rc:
+            raise RuntimeError(L.epp_last_error().decode())
+
+    step_host()
+    torch.cuda.synchronize()
+    if world > 1:
+        dist.barrier()
+    sampler.active = True
+    t0 = time.perf_counter()
+    for _ in range(3):
+        step_host()
+    e2e_s = time.perf_counter() - t0
+    sampler.active = False
+    t = torch.tensor([e2e_s], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    e2e_value = world * (n_s + n_e) * 3 / float(t.item())
+    assert np.array_equal(h_ms.numpy()[: n_s // 32], gs[rank][: n_s // 32].cpu().numpy())
+    assert np.array_equal(h_me.numpy()[: n_e // 32], ge[rank][: n_e // 32].cpu().numpy())
+    sampler.stop()
+
+    peak, peak_src = measured_peaks()
+    achieved = BYTES_PER_STATE * (se - sb) / (ms_states * 1e-3) / 1e9
+    line = {
+        "metric": "OBB state+motion validity checks/sec",
+        "value": value, "unit": "checks/s", "n_gpus": world, "steps": K, "warmup": W,
+        "ms_per_step": ms_total / K, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": WORKLOADS["config5"], "states": NS, "edges": NE,
+                   "world_obbs": gw.size(), "broadphase": epp_b200.BP_NAMES[gw.active_broadphase()],
+                   "l2": "per-rank inputs %.1f GB >> 126 MB L2" % ((24 * (se - sb) + 48 * (ee - eb)) / 1e9),
+                   "sharding": "contiguous index range per rank (align 1024); in-place NCCL all-gather of "
+                               "mask words, one per kind per step" if world > 1 else "single GPU",
+                   "states_mask_popcount": sum_s[0], "states_mask_xor": "%016x" % sum_s[1],
+                   "edges_mask_popcount": sum_e[0], "edges_mask_xor": "%016x" % sum_e[1],
+                   "rank0_ms_states_kernel": ms_states, "rank0_ms_edges_kernel": ms_edges},
+        "e2e": {"value": e2e_value, "unit": "checks/s", "h2d_bytes_per_step": 24 * n_s + 96 * n_e,
+                "d2h_bytes_per_step": (n_s + n_e) // 8, "steps": 3,
+                "api": "epp_check_states + epp_check_segments",
+                "sample": "first %d states + %d edges of each rank's range per step" % (n_s, n_e)},
+        "gpu_launches": gpu_launches,
+        "clocks": sampler.summary(),
+        "roofline": {"bound": "hbm", "kernel": "k_states_warp<grid>", "achieved": achieved, "peak": peak,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "bytes_per_launch": BYTES_PER_STATE * (se - sb), "launch_ms": ms_states},
+    }
+    if rank == 0 and not args.no_cpu_baseline:
+        line["cpu_baseline"] = cpu_parity_config5(gw, gs, ge, sb, eb, lo, hi, seed)
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def cpu_parity_config5(gw, gs, ge, sb, eb, lo, hi, seed, n_s=1 << 20, n_e=1 << 17):
+    """CPU arm on a subsample with the SAME global indices as the head of rank 0's range, timed, and
+    compared bit for bit with the GPU masks (mismatch count reported, target 0)."""
+    import oracle_py
+    threads = os.cpu_count() or 1
+    kind, w, _ = cpu_world("config5")
+    n_s = min(n_s, gs.shape[1] * 32) // 32 * 32
+    n_e = min(n_e, ge.shape[1] * 32) // 32 * 32
+    xyz = oracle_py.gen_states(seed, sb, n_s, lo, hi)
+    a, b = oracle_py.gen_segments(seed, eb, n_e, lo, hi, 1.0)
+    t0 = time.perf_counter()
+    ms = w.check_states(xyz, False, threads=threads)
+    me = w.check_segments(a, b, False, threads=threads)
+    el = time.perf_counter() - t0
+    got_s = gs[0][: n_s // 32].cpu().numpy().view(np.uint32)
+    got_e = ge[0][: n_e // 32].cpu().numpy().view(np.uint32)
+    bad = int(np.unpackbits((got_s ^ ms).view(np.uint8)).sum() + np.unpackbits((got_e ^ me).view(np.uint8)).sum())
+    return {"value": (n_s + n_e) / el, "unit": "checks/s", "cores": threads, "kind": kind,
+            "sample": "%d states + %d edges with the global indices of rank 0's range head, one pass (%.1f s); "
+                      "CPU broad phase = linear scan of the 10 000 stored AABBs (the R-tree stand-in is a list)"
+                      % (n_s, n_e, el),
+            "mask_mismatches_vs_gpu": bad}
+
+
 def load_traffic(kernel):
     """dram bytes per launch from the committed ncu capture (profiles/traffic.json), else null."""
     path = os.path.join(ROOT, "profiles", "traffic.json")
@@ -495,6 +673,8 @@ def main():
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)
+    elif args.workload == "config5":
+        run_b200_config5(args)
     else:
         run_b200(args)
 
