@@ -63,6 +63,11 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
+                    help="N > 1: mask exchange fused into the check kernel (default) or NCCL all-gather")
+    ap.add_argument("--tune", action="append", default=[], metavar="KEY=VALUE",
+                    help="epp_set_tuning knob (profiling sweeps; the default run sets none)")
+    ap.add_argument("--no-verify", action="store_true", help="profiling sweeps with gather_debug only")
     args = ap.parse_args()
     if args.steps is None:
         args.steps = 20 if args.workload == "config5" else 4000
@@ -178,6 +183,9 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=dev)
     L = epp_b200.lib()
+    for kv in args.tune:
+        k, v = kv.split("=")
+        epp_b200.set_tuning(k, int(v))
 
     config, g, o, lo, hi, seed = make_world_inputs(args.workload)
     gw = epp_b200.World(config)
@@ -195,13 +203,35 @@ def run_b200(args):
             ring.append(epp_b200.gen_segments_dev(seed, first, BATCH, lo, hi, 1.0, device=dev))
         else:
             ring.append((epp_b200.gen_states_dev(seed, first, BATCH, lo, hi, device=dev),))
-    # Gathered masks, double buffered; rank r's kernel writes row r in place (in-place allgather).
-    gathered = [torch.zeros((world, words), dtype=torch.int32, device=dev) for _ in range(2)]
+    # Gathered masks, double buffered.  N > 1: the check kernel itself stores its mask words into row r of
+    # the gathered buffer of EVERY rank over NVLink and ends when the peers' rows have arrived
+    # (epp_gather) — no collective launch per step.  --exchange nccl keeps the older form
+    # (kernel writes row r locally, in-place NCCL all-gather behind it) for comparison.
+    gather = None
+    exchange = "none (single GPU)"
+    if world > 1 and args.exchange == "fused":
+        try:
+            gather = epp_b200.Gather(rank, world, words, n_buffers=2).connect()
+            gathered = [gather.tensor(0, dev), gather.tensor(1, dev)]
+            exchange = "fused: peer stores from the check kernel + signal/wait in its last block"
+        except epp_b200.EppError as ex:  # CUDA IPC not permitted on this box: say so, use NCCL
+            gather = None
+            exchange = "nccl all-gather (fused exchange unavailable: %s)" % ex
+    if gather is None:
+        gathered = [torch.zeros((world, words), dtype=torch.int32, device=dev) for _ in range(2)]
+        if world > 1 and not exchange.startswith("nccl"):
+            exchange = "nccl all-gather, in place"
     torch.cuda.synchronize()
 
     def step_dev(s):
         buf = gathered[s & 1]
         mine = buf[rank]
+        if gather is not None:
+            if segs:
+                gather.check_segments(gw, ring[s % RING][0], ring[s % RING][1], s & 1)
+            else:
+                gather.check_states(gw, ring[s % RING][0], s & 1)
+            return
         if segs:
             gw.check_segments_dev(ring[s % RING][0], ring[s % RING][1], mask=mine)
         else:
@@ -214,7 +244,7 @@ def run_b200(args):
     sampler.start()
 
     # ---- value: device-resident inputs ------------------------------------------------------
-    use_graph = (world == 1) and not args.no_graph and K >= RING
+    use_graph = (world == 1 or gather is not None) and not args.no_graph and K >= RING
     for s in range(max(W, 3)):
         step_dev(s)
     torch.cuda.synchronize()
@@ -252,6 +282,24 @@ def run_b200(args):
     ms_total = float(t.item())
     value = world * BATCH * K / (ms_total * 1e-3)
     pop, xor = epp_b200.mask_summary_dev(gathered[0][rank])
+    exchange_ok = None
+    if world > 1:
+        # what the last two steps left in the gathered buffers vs an NCCL all-gather of plain local checks
+        exchange_ok = True
+        for s_ in (K - 2, K - 1):
+            slot = ring[s_ % RING]
+            ref_local = (gw.check_segments_dev(slot[0], slot[1]) if segs else gw.check_states_dev(slot[0]))
+            ref_all = torch.empty((world, words), dtype=torch.int32, device=dev)
+            dist.all_gather_into_tensor(ref_all.view(-1), ref_local)
+            exchange_ok = exchange_ok and bool(torch.equal(ref_all, gathered[s_ & 1]))
+        if gather is not None:
+            calls, timeouts = gather.status()
+            exchange_ok = exchange_ok and timeouts == 0
+        flag = torch.tensor([1 if exchange_ok else 0], device=dev)
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+        exchange_ok = bool(flag.item())
+        if not exchange_ok and not args.no_verify:
+            raise SystemExit("bench: gathered masks differ from the NCCL all-gather of the local masks")
 
     # ---- e2e: host buffers through the C ABI, copies inside the timed region ------------------
     e2e_steps = max(8, min(K, 64))
@@ -307,8 +355,9 @@ def run_b200(args):
                    "l2": "inputs rotate over a ring of %d distinct batches (%d MiB) > 126 MB L2" %
                          (RING, RING * in_bytes >> 20),
                    "launch": "cuda graph of one ring pass" if graph is not None else "direct launches",
-                   "sharding": "contiguous index range per rank; in-place NCCL allgather of mask words"
+                   "sharding": "contiguous index range per rank; every rank ends each step with all ranks' mask words"
                                if world > 1 else "single GPU",
+                   "exchange": exchange, "exchange_verified": exchange_ok, "tuning": args.tune,
                    "mask_popcount_slot0": pop, "mask_xor_slot0": "%016x" % xor},
         "e2e": {"value": e2e_value, "unit": "checks/s", "h2d_bytes_per_step": in_bytes,
                 "d2h_bytes_per_step": words * 4, "steps": e2e_steps,
@@ -327,7 +376,7 @@ def run_b200(args):
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(args.workload, budget_s=8.0)
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -363,12 +412,31 @@ def run_b200_config5(args):
     d_xyz = epp_b200.gen_states_dev(seed, sb, se - sb, lo, hi, device=dev)
     d_a, d_b = epp_b200.gen_segments_dev(seed, eb, ee - eb, lo, hi, 1.0, device=dev)
     sw_s, sw_e = sharding.slot_words(NS, world), sharding.slot_words(NE, world)
-    gs = torch.zeros((world, sw_s), dtype=torch.int32, device=dev)
-    ge = torch.zeros((world, sw_e), dtype=torch.int32, device=dev)
     ws, we = (se - sb + 31) // 32, (ee - eb + 31) // 32
+    gat_s = gat_e = None
+    exchange = "none (single GPU)"
+    if world > 1 and args.exchange == "fused":
+        try:
+            gat_s = epp_b200.Gather(rank, world, sw_s, n_buffers=1).connect()
+            gat_e = epp_b200.Gather(rank, world, sw_e, n_buffers=1).connect()
+            gs, ge = gat_s.tensor(0, dev), gat_e.tensor(0, dev)
+            exchange = ("fused: states - peer stores from the check kernel; edges - push kernel behind "
+                        "k_segments; signal/wait on the device, no collective launch")
+        except epp_b200.EppError as ex:
+            gat_s = gat_e = None
+            exchange = "nccl all-gather (fused exchange unavailable: %s)" % ex
+    if gat_s is None:
+        gs = torch.zeros((world, sw_s), dtype=torch.int32, device=dev)
+        ge = torch.zeros((world, sw_e), dtype=torch.int32, device=dev)
+        if world > 1 and not exchange.startswith("nccl"):
+            exchange = "nccl all-gather, in place"
     torch.cuda.synchronize()
 
     def step():
+        if gat_s is not None:
+            gat_s.check_states(gw, d_xyz, 0)
+            gat_e.check_segments(gw, d_a, d_b, 0)
+            return
         if se > sb:
             gw.check_states_dev(d_xyz, mask=gs[rank][:ws])
         if world > 1:
@@ -398,8 +466,17 @@ def run_b200_config5(args):
     value = (NS + NE) * K / (ms_total * 1e-3)
 
     # states-only kernel time on this rank (dominant kernel of the step) for the roofline
-    ms_states = timed_events(torch, lambda: [gw.check_states_dev(d_xyz, mask=gs[rank][:ws]) for _ in range(5)]) / 5
-    ms_edges = timed_events(torch, lambda: [gw.check_segments_dev(d_a, d_b, mask=ge[rank][:we]) for _ in range(5)]) / 5
+    timeouts = 0
+    if gat_s is not None:
+        timeouts = gat_s.status()[1] + gat_e.status()[1]
+        if timeouts:
+            raise SystemExit("bench: %d gather waits timed out" % timeouts)
+    tmp_s = torch.empty(max(ws, 1), dtype=torch.int32, device=dev)
+    tmp_e = torch.empty(max(we, 1), dtype=torch.int32, device=dev)
+    ms_states = timed_events(torch, lambda: [gw.check_states_dev(d_xyz, mask=tmp_s) for _ in range(5)]) / 5
+    ms_edges = timed_events(torch, lambda: [gw.check_segments_dev(d_a, d_b, mask=tmp_e) for _ in range(5)]) / 5
+    if not (torch.equal(tmp_s[:ws], gs[rank][:ws]) and torch.equal(tmp_e[:we], ge[rank][:we])):
+        raise SystemExit("bench: gathered slot of this rank differs from a plain local check")
 
     # Checksums of the WHOLE gathered masks: must not depend on the number of ranks.
     full_s = torch.from_numpy(sharding.assemble(gs, NS).view(np.int32)).to(dev)
@@ -449,8 +526,9 @@ def run_b200_config5(args):
         "config": {"workload": WORKLOADS["config5"], "states": NS, "edges": NE,
                    "world_obbs": gw.size(), "broadphase": epp_b200.BP_NAMES[gw.active_broadphase()],
                    "l2": "per-rank inputs %.1f GB >> 126 MB L2" % ((24 * (se - sb) + 48 * (ee - eb)) / 1e9),
-                   "sharding": "contiguous index range per rank (align 1024); in-place NCCL all-gather of "
-                               "mask words, one per kind per step" if world > 1 else "single GPU",
+                   "sharding": "contiguous index range per rank (align 1024); every rank ends each step with "
+                               "all ranks' mask words" if world > 1 else "single GPU",
+                   "exchange": exchange,
                    "states_mask_popcount": sum_s[0], "states_mask_xor": "%016x" % sum_s[1],
                    "edges_mask_popcount": sum_e[0], "edges_mask_xor": "%016x" % sum_e[1],
                    "rank0_ms_states_kernel": ms_states, "rank0_ms_edges_kernel": ms_edges},
@@ -467,7 +545,7 @@ def run_b200_config5(args):
     if rank == 0 and not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_parity_config5(gw, gs, ge, sb, eb, lo, hi, seed)
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -666,10 +744,28 @@ def run_reference(args):
         "e2e": {"value": value, "unit": "checks/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
+
+
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """The ONE JSON line goes to the real stdout; everything else any library prints (NCCL's version
+    banner goes to stdout) was redirected to stderr by main()."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is not None:
+        os.write(_REAL_STDOUT, data)
+    else:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
 
 
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     args = parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -89,6 +89,17 @@ SIGNATURES = {
     "epp_gen_states_dev": (C.c_int, [C.c_uint64, C.c_uint64, C.c_size_t, _dp, _dp, _vp, _vp]),
     "epp_gen_segments_dev": (C.c_int, [C.c_uint64, C.c_uint64, C.c_size_t, _dp, _dp, C.c_double,
                                        _vp, _vp, _vp]),
+    "epp_gather_create": (C.c_int, [C.c_int, C.c_int, C.c_size_t, C.c_int, C.POINTER(_vp)]),
+    "epp_gather_destroy": (C.c_int, [_vp]),
+    "epp_gather_export": (C.c_int, [_vp, _vp]),
+    "epp_gather_connect": (C.c_int, [_vp, _vp]),
+    "epp_gather_connect_local": (C.c_int, [C.POINTER(_vp), C.c_int]),
+    "epp_gather_buffer": (C.c_int, [_vp, C.c_int, C.POINTER(_vp)]),
+    "epp_gather_set_timeout_ms": (C.c_int, [_vp, C.c_uint]),
+    "epp_gather_status": (C.c_int, [_vp, C.POINTER(C.c_uint64), C.POINTER(C.c_uint64)]),
+    "epp_check_states_gather_dev": (C.c_int, [_vp, _vp, C.c_size_t, C.c_int, _vp, C.c_int, _vp]),
+    "epp_check_states_mindist_gather_dev": (C.c_int, [_vp, _vp, C.c_size_t, C.c_double, _vp, C.c_int, _vp]),
+    "epp_check_segments_gather_dev": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_int, _vp, C.c_int, _vp]),
     "epp_kernel_launch_count": (C.c_uint64, []),
     "epp_set_tuning": (C.c_int, [C.c_char_p, C.c_int]),
     "epp_get_tuning": (C.c_int, [C.c_char_p, C.POINTER(C.c_int)]),
@@ -438,6 +449,90 @@ class World:
                                                    smask.data_ptr() if want_samples else None,
                                                    ns.data_ptr(), first.data_ptr(), self._stream()))
         return valid, smask, ns, first
+
+
+class _DevWords:
+    """__cuda_array_interface__ view of library-owned device words (lets torch wrap them without a copy)."""
+
+    def __init__(self, ptr, shape, owner):
+        self.owner = owner
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": "<i4", "data": (int(ptr), False),
+                                         "version": 2, "strides": None}
+
+
+class Gather:
+    """Mask exchange fused into the check kernels (include/epp_c_api.h "Mask exchange").
+
+    One per rank.  ``connect()`` exchanges the CUDA IPC handles over ``torch.distributed`` (one process per
+    GPU); ``Gather.connect_local(list)`` wires several handles of ONE process together.  After
+    ``check_states(world, xyz, buffer)`` has completed in stream order, ``tensor(buffer)`` — a
+    (world_size, slot_words) int32 view of library memory — holds the masks of all ranks."""
+
+    def __init__(self, rank, world_size, slot_words, n_buffers=2):
+        self.rank, self.world_size, self.slot_words, self.n_buffers = rank, world_size, slot_words, n_buffers
+        h = _vp()
+        _chk(lib().epp_gather_create(rank, world_size, slot_words, n_buffers, C.byref(h)))
+        self._h = h
+
+    def __del__(self):
+        h, self._h = getattr(self, "_h", None), None
+        if h:
+            try:
+                lib().epp_gather_destroy(h)
+            except Exception:
+                pass
+
+    def export(self):
+        buf = (C.c_ubyte * 64)()
+        _chk(lib().epp_gather_export(self._h, buf))
+        return bytes(buf)
+
+    def connect(self, group=None):
+        """Collective over torch.distributed: all-gather the 64-byte handles, open the peers'."""
+        import torch.distributed as dist
+        if self.world_size == 1:
+            return self
+        handles = [None] * self.world_size
+        dist.all_gather_object(handles, self.export(), group=group)
+        blob = b"".join(handles)
+        _chk(lib().epp_gather_connect(self._h, C.c_char_p(blob)))
+        dist.barrier(group=group)
+        return self
+
+    @staticmethod
+    def connect_local(gathers):
+        arr = (_vp * len(gathers))(*[g._h for g in gathers])
+        _chk(lib().epp_gather_connect_local(arr, len(gathers)))
+
+    def set_timeout_ms(self, ms):
+        _chk(lib().epp_gather_set_timeout_ms(self._h, int(ms)))
+
+    def status(self):
+        calls, timeouts = C.c_uint64(0), C.c_uint64(0)
+        _chk(lib().epp_gather_status(self._h, C.byref(calls), C.byref(timeouts)))
+        return calls.value, timeouts.value
+
+    def tensor(self, buffer, device=None):
+        import torch
+        p = _vp()
+        _chk(lib().epp_gather_buffer(self._h, buffer, C.byref(p)))
+        dev = device if device is not None else torch.device("cuda", torch.cuda.current_device())
+        return torch.as_tensor(_DevWords(p.value, (self.world_size, self.slot_words), self), device=dev)
+
+    def check_states(self, world, xyz, buffer, can_pass_gate=False, min_distance=None):
+        world._sync()
+        n = xyz.numel() // 3
+        if min_distance is None:
+            _chk(lib().epp_check_states_gather_dev(world._h, xyz.data_ptr(), n, int(can_pass_gate), self._h,
+                                                   buffer, World._stream()))
+        else:
+            _chk(lib().epp_check_states_mindist_gather_dev(world._h, xyz.data_ptr(), n, float(min_distance),
+                                                           self._h, buffer, World._stream()))
+
+    def check_segments(self, world, a, b, buffer, can_pass_gate=False):
+        world._sync()
+        _chk(lib().epp_check_segments_gather_dev(world._h, a.data_ptr(), b.data_ptr(), a.numel() // 3,
+                                                 int(can_pass_gate), self._h, buffer, World._stream()))
 
 
 def gen_states_dev(seed, first, n, lo, hi, out=None, device="cuda"):

@@ -60,6 +60,7 @@ Knob g_knobs[] = {
     {"states_bits1", {1}},
     {"states_pdl", {1}},
     {"states_debug", {0}},               // profiling builds only
+    {"gather_debug", {0}},               // profiling only: 1 no wait, 2 no peer stores, 4 no signal
     {"bits_bins", {0}},                  // 0: by world size
     {"grid_max_cells", {1 << 22}},
     {"bits_max_obbs", {1024}},
@@ -794,6 +795,211 @@ extern "C" int epp_check_poly_trajectories_dev(epp_world *w, const double *d_coe
                                              n_segments, n_coeffs, min_distance, max_samples, d_traj_valid,
                                              d_sample_mask, d_n_samples, d_first_invalid, (long long *)d_first_invalid,
                                              (cudaStream_t)stream);
+    return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
+}
+
+// ---- mask exchange fused into the check kernels ----------------------------------------------------------
+
+struct epp_gather {
+    int rank = 0, world = 1, device = 0, n_buffers = 1;
+    size_t slot_words = 0;
+    unsigned char *base = nullptr;            // [signals + control: 256 B][n_buffers x world x slot_words words]
+    unsigned char *peer_base[kMaxRanks] = {}; // every rank's allocation in this process's address space
+    bool opened[kMaxRanks] = {};              // peer_base[p] came from cudaIpcOpenMemHandle
+    bool connected = false;
+    uint64_t timeout_ns = 2000000000ull;
+    size_t buffer_bytes() const { return (size_t)world * slot_words * 4; }
+    uint32_t *buffer_of(unsigned char *b, int i) const { return (uint32_t *)(b + 256 + (size_t)i * buffer_bytes()); }
+};
+
+namespace {
+
+constexpr size_t kGatherCtlOff = 128; // signals at +0 (kMaxRanks words), control words at +128
+
+int gather_view(epp_gather *g, int buffer, size_t n, GatherView &gv)
+{
+    if (!g) return fail(EPP_ERR_INVALID_ARG, "null gather");
+    if (!g->connected) return fail(EPP_ERR_INVALID_ARG, "gather is not connected to its peers");
+    if (buffer < 0 || buffer >= g->n_buffers) return fail(EPP_ERR_INVALID_ARG, "gather buffer index");
+    if ((n + 31) / 32 > g->slot_words) return fail(EPP_ERR_INVALID_ARG, "more units than the gather slot holds");
+    for (int p = 0; p < kMaxRanks; ++p) {
+        gv.peer[p] = p < g->world ? g->buffer_of(g->peer_base[p], buffer) : nullptr;
+        gv.peer_sig[p] = p < g->world ? (uint32_t *)g->peer_base[p] : nullptr;
+    }
+    gv.my_sig = (uint32_t *)g->base;
+    gv.ctl = (uint32_t *)(g->base + kGatherCtlOff);
+    gv.my_off = (uint64_t)g->rank * g->slot_words;
+    gv.timeout_ns = g->timeout_ns;
+    gv.world = g->world;
+    gv.rank = g->rank;
+    gv.debug = knob_value("gather_debug");
+    return EPP_OK;
+}
+
+} // namespace
+
+extern "C" int epp_gather_create(int rank, int world_size, size_t slot_words, int n_buffers, epp_gather **out)
+{
+    if (!out || world_size < 1 || world_size > kMaxRanks || rank < 0 || rank >= world_size || n_buffers < 1 ||
+        n_buffers > 64 || slot_words == 0 || slot_words % 4)
+        return fail(EPP_ERR_INVALID_ARG, "gather shape (slot_words must be a positive multiple of 4, world_size <= 8)");
+    std::unique_ptr<epp_gather> g(new (std::nothrow) epp_gather);
+    if (!g) return fail(EPP_ERR_INVALID_ARG, "out of memory");
+    g->rank = rank;
+    g->world = world_size;
+    g->slot_words = slot_words;
+    g->n_buffers = n_buffers;
+    EPP_CUDA(cudaGetDevice(&g->device));
+    const size_t bytes = 256 + (size_t)n_buffers * g->buffer_bytes();
+    EPP_CUDA(cudaMalloc((void **)&g->base, bytes));
+    EPP_CUDA(cudaMemset(g->base, 0, bytes));
+    EPP_CUDA(cudaDeviceSynchronize());
+    g->peer_base[rank] = g->base;
+    g->connected = world_size == 1;
+    *out = g.release();
+    return EPP_OK;
+}
+
+extern "C" int epp_gather_destroy(epp_gather *g)
+{
+    if (!g) return EPP_OK;
+    int prev = -1;
+    cudaGetDevice(&prev);
+    cudaSetDevice(g->device);
+    cudaDeviceSynchronize();
+    for (int p = 0; p < g->world; ++p)
+        if (g->opened[p]) cudaIpcCloseMemHandle(g->peer_base[p]);
+    if (g->base) cudaFree(g->base);
+    if (prev >= 0) cudaSetDevice(prev);
+    delete g;
+    return EPP_OK;
+}
+
+extern "C" int epp_gather_export(epp_gather *g, unsigned char handle[EPP_GATHER_HANDLE_BYTES])
+{
+    static_assert(sizeof(cudaIpcMemHandle_t) == EPP_GATHER_HANDLE_BYTES, "CUDA IPC handle size");
+    if (!g || !handle) return fail(EPP_ERR_INVALID_ARG, "null gather");
+    cudaIpcMemHandle_t h;
+    EPP_CUDA(cudaIpcGetMemHandle(&h, g->base));
+    std::memcpy(handle, &h, sizeof h);
+    return EPP_OK;
+}
+
+extern "C" int epp_gather_connect(epp_gather *g, const unsigned char *handles)
+{
+    if (!g || !handles) return fail(EPP_ERR_INVALID_ARG, "null gather");
+    DeviceGuard guard;
+    EPP_CUDA(guard.enter(g->device));
+    for (int p = 0; p < g->world; ++p) {
+        if (p == g->rank || g->peer_base[p]) continue;
+        cudaIpcMemHandle_t h;
+        std::memcpy(&h, handles + (size_t)p * EPP_GATHER_HANDLE_BYTES, sizeof h);
+        void *ptr = nullptr;
+        EPP_CUDA(cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess));
+        g->peer_base[p] = (unsigned char *)ptr;
+        g->opened[p] = true;
+    }
+    g->connected = true;
+    return EPP_OK;
+}
+
+extern "C" int epp_gather_connect_local(epp_gather *const *all, int world_size)
+{
+    if (!all || world_size < 1 || world_size > kMaxRanks) return fail(EPP_ERR_INVALID_ARG, "gather list");
+    for (int r = 0; r < world_size; ++r)
+        if (!all[r] || all[r]->rank != r || all[r]->world != world_size || all[r]->slot_words != all[0]->slot_words ||
+            all[r]->n_buffers != all[0]->n_buffers)
+            return fail(EPP_ERR_INVALID_ARG, "gather handles must be given in rank order and share one shape");
+    int prev = -1;
+    EPP_CUDA(cudaGetDevice(&prev));
+    for (int r = 0; r < world_size; ++r) {
+        EPP_CUDA(cudaSetDevice(all[r]->device));
+        for (int p = 0; p < world_size; ++p) {
+            if (all[p]->device != all[r]->device) {
+                cudaError_t e = cudaDeviceEnablePeerAccess(all[p]->device, 0);
+                if (e == cudaErrorPeerAccessAlreadyEnabled) cudaGetLastError();
+                else if (e != cudaSuccess) {
+                    cudaSetDevice(prev);
+                    return cuda_fail(e, "cudaDeviceEnablePeerAccess");
+                }
+            }
+            all[r]->peer_base[p] = all[p]->base;
+        }
+        all[r]->connected = true;
+    }
+    EPP_CUDA(cudaSetDevice(prev));
+    return EPP_OK;
+}
+
+extern "C" int epp_gather_buffer(epp_gather *g, int buffer, uint32_t **d_words)
+{
+    if (!g || !d_words || buffer < 0 || buffer >= g->n_buffers) return fail(EPP_ERR_INVALID_ARG, "gather buffer index");
+    *d_words = g->buffer_of(g->base, buffer);
+    return EPP_OK;
+}
+
+extern "C" int epp_gather_set_timeout_ms(epp_gather *g, unsigned ms)
+{
+    if (!g) return fail(EPP_ERR_INVALID_ARG, "null gather");
+    g->timeout_ns = (uint64_t)ms * 1000000ull;
+    return EPP_OK;
+}
+
+extern "C" int epp_gather_status(epp_gather *g, uint64_t *calls, uint64_t *timeouts)
+{
+    if (!g) return fail(EPP_ERR_INVALID_ARG, "null gather");
+    DeviceGuard guard;
+    EPP_CUDA(guard.enter(g->device));
+    uint32_t ctl[4];
+    EPP_CUDA(cudaDeviceSynchronize());
+    EPP_CUDA(cudaMemcpy(ctl, g->base + kGatherCtlOff, sizeof ctl, cudaMemcpyDeviceToHost));
+    if (calls) *calls = ctl[1];
+    if (timeouts) *timeouts = ctl[2];
+    return EPP_OK;
+}
+
+extern "C" int epp_check_states_gather_dev(epp_world *w, const double *d_xyz, size_t n, int can_pass_gate,
+                                           epp_gather *g, int buffer, void *stream)
+{
+    std::shared_ptr<DeviceEpoch> ep;
+    int rc = snapshot(w, ep);
+    if (rc) return rc;
+    if (n && !d_xyz) return fail(EPP_ERR_INVALID_ARG, "null buffer");
+    GatherView gv;
+    rc = gather_view(g, buffer, n, gv);
+    if (rc) return rc;
+    cudaError_t e = launch_states(launch_cfg(*ep), ep->view, ep->bp, d_xyz, n, kModeBool, can_pass_gate, 0.0,
+                                  gv.peer[gv.rank] + gv.my_off, (cudaStream_t)stream, g->world > 1 ? &gv : nullptr);
+    return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
+}
+
+extern "C" int epp_check_states_mindist_gather_dev(epp_world *w, const double *d_xyz, size_t n, double min_distance,
+                                                   epp_gather *g, int buffer, void *stream)
+{
+    std::shared_ptr<DeviceEpoch> ep;
+    int rc = snapshot(w, ep);
+    if (rc) return rc;
+    if (n && !d_xyz) return fail(EPP_ERR_INVALID_ARG, "null buffer");
+    GatherView gv;
+    rc = gather_view(g, buffer, n, gv);
+    if (rc) return rc;
+    cudaError_t e = launch_states(launch_cfg(*ep), ep->view, ep->bp, d_xyz, n, kModeMinDist, 0, min_distance,
+                                  gv.peer[gv.rank] + gv.my_off, (cudaStream_t)stream, g->world > 1 ? &gv : nullptr);
+    return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
+}
+
+extern "C" int epp_check_segments_gather_dev(epp_world *w, const double *d_a, const double *d_b, size_t n,
+                                             int can_pass_gate, epp_gather *g, int buffer, void *stream)
+{
+    std::shared_ptr<DeviceEpoch> ep;
+    int rc = snapshot(w, ep);
+    if (rc) return rc;
+    if (n && (!d_a || !d_b)) return fail(EPP_ERR_INVALID_ARG, "null buffer");
+    GatherView gv;
+    rc = gather_view(g, buffer, n, gv);
+    if (rc) return rc;
+    cudaError_t e = launch_segments(launch_cfg(*ep), ep->view, ep->bp, d_a, d_b, n, can_pass_gate,
+                                    gv.peer[gv.rank] + gv.my_off, (cudaStream_t)stream, g->world > 1 ? &gv : nullptr);
     return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
 }
 

@@ -438,6 +438,84 @@ __global__ void k_trace_base(uint32_t base) { g_trace_base = base; }
 #define EPP_TRACE_EV(g, ev)
 #endif
 
+
+// ---- mask exchange over peer memory (GatherView, kernels.h) --------------------------------------------
+//
+// Called by ONE warp of a block after every peer store of the block has been followed by
+// __threadfence_system() in the storing thread and the block's threads have met (barrier or counter).
+// The last block of the grid raises this call's sequence number on every peer and waits for theirs.
+__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t *p)
+{
+    uint32_t v;
+    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+
+__device__ __forceinline__ void st_relaxed_sys(uint32_t *p, uint32_t v)
+{
+    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
+}
+
+// Ordering (the chain NCCL's own protocols rely on): a thread's peer stores -> block-level meeting (barrier
+// or release/acquire counter) -> ONE thread: fence.gpu + grid counter -> last block: ONE fence.sys, then
+// relaxed stores of the sequence number to the peers.  Causality is cumulative across the scopes, so a peer
+// that has observed the sequence number observes every word of every block.
+__device__ __forceinline__ void gather_finish(const GatherView &gv, int lane)
+{
+    uint32_t seq = 0;
+    if (lane == 0) {
+        __threadfence();
+        if (atomicAdd(&gv.ctl[0], 1u) == gridDim.x - 1u) {
+            __threadfence_system();
+            seq = gv.ctl[1] + 1u; // launches on one gather are stream ordered: only this thread touches it now
+            gv.ctl[0] = 0u;
+            gv.ctl[1] = seq;
+        }
+    }
+    seq = __shfl_sync(0xffffffffu, seq, 0);
+    if (seq == 0u) return;
+    if (lane < gv.world && lane != gv.rank) {
+        if (!(gv.debug & 4)) st_relaxed_sys(gv.peer_sig[lane] + gv.rank, seq);
+        if (!(gv.debug & 1)) {
+            unsigned long long t0, t;
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
+            while ((int32_t)(ld_relaxed_sys(gv.my_sig + lane) - seq) < 0) {
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                if (t - t0 > gv.timeout_ns) {
+                    atomicAdd(&gv.ctl[2], 1u);
+                    break;
+                }
+            }
+        }
+    }
+    __syncwarp();
+    __threadfence_system();
+}
+
+// Generic push: any check kernel wrote this rank's words into its own slot of the local gathered buffer;
+// copy the slot to every peer (16 B vector stores where the slot allows), then signal and wait.
+__global__ void __launch_bounds__(256) k_gather_push(GatherView gv, size_t words)
+{
+    __shared__ uint32_t s_warps_done;
+    if (threadIdx.x == 0) s_warps_done = 0u;
+    __syncthreads();
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    const uint32_t *src = gv.peer[gv.rank] + gv.my_off;
+    const bool vec = ((gv.my_off & 3u) == 0) && ((reinterpret_cast<uintptr_t>(gv.peer[gv.rank]) & 15u) == 0);
+    const size_t stride = (size_t)gridDim.x * blockDim.x, t0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    for (int p = 0; p < gv.world; ++p) {
+        if (p == gv.rank) continue;
+        uint32_t *dst = gv.peer[p] + gv.my_off;
+        const bool v = vec && ((reinterpret_cast<uintptr_t>(gv.peer[p]) & 15u) == 0);
+        const size_t quads = v ? words / 4 : 0;
+        for (size_t i = t0; i < quads; i += stride)
+            reinterpret_cast<uint4 *>(dst)[i] = reinterpret_cast<const uint4 *>(src)[i];
+        for (size_t i = quads * 4 + t0; i < words; i += stride) dst[i] = src[i];
+    }
+    __syncthreads();
+    if (threadIdx.x < 32) gather_finish(gv, threadIdx.x);
+}
+
 constexpr int kRecDoubles = 17;
 constexpr int kRecSmemMax = 64;
 constexpr int kWordBytes = 32 * 3 * 8; // one mask word of states = 768 B of coordinates
@@ -451,11 +529,12 @@ __device__ __forceinline__ bool rec_hit(const double *__restrict__ r, const P3 &
     return in & (fabs(lx) <= r[13]) & (fabs(ly) <= r[14]) & (fabs(d2) <= r[15]);
 }
 
-template <int BP, int S, bool RS>
+template <int BP, int S, bool RS, bool GA>
 __device__ __forceinline__ void warp_states_step(const PointWorld<BP> &world, const WorldView &wv,
                                                  const double *__restrict__ rec, const double *__restrict__ pts,
                                                  int units, int mode, bool cpg, double md, unsigned char *queue,
-                                                 uint32_t *inv, uint32_t *__restrict__ mask_out, int lane)
+                                                 uint32_t *inv, uint32_t *__restrict__ mask_out, int lane,
+                                                 const GatherView &gv, size_t word0)
 {
     // ---- phase 1: which of my S states have a broad-phase candidate at all
     const uint32_t lt = (1u << lane) - 1u;
@@ -496,7 +575,12 @@ __device__ __forceinline__ void warp_states_step(const PointWorld<BP> &world, co
     if (lane < S && lane * 32 < units) {
         const int live = units - 32 * lane;
         const uint32_t active = live >= 32 ? 0xffffffffu : ((1u << live) - 1u);
-        mask_out[lane] = ~inv[lane] & active;
+        const uint32_t verdict = ~inv[lane] & active;
+        mask_out[lane] = verdict;
+        if (GA && !(gv.debug & 2)) { // the same word into this rank's slot of every peer's gathered buffer (NVLink stores)
+            for (int p = 0; p < gv.world; ++p)
+                if (p != gv.rank) gv.peer[p][gv.my_off + word0 + lane] = verdict;
+        }
         inv[lane] = 0u;
     }
     __syncwarp();
@@ -524,12 +608,14 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_addr(bar)) : "memory");
 }
 
-template <int BP, int S, bool RS>
+template <int BP, int S, bool RS, bool GA>
 __global__ void __launch_bounds__(1024) k_states_warp(WorldView wv, const double *__restrict__ xyz, size_t n, int mode,
                                                       int can_pass_gate, double min_distance, int aabb_in_smem,
                                                       int log2_slots, uint32_t table_bytes, uint32_t rec_bytes,
-                                                      uint32_t wpb, uint32_t rem, uint32_t *__restrict__ mask)
+                                                      uint32_t wpb, uint32_t rem, uint32_t *__restrict__ mask,
+                                                      GatherView gv)
 {
+    __shared__ uint32_t s_warps_done; // GA: consumer warps that have finished (the last one runs gather_finish)
     __shared__ __align__(8) uint64_t s_full[kMaxSlots];
     __shared__ __align__(8) uint64_t s_empty[kMaxSlots];
     __shared__ __align__(8) uint64_t s_table;
@@ -574,6 +660,7 @@ __global__ void __launch_bounds__(1024) k_states_warp(WorldView wv, const double
     }
     if (threadIdx.x == 0) {
         s_next = 0u;
+        s_warps_done = 0u;
         mbar_init(&s_table, 1);
         mbar_init_fence();
         const void *tsrc;
@@ -691,8 +778,8 @@ __global__ void __launch_bounds__(1024) k_states_warp(WorldView wv, const double
             __syncwarp();
         }
         EPP_TRACE_EV(g, 4 + 2 * tstep);
-        warp_states_step<BP, S, RS>(world, wv, rec, pts, units, mode, cpg, min_distance, queue, inv, mask + b0 + i * S,
-                                    lane);
+        warp_states_step<BP, S, RS, GA>(world, wv, rec, pts, units, mode, cpg, min_distance, queue, inv,
+                                        mask + b0 + i * S, lane, gv, (size_t)b0 + (size_t)i * S);
         EPP_TRACE_EV(g, 5 + 2 * tstep);
 #ifdef EPP_TRACE
         if (tstep < 3) ++tstep;
@@ -704,6 +791,18 @@ __global__ void __launch_bounds__(1024) k_states_warp(WorldView wv, const double
         }
     }
     EPP_TRACE_EV(g, 15);
+    if (GA) {
+        // this warp is counted (release: its peer stores are ordered before the count); the block's last
+        // consumer warp (acquire) takes the block to the grid-level counter / signal / wait
+        __syncwarp();
+        uint32_t last = 0;
+        if (lane == 0) {
+            uint32_t old;
+            asm volatile("atom.acq_rel.cta.shared.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(smem_addr(&s_warps_done)) : "memory");
+            last = old == consumers - 1u ? 1u : 0u;
+        }
+        if (__shfl_sync(0xffffffffu, last, 0)) gather_finish(gv, lane);
+    }
 }
 
 // ---- K2: segments --------------------------------------------------------------------------
@@ -1052,10 +1151,10 @@ extern "C" int epp_debug_trace_copy(unsigned long long *host, size_t n, int clea
     default: { constexpr int BP = EPP_BP_GRID; __VA_ARGS__; } break;             \
     }
 
-template <int BP, int S, bool RS>
+template <int BP, int S, bool RS, bool GA>
 cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const double *d_xyz, size_t n, int mode,
                                int can_pass_gate, double min_distance, bool in_smem, size_t table_bytes, int stages,
-                               uint32_t *d_mask, cudaStream_t stream, bool &launched)
+                               uint32_t *d_mask, cudaStream_t stream, bool &launched, const GatherView &gv)
 {
     launched = false;
     const size_t words = (n + 31) / 32;
@@ -1085,7 +1184,7 @@ cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const 
     // well defined if chunk i - slots has been consumed, which in-order hand-out guarantees iff slots >= consumers.
     if (cons > (1 << log2_slots)) cons = 1 << log2_slots;
     const size_t smem = table_bytes + rec_bytes + cons * warp_bytes + (slot_bytes << log2_slots);
-    cudaError_t err = cudaFuncSetAttribute(k_states_warp<BP, S, RS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaError_t err = cudaFuncSetAttribute(k_states_warp<BP, S, RS, GA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
     cudaLaunchConfig_t lc = {};
     lc.gridDim = dim3((unsigned)grid);
@@ -1097,18 +1196,40 @@ cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const 
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     lc.attrs = attr;
     lc.numAttrs = cfg.states_pdl ? 1 : 0;
-    err = cudaLaunchKernelEx(&lc, k_states_warp<BP, S, RS>, wv, d_xyz, n, mode | (cfg.states_debug << 8), can_pass_gate,
-                             min_distance, in_smem ? 1 : 0, log2_slots, (uint32_t)table_bytes, (uint32_t)rec_bytes,
-                             (uint32_t)(words / grid), (uint32_t)(words % grid), d_mask);
+    err = cudaLaunchKernelEx(&lc, k_states_warp<BP, S, RS, GA>, wv, d_xyz, n, mode | (cfg.states_debug << 8),
+                             can_pass_gate, min_distance, in_smem ? 1 : 0, log2_slots, (uint32_t)table_bytes,
+                             (uint32_t)rec_bytes, (uint32_t)(words / grid), (uint32_t)(words % grid), d_mask, gv);
     if (err != cudaSuccess) return err;
     launched = true;
     return cudaGetLastError();
 }
 
-cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_xyz, size_t n, int mode,
-                          int can_pass_gate, double min_distance, uint32_t *d_mask, cudaStream_t stream)
+cudaError_t launch_gather_push(const LaunchCfg &cfg, const GatherView &gv, size_t words, cudaStream_t stream)
 {
-    if (n == 0) return cudaSuccess;
+    size_t blocks = (words / 4 + 255) / 256;
+    const size_t cap = (size_t)cfg.sm_count * 4;
+    blocks = blocks < 1 ? 1 : (blocks > cap ? cap : blocks);
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3((unsigned)blocks);
+    lc.blockDim = dim3(256);
+    lc.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = attr;
+    lc.numAttrs = 1;
+    cudaError_t err = cudaLaunchKernelEx(&lc, k_gather_push, gv, words);
+    g_launches++;
+    return err != cudaSuccess ? err : cudaGetLastError();
+}
+
+cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_xyz, size_t n, int mode,
+                          int can_pass_gate, double min_distance, uint32_t *d_mask, cudaStream_t stream,
+                          const GatherView *gv)
+{
+    // A gathering call is a collective: it signals and waits even when this rank has no units.
+    if (n == 0) return gv ? launch_gather_push(cfg, *gv, 0, stream) : cudaSuccess;
+    const GatherView no_gather = {};
     bool in_smem;
     const size_t smem = point_smem_bytes(wv, bp, in_smem);
     cudaError_t err = cudaSuccess;
@@ -1120,14 +1241,17 @@ cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, con
         const bool rs = wv.M <= kRecSmemMax && wv.zrot && cfg.states_rec_smem != 0;
         const int wbp = (bp == EPP_BP_BITS && wv.W == 1 && cfg.states_bits1 != 0) ? kBpBits1 : bp;
         bool launched = false;
-#define EPP_LAUNCH_WARP(S_, RS_)                                                                                       \
-    err = launch_states_warp<BP, S_, RS_>(cfg, wv, d_xyz, n, mode, can_pass_gate, min_distance, in_smem, table_bytes, \
-                                          stages, d_mask, stream, launched)
-#define EPP_LAUNCH_WARP_S()                      \
-    if (S == 8 && rs) EPP_LAUNCH_WARP(8, true);  \
-    else if (S == 8) EPP_LAUNCH_WARP(8, false);  \
-    else if (rs) EPP_LAUNCH_WARP(4, true);       \
-    else EPP_LAUNCH_WARP(4, false)
+#define EPP_LAUNCH_WARP(S_, RS_, GA_)                                                                                 \
+    err = launch_states_warp<BP, S_, RS_, GA_>(cfg, wv, d_xyz, n, mode, can_pass_gate, min_distance, in_smem,          \
+                                               table_bytes, stages, d_mask, stream, launched, gv ? *gv : no_gather)
+        // the fused exchange exists for the default chunk size; S = 8 (a tuning knob) takes the push kernel
+#define EPP_LAUNCH_WARP_S()                                  \
+    if (S == 8 && rs) EPP_LAUNCH_WARP(8, true, false);       \
+    else if (S == 8) EPP_LAUNCH_WARP(8, false, false);       \
+    else if (rs && gv) EPP_LAUNCH_WARP(4, true, true);       \
+    else if (rs) EPP_LAUNCH_WARP(4, true, false);            \
+    else if (gv) EPP_LAUNCH_WARP(4, false, true);            \
+    else EPP_LAUNCH_WARP(4, false, false)
         if (wbp == kBpBits1) {
             constexpr int BP = kBpBits1;
             EPP_LAUNCH_WARP_S();
@@ -1139,6 +1263,7 @@ cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, con
         if (err != cudaSuccess) return err;
         if (launched) {
             g_launches++;
+            if (gv && S == 8) return launch_gather_push(cfg, *gv, (n + 31) / 32, stream);
             return cudaSuccess;
         }
     }
@@ -1152,13 +1277,14 @@ cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, con
         }
     });
     g_launches++;
+    if (err == cudaSuccess && gv) err = launch_gather_push(cfg, *gv, (n + 31) / 32, stream);
     return err;
 }
 
 cudaError_t launch_segments(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_a, const double *d_b,
-                            size_t n, int can_pass_gate, uint32_t *d_mask, cudaStream_t stream)
+                            size_t n, int can_pass_gate, uint32_t *d_mask, cudaStream_t stream, const GatherView *gv)
 {
-    if (n == 0) return cudaSuccess;
+    if (n == 0) return gv ? launch_gather_push(cfg, *gv, 0, stream) : cudaSuccess;
     bool in_smem;
     const size_t smem = ray_smem_bytes(wv, bp, in_smem);
     const size_t tiles = (n + kBlock - 1) / kBlock;
@@ -1172,6 +1298,7 @@ cudaError_t launch_segments(const LaunchCfg &cfg, const WorldView &wv, int bp, c
         }
     });
     g_launches++;
+    if (err == cudaSuccess && gv) err = launch_gather_push(cfg, *gv, (n + 31) / 32, stream);
     return err;
 }
 

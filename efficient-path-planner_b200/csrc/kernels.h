@@ -23,15 +23,38 @@ struct LaunchCfg {
     int states_pdl = 1;             // warp form: programmatic dependent launch (prologue overlaps the previous kernel's tail)
     int states_bits1 = 1;           // warp form: single-word candidate masks for worlds of <= 32 OBBs
     int states_rec_smem = 1;        // warp-pipelined form: fold the world records into shared memory (M <= 64)
+    int gather_debug = 0;           // profiling only, see GatherView::debug
     int states_per_thread = 0;      // warp form: mask words (32 states) per chunk and warp step, 4 (default) or 8
 };
 
 extern std::atomic<uint64_t> g_launches;
 
+// Mask exchange between the GPUs of one box, written by the check kernels themselves.  Every
+// rank owns a "gathered" buffer of world x slot_words mask words; a gathering check writes the words of its
+// units into slot `rank` of that buffer ON EVERY RANK (peer stores over NVLink), then its last block raises
+// the call's sequence number in every peer's signal array and waits until every peer has raised it here.
+// When the kernel has ended, the local gathered buffer holds the words of all ranks: an all-gather with no
+// collective launch behind the kernel.
+constexpr int kMaxRanks = 8;
+struct GatherView {
+    uint32_t *peer[kMaxRanks];     // rank p's gathered buffer (of this call) in this process's address space
+    uint32_t *peer_sig[kMaxRanks]; // rank p's signal array (kMaxRanks words); this rank raises word [rank]
+    uint32_t *my_sig;              // this rank's signal array
+    uint32_t *ctl;                 // local: [0] blocks done, [1] sequence number, [2] wait time-outs
+    uint64_t my_off;               // word offset of this rank's slot = rank * slot_words
+    uint64_t timeout_ns;           // bound on the wait for the peers (a peer that never calls must not hang the GPU)
+    int world, rank;
+    int debug; // profiling only (tuning knob gather_debug): 1 no wait, 2 no peer stores, 4 no signal (wrong results)
+};
+
 cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_xyz, size_t n, int mode,
-                          int can_pass_gate, double min_distance, uint32_t *d_mask, cudaStream_t stream);
+                          int can_pass_gate, double min_distance, uint32_t *d_mask, cudaStream_t stream,
+                          const GatherView *gv = nullptr);
 cudaError_t launch_segments(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_a, const double *d_b,
-                            size_t n, int can_pass_gate, uint32_t *d_mask, cudaStream_t stream);
+                            size_t n, int can_pass_gate, uint32_t *d_mask, cudaStream_t stream,
+                            const GatherView *gv = nullptr);
+// Push words [my_off, my_off + words) of the local gathered buffer to every peer, signal and wait.
+cudaError_t launch_gather_push(const LaunchCfg &cfg, const GatherView &gv, size_t words, cudaStream_t stream);
 cudaError_t launch_trajectories(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_mats, size_t n_traj,
                                 size_t rows, size_t ld, size_t traj_stride, double min_distance, uint32_t *d_traj_valid,
                                 uint32_t *d_sample_mask, int64_t *d_first_invalid, long long *d_first_scratch,

@@ -175,6 +175,45 @@ int epp_shard_range(size_t n, int rank, int world_size, size_t align, size_t *be
 int epp_mask_summary_dev(const uint32_t *d_mask, size_t n_words, uint64_t first_word, uint64_t *d_popcount_xor,
                          void *stream);
 
+/* ---- Mask exchange fused into the check kernels --------------------------
+ *
+ * One epp_gather per rank (= per GPU; one process per GPU, or several handles in one process).
+ * It owns `n_buffers` gathered buffers of world_size x slot_words mask words in device memory.
+ * A gathering check writes the words of this rank's units into slot `rank` of buffer `buffer`
+ * ON EVERY RANK, straight from the check kernel with stores over NVLink, and the kernel ends
+ * only when the slots of all peers have arrived here: when it has completed in stream order,
+ * epp_gather_buffer(g, buffer) holds the all-gathered mask — no collective launch follows the
+ * kernel.  Gathering calls are collective: every rank issues the same sequence of them on one
+ * stream each; a peer that does not show up within the time-out (default 2 s) is counted in
+ * epp_gather_status and the kernel ends, it never hangs the GPU.  A buffer may be rewritten
+ * once the calls on the other buffers in between have completed (use n_buffers >= 2). */
+typedef struct epp_gather epp_gather;
+#define EPP_GATHER_HANDLE_BYTES 64
+#define EPP_GATHER_MAX_RANKS 8
+
+int epp_gather_create(int rank, int world_size, size_t slot_words, int n_buffers, epp_gather **out);
+int epp_gather_destroy(epp_gather *g);
+/* Inter-process: export this rank's allocation (a CUDA IPC handle), exchange the handles by
+ * any means (torch.distributed, MPI, a file), connect with all of them in rank order. */
+int epp_gather_export(epp_gather *g, unsigned char handle[EPP_GATHER_HANDLE_BYTES]);
+int epp_gather_connect(epp_gather *g, const unsigned char *handles /* world_size x 64 B */);
+/* In-process (one host process driving several GPUs, or several ranks on one GPU in tests):
+ * connects all handles with each other; enables peer access between their devices. */
+int epp_gather_connect_local(epp_gather *const *all, int world_size);
+/* Device pointer of gathered buffer `buffer` (world_size x slot_words words, rank-major). */
+int epp_gather_buffer(epp_gather *g, int buffer, uint32_t **d_words);
+int epp_gather_set_timeout_ms(epp_gather *g, unsigned ms);
+/* Calls completed so far on this rank and how many of their waits timed out (synchronises the device). */
+int epp_gather_status(epp_gather *g, uint64_t *calls, uint64_t *timeouts);
+
+/* epp_check_states_dev / epp_check_segments_dev for this rank's n units + the exchange. */
+int epp_check_states_gather_dev(epp_world *w, const double *d_xyz, size_t n, int can_pass_gate,
+                                epp_gather *g, int buffer, void *stream);
+int epp_check_states_mindist_gather_dev(epp_world *w, const double *d_xyz, size_t n, double min_distance,
+                                        epp_gather *g, int buffer, void *stream);
+int epp_check_segments_gather_dev(epp_world *w, const double *d_a, const double *d_b, size_t n,
+                                  int can_pass_gate, epp_gather *g, int buffer, void *stream);
+
 /* ---- Synthetic inputs generated on the device (counter based, bit-identical to the
  *      oracle's host generators; DESIGN.md "Synthetic inputs") -------------------------- */
 

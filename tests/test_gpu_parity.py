@@ -435,3 +435,125 @@ def test_states_warp_form_ring_wrap_stress(oracle, config, track):
     finally:
         for k, v in saved.items():
             epp_b200.set_tuning(k, v)
+
+
+# ---- mask exchange fused into the check kernels (epp_gather) -------------------------------------------
+
+def _run_logical_ranks(gathers, fn):
+    """Issue fn(rank, gather) for every logical rank on its own stream (the calls wait for each other on
+    the device, so they must be able to run concurrently), then synchronise."""
+    import torch
+    streams = [torch.cuda.Stream() for _ in gathers]
+    torch.cuda.synchronize()
+    for r, (g, st) in enumerate(zip(gathers, streams)):
+        with torch.cuda.stream(st):
+            fn(r, g)
+    torch.cuda.synchronize()
+
+
+@pytest.mark.parametrize("world_size", [2, 3])
+@pytest.mark.parametrize("n", [100_000, 3_000, 1 << 20])
+def test_gather_states_logical_ranks(oracle, config, track, world_size, n):
+    """world_size logical ranks on ONE GPU (in-process peers): the fused exchange of the warp form
+    (n >= 4096 per rank) and the push kernel behind the direct form leave the all-gathered mask, equal to
+    the oracle's, in every rank's buffer; sequence numbers survive repeated calls and both buffers."""
+    import torch
+    from epp_b200 import sharding
+    g, o, lo, hi = track
+    ow, gw = build_pair(oracle, epp_b200, config, g, o)
+    xyz = worlds.gen_states(worlds.SEED_STATES, 777, n, lo, hi)
+    want = ow.check_states(xyz, threads=8)
+    d_xyz = torch.from_numpy(xyz).cuda()
+    sw = sharding.slot_words(n, world_size)
+    gathers = [epp_b200.Gather(r, world_size, sw, n_buffers=2) for r in range(world_size)]
+    epp_b200.Gather.connect_local(gathers)
+    for call in range(4):
+        buf = call & 1
+        for gth in gathers:
+            gth.tensor(buf).fill_(-1 if call < 2 else 0)  # stale contents must be overwritten
+        torch.cuda.synchronize()
+
+        def issue(r, gth):
+            b, e = epp_b200.shard_range(n, r, world_size, 1024)
+            gth.check_states(gw, d_xyz[b:e], buf)
+
+        _run_logical_ranks(gathers, issue)
+        for r, gth in enumerate(gathers):
+            t = gth.tensor(buf)
+            # words beyond a rank's units are not part of the exchange: assemble() reads only the live ones
+            got = sharding.assemble(t, n)
+            assert mismatches(got, want) == 0, "rank %d call %d" % (r, call)
+    for gth in gathers:
+        calls, timeouts = gth.status()
+        assert calls == 4 and timeouts == 0
+
+
+def test_gather_segments_and_mindist_logical_ranks(oracle, config):
+    import torch
+    from epp_b200 import sharding
+    g, o, lo, hi = worlds.world_256()
+    ow, gw = build_pair(oracle, epp_b200, config, g, o)
+    world_size, n = 2, 150_001
+    a, b = worlds.gen_segments(worlds.SEED_SEGMENTS, 5, n, lo, hi, 1.0)
+    want_seg = ow.check_segments(a, b, threads=8)
+    want_md = ow.check_states_mindist(a, 0.3, threads=8)
+    d_a, d_b = torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()
+    sw = sharding.slot_words(n, world_size)
+    gathers = [epp_b200.Gather(r, world_size, sw, n_buffers=2) for r in range(world_size)]
+    epp_b200.Gather.connect_local(gathers)
+
+    def seg(r, gth):
+        lo_, hi_ = epp_b200.shard_range(n, r, world_size, 1024)
+        gth.check_segments(gw, d_a[lo_:hi_], d_b[lo_:hi_], 0)
+
+    def md(r, gth):
+        lo_, hi_ = epp_b200.shard_range(n, r, world_size, 1024)
+        gth.check_states(gw, d_a[lo_:hi_], 1, min_distance=0.3)
+
+    _run_logical_ranks(gathers, seg)
+    _run_logical_ranks(gathers, md)
+    for gth in gathers:
+        assert mismatches(sharding.assemble(gth.tensor(0), n), want_seg) == 0
+        assert mismatches(sharding.assemble(gth.tensor(1), n), want_md) == 0
+        assert gth.status() == (2, 0)
+
+
+def test_gather_missing_peer_times_out_instead_of_hanging(oracle, config, track):
+    """A peer that never issues its call must not hang the GPU: the wait is bounded and counted."""
+    import torch
+    g, o, lo, hi = track
+    ow, gw = build_pair(oracle, epp_b200, config, g, o)
+    n = 50_000
+    d_xyz = epp_b200.gen_states_dev(worlds.SEED_STATES, 0, n, lo, hi)
+    gathers = [epp_b200.Gather(r, 2, 2048, n_buffers=1) for r in range(2)]
+    epp_b200.Gather.connect_local(gathers)
+    gathers[0].set_timeout_ms(50)
+    gathers[0].check_states(gw, d_xyz, 0)
+    torch.cuda.synchronize()
+    calls, timeouts = gathers[0].status()
+    assert calls == 1 and timeouts == 1
+    # the local slot is still correct
+    want = gw.check_states_dev(d_xyz)
+    assert torch.equal(gathers[0].tensor(0)[0][: (n + 31) // 32], want)
+
+
+def test_gather_argument_errors(config, track):
+    g, o, lo, hi = track
+    gw = epp_b200.World(config)
+    gw.parse_gates_and_obstacles(g, o)
+    with pytest.raises(epp_b200.EppError):
+        epp_b200.Gather(0, 9, 1024)          # more than 8 ranks
+    with pytest.raises(epp_b200.EppError):
+        epp_b200.Gather(2, 2, 1024)          # rank out of range
+    gth = epp_b200.Gather(0, 2, 1024)
+    d_xyz = epp_b200.gen_states_dev(worlds.SEED_STATES, 0, 1024, lo, hi)
+    with pytest.raises(epp_b200.EppError):
+        gth.check_states(gw, d_xyz, 0)       # not connected
+    one = epp_b200.Gather(0, 1, 28)
+    with pytest.raises(epp_b200.EppError):
+        one.check_states(gw, d_xyz, 0)       # 1024 states need 32 words, the slot holds 28
+    with pytest.raises(epp_b200.EppError):
+        one.check_states(gw, d_xyz[:64], 2)  # buffer index out of range (n_buffers = 2)
+    one.check_states(gw, d_xyz[:512], 0)     # world_size 1: a plain check into the buffer
+    import torch
+    assert torch.equal(one.tensor(0)[0][:16], gw.check_states_dev(d_xyz[:512]))
