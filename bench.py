@@ -63,7 +63,7 @@ def parse_args():
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-extras", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
-    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl"],
+    ap.add_argument("--exchange", default="fused", choices=["fused", "nccl", "none", "none-ipc"],
                     help="N > 1: mask exchange fused into the check kernel (default) or NCCL all-gather")
     ap.add_argument("--tune", action="append", default=[], metavar="KEY=VALUE",
                     help="epp_set_tuning knob (profiling sweeps; the default run sets none)")
@@ -209,16 +209,22 @@ def run_b200(args):
     # (kernel writes row r locally, in-place NCCL all-gather behind it) for comparison.
     gather = None
     exchange = "none (single GPU)"
+    ipc_probe = None
+    if world > 1 and args.exchange == "none-ipc":  # profiling only: plain kernels writing into IPC-exported memory
+        ipc_probe = epp_b200.Gather(rank, world, words, n_buffers=2).connect()
     if world > 1 and args.exchange == "fused":
         try:
             gather = epp_b200.Gather(rank, world, words, n_buffers=2).connect()
             gathered = [gather.tensor(0, dev), gather.tensor(1, dev)]
-            exchange = "fused: peer stores from the check kernel + signal/wait in its last block"
+            exchange = ("fused: every mask word goes to every peer as a (word, call number) pair straight from "
+                        "the check kernel; its warps unpack the peers' pairs; no collective launch")
         except epp_b200.EppError as ex:  # CUDA IPC not permitted on this box: say so, use NCCL
             gather = None
             exchange = "nccl all-gather (fused exchange unavailable: %s)" % ex
     if gather is None:
         gathered = [torch.zeros((world, words), dtype=torch.int32, device=dev) for _ in range(2)]
+        if ipc_probe is not None:
+            gathered = [ipc_probe.tensor(0, dev), ipc_probe.tensor(1, dev)]
         if world > 1 and not exchange.startswith("nccl"):
             exchange = "nccl all-gather, in place"
     torch.cuda.synchronize()
@@ -236,7 +242,7 @@ def run_b200(args):
             gw.check_segments_dev(ring[s % RING][0], ring[s % RING][1], mask=mine)
         else:
             gw.check_states_dev(ring[s % RING][0], mask=mine)
-        if world > 1:
+        if world > 1 and not args.exchange.startswith("none"):  # "none*": profiling only, the ranks never exchange
             dist.all_gather_into_tensor(buf.view(-1), mine)
 
     K, W = args.steps, args.warmup
@@ -244,7 +250,7 @@ def run_b200(args):
     sampler.start()
 
     # ---- value: device-resident inputs ------------------------------------------------------
-    use_graph = (world == 1 or gather is not None) and not args.no_graph and K >= RING
+    use_graph = (world == 1 or gather is not None or args.exchange.startswith("none")) and not args.no_graph and K >= RING
     for s in range(max(W, 3)):
         step_dev(s)
     torch.cuda.synchronize()

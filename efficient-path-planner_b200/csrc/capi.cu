@@ -60,7 +60,8 @@ Knob g_knobs[] = {
     {"states_bits1", {1}},
     {"states_pdl", {1}},
     {"states_debug", {0}},               // profiling builds only
-    {"gather_debug", {0}},               // profiling only: 1 no wait, 2 no peer stores, 4 no signal
+    {"gather_debug", {0}},               // profiling only: 1 no wait/unpack, 2 no peer stores
+    {"sm_limit", {0}},                   // 0: all SMs; > 0: size grids for this many SMs (several ranks on one GPU in tests)
     {"bits_bins", {0}},                  // 0: by world size
     {"grid_max_cells", {1 << 22}},
     {"bits_max_obbs", {1024}},
@@ -231,6 +232,8 @@ LaunchCfg launch_cfg(const DeviceEpoch &ep)
 {
     LaunchCfg c;
     c.sm_count = ep.sm_count;
+    const int sm_limit = knob_value("sm_limit");
+    if (sm_limit > 0 && sm_limit < c.sm_count) c.sm_count = sm_limit;
     c.states_blocks_per_sm = knob_value("states_blocks_per_sm");
     c.segments_blocks_per_sm = knob_value("segments_blocks_per_sm");
     c.states_variant = knob_value("states_variant");
@@ -803,18 +806,21 @@ extern "C" int epp_check_poly_trajectories_dev(epp_world *w, const double *d_coe
 struct epp_gather {
     int rank = 0, world = 1, device = 0, n_buffers = 1;
     size_t slot_words = 0;
-    unsigned char *base = nullptr;            // [signals + control: 256 B][n_buffers x world x slot_words words]
+    // [control words: 256 B][n_buffers x world x slot_words words][staging: 2 x world x (2 + slot_words) pairs]
+    unsigned char *base = nullptr;
     unsigned char *peer_base[kMaxRanks] = {}; // every rank's allocation in this process's address space
     bool opened[kMaxRanks] = {};              // peer_base[p] came from cudaIpcOpenMemHandle
     bool connected = false;
     uint64_t timeout_ns = 2000000000ull;
     size_t buffer_bytes() const { return (size_t)world * slot_words * 4; }
     uint32_t *buffer_of(unsigned char *b, int i) const { return (uint32_t *)(b + 256 + (size_t)i * buffer_bytes()); }
+    size_t staging_off() const { return (256 + (size_t)n_buffers * buffer_bytes() + 255) / 256 * 256; }
+    size_t staging_bytes() const { return (size_t)2 * world * (slot_words + 2) * 8; }
 };
 
 namespace {
 
-constexpr size_t kGatherCtlOff = 128; // signals at +0 (kMaxRanks words), control words at +128
+constexpr size_t kGatherCtlOff = 0; // control words: blocks done, calls completed, time-outs
 
 int gather_view(epp_gather *g, int buffer, size_t n, GatherView &gv)
 {
@@ -822,13 +828,13 @@ int gather_view(epp_gather *g, int buffer, size_t n, GatherView &gv)
     if (!g->connected) return fail(EPP_ERR_INVALID_ARG, "gather is not connected to its peers");
     if (buffer < 0 || buffer >= g->n_buffers) return fail(EPP_ERR_INVALID_ARG, "gather buffer index");
     if ((n + 31) / 32 > g->slot_words) return fail(EPP_ERR_INVALID_ARG, "more units than the gather slot holds");
-    for (int p = 0; p < kMaxRanks; ++p) {
-        gv.peer[p] = p < g->world ? g->buffer_of(g->peer_base[p], buffer) : nullptr;
-        gv.peer_sig[p] = p < g->world ? (uint32_t *)g->peer_base[p] : nullptr;
-    }
-    gv.my_sig = (uint32_t *)g->base;
+    for (int p = 0; p < kMaxRanks; ++p)
+        gv.peer_ll[p] = p < g->world ? (uint2 *)(g->peer_base[p] + g->staging_off()) : nullptr;
+    gv.my_ll = (const uint2 *)(g->base + g->staging_off());
+    gv.out = g->buffer_of(g->base, buffer);
     gv.ctl = (uint32_t *)(g->base + kGatherCtlOff);
-    gv.my_off = (uint64_t)g->rank * g->slot_words;
+    gv.slot_words = g->slot_words;
+    gv.my_words = (n + 31) / 32;
     gv.timeout_ns = g->timeout_ns;
     gv.world = g->world;
     gv.rank = g->rank;
@@ -850,7 +856,7 @@ extern "C" int epp_gather_create(int rank, int world_size, size_t slot_words, in
     g->slot_words = slot_words;
     g->n_buffers = n_buffers;
     EPP_CUDA(cudaGetDevice(&g->device));
-    const size_t bytes = 256 + (size_t)n_buffers * g->buffer_bytes();
+    const size_t bytes = g->staging_off() + g->staging_bytes();
     EPP_CUDA(cudaMalloc((void **)&g->base, bytes));
     EPP_CUDA(cudaMemset(g->base, 0, bytes));
     EPP_CUDA(cudaDeviceSynchronize());
@@ -969,7 +975,7 @@ extern "C" int epp_check_states_gather_dev(epp_world *w, const double *d_xyz, si
     rc = gather_view(g, buffer, n, gv);
     if (rc) return rc;
     cudaError_t e = launch_states(launch_cfg(*ep), ep->view, ep->bp, d_xyz, n, kModeBool, can_pass_gate, 0.0,
-                                  gv.peer[gv.rank] + gv.my_off, (cudaStream_t)stream, g->world > 1 ? &gv : nullptr);
+                                  gv.out + (size_t)gv.rank * gv.slot_words, (cudaStream_t)stream, g->world > 1 ? &gv : nullptr);
     return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
 }
 
@@ -984,7 +990,7 @@ extern "C" int epp_check_states_mindist_gather_dev(epp_world *w, const double *d
     rc = gather_view(g, buffer, n, gv);
     if (rc) return rc;
     cudaError_t e = launch_states(launch_cfg(*ep), ep->view, ep->bp, d_xyz, n, kModeMinDist, 0, min_distance,
-                                  gv.peer[gv.rank] + gv.my_off, (cudaStream_t)stream, g->world > 1 ? &gv : nullptr);
+                                  gv.out + (size_t)gv.rank * gv.slot_words, (cudaStream_t)stream, g->world > 1 ? &gv : nullptr);
     return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
 }
 
@@ -999,7 +1005,7 @@ extern "C" int epp_check_segments_gather_dev(epp_world *w, const double *d_a, co
     rc = gather_view(g, buffer, n, gv);
     if (rc) return rc;
     cudaError_t e = launch_segments(launch_cfg(*ep), ep->view, ep->bp, d_a, d_b, n, can_pass_gate,
-                                    gv.peer[gv.rank] + gv.my_off, (cudaStream_t)stream, g->world > 1 ? &gv : nullptr);
+                                    gv.out + (size_t)gv.rank * gv.slot_words, (cudaStream_t)stream, g->world > 1 ? &gv : nullptr);
     return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
 }
 

@@ -440,80 +440,116 @@ __global__ void k_trace_base(uint32_t base) { g_trace_base = base; }
 
 
 // ---- mask exchange over peer memory (GatherView, kernels.h) --------------------------------------------
-//
-// Called by ONE warp of a block after every peer store of the block has been followed by
-// __threadfence_system() in the storing thread and the block's threads have met (barrier or counter).
-// The last block of the grid raises this call's sequence number on every peer and waits for theirs.
-__device__ __forceinline__ uint32_t ld_relaxed_sys(const uint32_t *p)
+
+// This call's number = calls completed + 1, read by ONE thread per block at its start (after the previous
+// launch on the gather has completed).  The block that reads last closes the count for the next launch, so
+// nothing is left to do at the tail of the kernel.  Requires what the launchers guarantee: the next launch on
+// this gather does not read before this grid has completed (stream order / griddepcontrol.wait).
+__device__ __forceinline__ uint32_t gather_seq(const GatherView &gv)
 {
     uint32_t v;
-    asm volatile("ld.relaxed.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
-    return v;
-}
-
-__device__ __forceinline__ void st_relaxed_sys(uint32_t *p, uint32_t v)
-{
-    asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(p), "r"(v) : "memory");
-}
-
-// Ordering (the chain NCCL's own protocols rely on): a thread's peer stores -> block-level meeting (barrier
-// or release/acquire counter) -> ONE thread: fence.gpu + grid counter -> last block: ONE fence.sys, then
-// relaxed stores of the sequence number to the peers.  Causality is cumulative across the scopes, so a peer
-// that has observed the sequence number observes every word of every block.
-__device__ __forceinline__ void gather_finish(const GatherView &gv, int lane)
-{
-    uint32_t seq = 0;
-    if (lane == 0) {
-        __threadfence();
-        if (atomicAdd(&gv.ctl[0], 1u) == gridDim.x - 1u) {
-            __threadfence_system();
-            seq = gv.ctl[1] + 1u; // launches on one gather are stream ordered: only this thread touches it now
-            gv.ctl[0] = 0u;
-            gv.ctl[1] = seq;
-        }
+    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(gv.ctl + 1) : "memory");
+    if (atomicAdd(&gv.ctl[0], 1u) == gridDim.x - 1u) {
+        gv.ctl[0] = 0u;
+        asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(gv.ctl + 1), "r"(v + 1u) : "memory");
     }
-    seq = __shfl_sync(0xffffffffu, seq, 0);
-    if (seq == 0u) return;
-    if (lane < gv.world && lane != gv.rank) {
-        if (!(gv.debug & 4)) st_relaxed_sys(gv.peer_sig[lane] + gv.rank, seq);
-        if (!(gv.debug & 1)) {
-            unsigned long long t0, t;
-            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t0));
-            while ((int32_t)(ld_relaxed_sys(gv.my_sig + lane) - seq) < 0) {
-                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
-                if (t - t0 > gv.timeout_ns) {
-                    atomicAdd(&gv.ctl[2], 1u);
-                    break;
-                }
+    return v + 1u;
+}
+
+// pair index of word 0 of (parity of seq, source rank) in a staging area
+__device__ __forceinline__ uint64_t gather_row(const GatherView &gv, uint32_t seq, int src)
+{
+    return ((uint64_t)(seq & 1u) * (uint64_t)gv.world + (uint64_t)src) * (gv.slot_words + 2u) + 2u;
+}
+
+__device__ __forceinline__ void ll_store(uint2 *p, uint32_t word, uint32_t seq)
+{
+    asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(word), "r"(seq) : "memory");
+}
+
+// Wait until the pair carries this call's sequence number (8-byte stores are single-copy atomic, so the word
+// next to it is the word of this call).  Bounded: a time-out is counted and reads as 0.
+__device__ __forceinline__ uint32_t ll_wait(const uint2 *p, uint32_t seq, const GatherView &gv, bool &dead)
+{
+    uint32_t w, f, spins = 0;
+    unsigned long long t0 = 0, t;
+    for (;;) {
+        asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(w), "=r"(f) : "l"(p) : "memory");
+        if (f == seq) return w;
+        if (dead) return 0u; // this thread has already waited one full time-out in this call
+        if ((++spins & 63u) == 0u) {
+            asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+            if (t0 == 0) t0 = t;
+            else if (t - t0 > gv.timeout_ns) {
+                atomicAdd(&gv.ctl[2], 1u);
+                dead = true;
+                return 0u;
             }
         }
     }
-    __syncwarp();
-    __threadfence_system();
 }
 
-// Generic push: any check kernel wrote this rank's words into its own slot of the local gathered buffer;
-// copy the slot to every peer (16 B vector stores where the slot allows), then signal and wait.
-__global__ void __launch_bounds__(256) k_gather_push(GatherView gv, size_t words)
+// One thread per peer announces how many words this rank sends in this call.
+__device__ __forceinline__ void gather_send_header(const GatherView &gv, uint32_t seq, int lane)
 {
-    __shared__ uint32_t s_warps_done;
-    if (threadIdx.x == 0) s_warps_done = 0u;
-    __syncthreads();
-    asm volatile("griddepcontrol.wait;" ::: "memory");
-    const uint32_t *src = gv.peer[gv.rank] + gv.my_off;
-    const bool vec = ((gv.my_off & 3u) == 0) && ((reinterpret_cast<uintptr_t>(gv.peer[gv.rank]) & 15u) == 0);
-    const size_t stride = (size_t)gridDim.x * blockDim.x, t0 = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (lane < gv.world && lane != gv.rank && !(gv.debug & 2))
+        ll_store(gv.peer_ll[lane] + gather_row(gv, seq, gv.rank) - 2u, (uint32_t)gv.my_words, seq);
+}
+
+// How many words each peer sends in this call (its header pair), one lane per peer, into cnt[] (shared memory).
+// One warp per BLOCK does this: thousands of warps polling one address would serialise on its L2 slice.
+__device__ __forceinline__ void gather_read_headers(const GatherView &gv, uint32_t seq, uint32_t *cnt, int lane)
+{
+    bool dead = false;
+    if (lane < gv.world && lane != gv.rank) cnt[lane] = ll_wait(gv.my_ll + gather_row(gv, seq, lane) - 2, seq, gv, dead);
+}
+
+// A warp unpacks words [u0, u1) of every peer's slot into the local gathered buffer (0 beyond what the peer sends).
+__device__ __forceinline__ void gather_unpack(const GatherView &gv, uint32_t seq, const uint32_t *cnt, uint64_t u0,
+                                              uint64_t u1, int lane)
+{
+    bool dead = false;
     for (int p = 0; p < gv.world; ++p) {
-        if (p == gv.rank) continue;
-        uint32_t *dst = gv.peer[p] + gv.my_off;
-        const bool v = vec && ((reinterpret_cast<uintptr_t>(gv.peer[p]) & 15u) == 0);
-        const size_t quads = v ? words / 4 : 0;
-        for (size_t i = t0; i < quads; i += stride)
-            reinterpret_cast<uint4 *>(dst)[i] = reinterpret_cast<const uint4 *>(src)[i];
-        for (size_t i = quads * 4 + t0; i < words; i += stride) dst[i] = src[i];
+        uint32_t *dst = gv.out + (uint64_t)p * gv.slot_words;
+        if (p == gv.rank) { // own slot: the check wrote words [0, my_words); the rest of the slot reads 0
+            for (uint64_t w = (u0 > gv.my_words ? u0 : gv.my_words) + (uint64_t)lane; w < u1; w += 32u) dst[w] = 0u;
+            continue;
+        }
+        const uint2 *src = gv.my_ll + gather_row(gv, seq, p);
+        const uint64_t n = cnt[p];
+        for (uint64_t w = u0 + (uint64_t)lane; w < u1; w += 32u) dst[w] = w < n ? ll_wait(src + w, seq, gv, dead) : 0u;
     }
+}
+
+// Generic form: any check kernel wrote this rank's words into its own slot of the local gathered buffer;
+// send them to every peer as (word, sequence number) pairs, then unpack the peers' slots.
+__global__ void __launch_bounds__(256) k_gather_push(const __grid_constant__ GatherView gv)
+{
+    __shared__ uint32_t s_seq, s_cnt[kMaxRanks];
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (threadIdx.x == 0) s_seq = gather_seq(gv);
     __syncthreads();
-    if (threadIdx.x < 32) gather_finish(gv, threadIdx.x);
+    const uint32_t seq = s_seq;
+    const int lane = threadIdx.x & 31;
+    if (blockIdx.x == 0 && threadIdx.x < 32) gather_send_header(gv, seq, lane);
+    const uint32_t *src = gv.out + (uint64_t)gv.rank * gv.slot_words;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x, t0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (!(gv.debug & 2))
+        for (int p = 0; p < gv.world; ++p) {
+            if (p == gv.rank) continue;
+            uint2 *dst = gv.peer_ll[p] + gather_row(gv, seq, gv.rank);
+            for (uint64_t i = t0; i < gv.my_words; i += stride) ll_store(dst + i, src[i], seq);
+        }
+    // this block's share of the peers' slots, a warp at a time
+    const uint64_t warps = (uint64_t)gridDim.x * (blockDim.x >> 5), wid = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const uint64_t per = (gv.slot_words + warps - 1) / warps;
+    const uint64_t u0 = wid * per < gv.slot_words ? wid * per : gv.slot_words;
+    const uint64_t u1 = u0 + per < gv.slot_words ? u0 + per : gv.slot_words;
+    if (!(gv.debug & 1)) {
+        if (threadIdx.x < 32) gather_read_headers(gv, seq, s_cnt, lane);
+        __syncthreads();
+        gather_unpack(gv, seq, s_cnt, u0, u1, lane);
+    }
 }
 
 constexpr int kRecDoubles = 17;
@@ -534,7 +570,7 @@ __device__ __forceinline__ void warp_states_step(const PointWorld<BP> &world, co
                                                  const double *__restrict__ rec, const double *__restrict__ pts,
                                                  int units, int mode, bool cpg, double md, unsigned char *queue,
                                                  uint32_t *inv, uint32_t *__restrict__ mask_out, int lane,
-                                                 const GatherView &gv, size_t word0)
+                                                 const GatherView &gv, uint32_t seq, uint64_t ll_word0)
 {
     // ---- phase 1: which of my S states have a broad-phase candidate at all
     const uint32_t lt = (1u << lane) - 1u;
@@ -577,9 +613,9 @@ __device__ __forceinline__ void warp_states_step(const PointWorld<BP> &world, co
         const uint32_t active = live >= 32 ? 0xffffffffu : ((1u << live) - 1u);
         const uint32_t verdict = ~inv[lane] & active;
         mask_out[lane] = verdict;
-        if (GA && !(gv.debug & 2)) { // the same word into this rank's slot of every peer's gathered buffer (NVLink stores)
+        if (GA && !(gv.debug & 2)) { // the same word, with this call's number, into every peer's staging row of this rank
             for (int p = 0; p < gv.world; ++p)
-                if (p != gv.rank) gv.peer[p][gv.my_off + word0 + lane] = verdict;
+                if (p != gv.rank) ll_store(gv.peer_ll[p] + ll_word0 + lane, verdict, seq);
         }
         inv[lane] = 0u;
     }
@@ -613,9 +649,9 @@ __global__ void __launch_bounds__(1024) k_states_warp(WorldView wv, const double
                                                       int can_pass_gate, double min_distance, int aabb_in_smem,
                                                       int log2_slots, uint32_t table_bytes, uint32_t rec_bytes,
                                                       uint32_t wpb, uint32_t rem, uint32_t *__restrict__ mask,
-                                                      GatherView gv)
+                                                      const __grid_constant__ GatherView gv)
 {
-    __shared__ uint32_t s_warps_done; // GA: consumer warps that have finished (the last one runs gather_finish)
+    __shared__ uint32_t s_seq, s_hdr, s_cnt[kMaxRanks]; // GA: call number; header state (0 none, 1 claimed, 2 read)
     __shared__ __align__(8) uint64_t s_full[kMaxSlots];
     __shared__ __align__(8) uint64_t s_empty[kMaxSlots];
     __shared__ __align__(8) uint64_t s_table;
@@ -660,7 +696,7 @@ __global__ void __launch_bounds__(1024) k_states_warp(WorldView wv, const double
     }
     if (threadIdx.x == 0) {
         s_next = 0u;
-        s_warps_done = 0u;
+        s_hdr = 0u;
         mbar_init(&s_table, 1);
         mbar_init_fence();
         const void *tsrc;
@@ -723,6 +759,9 @@ __global__ void __launch_bounds__(1024) k_states_warp(WorldView wv, const double
 
     // ---- consumers
     const uint32_t c = (uint32_t)warp - 1u;
+    uint32_t seq = 0;
+    uint64_t ll_row = 0;
+    if (GA && threadIdx.x == 32) s_seq = (gv.debug & 4) ? 1u : gather_seq(gv); // one read per block, published by the barrier below
 #ifdef EPP_TRACE
     const uint32_t g = blockIdx.x * consumers + c;
     int tstep = 0;
@@ -747,6 +786,11 @@ __global__ void __launch_bounds__(1024) k_states_warp(WorldView wv, const double
     world.bind(wv, aabb_in_smem != 0);
     EPP_TRACE_EV(g, 1);
     asm volatile("bar.sync 1, %0;" ::"r"(consumers * 32u) : "memory"); // consumers only: publishes the records
+    if (GA) {
+        seq = s_seq;
+        ll_row = gather_row(gv, seq, gv.rank);
+        if (blockIdx.x == 0 && c == 0) gather_send_header(gv, seq, lane);
+    }
     EPP_TRACE_EV(g, 2);
     {
         const void *tsrc;
@@ -779,7 +823,7 @@ __global__ void __launch_bounds__(1024) k_states_warp(WorldView wv, const double
         }
         EPP_TRACE_EV(g, 4 + 2 * tstep);
         warp_states_step<BP, S, RS, GA>(world, wv, rec, pts, units, mode, cpg, min_distance, queue, inv,
-                                        mask + b0 + i * S, lane, gv, (size_t)b0 + (size_t)i * S);
+                                        mask + b0 + i * S, lane, gv, seq, ll_row + b0 + i * S);
         EPP_TRACE_EV(g, 5 + 2 * tstep);
 #ifdef EPP_TRACE
         if (tstep < 3) ++tstep;
@@ -792,16 +836,30 @@ __global__ void __launch_bounds__(1024) k_states_warp(WorldView wv, const double
     }
     EPP_TRACE_EV(g, 15);
     if (GA) {
-        // this warp is counted (release: its peer stores are ordered before the count); the block's last
-        // consumer warp (acquire) takes the block to the grid-level counter / signal / wait
-        __syncwarp();
-        uint32_t last = 0;
-        if (lane == 0) {
-            uint32_t old;
-            asm volatile("atom.acq_rel.cta.shared.add.u32 %0, [%1], 1;" : "=r"(old) : "r"(smem_addr(&s_warps_done)) : "memory");
-            last = old == consumers - 1u ? 1u : 0u;
+        // Out of states: take this warp's share of the peers' slots.  Block b owns words
+        // [b, b + 1) * slot_words / blocks of every peer's slot, its consumer warps split that range.
+        const uint64_t per_b = (gv.slot_words + gridDim.x - 1) / gridDim.x;
+        const uint64_t per_w = (per_b + consumers - 1) / consumers;
+        uint64_t e = ((uint64_t)blockIdx.x + 1u) * per_b;
+        e = e < gv.slot_words ? e : gv.slot_words;
+        uint64_t u0 = (uint64_t)blockIdx.x * per_b + (uint64_t)c * per_w;
+        u0 = u0 < e ? u0 : e;
+        const uint64_t u1 = u0 + per_w < e ? u0 + per_w : e;
+        if (!(gv.debug & 1)) {
+            // the first warp of the block to get here reads the peers' headers for all of them
+            uint32_t st = 0;
+            if (lane == 0) st = atomicCAS(&s_hdr, 0u, 1u);
+            st = __shfl_sync(0xffffffffu, st, 0);
+            if (st == 0u) {
+                gather_read_headers(gv, seq, s_cnt, lane);
+                __syncwarp();
+                if (lane == 0) asm volatile("st.release.cta.shared.u32 [%0], 2;" ::"r"(smem_addr(&s_hdr)) : "memory");
+            } else {
+                while (st != 2u) asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(st) : "r"(smem_addr(&s_hdr)) : "memory");
+            }
+            __syncwarp();
+            gather_unpack(gv, seq, s_cnt, u0, u1, lane);
         }
-        if (__shfl_sync(0xffffffffu, last, 0)) gather_finish(gv, lane);
     }
 }
 
@@ -1204,9 +1262,9 @@ cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const 
     return cudaGetLastError();
 }
 
-cudaError_t launch_gather_push(const LaunchCfg &cfg, const GatherView &gv, size_t words, cudaStream_t stream)
+cudaError_t launch_gather_push(const LaunchCfg &cfg, const GatherView &gv, cudaStream_t stream)
 {
-    size_t blocks = (words / 4 + 255) / 256;
+    size_t blocks = (gv.slot_words / 4 + 255) / 256;
     const size_t cap = (size_t)cfg.sm_count * 4;
     blocks = blocks < 1 ? 1 : (blocks > cap ? cap : blocks);
     cudaLaunchConfig_t lc = {};
@@ -1218,7 +1276,7 @@ cudaError_t launch_gather_push(const LaunchCfg &cfg, const GatherView &gv, size_
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     lc.attrs = attr;
     lc.numAttrs = 1;
-    cudaError_t err = cudaLaunchKernelEx(&lc, k_gather_push, gv, words);
+    cudaError_t err = cudaLaunchKernelEx(&lc, k_gather_push, gv);
     g_launches++;
     return err != cudaSuccess ? err : cudaGetLastError();
 }
@@ -1227,8 +1285,8 @@ cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, con
                           int can_pass_gate, double min_distance, uint32_t *d_mask, cudaStream_t stream,
                           const GatherView *gv)
 {
-    // A gathering call is a collective: it signals and waits even when this rank has no units.
-    if (n == 0) return gv ? launch_gather_push(cfg, *gv, 0, stream) : cudaSuccess;
+    // A gathering call is a collective: it announces its (empty) slot and unpacks the peers' even without units.
+    if (n == 0) return gv ? launch_gather_push(cfg, *gv, stream) : cudaSuccess;
     const GatherView no_gather = {};
     bool in_smem;
     const size_t smem = point_smem_bytes(wv, bp, in_smem);
@@ -1263,7 +1321,7 @@ cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, con
         if (err != cudaSuccess) return err;
         if (launched) {
             g_launches++;
-            if (gv && S == 8) return launch_gather_push(cfg, *gv, (n + 31) / 32, stream);
+            if (gv && S == 8) return launch_gather_push(cfg, *gv, stream);
             return cudaSuccess;
         }
     }
@@ -1277,14 +1335,14 @@ cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, con
         }
     });
     g_launches++;
-    if (err == cudaSuccess && gv) err = launch_gather_push(cfg, *gv, (n + 31) / 32, stream);
+    if (err == cudaSuccess && gv) err = launch_gather_push(cfg, *gv, stream);
     return err;
 }
 
 cudaError_t launch_segments(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_a, const double *d_b,
                             size_t n, int can_pass_gate, uint32_t *d_mask, cudaStream_t stream, const GatherView *gv)
 {
-    if (n == 0) return gv ? launch_gather_push(cfg, *gv, 0, stream) : cudaSuccess;
+    if (n == 0) return gv ? launch_gather_push(cfg, *gv, stream) : cudaSuccess;
     bool in_smem;
     const size_t smem = ray_smem_bytes(wv, bp, in_smem);
     const size_t tiles = (n + kBlock - 1) / kBlock;
@@ -1298,7 +1356,7 @@ cudaError_t launch_segments(const LaunchCfg &cfg, const WorldView &wv, int bp, c
         }
     });
     g_launches++;
-    if (err == cudaSuccess && gv) err = launch_gather_push(cfg, *gv, (n + 31) / 32, stream);
+    if (err == cudaSuccess && gv) err = launch_gather_push(cfg, *gv, stream);
     return err;
 }
 

@@ -29,22 +29,27 @@ struct LaunchCfg {
 
 extern std::atomic<uint64_t> g_launches;
 
-// Mask exchange between the GPUs of one box, written by the check kernels themselves.  Every
-// rank owns a "gathered" buffer of world x slot_words mask words; a gathering check writes the words of its
-// units into slot `rank` of that buffer ON EVERY RANK (peer stores over NVLink), then its last block raises
-// the call's sequence number in every peer's signal array and waits until every peer has raised it here.
-// When the kernel has ended, the local gathered buffer holds the words of all ranks: an all-gather with no
-// collective launch behind the kernel.
+// Mask exchange between the GPUs of one box, done by the check kernels themselves.  Every
+// rank owns a "gathered" buffer of world x slot_words mask words plus a staging area the peers write into.
+// A gathering check sends every mask word it produces to every peer as an 8-byte (word, sequence number)
+// pair — one store over NVLink per peer, the flag travels WITH the data, so no fence and no signal follow —
+// and each of its warps, when it has run out of states, takes a share of the peers' slots: it polls the
+// staging pairs until they carry this call's sequence number and writes the words into the local gathered
+// buffer.  When the kernel has ended, the local gathered buffer holds the words of all ranks: an all-gather
+// with no collective launch, overlapped with the checks chunk by chunk.
+// Staging: 2 parities (sequence number & 1) x world source ranks x (2 + slot_words) pairs; pair 0 of a row
+// is the header (number of words the source sends in this call, sequence number).
 constexpr int kMaxRanks = 8;
 struct GatherView {
-    uint32_t *peer[kMaxRanks];     // rank p's gathered buffer (of this call) in this process's address space
-    uint32_t *peer_sig[kMaxRanks]; // rank p's signal array (kMaxRanks words); this rank raises word [rank]
-    uint32_t *my_sig;              // this rank's signal array
-    uint32_t *ctl;                 // local: [0] blocks done, [1] sequence number, [2] wait time-outs
-    uint64_t my_off;               // word offset of this rank's slot = rank * slot_words
-    uint64_t timeout_ns;           // bound on the wait for the peers (a peer that never calls must not hang the GPU)
+    uint2 *peer_ll[kMaxRanks]; // rank p's staging area in this process's address space
+    const uint2 *my_ll;        // this rank's staging area
+    uint32_t *out;             // this rank's gathered buffer of this call (world x slot_words words)
+    uint32_t *ctl;             // local: [0] blocks done, [1] calls completed (sequence number), [2] wait time-outs
+    uint64_t slot_words;
+    uint64_t my_words;         // words this rank sends in this call
+    uint64_t timeout_ns;       // bound on every wait (a peer that never calls must not hang the GPU)
     int world, rank;
-    int debug; // profiling only (tuning knob gather_debug): 1 no wait, 2 no peer stores, 4 no signal (wrong results)
+    int debug; // profiling only (tuning knob gather_debug): 1 no wait/unpack, 2 no peer stores (wrong results)
 };
 
 cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_xyz, size_t n, int mode,
@@ -53,8 +58,8 @@ cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, con
 cudaError_t launch_segments(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_a, const double *d_b,
                             size_t n, int can_pass_gate, uint32_t *d_mask, cudaStream_t stream,
                             const GatherView *gv = nullptr);
-// Push words [my_off, my_off + words) of the local gathered buffer to every peer, signal and wait.
-cudaError_t launch_gather_push(const LaunchCfg &cfg, const GatherView &gv, size_t words, cudaStream_t stream);
+// Send words [0, gv.my_words) of this rank's slot of the local gathered buffer to every peer, unpack theirs.
+cudaError_t launch_gather_push(const LaunchCfg &cfg, const GatherView &gv, cudaStream_t stream);
 cudaError_t launch_trajectories(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_mats, size_t n_traj,
                                 size_t rows, size_t ld, size_t traj_stride, double min_distance, uint32_t *d_traj_valid,
                                 uint32_t *d_sample_mask, int64_t *d_first_invalid, long long *d_first_scratch,

@@ -179,14 +179,16 @@ int epp_mask_summary_dev(const uint32_t *d_mask, size_t n_words, uint64_t first_
  *
  * One epp_gather per rank (= per GPU; one process per GPU, or several handles in one process).
  * It owns `n_buffers` gathered buffers of world_size x slot_words mask words in device memory.
- * A gathering check writes the words of this rank's units into slot `rank` of buffer `buffer`
- * ON EVERY RANK, straight from the check kernel with stores over NVLink, and the kernel ends
- * only when the slots of all peers have arrived here: when it has completed in stream order,
- * epp_gather_buffer(g, buffer) holds the all-gathered mask — no collective launch follows the
- * kernel.  Gathering calls are collective: every rank issues the same sequence of them on one
- * stream each; a peer that does not show up within the time-out (default 2 s) is counted in
- * epp_gather_status and the kernel ends, it never hangs the GPU.  A buffer may be rewritten
- * once the calls on the other buffers in between have completed (use n_buffers >= 2). */
+ * A gathering check sends every mask word it produces to every peer as an 8-byte
+ * (word, call number) pair — one NVLink store per peer, straight from the check kernel, the
+ * flag travelling with the data so that no fence, signal or collective launch follows — and
+ * the kernel's warps, once out of units, unpack the pairs the peers sent into slot p of the
+ * local buffer.  When the call has completed in stream order, epp_gather_buffer(g, buffer)
+ * holds the all-gathered mask (words beyond a rank's units are 0).  Gathering calls are
+ * collective: every rank issues the same sequence of them, each on one stream; the ranks'
+ * kernels wait for each other on the device, so they must be able to run concurrently (one
+ * GPU each).  A peer that does not show up within the time-out (default 2 s) is counted in
+ * epp_gather_status and read as 0 — the GPU never hangs. */
 typedef struct epp_gather epp_gather;
 #define EPP_GATHER_HANDLE_BYTES 64
 #define EPP_GATHER_MAX_RANKS 8
