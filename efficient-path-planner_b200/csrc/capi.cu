@@ -50,6 +50,7 @@ struct Knob {
 Knob g_knobs[] = {
     {"states_blocks_per_sm", {8}},       // direct form of K1: persistent blocks per SM
     {"segments_blocks_per_sm", {4}},
+    {"segments_variant", {0}},           // 0: auto (records in shared memory when they fit), 1: records in global memory
     {"states_variant", {0}},             // 0: auto, 1: direct, 3: warp-pipelined
     {"states_per_thread", {0}},          // warp form: mask words per chunk (4 default, 8)
     {"states_warp_blocks_per_sm", {1}},
@@ -236,6 +237,7 @@ LaunchCfg launch_cfg(const DeviceEpoch &ep)
     if (sm_limit > 0 && sm_limit < c.sm_count) c.sm_count = sm_limit;
     c.states_blocks_per_sm = knob_value("states_blocks_per_sm");
     c.segments_blocks_per_sm = knob_value("segments_blocks_per_sm");
+    c.segments_variant = knob_value("segments_variant");
     c.states_variant = knob_value("states_variant");
     c.states_per_thread = knob_value("states_per_thread");
     c.states_warp_blocks_per_sm = knob_value("states_warp_blocks_per_sm");
@@ -544,6 +546,7 @@ extern "C" int epp_world_commit(epp_world *w)
     v.bits_max_ge = (const uint32_t *)(base + parts[4].off);
     v.nb = bits.nb;
     v.W = bits.W;
+    v.Ws = bits.Ws;
     v.kb = bits.bins;
     v.zrot = 1;
     for (const ObbRec &o : obbs)

@@ -88,23 +88,23 @@ struct PointWorld<EPP_BP_BITS> {
     __device__ void init(const WorldView &wv, bool)
     {
         uint32_t *dst = reinterpret_cast<uint32_t *>(g_smem);
-        block_copy_words(dst, wv.bits_inside, 3 * wv.nb * wv.W);
+        block_copy_words(dst, wv.bits_inside, 3 * wv.nb * wv.Ws);
         __syncthreads();
         inside = dst;
     }
     __device__ static uint32_t table(const WorldView &wv, bool, const void *&src)
     {
         src = wv.bits_inside;
-        return (uint32_t)(3 * wv.nb * wv.W * 4);
+        return (uint32_t)(3 * wv.nb * wv.Ws * 4);
     }
     __device__ void bind(const WorldView &, bool) { inside = reinterpret_cast<const uint32_t *>(g_smem); }
     template <class F>
     __device__ __forceinline__ bool any(const WorldView &wv, const P3 &p, F test) const
     {
-        const int nb = wv.nb, W = wv.W;
-        const uint32_t *tx = inside + dev_key_bin(p.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb) * W;
-        const uint32_t *ty = inside + (nb + dev_key_bin(p.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb)) * W;
-        const uint32_t *tz = inside + (2 * nb + dev_key_bin(p.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb)) * W;
+        const int nb = wv.nb, W = wv.W, Ws = wv.Ws;
+        const uint32_t *tx = inside + dev_key_bin(p.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb) * Ws;
+        const uint32_t *ty = inside + (nb + dev_key_bin(p.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb)) * Ws;
+        const uint32_t *tz = inside + (2 * nb + dev_key_bin(p.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb)) * Ws;
         for (int w = 0; w < W; ++w) {
             uint32_t m = tx[w] & ty[w] & tz[w];
             while (m) {
@@ -117,10 +117,10 @@ struct PointWorld<EPP_BP_BITS> {
     }
     __device__ __forceinline__ bool has_candidates(const WorldView &wv, const P3 &p) const
     {
-        const int nb = wv.nb, W = wv.W;
-        const uint32_t *tx = inside + dev_key_bin(p.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb) * W;
-        const uint32_t *ty = inside + (nb + dev_key_bin(p.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb)) * W;
-        const uint32_t *tz = inside + (2 * nb + dev_key_bin(p.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb)) * W;
+        const int nb = wv.nb, W = wv.W, Ws = wv.Ws;
+        const uint32_t *tx = inside + dev_key_bin(p.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb) * Ws;
+        const uint32_t *ty = inside + (nb + dev_key_bin(p.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb)) * Ws;
+        const uint32_t *tz = inside + (2 * nb + dev_key_bin(p.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb)) * Ws;
         if (W == 1) return (tx[0] & ty[0] & tz[0]) != 0u;
         uint32_t m = 0u;
         for (int w = 0; w < W; ++w) m |= tx[w] & ty[w] & tz[w];
@@ -214,6 +214,8 @@ struct PointWorld<EPP_BP_GRID> {
 template <int BP>
 struct RayWorld;
 
+// Every RayWorld offers any(wv, mn, mx, f): calls f(k) for the broad-phase candidates k of the ray box
+// [mn, mx] (a superset of the OBBs whose stored AABB the box touches) until one returns true.
 template <>
 struct RayWorld<EPP_BP_BRUTE> {
     const AabbRec *aabb;
@@ -227,6 +229,13 @@ struct RayWorld<EPP_BP_BRUTE> {
             aabb = reinterpret_cast<const AabbRec *>(g_smem);
         }
     }
+    template <typename F>
+    __device__ __forceinline__ bool any(const WorldView &wv, const P3 &, const P3 &, F f) const
+    {
+        for (int k = 0; k < wv.M; ++k)
+            if (f(k)) return true;
+        return false;
+    }
     __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &a, const P3 &b, bool cpg) const
     {
         P3 mn, mx;
@@ -239,14 +248,16 @@ struct RayWorld<EPP_BP_BRUTE> {
     }
 };
 
-// candidates = AND over axes of max_ge[bin(rayMin)] & min_le[bin(rayMax)].
+// candidates = AND over axes of max_ge[bin(rayMin)] & min_le[bin(rayMax)].  Rows have an ODD stride of
+// Ws = W | 1 words (built that way on the host): lanes look up unrelated bins, and with the natural stride of W = 8 words every row
+// starts in one of four banks (ncu: 10.5 M bank-conflict cycles per 1 M segments, 40 % of the kernel's cycles).
 template <>
 struct RayWorld<EPP_BP_BITS> {
     const uint32_t *min_le;
     const uint32_t *max_ge;
     __device__ void init(const WorldView &wv, bool)
     {
-        const int words = 3 * wv.nb * wv.W;
+        const int words = 3 * wv.nb * wv.Ws;
         uint32_t *dst = reinterpret_cast<uint32_t *>(g_smem);
         block_copy_words(dst, wv.bits_min_le, words);
         block_copy_words(dst + words, wv.bits_max_ge, words);
@@ -254,26 +265,31 @@ struct RayWorld<EPP_BP_BITS> {
         min_le = dst;
         max_ge = dst + words;
     }
-    __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &a, const P3 &b, bool cpg) const
+    template <typename F>
+    __device__ __forceinline__ bool any(const WorldView &wv, const P3 &mn, const P3 &mx, F f) const
     {
-        P3 mn, mx;
-        ray_box(a, b, mn, mx);
-        const int nb = wv.nb, W = wv.W;
-        const uint32_t *gx = max_ge + dev_key_bin(mn.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb) * W;
-        const uint32_t *gy = max_ge + (nb + dev_key_bin(mn.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb)) * W;
-        const uint32_t *gz = max_ge + (2 * nb + dev_key_bin(mn.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb)) * W;
-        const uint32_t *lx = min_le + dev_key_bin(mx.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb) * W;
-        const uint32_t *ly = min_le + (nb + dev_key_bin(mx.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb)) * W;
-        const uint32_t *lz = min_le + (2 * nb + dev_key_bin(mx.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb)) * W;
+        const int nb = wv.nb, W = wv.W, Ws = wv.Ws;
+        const uint32_t *gx = max_ge + dev_key_bin(mn.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb) * Ws;
+        const uint32_t *gy = max_ge + (nb + dev_key_bin(mn.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb)) * Ws;
+        const uint32_t *gz = max_ge + (2 * nb + dev_key_bin(mn.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb)) * Ws;
+        const uint32_t *lx = min_le + dev_key_bin(mx.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb) * Ws;
+        const uint32_t *ly = min_le + (nb + dev_key_bin(mx.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb)) * Ws;
+        const uint32_t *lz = min_le + (2 * nb + dev_key_bin(mx.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb)) * Ws;
         for (int w = 0; w < W; ++w) {
             uint32_t m = gx[w] & gy[w] & gz[w] & lx[w] & ly[w] & lz[w];
             while (m) {
                 const int k = (w << 5) + __ffs(m) - 1;
                 m &= m - 1;
-                if (ray_candidate_invalid(wv.aabb, wv.obb, k, a, b, mn, mx, cpg)) return true;
+                if (f(k)) return true;
             }
         }
         return false;
+    }
+    __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &a, const P3 &b, bool cpg) const
+    {
+        P3 mn, mx;
+        ray_box(a, b, mn, mx);
+        return any(wv, mn, mx, [&](int k) -> bool { return ray_candidate_invalid(wv.aabb, wv.obb, k, a, b, mn, mx, cpg); });
     }
 };
 
@@ -282,10 +298,9 @@ struct RayWorld<EPP_BP_BITS> {
 template <>
 struct RayWorld<EPP_BP_GRID> {
     __device__ void init(const WorldView &, bool) {}
-    __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &a, const P3 &b, bool cpg) const
+    template <typename F>
+    __device__ __forceinline__ bool any(const WorldView &wv, const P3 &mn, const P3 &mx, F f) const
     {
-        P3 mn, mx;
-        ray_box(a, b, mn, mx);
         const AxisBins &g = wv.gbins;
         const int x0 = dev_bin(mn.x, g.lo[0], g.inv[0], g.n[0]), x1 = dev_bin(mx.x, g.lo[0], g.inv[0], g.n[0]);
         const int y0 = dev_bin(mn.y, g.lo[1], g.inv[1], g.n[1]), y1 = dev_bin(mx.y, g.lo[1], g.inv[1], g.n[1]);
@@ -300,11 +315,17 @@ struct RayWorld<EPP_BP_GRID> {
                         const uint64_t cm = wv.obb[k].cell_min;
                         const int kx = (int)(cm & 0x1FFFFF), ky = (int)((cm >> 21) & 0x1FFFFF), kz = (int)(cm >> 42);
                         if (x != (kx > x0 ? kx : x0) || y != (ky > y0 ? ky : y0) || z != (kz > z0 ? kz : z0)) continue;
-                        if (ray_candidate_invalid(wv.aabb, wv.obb, k, a, b, mn, mx, cpg)) return true;
+                        if (f(k)) return true;
                     }
                 }
             }
         return false;
+    }
+    __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &a, const P3 &b, bool cpg) const
+    {
+        P3 mn, mx;
+        ray_box(a, b, mn, mx);
+        return any(wv, mn, mx, [&](int k) -> bool { return ray_candidate_invalid(wv.aabb, wv.obb, k, a, b, mn, mx, cpg); });
     }
 };
 
@@ -645,7 +666,7 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
 }
 
 template <int BP, int S, bool RS, bool GA>
-__global__ void __launch_bounds__(1024) k_states_warp(WorldView wv, const double *__restrict__ xyz, size_t n, int mode,
+__global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const double *__restrict__ xyz, size_t n, int mode,
                                                       int can_pass_gate, double min_distance, int aabb_in_smem,
                                                       int log2_slots, uint32_t table_bytes, uint32_t rec_bytes,
                                                       uint32_t wpb, uint32_t rem, uint32_t *__restrict__ mask,
@@ -883,6 +904,106 @@ __global__ void __launch_bounds__(kBlock) k_segments(WorldView wv, const double 
         }
         const uint32_t word = __ballot_sync(0xffffffffu, valid);
         if ((threadIdx.x & 31) == 0 && i < n) mask[i >> 5] = word;
+    }
+}
+
+// ---- K2 with the world's records in shared memory ------------------------------------------------------------
+//
+// ncu on the form above (256-OBB world): FP64 pipe 5 % busy, 25 % of issue slots used, the rest is waiting on
+// the per-lane record fetches of the candidate loop — every lane reads a DIFFERENT AabbRec / ObbRec, so one load
+// instruction touches up to 32 cache lines.  For worlds of up to kRayRecMax OBBs whose rotations are all about z
+// (the only kind World::addGate / addObstacle build, src/Object.cpp:38-47) the prologue folds the call's rules
+// into one 21-double record per OBB in shared memory (odd stride: lanes on different records hit different
+// banks) and the next tile's end points are fetched while the current tile is evaluated.
+// Record: [0..5] stored AABB min / max (min.x = +inf for a box the call skips: filling && canPassGate,
+// src/World.cpp:150-153), [6..8] centre, [9..12] R(0,0) R(0,1) R(1,0) R(1,1), [13..15] half sizes of the END
+// POINT tests (half + inflate for collision boxes, half for filling ones, src/OBB.cpp:67-72), [16..18] half sizes
+// of the SLAB test (half + inflate for every type, :28).  With R(2,0) = R(2,1) = R(0,2) = R(1,2) = 0 and
+// R(2,2) = 1 the reference's 3-term sums are (a + b) + (+-0) and (+-0 + +-0) + d2: dropping the zero terms can
+// only change the sign of a zero, which fabs() and the comparisons cannot see.
+constexpr int kRayRec = 21;
+constexpr int kRayRecMax = 256;
+
+__device__ __forceinline__ bool ray_rec_invalid(const double *__restrict__ r, const P3 &a, const P3 &b, const P3 &mn,
+                                                const P3 &mx)
+{
+    if (mx.x < r[0] || mn.x > r[3] || mx.y < r[1] || mn.y > r[4] || mx.z < r[2] || mn.z > r[5]) return false;
+    const double a0 = dsub(a.x, r[6]), a1 = dsub(a.y, r[7]), a2 = dsub(a.z, r[8]);
+    const double b0 = dsub(b.x, r[6]), b1 = dsub(b.y, r[7]), b2 = dsub(b.z, r[8]);
+    const double ax = dadd(dmul(r[9], a0), dmul(r[11], a1)), ay = dadd(dmul(r[10], a0), dmul(r[12], a1));
+    const double bx = dadd(dmul(r[9], b0), dmul(r[11], b1)), by = dadd(dmul(r[10], b0), dmul(r[12], b1));
+    // end points first (src/OBB.cpp:13-18)
+    if (fabs(ax) <= r[13] && fabs(ay) <= r[14] && fabs(a2) <= r[15]) return true;
+    if (fabs(bx) <= r[13] && fabs(by) <= r[14] && fabs(b2) <= r[15]) return true;
+    double t_min = 0.0, t_max = 1.0;
+    if (!slab_axis(dsub(bx, ax), ax, r[16], t_min, t_max)) return false;
+    if (!slab_axis(dsub(by, ay), ay, r[17], t_min, t_max)) return false;
+    if (!slab_axis(dsub(b2, a2), a2, r[18], t_min, t_max)) return false;
+    return 0.0 <= t_min && t_min <= 1.0 && 0.0 <= t_max && t_max <= 1.0;
+}
+
+template <int BP>
+__global__ void __launch_bounds__(kBlock, 4) k_segments_rs(WorldView wv, const double *__restrict__ pa,
+                                                            const double *__restrict__ pb, size_t n, int can_pass_gate,
+                                                            uint32_t table_bytes, uint32_t *__restrict__ mask)
+{
+    RayWorld<BP> world;
+    world.init(wv, false);
+    double *rec = reinterpret_cast<double *>(g_smem + table_bytes);
+    for (int k = threadIdx.x; k < wv.M; k += blockDim.x) {
+        const AabbRec *ab = wv.aabb + k;
+        const ObbRec *o = wv.obb + k;
+        double *r = rec + k * kRayRec;
+        const uint32_t flags = __ldg(&o->flags);
+        const bool filling = (flags & kFlagFilling) != 0;
+        const double infl = __ldg(&o->inflate);
+#pragma unroll
+        for (int d = 0; d < 3; ++d) {
+            r[d] = __ldg(&ab->mn[d]);
+            r[3 + d] = __ldg(&ab->mx[d]);
+            r[6 + d] = __ldg(&o->center[d]);
+            const double h = __ldg(&o->half[d]);
+            r[13 + d] = filling ? h : dadd(h, infl);
+            r[16 + d] = dadd(h, infl);
+        }
+        if (filling && can_pass_gate) r[0] = __longlong_as_double(0x7ff0000000000000ll);
+        r[9] = __ldg(&o->rot[0]);
+        r[10] = __ldg(&o->rot[1]);
+        r[11] = __ldg(&o->rot[3]);
+        r[12] = __ldg(&o->rot[4]);
+        r[19] = r[20] = 0.0;
+    }
+    __syncthreads();
+    const size_t tiles = (n + kBlock - 1) / kBlock;
+    size_t tile = blockIdx.x;
+    if (tile >= tiles) return;
+    size_t i = tile * kBlock + threadIdx.x;
+    P3 a = {0.0, 0.0, 0.0}, b = {0.0, 0.0, 0.0};
+    if (i < n) {
+        a = {__ldg(pa + 3 * i), __ldg(pa + 3 * i + 1), __ldg(pa + 3 * i + 2)};
+        b = {__ldg(pb + 3 * i), __ldg(pb + 3 * i + 1), __ldg(pb + 3 * i + 2)};
+    }
+    for (;;) {
+        const size_t next_tile = tile + gridDim.x;
+        const size_t ni = next_tile * kBlock + threadIdx.x;
+        P3 na = {0.0, 0.0, 0.0}, nb = {0.0, 0.0, 0.0};
+        if (next_tile < tiles && ni < n) {
+            na = {__ldg(pa + 3 * ni), __ldg(pa + 3 * ni + 1), __ldg(pa + 3 * ni + 2)};
+            nb = {__ldg(pb + 3 * ni), __ldg(pb + 3 * ni + 1), __ldg(pb + 3 * ni + 2)};
+        }
+        bool valid = false;
+        if (i < n) {
+            P3 mn, mx;
+            ray_box(a, b, mn, mx);
+            valid = !world.any(wv, mn, mx, [&](int k) -> bool { return ray_rec_invalid(rec + k * kRayRec, a, b, mn, mx); });
+        }
+        const uint32_t word = __ballot_sync(0xffffffffu, valid);
+        if ((threadIdx.x & 31) == 0 && i < n) mask[i >> 5] = word;
+        if (next_tile >= tiles) break;
+        tile = next_tile;
+        i = ni;
+        a = na;
+        b = nb;
     }
 }
 
@@ -1143,7 +1264,7 @@ __global__ void k_mask_summary(const uint32_t *__restrict__ mask, size_t n_words
 size_t point_smem_bytes(const WorldView &wv, int bp, bool &aabb_in_smem)
 {
     aabb_in_smem = false;
-    if (bp == EPP_BP_BITS) return (size_t)3 * wv.nb * wv.W * 4;
+    if (bp == EPP_BP_BITS) return (size_t)3 * wv.nb * wv.Ws * 4;
     if (bp == EPP_BP_BRUTE && wv.M <= 2048) {
         aabb_in_smem = true;
         return (size_t)wv.M * sizeof(AabbRec);
@@ -1154,7 +1275,7 @@ size_t point_smem_bytes(const WorldView &wv, int bp, bool &aabb_in_smem)
 size_t ray_smem_bytes(const WorldView &wv, int bp, bool &aabb_in_smem)
 {
     aabb_in_smem = false;
-    if (bp == EPP_BP_BITS) return (size_t)6 * wv.nb * wv.W * 4;
+    if (bp == EPP_BP_BITS) return (size_t)6 * wv.nb * wv.Ws * 4;
     if (bp == EPP_BP_BRUTE && wv.M <= 2048) {
         aabb_in_smem = true;
         return (size_t)wv.M * sizeof(AabbRec);
@@ -1224,7 +1345,10 @@ cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const 
     bps = bps > 8 ? 8 : bps;
     int cons = (cfg.states_warp_threads > 0 ? cfg.states_warp_threads / 32 : kMaxWarps) - 1;
     cons = cons < 1 ? 1 : (cons > kMaxWarps - 1 ? kMaxWarps - 1 : cons);
-    if ((cons + 1) * 32 * bps > 2048) bps = 2048 / ((cons + 1) * 32);
+    // the kernel is compiled for one 1024-thread block per SM (up to 64 registers per thread): several
+    // resident blocks share that budget
+    if ((cons + 1) * 32 * bps > 1024) cons = 1024 / (32 * bps) - 1;
+    cons = cons < 1 ? 1 : cons;
     const size_t chunks_total = (words + S - 1) / S;
     const size_t blocks_cap = (size_t)cfg.sm_count * bps;
     const size_t grid = chunks_total < blocks_cap ? chunks_total : blocks_cap;
@@ -1345,9 +1469,29 @@ cudaError_t launch_segments(const LaunchCfg &cfg, const WorldView &wv, int bp, c
     if (n == 0) return gv ? launch_gather_push(cfg, *gv, stream) : cudaSuccess;
     bool in_smem;
     const size_t smem = ray_smem_bytes(wv, bp, in_smem);
-    const size_t tiles = (n + kBlock - 1) / kBlock;
-    const unsigned grid = persistent_grid(cfg, tiles, cfg.segments_blocks_per_sm);
     cudaError_t err = cudaSuccess;
+    const size_t tiles = (n + kBlock - 1) / kBlock;
+    if (cfg.segments_variant != 1 && wv.zrot && wv.M <= kRayRecMax) {
+        // records in shared memory (the broad-phase table of the brute form is the records themselves)
+        const size_t table_bytes = bp == EPP_BP_BRUTE ? 0 : (smem + 127) / 128 * 128;
+        const size_t total = table_bytes + (size_t)wv.M * kRayRec * 8;
+        // persistent blocks: as many per SM as the shared memory holds at once (a second wave would start late)
+        int bps = (int)((size_t)(227 * 1024) / (total + 1024));
+        bps = bps < 1 ? 1 : (bps > cfg.segments_blocks_per_sm ? cfg.segments_blocks_per_sm : bps);
+        const unsigned grid_rs = persistent_grid(cfg, tiles, bps);
+        EPP_DISPATCH_BP(bp, {
+            err = ensure_smem(k_segments_rs<BP>, total);
+            if (err == cudaSuccess) {
+                k_segments_rs<BP><<<grid_rs, kBlock, total, stream>>>(wv, d_a, d_b, n, can_pass_gate,
+                                                                     (uint32_t)table_bytes, d_mask);
+                err = cudaGetLastError();
+            }
+        });
+        g_launches++;
+        if (err == cudaSuccess && gv) err = launch_gather_push(cfg, *gv, stream);
+        return err;
+    }
+    const unsigned grid = persistent_grid(cfg, tiles, cfg.segments_blocks_per_sm);
     EPP_DISPATCH_BP(bp, {
         err = ensure_smem(k_segments<BP>, smem);
         if (err == cudaSuccess) {

@@ -14,6 +14,7 @@ struct LaunchCfg {
     int sm_count = 148;
     int states_blocks_per_sm = 8;   // 0: one block per tile (non-persistent)
     int segments_blocks_per_sm = 4; // 0: one block per tile
+    int segments_variant = 0;       // 0: auto (records in shared memory for worlds of <= 256 z-rotated OBBs), 1: records in global memory
     int states_variant = 0;         // 0: auto (warp-pipelined from states_warp_min_n states up), 1: direct, 3: warp-pipelined
     int states_warp_blocks_per_sm = 1;
     int states_warp_threads = 1024; // block size of the warp-pipelined form

@@ -328,13 +328,14 @@ void build_bits(const std::vector<AabbRec> &aabbs, int bins_per_axis, BitsTables
 {
     const int M = static_cast<int>(aabbs.size());
     out.W = std::max(1, (M + 31) / 32);
+    out.Ws = out.W | 1;
     double lo[3], hi[3];
     world_extent(aabbs, lo, hi);
     for (int a = 0; a < 3; ++a)
         make_key_axis(lo[a], hi[a], std::max(2, bins_per_axis), out.bins.off[a], out.bins.h0[a], out.bins.shift[a],
                       out.bins.n[a]);
     out.nb = out.bins.n[0]; // the same power of two + 1 on every axis
-    const size_t words = static_cast<size_t>(3) * out.nb * out.W;
+    const size_t words = static_cast<size_t>(3) * out.nb * out.Ws;
     out.inside.assign(words, 0u);
     out.min_le.assign(words, 0u);
     out.max_ge.assign(words, 0u);
@@ -345,7 +346,7 @@ void build_bits(const std::vector<AabbRec> &aabbs, int bins_per_axis, BitsTables
             const uint32_t bit = 1u << (k & 31);
             const size_t w = static_cast<size_t>(k >> 5);
             for (int b = 0; b < out.nb; ++b) {
-                const size_t at = (static_cast<size_t>(a) * out.nb + b) * out.W + w;
+                const size_t at = (static_cast<size_t>(a) * out.nb + b) * out.Ws + w;
                 if (b0 <= b && b <= b1) out.inside[at] |= bit;
                 if (b0 <= b) out.min_le[at] |= bit;
                 if (b1 >= b) out.max_ge[at] |= bit;

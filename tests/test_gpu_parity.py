@@ -565,3 +565,32 @@ def test_gather_argument_errors(config, track):
     one.check_states(gw, d_xyz[:512], 0)     # world_size 1: a plain check into the buffer
     import torch
     assert torch.equal(one.tensor(0)[0][:16], gw.check_states_dev(d_xyz[:512]))
+
+
+@pytest.mark.parametrize("bp", BPS, ids=BP_IDS)
+def test_segments_smem_record_form_equals_global_record_form(oracle, config, bp):
+    """K2's two forms (records folded into shared memory / records in global memory) and the oracle agree,
+    incl. canPassGate with filling boxes, ragged tails and zero-length segments."""
+    import torch
+    g, o, lo, hi = worlds.world_256()
+    cfgf = filling_config(config)
+    ow, gw = build_pair(oracle, epp_b200, cfgf, g, o, broadphase=bp)
+    rng = np.random.default_rng(99)
+    for n in (1, 31, 33, 4097, 70_001):
+        a, b = worlds.gen_segments(worlds.SEED_SEGMENTS, 1000 + n, n, lo, hi, 1.0)
+        b[::17] = a[::17]  # zero-length segments
+        extra_a, extra_b = adversarial_segments(gw.obbs(), rng, lo, hi, per_obb=2)
+        m = min(len(extra_a), n // 2)
+        a[:m], b[:m] = np.asarray(extra_a)[:m], np.asarray(extra_b)[:m]
+        d_a, d_b = torch.from_numpy(a).cuda(), torch.from_numpy(b).cuda()
+        for cpg in (False, True):
+            want = ow.check_segments(a, b, cpg, threads=8)
+            got = {}
+            for variant in (0, 1):
+                epp_b200.set_tuning("segments_variant", variant)
+                try:
+                    got[variant] = gw.check_segments_dev(d_a, d_b, can_pass_gate=cpg).cpu().numpy().view(np.uint32)
+                finally:
+                    epp_b200.set_tuning("segments_variant", 0)
+            assert mismatches(got[0], want) == 0, (n, cpg)
+            assert mismatches(got[1], want) == 0, (n, cpg)
