@@ -1071,31 +1071,34 @@ __device__ __forceinline__ double horner(const double *__restrict__ c, int n, do
     return r;
 }
 
-// A warp owns 32 trajectories.  Phase 1: lane l advances the reference's sequential sampler
-// (trajectory.cpp:121-140: running sums, not k*dt) of ITS trajectory by up to 32 samples and
-// parks (segment, time_in_segment) in shared memory.  Phase 2: for each of the 32 trajectories
-// in turn, the 32 lanes evaluate its 32 parked samples (Horner x 3 + world check) and ballot
-// them into one mask word.
+// A warp owns G trajectories (G = 1..32, chosen by the launcher so that the batch fills the GPU: 10 000
+// trajectories at G = 32 are only 313 warps, two per SM).  Phase 1: lane l < G advances the reference's
+// sequential sampler (trajectory.cpp:121-140: running sums, not k*dt) of ITS trajectory by up to 32 samples
+// and parks (segment, time_in_segment) in shared memory.  Phase 2: for each of the G trajectories in turn,
+// the 32 lanes evaluate its 32 parked samples (Horner x 3 + world check) and ballot them into one mask word.
 template <int BP>
 __global__ void __launch_bounds__(kPolyWarps * 32) k_poly_traj(WorldView wv, const double *__restrict__ coeffs,
                                                                const double *__restrict__ durations,
                                                                const double *__restrict__ dts, size_t n_traj,
                                                                int n_segments, int n_coeffs, double min_distance,
-                                                               size_t max_samples, int aabb_in_smem,
+                                                               size_t max_samples, int aabb_in_smem, int G,
+                                                               uint32_t table_bytes,
                                                                uint32_t *__restrict__ sample_mask,
                                                                uint32_t *__restrict__ n_samples_out,
                                                                long long *__restrict__ first_row)
 {
-    __shared__ double s_t[kPolyWarps][32 * kPolyPitch];
-    __shared__ unsigned short s_seg[kPolyWarps][32 * kPolyPitch];
     PointWorld<BP> world;
     world.init(wv, aabb_in_smem != 0);
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    const size_t traj0 = ((size_t)blockIdx.x * kPolyWarps + warp) * 32;
+    // shared memory behind the broad-phase table: per warp G rows of parked times, then G rows of segment numbers
+    double *s_t = reinterpret_cast<double *>(g_smem + table_bytes) + (size_t)warp * G * kPolyPitch;
+    unsigned short *s_seg = reinterpret_cast<unsigned short *>(g_smem + table_bytes + (size_t)kPolyWarps * G * kPolyPitch * 8) +
+                            (size_t)warp * G * kPolyPitch;
+    const size_t traj0 = ((size_t)blockIdx.x * kPolyWarps + warp) * (size_t)G;
     if (traj0 >= n_traj) return;
     const size_t my = traj0 + lane;
-    const bool have = my < n_traj;
+    const bool have = lane < G && my < n_traj;
     const size_t words_per_traj = max_samples / 32;
 
     // Sampler state of my trajectory: evaluateRange(0, maxTime, dt), trajectory.cpp:95-119.
@@ -1142,8 +1145,8 @@ __global__ void __launch_bounds__(kPolyWarps * 32) k_poly_traj(WorldView wv, con
                 seg_T = __ldg(dur + seg);
                 continue;
             }
-            s_t[warp][lane * kPolyPitch + cnt] = tin; // :132
-            s_seg[warp][lane * kPolyPitch + cnt] = (unsigned short)seg;
+            s_t[lane * kPolyPitch + cnt] = tin; // :132
+            s_seg[lane * kPolyPitch + cnt] = (unsigned short)seg;
             ++cnt;
             tin = dadd(tin, dt); // :138-139
             acc = dadd(acc, dt);
@@ -1153,14 +1156,14 @@ __global__ void __launch_bounds__(kPolyWarps * 32) k_poly_traj(WorldView wv, con
         if (__ballot_sync(0xffffffffu, cnt > 0) == 0) break;
 
         // ---- phase 2: evaluate trajectory j's parked samples, one per lane
-        for (int j = 0; j < 32; ++j) {
+        for (int j = 0; j < G; ++j) {
             const int cj = __shfl_sync(0xffffffffu, cnt, j);
             if (cj == 0) continue;
             const size_t tj = traj0 + j;
             bool valid = false;
             if (lane < cj) {
-                const double t = s_t[warp][j * kPolyPitch + lane];
-                const int sg = s_seg[warp][j * kPolyPitch + lane];
+                const double t = s_t[j * kPolyPitch + lane];
+                const int sg = s_seg[j * kPolyPitch + lane];
                 const double *c = coeffs + ((tj * n_segments + sg) * 3) * (size_t)n_coeffs; // segment.cpp:51-58
                 const P3 p = {horner(c, n_coeffs, t), horner(c + n_coeffs, n_coeffs, t),
                               horner(c + 2 * n_coeffs, n_coeffs, t)};
@@ -1537,7 +1540,7 @@ cudaError_t launch_trajectories(const LaunchCfg &, const WorldView &wv, int bp, 
     return cudaGetLastError();
 }
 
-cudaError_t launch_poly_trajectories(const LaunchCfg &, const WorldView &wv, int bp, const double *d_coeffs,
+cudaError_t launch_poly_trajectories(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_coeffs,
                                      const double *d_durations, const double *d_dt, size_t n_traj, int n_segments,
                                      int n_coeffs, double min_distance, size_t max_samples, uint32_t *d_traj_valid,
                                      uint32_t *d_sample_mask, uint32_t *d_n_samples, int64_t *d_first_invalid,
@@ -1555,14 +1558,24 @@ cudaError_t launch_poly_trajectories(const LaunchCfg &, const WorldView &wv, int
     }
     bool in_smem;
     const size_t smem = point_smem_bytes(wv, bp, in_smem);
-    const size_t per_block = (size_t)kPolyWarps * 32;
+    // trajectories per warp: 32 for big batches, fewer while the batch would leave SMs without warps
+    int G = cfg.poly_traj_per_warp;
+    if (G <= 0) {
+        G = 32;
+        while (G > 1 && n_traj / (size_t)G < (size_t)cfg.sm_count * 24) G >>= 1;
+    }
+    G = G > 32 ? 32 : G;
+    const size_t per_block = (size_t)kPolyWarps * (size_t)G;
     const unsigned grid = (unsigned)((n_traj + per_block - 1) / per_block);
+    const size_t table_bytes = (smem + 127) / 128 * 128;
+    const size_t total = table_bytes + (size_t)kPolyWarps * G * kPolyPitch * (8 + 2);
     EPP_DISPATCH_BP(bp, {
-        err = ensure_smem(k_poly_traj<BP>, smem, sizeof(double) * kPolyWarps * 32 * kPolyPitch + 2 * kPolyWarps * 32 * kPolyPitch);
+        err = ensure_smem(k_poly_traj<BP>, total);
         if (err == cudaSuccess) {
-            k_poly_traj<BP><<<grid, kPolyWarps * 32, smem, stream>>>(wv, d_coeffs, d_durations, d_dt, n_traj, n_segments,
-                                                                     n_coeffs, min_distance, max_samples, in_smem ? 1 : 0,
-                                                                     d_sample_mask, d_n_samples, d_first_scratch);
+            k_poly_traj<BP><<<grid, kPolyWarps * 32, total, stream>>>(wv, d_coeffs, d_durations, d_dt, n_traj, n_segments,
+                                                                      n_coeffs, min_distance, max_samples, in_smem ? 1 : 0, G,
+                                                                      (uint32_t)table_bytes, d_sample_mask, d_n_samples,
+                                                                      d_first_scratch);
             err = cudaGetLastError();
         }
     });
