@@ -62,6 +62,7 @@ Knob g_knobs[] = {
     {"states_pdl", {1}},
     {"states_debug", {0}},               // profiling builds only
     {"poly_traj_per_warp", {0}},         // K3b: trajectories per warp, 0 = by batch size
+    {"gather_group_chunks", {8}},        // fused exchange: chunks per NVLink run (1: every chunk alone)
     {"gather_debug", {0}},               // profiling only: 1 no wait/unpack, 2 no peer stores
     {"sm_limit", {0}},                   // 0: all SMs; > 0: size grids for this many SMs (several ranks on one GPU in tests)
     {"bits_bins", {0}},                  // 0: by world size
@@ -251,6 +252,7 @@ LaunchCfg launch_cfg(const DeviceEpoch &ep)
     c.states_debug = knob_value("states_debug");
     c.poly_traj_per_warp = knob_value("poly_traj_per_warp");
     c.gather_debug = knob_value("gather_debug");
+    c.gather_group_chunks = knob_value("gather_group_chunks");
     return c;
 }
 

@@ -526,19 +526,34 @@ __device__ __forceinline__ void gather_read_headers(const GatherView &gv, uint32
 }
 
 // A warp unpacks words [u0, u1) of every peer's slot into the local gathered buffer (0 beyond what the peer sends).
+// The pairs of ALL peers for a lane's word are requested before any is examined: one L2 round trip per word
+// instead of one per peer (7 dependent round trips at 8 ranks were ~2.5 us at the tail of every launch).
 __device__ __forceinline__ void gather_unpack(const GatherView &gv, uint32_t seq, const uint32_t *cnt, uint64_t u0,
                                               uint64_t u1, int lane)
 {
     bool dead = false;
-    for (int p = 0; p < gv.world; ++p) {
-        uint32_t *dst = gv.out + (uint64_t)p * gv.slot_words;
-        if (p == gv.rank) { // own slot: the check wrote words [0, my_words); the rest of the slot reads 0
-            for (uint64_t w = (u0 > gv.my_words ? u0 : gv.my_words) + (uint64_t)lane; w < u1; w += 32u) dst[w] = 0u;
-            continue;
+    const uint64_t row = gv.slot_words + 2u;
+    const uint2 *base = gv.my_ll + (uint64_t)(seq & 1u) * (uint64_t)gv.world * row + 2u;
+    uint32_t *own = gv.out + (uint64_t)gv.rank * gv.slot_words; // own slot: the check wrote [0, my_words); the rest reads 0
+    for (uint64_t w = (u0 > gv.my_words ? u0 : gv.my_words) + (uint64_t)lane; w < u1; w += 32u) own[w] = 0u;
+    for (uint64_t w = u0 + (uint64_t)lane; w < u1; w += 32u) {
+        uint32_t word[kMaxRanks], flag[kMaxRanks];
+#pragma unroll
+        for (int p = 0; p < kMaxRanks; ++p) {
+            word[p] = 0u;
+            flag[p] = seq;
+            if (p < gv.world && p != gv.rank && w < cnt[p])
+                asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];"
+                             : "=r"(word[p]), "=r"(flag[p])
+                             : "l"(base + (uint64_t)p * row + w)
+                             : "memory");
         }
-        const uint2 *src = gv.my_ll + gather_row(gv, seq, p);
-        const uint64_t n = cnt[p];
-        for (uint64_t w = u0 + (uint64_t)lane; w < u1; w += 32u) dst[w] = w < n ? ll_wait(src + w, seq, gv, dead) : 0u;
+#pragma unroll
+        for (int p = 0; p < kMaxRanks; ++p) {
+            if (p >= gv.world || p == gv.rank) continue;
+            if (flag[p] != seq) word[p] = ll_wait(base + (uint64_t)p * row + w, seq, gv, dead);
+            gv.out[(uint64_t)p * gv.slot_words + w] = word[p];
+        }
     }
 }
 
@@ -591,7 +606,8 @@ __device__ __forceinline__ void warp_states_step(const PointWorld<BP> &world, co
                                                  const double *__restrict__ rec, const double *__restrict__ pts,
                                                  int units, int mode, bool cpg, double md, unsigned char *queue,
                                                  uint32_t *inv, uint32_t *__restrict__ mask_out, int lane,
-                                                 const GatherView &gv, uint32_t seq, uint64_t ll_word0)
+                                                 const GatherView &gv, uint32_t seq, uint64_t ll_word0,
+                                                 uint32_t *stage_words)
 {
     // ---- phase 1: which of my S states have a broad-phase candidate at all
     const uint32_t lt = (1u << lane) - 1u;
@@ -634,7 +650,9 @@ __device__ __forceinline__ void warp_states_step(const PointWorld<BP> &world, co
         const uint32_t active = live >= 32 ? 0xffffffffu : ((1u << live) - 1u);
         const uint32_t verdict = ~inv[lane] & active;
         mask_out[lane] = verdict;
-        if (GA && !(gv.debug & 2)) { // the same word, with this call's number, into every peer's staging row of this rank
+        if (GA && stage_words) {
+            stage_words[lane] = verdict; // sent with its group (k_states_warp)
+        } else if (GA && !(gv.debug & 2)) { // the same word, with this call's number, into every peer's row of this rank
             for (int p = 0; p < gv.world; ++p)
                 if (p != gv.rank) ll_store(gv.peer_ll[p] + ll_word0 + lane, verdict, seq);
         }
@@ -659,6 +677,7 @@ __device__ __forceinline__ void warp_states_step(const PointWorld<BP> &world, co
 // coordinate so they are not queued behind the coordinates.
 constexpr int kMaxWarps = 32;
 constexpr int kMaxSlots = 64;
+constexpr uint32_t kGaStageWords = 1024; // GA: blocks of up to this many mask words send them in groups
 
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
 {
@@ -670,7 +689,7 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
                                                       int can_pass_gate, double min_distance, int aabb_in_smem,
                                                       int log2_slots, uint32_t table_bytes, uint32_t rec_bytes,
                                                       uint32_t wpb, uint32_t rem, uint32_t *__restrict__ mask,
-                                                      const __grid_constant__ GatherView gv)
+                                                      const __grid_constant__ GatherView gv, uint32_t ga_group)
 {
     __shared__ uint32_t s_seq, s_hdr, s_cnt[kMaxRanks]; // GA: call number; header state (0 none, 1 claimed, 2 read)
     __shared__ __align__(8) uint64_t s_full[kMaxSlots];
@@ -687,6 +706,11 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
     double *rec = reinterpret_cast<double *>(g_smem + table_bytes);
     unsigned char *ring = g_smem + table_bytes + rec_bytes;
     unsigned char *areas = ring + slots * kSlotBytes;
+    // GA, small blocks of words (ga_group > 0): verdict words are parked here and leave for the peers in groups of
+    // ga_group chunks (one 8 * S * ga_group byte run per peer instead of ga_group runs of 8 * S bytes: at 8 ranks the
+    // exchange is bound by the NUMBER of NVLink writes, not their bytes); behind them one counter per group.
+    uint32_t *ga_words = reinterpret_cast<uint32_t *>(areas + ((blockDim.x >> 5) - 1u) * (S * 32u + 32u));
+    uint32_t *ga_count = ga_words + kGaStageWords;
     EPP_TRACE_EV(blockIdx.x * consumers + (warp == 0 ? 0 : warp - 1), warp == 0 ? 13 : 14);
 
     const uint32_t b0 = blockIdx.x * wpb + (blockIdx.x < rem ? blockIdx.x : rem);
@@ -713,6 +737,8 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
             mbar_init(&s_empty[s], 1);
             s_rounds_done[s] = 0u;
         }
+        if (GA && ga_group)
+            for (uint32_t s = threadIdx.x - 32; s < kGaStageWords / S; s += blockDim.x - 32) ga_count[s] = 0u;
         if (threadIdx.x - 32 < slots) mbar_init_fence();
     }
     if (threadIdx.x == 0) {
@@ -843,8 +869,32 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
             __syncwarp();
         }
         EPP_TRACE_EV(g, 4 + 2 * tstep);
+        const bool staged = GA && ga_group != 0u;
         warp_states_step<BP, S, RS, GA>(world, wv, rec, pts, units, mode, cpg, min_distance, queue, inv,
-                                        mask + b0 + i * S, lane, gv, seq, ll_row + b0 + i * S);
+                                        mask + b0 + i * S, lane, gv, seq, ll_row + b0 + i * S,
+                                        staged ? ga_words + i * S : nullptr);
+        if (staged) {
+            // count the chunk into its group; the warp that completes a group sends it
+            const uint32_t grp = i / ga_group, g0 = grp * ga_group;
+            const uint32_t g_chunks = (chunks - g0) < ga_group ? (chunks - g0) : ga_group;
+            uint32_t old = 0;
+            if (lane == 0) {
+                __threadfence_block();
+                old = atomicAdd(&ga_count[grp], 1u);
+            }
+            old = __shfl_sync(0xffffffffu, old, 0);
+            if (old + 1u == g_chunks && !(gv.debug & 2)) {
+                __threadfence_block();
+                const uint32_t w0 = g0 * S;
+                const uint32_t w1 = (w0 + g_chunks * S) < (b1 - b0) ? (w0 + g_chunks * S) : (b1 - b0);
+                for (int p = 0; p < gv.world; ++p) {
+                    if (p == gv.rank) continue;
+                    uint2 *dst = gv.peer_ll[p] + ll_row + b0;
+                    for (uint32_t w = w0 + (uint32_t)lane; w < w1; w += 32u)
+                        ll_store(dst + w, *(volatile uint32_t *)&ga_words[w], seq);
+                }
+            }
+        }
         EPP_TRACE_EV(g, 5 + 2 * tstep);
 #ifdef EPP_TRACE
         if (tstep < 3) ++tstep;
@@ -1358,7 +1408,12 @@ cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const 
     const size_t chunks_per_block = (chunks_total + grid - 1) / grid;
     if ((size_t)cons > chunks_per_block) cons = (int)chunks_per_block;
     const size_t budget = (size_t)(228 * 1024) / bps - 1024 - 4096; // 1 KB reserved per block + static + slack
-    const size_t fixed = table_bytes + rec_bytes + cons * warp_bytes;
+    // GA: group staging when a block's words fit it (small batches, where the exchange is the cost that matters)
+    const size_t words_per_block = (words + grid - 1) / grid + S;
+    uint32_t ga_group = 0;
+    if (GA && cfg.gather_group_chunks > 1 && words_per_block <= kGaStageWords) ga_group = (uint32_t)cfg.gather_group_chunks;
+    const size_t ga_bytes = ga_group ? (size_t)kGaStageWords * 4 + (kGaStageWords / S) * 4 : 0;
+    const size_t fixed = table_bytes + rec_bytes + cons * warp_bytes + ga_bytes;
     if (fixed + 2 * slot_bytes > budget) return cudaSuccess;
     int log2_slots = 1;
     while (log2_slots < 6 && fixed + (slot_bytes << (log2_slots + 1)) <= budget &&
@@ -1368,7 +1423,7 @@ cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const 
     // A consumer that takes chunk i waits on phase (i / slots) of the slot's `full` barrier; that is only
     // well defined if chunk i - slots has been consumed, which in-order hand-out guarantees iff slots >= consumers.
     if (cons > (1 << log2_slots)) cons = 1 << log2_slots;
-    const size_t smem = table_bytes + rec_bytes + cons * warp_bytes + (slot_bytes << log2_slots);
+    const size_t smem = fixed + (slot_bytes << log2_slots);
     cudaError_t err = cudaFuncSetAttribute(k_states_warp<BP, S, RS, GA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
     cudaLaunchConfig_t lc = {};
@@ -1383,7 +1438,7 @@ cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const 
     lc.numAttrs = cfg.states_pdl ? 1 : 0;
     err = cudaLaunchKernelEx(&lc, k_states_warp<BP, S, RS, GA>, wv, d_xyz, n, mode | (cfg.states_debug << 8),
                              can_pass_gate, min_distance, in_smem ? 1 : 0, log2_slots, (uint32_t)table_bytes,
-                             (uint32_t)rec_bytes, (uint32_t)(words / grid), (uint32_t)(words % grid), d_mask, gv);
+                             (uint32_t)rec_bytes, (uint32_t)(words / grid), (uint32_t)(words % grid), d_mask, gv, ga_group);
     if (err != cudaSuccess) return err;
     launched = true;
     return cudaGetLastError();

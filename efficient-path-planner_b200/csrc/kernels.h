@@ -25,6 +25,7 @@ struct LaunchCfg {
     int states_bits1 = 1;           // warp form: single-word candidate masks for worlds of <= 32 OBBs
     int states_rec_smem = 1;        // warp-pipelined form: fold the world records into shared memory (M <= 64)
     int poly_traj_per_warp = 0;     // K3b: trajectories per warp (0: by batch size)
+    int gather_group_chunks = 8;    // fused exchange: chunks whose mask words travel to a peer in one run (1: each chunk alone)
     int gather_debug = 0;           // profiling only, see GatherView::debug
     int states_per_thread = 0;      // warp form: mask words (32 states) per chunk and warp step, 4 (default) or 8
 };
