@@ -58,6 +58,7 @@ Knob g_knobs[] = {
     {"states_warp_log2_slots", {0}},
     {"states_warp_min_n", {4096}},
     {"states_rec_smem", {1}},
+    {"states_rec_smem_max", {0}},        // 0: 256 OBBs
     {"states_bits1", {1}},
     {"states_pdl", {1}},
     {"states_debug", {0}},               // profiling builds only
@@ -247,6 +248,7 @@ LaunchCfg launch_cfg(const DeviceEpoch &ep)
     c.states_warp_log2_slots = knob_value("states_warp_log2_slots");
     c.states_warp_min_n = knob_value("states_warp_min_n");
     c.states_rec_smem = knob_value("states_rec_smem");
+    c.states_rec_smem_max = knob_value("states_rec_smem_max");
     c.states_bits1 = knob_value("states_bits1");
     c.states_pdl = knob_value("states_pdl");
     c.states_debug = knob_value("states_debug");

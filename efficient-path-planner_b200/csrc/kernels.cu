@@ -589,7 +589,7 @@ __global__ void __launch_bounds__(256) k_gather_push(const __grid_constant__ Gat
 }
 
 constexpr int kRecDoubles = 17;
-constexpr int kRecSmemMax = 64;
+constexpr int kRecSmemMax = 256; // default of the states_rec_smem_max knob; one prologue thread per record (<= 992)
 constexpr int kWordBytes = 32 * 3 * 8; // one mask word of states = 768 B of coordinates
 
 __device__ __forceinline__ bool rec_hit(const double *__restrict__ r, const P3 &p)
@@ -1478,7 +1478,8 @@ cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, con
         const size_t table_bytes = (smem + 127) / 128 * 128;
         const int stages = 0; // ring depth comes from the shared-memory budget
         const int S = cfg.states_per_thread == 8 ? 8 : 4;
-        const bool rs = wv.M <= kRecSmemMax && wv.zrot && cfg.states_rec_smem != 0;
+        const int rec_max = cfg.states_rec_smem_max > 0 ? (cfg.states_rec_smem_max < 992 ? cfg.states_rec_smem_max : 992) : kRecSmemMax;
+        const bool rs = wv.M <= rec_max && wv.zrot && cfg.states_rec_smem != 0;
         const int wbp = (bp == EPP_BP_BITS && wv.W == 1 && cfg.states_bits1 != 0) ? kBpBits1 : bp;
         bool launched = false;
 #define EPP_LAUNCH_WARP(S_, RS_, GA_)                                                                                 \
