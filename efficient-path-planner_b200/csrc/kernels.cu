@@ -1423,6 +1423,9 @@ cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const 
     // A consumer that takes chunk i waits on phase (i / slots) of the slot's `full` barrier; that is only
     // well defined if chunk i - slots has been consumed, which in-order hand-out guarantees iff slots >= consumers.
     if (cons > (1 << log2_slots)) cons = 1 << log2_slots;
+    // records are folded by one consumer thread each: a batch too small for M consumer threads per block takes
+    // the records from global memory instead (the caller retries with RS = false)
+    if (RS && cons * 32 < wv.M) return cudaSuccess;
     const size_t smem = fixed + (slot_bytes << log2_slots);
     cudaError_t err = cudaFuncSetAttribute(k_states_warp<BP, S, RS, GA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
@@ -1479,7 +1482,7 @@ cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, con
         const int stages = 0; // ring depth comes from the shared-memory budget
         const int S = cfg.states_per_thread == 8 ? 8 : 4;
         const int rec_max = cfg.states_rec_smem_max > 0 ? (cfg.states_rec_smem_max < 992 ? cfg.states_rec_smem_max : 992) : kRecSmemMax;
-        const bool rs = wv.M <= rec_max && wv.zrot && cfg.states_rec_smem != 0;
+        bool rs = wv.M <= rec_max && wv.zrot && cfg.states_rec_smem != 0;
         const int wbp = (bp == EPP_BP_BITS && wv.W == 1 && cfg.states_bits1 != 0) ? kBpBits1 : bp;
         bool launched = false;
 #define EPP_LAUNCH_WARP(S_, RS_, GA_)                                                                                 \
@@ -1493,11 +1496,17 @@ cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, con
     else if (rs) EPP_LAUNCH_WARP(4, true, false);            \
     else if (gv) EPP_LAUNCH_WARP(4, false, true);            \
     else EPP_LAUNCH_WARP(4, false, false)
-        if (wbp == kBpBits1) {
-            constexpr int BP = kBpBits1;
-            EPP_LAUNCH_WARP_S();
-        } else {
-            EPP_DISPATCH_BP(bp, { EPP_LAUNCH_WARP_S(); });
+        for (int attempt = 0; attempt < 2 && !launched && err == cudaSuccess; ++attempt) {
+            if (attempt == 1) {
+                if (!rs) break;
+                rs = false; // too few consumer threads for the records: second try with global records
+            }
+            if (wbp == kBpBits1) {
+                constexpr int BP = kBpBits1;
+                EPP_LAUNCH_WARP_S();
+            } else {
+                EPP_DISPATCH_BP(bp, { EPP_LAUNCH_WARP_S(); });
+            }
         }
 #undef EPP_LAUNCH_WARP_S
 #undef EPP_LAUNCH_WARP

@@ -594,3 +594,16 @@ def test_segments_smem_record_form_equals_global_record_form(oracle, config, bp)
                     epp_b200.set_tuning("segments_variant", 0)
             assert mismatches(got[0], want) == 0, (n, cpg)
             assert mismatches(got[1], want) == 0, (n, cpg)
+
+
+@pytest.mark.parametrize("bp", BPS, ids=BP_IDS)
+def test_states_warp_form_record_fold_small_batches(oracle, config, bp):
+    """Worlds of up to 256 OBBs fold their records into shared memory, one consumer thread per record; a batch
+    with few chunks per block has fewer consumer threads than records and must take the global-record form."""
+    g, o, lo, hi = worlds.world_256()
+    ow, gw = build_pair(oracle, epp_b200, config, g, o, bp)
+    for n in (4096, 4097, 9000, 20_000, 70_000, 108_544, 300_000):
+        xyz = worlds.gen_states(4242, n, n, lo, hi)
+        for cpg in (False, True):
+            assert mismatches(gw.check_states(xyz, cpg), ow.check_states(xyz, cpg, threads=8)) == 0, (n, cpg)
+        assert mismatches(gw.check_states_mindist(xyz, 0.15), ow.check_states_mindist(xyz, 0.15, threads=8)) == 0, n
