@@ -100,6 +100,9 @@ SIGNATURES = {
     "epp_check_states_gather_dev": (C.c_int, [_vp, _vp, C.c_size_t, C.c_int, _vp, C.c_int, _vp]),
     "epp_check_states_mindist_gather_dev": (C.c_int, [_vp, _vp, C.c_size_t, C.c_double, _vp, C.c_int, _vp]),
     "epp_check_segments_gather_dev": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_int, _vp, C.c_int, _vp]),
+    "epp_segment_times": (C.c_int, [_vp, C.c_int, C.c_double, C.c_double, _vp]),
+    "epp_minsnap": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_int, _vp]),
+    "epp_minsnap_dev": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_int, _vp, _vp]),
     "epp_kernel_launch_count": (C.c_uint64, []),
     "epp_set_tuning": (C.c_int, [C.c_char_p, C.c_int]),
     "epp_get_tuning": (C.c_int, [C.c_char_p, C.POINTER(C.c_int)]),
@@ -533,6 +536,39 @@ class Gather:
         world._sync()
         _chk(lib().epp_check_segments_gather_dev(world._h, a.data_ptr(), b.data_ptr(), a.numel() // 3,
                                                  int(can_pass_gate), self._h, buffer, World._stream()))
+
+
+def segment_times(waypoints, v_max, a_max):
+    """estimateSegmentTimesNfabian (external/poly_traj/src/vertex.cpp:272-289): (..., V, 3) -> (..., V - 1)."""
+    w = _f64(waypoints)
+    lead, V = w.shape[:-2], w.shape[-2]
+    w2 = w.reshape(-1, V, 3)
+    out = np.zeros((w2.shape[0], V - 1))
+    for i in range(w2.shape[0]):
+        _chk(lib().epp_segment_times(_ptr(w2[i]), V, float(v_max), float(a_max), _ptr(out[i])))
+    return out.reshape(lead + (V - 1,))
+
+
+def minsnap(waypoints, durations, start_vel_acc=None):
+    """Batched linear min-snap solve on the GPU: waypoints (n, K+1, 3), durations (n, K), optional start
+    velocity / acceleration (n, 6) -> coefficients (n, K, 3, 10) in check_poly_trajectories' layout."""
+    w, d = _f64(waypoints), _f64(durations)
+    n, K = d.shape
+    va = _f64(start_vel_acc, (n, 6)) if start_vel_acc is not None else None
+    out = np.zeros((n, K, 3, 10))
+    _chk(lib().epp_minsnap(_ptr(w), _ptr(d), _ptr(va) if va is not None else None, n, K, _ptr(out)))
+    return out
+
+
+def minsnap_dev(waypoints, durations, start_vel_acc=None, out=None):
+    import torch
+    n, K = durations.shape
+    if out is None:
+        out = torch.empty((n, K, 3, 10), dtype=torch.float64, device=durations.device)
+    _chk(lib().epp_minsnap_dev(waypoints.data_ptr(), durations.data_ptr(),
+                               start_vel_acc.data_ptr() if start_vel_acc is not None else None, n, K,
+                               out.data_ptr(), torch.cuda.current_stream().cuda_stream))
+    return out
 
 
 def gen_states_dev(seed, first, n, lo, hi, out=None, device="cuda"):

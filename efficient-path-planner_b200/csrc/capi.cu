@@ -5,6 +5,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <cmath>
 #include <cstring>
 #include <memory>
 #include <mutex>
@@ -1017,6 +1018,63 @@ extern "C" int epp_check_segments_gather_dev(epp_world *w, const double *d_a, co
     cudaError_t e = launch_segments(launch_cfg(*ep), ep->view, ep->bp, d_a, d_b, n, can_pass_gate,
                                     gv.out + (size_t)gv.rank * gv.slot_words, (cudaStream_t)stream, g->world > 1 ? &gv : nullptr);
     return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
+}
+
+// ---- min-snap trajectory generation ------------------------------------------------------------------------
+
+extern "C" int epp_segment_times(const double *waypoints, int n_vertices, double v_max, double a_max, double *durations)
+{
+    if (!waypoints || !durations || n_vertices < 2 || !(v_max > 0.0) || !(a_max > 0.0))
+        return fail(EPP_ERR_INVALID_ARG, "segment times");
+    const double magic_fabian_constant = 6.5; // vertex.h default
+    for (int i = 0; i + 1 < n_vertices; ++i) {
+        const double *s = waypoints + 3 * i, *e = s + 3;
+        const double dx = e[0] - s[0], dy = e[1] - s[1], dz = e[2] - s[2];
+        const double distance = std::sqrt(dx * dx + dy * dy + dz * dz);
+        durations[i] = distance / v_max * 2 * (1.0 + magic_fabian_constant * v_max / a_max * std::exp(-distance / v_max * 2));
+    }
+    return EPP_OK;
+}
+
+extern "C" int epp_minsnap_dev(const double *d_waypoints, const double *d_durations, const double *d_start_vel_acc,
+                               size_t n_traj, int n_segments, double *d_coeffs, void *stream)
+{
+    if (n_traj && (!d_waypoints || !d_durations || !d_coeffs)) return fail(EPP_ERR_INVALID_ARG, "null buffer");
+    if (n_segments < 1 || n_segments > 16) return fail(EPP_ERR_INVALID_ARG, "1 to 16 segments per trajectory");
+    cudaError_t e = launch_minsnap(d_waypoints, d_durations, d_start_vel_acc, n_traj, n_segments, d_coeffs,
+                                   (cudaStream_t)stream);
+    return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
+}
+
+extern "C" int epp_minsnap(const double *waypoints, const double *durations, const double *start_vel_acc, size_t n_traj,
+                           int n_segments, double *coeffs)
+{
+    if (n_traj == 0) return EPP_OK;
+    if (!waypoints || !durations || !coeffs) return fail(EPP_ERR_INVALID_ARG, "null buffer");
+    if (n_segments < 1 || n_segments > 16) return fail(EPP_ERR_INVALID_ARG, "1 to 16 segments per trajectory");
+    int device = 0;
+    EPP_CUDA(cudaGetDevice(&device));
+    Staging *s;
+    int rc = get_staging(device, &s);
+    if (rc) return rc;
+    const size_t K = (size_t)n_segments;
+    const size_t b_wp = n_traj * (K + 1) * 3 * 8, b_T = n_traj * K * 8, b_va = start_vel_acc ? n_traj * 6 * 8 : 0;
+    const size_t b_c = n_traj * K * 30 * 8;
+    const size_t o_T = align_up(b_wp, 256), o_va = o_T + align_up(b_T, 256), o_c = o_va + align_up(b_va, 256);
+    rc = reserve_device(s, o_c + b_c);
+    if (rc) return rc;
+    rc = reserve_host(s, 2 * kChunk);
+    if (rc) return rc;
+    if ((rc = upload(s, s->d, waypoints, b_wp, 0))) return rc;
+    if ((rc = upload(s, s->d + o_T, durations, b_T, 0))) return rc;
+    if (b_va && (rc = upload(s, s->d + o_va, start_vel_acc, b_va, 0))) return rc;
+    cudaError_t e = launch_minsnap((const double *)s->d, (const double *)(s->d + o_T),
+                                   b_va ? (const double *)(s->d + o_va) : nullptr, n_traj, n_segments,
+                                   (double *)(s->d + o_c), s->stream);
+    if (e != cudaSuccess) return cuda_fail(e, "kernel launch");
+    EPP_CUDA(cudaMemcpyAsync(coeffs, s->d + o_c, b_c, cudaMemcpyDeviceToHost, s->stream));
+    EPP_CUDA(cudaStreamSynchronize(s->stream));
+    return EPP_OK;
 }
 
 // ---- multi-GPU helpers, generators ---------------------------------------------------------------------

@@ -73,6 +73,10 @@ cudaError_t launch_poly_trajectories(const LaunchCfg &cfg, const WorldView &wv, 
                                      int n_coeffs, double min_distance, size_t max_samples, uint32_t *d_traj_valid,
                                      uint32_t *d_sample_mask, uint32_t *d_n_samples, int64_t *d_first_invalid,
                                      long long *d_first_scratch, cudaStream_t stream);
+// Batched linear min-snap solve (minsnap.cu): waypoints [n][K+1][3], durations [n][K], optional start velocity /
+// acceleration [n][6] -> coefficients [n][K][3][10].
+cudaError_t launch_minsnap(const double *d_waypoints, const double *d_durations, const double *d_start_vel_acc,
+                           size_t n_traj, int n_segments, double *d_coeffs, cudaStream_t stream);
 cudaError_t launch_gen_states(uint64_t seed, uint64_t first, size_t n, const double lo[3], const double hi[3],
                               double *d_xyz, cudaStream_t stream);
 cudaError_t launch_gen_segments(uint64_t seed, uint64_t first, size_t n, const double lo[3], const double hi[3],

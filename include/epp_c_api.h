@@ -166,6 +166,25 @@ int epp_check_poly_trajectories_dev(epp_world *w, const double *d_coeffs, const 
                                     uint32_t *d_sample_mask, uint32_t *d_n_samples,
                                     int64_t *d_first_invalid, void *stream);
 
+/* ---- Min-snap trajectory generation, batched --------------------------
+ *
+ * Replaces, for many waypoint sets at once, the solve inside poly_traj::generateTrajectory
+ * (external/poly_traj/src/trajectory_generator.cpp:12-58): vertices with the start fully
+ * constrained (position, velocity, acceleration given; jerk = snap = 0), interior vertices
+ * position-only, the end at rest; PolynomialOptimization<10>::setupFromVertices + solveLinear
+ * (impl/polynomial_optimization_linear_impl.h:56-380), derivative_to_optimize = SNAP.
+ * Output layout = input layout of epp_check_poly_trajectories: coeffs[n][K][3][10] (increasing
+ * powers).  Floating-point result: agrees with the reference formulation to ~1e-9 m along the
+ * trajectory (tests/test_minsnap.py), not bit for bit. */
+/* estimateSegmentTimes = estimateSegmentTimesNfabian (vertex.cpp:245-289), host side (libm exp):
+ * waypoints[n_vertices][3] -> durations[n_vertices - 1]. */
+int epp_segment_times(const double *waypoints, int n_vertices, double v_max, double a_max, double *durations);
+/* start_vel_acc: n_traj x 6 (velocity xyz, acceleration xyz) or NULL for a start at rest. */
+int epp_minsnap(const double *waypoints, const double *durations, const double *start_vel_acc, size_t n_traj,
+                int n_segments, double *coeffs);
+int epp_minsnap_dev(const double *d_waypoints, const double *d_durations, const double *d_start_vel_acc,
+                    size_t n_traj, int n_segments, double *d_coeffs, void *stream);
+
 /* ---- Multi-GPU sharding helpers (host logic) --------------------------- */
 
 /* Contiguous range of units for `rank` of `world_size`, boundaries aligned to `align`
