@@ -103,6 +103,9 @@ SIGNATURES = {
     "epp_segment_times": (C.c_int, [_vp, C.c_int, C.c_double, C.c_double, _vp]),
     "epp_minsnap": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_int, _vp]),
     "epp_minsnap_dev": (C.c_int, [_vp, _vp, _vp, C.c_size_t, C.c_int, _vp, _vp]),
+    "epp_sample_trajectories": (C.c_int, [_vp, _vp, _vp, _vp, C.c_size_t, C.c_int, C.c_int, C.c_size_t, _vp, _vp]),
+    "epp_sample_trajectories_dev": (C.c_int, [_vp, _vp, _vp, _vp, C.c_size_t, C.c_int, C.c_int, C.c_size_t, _vp,
+                                              _vp, _vp]),
     "epp_kernel_launch_count": (C.c_uint64, []),
     "epp_set_tuning": (C.c_int, [C.c_char_p, C.c_int]),
     "epp_get_tuning": (C.c_int, [C.c_char_p, C.POINTER(C.c_int)]),
@@ -569,6 +572,21 @@ def minsnap_dev(waypoints, durations, start_vel_acc=None, out=None):
                                start_vel_acc.data_ptr() if start_vel_acc is not None else None, n, K,
                                out.data_ptr(), torch.cuda.current_stream().cuda_stream))
     return out
+
+
+def sample_trajectories(coeffs, durations, dt, time_offsets=None, max_rows=1024):
+    """The reference's trajectory matrices (poly_traj::generateTrajectory's sampling, trajectory_generator.cpp:60-97):
+    coeffs (n, K, 3, N), durations (n, K), dt (n,) -> list of (rows_i, 10) arrays [px vx ax py vy ay pz vz az t]."""
+    c, d = _f64(coeffs), _f64(durations)
+    n, K, _, N = c.shape
+    dts = np.ascontiguousarray(np.broadcast_to(np.asarray(dt, dtype=np.float64), (n,)))
+    offs = _f64(np.broadcast_to(np.asarray(time_offsets, dtype=np.float64), (n,))) if time_offsets is not None else None
+    out = np.zeros((n, 10, max_rows))
+    rows = np.zeros(n, dtype=np.uint32)
+    _chk(lib().epp_sample_trajectories(_ptr(c), _ptr(d), _ptr(dts), _ptr(offs), n, K, N, max_rows, _ptr(out), _ptr(rows)))
+    if (rows > max_rows).any():
+        raise EppError(6, "sample_trajectories: a trajectory has %d rows, max_rows is %d" % (rows.max(), max_rows))
+    return [np.ascontiguousarray(out[i, :, : rows[i]].T) for i in range(n)]
 
 
 def gen_states_dev(seed, first, n, lo, hi, out=None, device="cuda"):

@@ -1077,6 +1077,55 @@ extern "C" int epp_minsnap(const double *waypoints, const double *durations, con
     return EPP_OK;
 }
 
+extern "C" int epp_sample_trajectories_dev(const double *d_coeffs, const double *d_durations, const double *d_dt,
+                                           const double *d_time_offsets, size_t n_traj, int n_segments, int n_coeffs,
+                                           size_t ld, double *d_out, uint32_t *d_n_rows, void *stream)
+{
+    if (n_traj == 0) return EPP_OK;
+    if (!d_coeffs || !d_durations || !d_dt || !d_out || n_segments < 1 || n_coeffs < 1 || ld == 0)
+        return fail(EPP_ERR_INVALID_ARG, "trajectory sampling arguments");
+    cudaError_t e = launch_sample_poly(d_coeffs, d_durations, d_dt, d_time_offsets, n_traj, n_segments, n_coeffs, ld, d_out,
+                                       d_n_rows, (cudaStream_t)stream);
+    return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
+}
+
+extern "C" int epp_sample_trajectories(const double *coeffs, const double *durations, const double *dt,
+                                       const double *time_offsets, size_t n_traj, int n_segments, int n_coeffs, size_t ld,
+                                       double *out, uint32_t *n_rows)
+{
+    if (n_traj == 0) return EPP_OK;
+    if (!coeffs || !durations || !dt || !out || n_segments < 1 || n_coeffs < 1 || ld == 0)
+        return fail(EPP_ERR_INVALID_ARG, "trajectory sampling arguments");
+    int device = 0;
+    EPP_CUDA(cudaGetDevice(&device));
+    Staging *s;
+    int rc = get_staging(device, &s);
+    if (rc) return rc;
+    const size_t K = (size_t)n_segments;
+    const size_t b_c = n_traj * K * 3 * (size_t)n_coeffs * 8, b_T = n_traj * K * 8, b_dt = n_traj * 8;
+    const size_t b_off = time_offsets ? n_traj * 8 : 0, b_out = n_traj * 10 * ld * 8, b_n = n_traj * 4;
+    const size_t o_T = align_up(b_c, 256), o_dt = o_T + align_up(b_T, 256), o_off = o_dt + align_up(b_dt, 256);
+    const size_t o_out = o_off + align_up(b_off, 256), o_n = o_out + align_up(b_out, 256);
+    rc = reserve_device(s, o_n + b_n);
+    if (rc) return rc;
+    rc = reserve_host(s, 2 * kChunk + b_n);
+    if (rc) return rc;
+    if ((rc = upload(s, s->d, coeffs, b_c, 0))) return rc;
+    if ((rc = upload(s, s->d + o_T, durations, b_T, 0))) return rc;
+    if ((rc = upload(s, s->d + o_dt, dt, b_dt, 0))) return rc;
+    if (b_off && (rc = upload(s, s->d + o_off, time_offsets, b_off, 0))) return rc;
+    cudaError_t e = launch_sample_poly((const double *)s->d, (const double *)(s->d + o_T), (const double *)(s->d + o_dt),
+                                       b_off ? (const double *)(s->d + o_off) : nullptr, n_traj, n_segments, n_coeffs, ld,
+                                       (double *)(s->d + o_out), (uint32_t *)(s->d + o_n), s->stream);
+    if (e != cudaSuccess) return cuda_fail(e, "kernel launch");
+    EPP_CUDA(cudaMemcpyAsync(out, s->d + o_out, b_out, cudaMemcpyDeviceToHost, s->stream));
+    uint32_t *h_n = (uint32_t *)(s->h + 2 * kChunk);
+    EPP_CUDA(cudaMemcpyAsync(h_n, s->d + o_n, b_n, cudaMemcpyDeviceToHost, s->stream));
+    EPP_CUDA(cudaStreamSynchronize(s->stream));
+    if (n_rows) std::memcpy(n_rows, h_n, b_n);
+    return EPP_OK;
+}
+
 // ---- multi-GPU helpers, generators ---------------------------------------------------------------------
 
 extern "C" int epp_shard_range(size_t n, int rank, int world_size, size_t align, size_t *begin, size_t *end)

@@ -77,6 +77,10 @@ cudaError_t launch_poly_trajectories(const LaunchCfg &cfg, const WorldView &wv, 
 // acceleration [n][6] -> coefficients [n][K][3][10].
 cudaError_t launch_minsnap(const double *d_waypoints, const double *d_durations, const double *d_start_vel_acc,
                            size_t n_traj, int n_segments, double *d_coeffs, cudaStream_t stream);
+// The sampling half of poly_traj::generateTrajectory: column-major rows x 10 matrices [px vx ax py vy ay pz vz az t].
+cudaError_t launch_sample_poly(const double *d_coeffs, const double *d_durations, const double *d_dt,
+                               const double *d_time_offsets, size_t n_traj, int n_segments, int n_coeffs, size_t ld,
+                               double *d_out, uint32_t *d_n_rows, cudaStream_t stream);
 cudaError_t launch_gen_states(uint64_t seed, uint64_t first, size_t n, const double lo[3], const double hi[3],
                               double *d_xyz, cudaStream_t stream);
 cudaError_t launch_gen_segments(uint64_t seed, uint64_t first, size_t n, const double lo[3], const double hi[3],

@@ -162,6 +162,113 @@ __global__ void __launch_bounds__(32) k_minsnap(const double *__restrict__ waypo
     }
 }
 
+// ---- trajectory matrix: the sampling half of poly_traj::generateTrajectory ---------------------------------
+//
+// trajectory_generator.cpp:60-97: three evaluateRange passes (position, velocity, acceleration) over
+// [getMinTime(), getMaxTime()] at the sampling interval, written as rows
+// [px vx ax  py vy ay  pz vz az  t + startTimeOffset].  One warp per trajectory: lane 0 advances the reference's
+// sequential sampler (trajectory.cpp:81-141, running sums) by 32 samples, then the 32 lanes evaluate one sample
+// each: Polynomial::evaluate(t, derivative) (polynomial.h:136-150) — Horner from the top coefficient with the
+// base coefficients j! / (j - derivative)! (polynomial.cpp:145-160), every operation individually rounded, so
+// the matrix is bit-equal to the reference's.  Output is column-major rows x 10 with leading dimension ld
+// (Eigen's MatrixXd layout), one matrix per trajectory.
+__device__ __forceinline__ double ms_eval(const double *__restrict__ c, int n, double t, int derivative)
+{
+    auto bc = [&](int j) -> double { // base_coefficients_(derivative, j)
+        double v = 1.0;
+        for (int r = 0; r < derivative; ++r) v *= (double)(j - r);
+        return v;
+    };
+    double r = __dmul_rn(bc(n - 1), c[n - 1]);
+    for (int j = n - 2; j >= derivative; --j) {
+        r = __dmul_rn(r, t);
+        r = __dadd_rn(r, __dmul_rn(bc(j), c[j]));
+    }
+    return r;
+}
+
+__global__ void __launch_bounds__(32) k_sample_poly(const double *__restrict__ coeffs, const double *__restrict__ durations,
+                                                    const double *__restrict__ dts, const double *__restrict__ time_offsets,
+                                                    size_t n_traj, int K, int N, size_t ld, double *__restrict__ out,
+                                                    uint32_t *__restrict__ n_rows)
+{
+    __shared__ double s_t[32], s_acc[32];
+    __shared__ int s_seg[32];
+    const size_t tr = blockIdx.x;
+    if (tr >= n_traj) return;
+    const int lane = threadIdx.x;
+    const double *dur = durations + tr * (size_t)K;
+    const double dt = dts[tr], off = time_offsets ? time_offsets[tr] : 0.0;
+    double *m = out + tr * 10 * ld;
+    // sampler state (lane 0 is the only one that advances it)
+    double t_end = 0.0, acc = 0.0, tin = 0.0, seg_T = 0.0;
+    int seg = 0;
+    bool done = false;
+    if (lane == 0) {
+        for (int k = 0; k < K; ++k) t_end = __dadd_rn(t_end, dur[k]); // trajectory.h:64-71
+        double a = 0.0;
+        int k = 0;
+        for (k = 0; k < K; ++k) { // start-segment search with t_start = 0 (trajectory.cpp:99-110)
+            a = __dadd_rn(a, dur[k]);
+            if (a > 0.0) break;
+        }
+        if (0.0 > a || k >= K) {
+            done = true;
+        } else {
+            seg = k;
+            seg_T = dur[seg];
+            acc = __dsub_rn(a, seg_T);
+            tin = __dsub_rn(0.0, acc);
+        }
+    }
+    size_t rows = 0;
+    for (;;) {
+        int cnt = 0;
+        if (lane == 0) {
+            while (!done && cnt < 32) {
+                if (!(acc < t_end)) {
+                    done = true;
+                    break;
+                }
+                if (tin > seg_T) {
+                    tin = __dsub_rn(tin, seg_T);
+                    ++seg;
+                    if (seg >= K) {
+                        done = true;
+                        break;
+                    }
+                    seg_T = dur[seg];
+                    continue;
+                }
+                s_t[cnt] = tin;
+                s_acc[cnt] = acc;
+                s_seg[cnt] = seg;
+                ++cnt;
+                tin = __dadd_rn(tin, dt);
+                acc = __dadd_rn(acc, dt);
+            }
+        }
+        cnt = __shfl_sync(0xffffffffu, cnt, 0);
+        if (cnt == 0) break;
+        __syncwarp();
+        const size_t row = rows + (size_t)lane;
+        if (lane < cnt && row < ld) {
+            const double t = s_t[lane];
+            const double *c = coeffs + ((tr * (size_t)K + (size_t)s_seg[lane]) * 3) * (size_t)N;
+#pragma unroll
+            for (int d = 0; d < 3; ++d) {
+                m[(size_t)(3 * d) * ld + row] = ms_eval(c + d * N, N, t, 0);
+                m[(size_t)(3 * d + 1) * ld + row] = N > 1 ? ms_eval(c + d * N, N, t, 1) : 0.0;
+                m[(size_t)(3 * d + 2) * ld + row] = N > 2 ? ms_eval(c + d * N, N, t, 2) : 0.0;
+            }
+            m[9 * ld + row] = __dadd_rn(s_acc[lane], off);
+        }
+        rows += (size_t)cnt;
+        __syncwarp();
+    }
+    if (lane == 0 && n_rows) n_rows[tr] = (uint32_t)rows;
+}
+
 bool g_ms_constants_ready[64] = {};
 std::mutex g_ms_mu;
 
@@ -190,6 +297,18 @@ cudaError_t launch_minsnap(const double *d_waypoints, const double *d_durations,
         if (err != cudaSuccess) return err;
     }
     k_minsnap<<<(unsigned)n_traj, 32, smem, stream>>>(d_waypoints, d_durations, d_start_vel_acc, n_traj, K, d_coeffs);
+    g_launches++;
+    return cudaGetLastError();
+}
+
+cudaError_t launch_sample_poly(const double *d_coeffs, const double *d_durations, const double *d_dt,
+                               const double *d_time_offsets, size_t n_traj, int n_segments, int n_coeffs, size_t ld,
+                               double *d_out, uint32_t *d_n_rows, cudaStream_t stream)
+{
+    if (n_traj == 0) return cudaSuccess;
+    if (n_segments < 1 || n_coeffs < 1 || ld == 0 || n_traj > 0x7fffffffull) return cudaErrorInvalidValue;
+    k_sample_poly<<<(unsigned)n_traj, 32, 0, stream>>>(d_coeffs, d_durations, d_dt, d_time_offsets, n_traj, n_segments,
+                                                      n_coeffs, ld, d_out, d_n_rows);
     g_launches++;
     return cudaGetLastError();
 }

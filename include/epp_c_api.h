@@ -185,6 +185,17 @@ int epp_minsnap(const double *waypoints, const double *durations, const double *
 int epp_minsnap_dev(const double *d_waypoints, const double *d_durations, const double *d_start_vel_acc,
                     size_t n_traj, int n_segments, double *d_coeffs, void *stream);
 
+/* The sampling half of poly_traj::generateTrajectory (trajectory_generator.cpp:60-97): for every trajectory
+ * the rows x 10 matrix [px vx ax py vy ay pz vz az t + offset] of evaluateRange(0, maxTime, dt) in
+ * position, velocity and acceleration — bit-equal to the reference's — column-major with leading
+ * dimension ld (rows beyond ld are counted in n_rows but not written), matrices ld * 10 doubles apart. */
+int epp_sample_trajectories_dev(const double *d_coeffs, const double *d_durations, const double *d_dt,
+                                const double *d_time_offsets /* nullable */, size_t n_traj, int n_segments,
+                                int n_coeffs, size_t ld, double *d_out, uint32_t *d_n_rows, void *stream);
+int epp_sample_trajectories(const double *coeffs, const double *durations, const double *dt,
+                            const double *time_offsets /* nullable */, size_t n_traj, int n_segments, int n_coeffs,
+                            size_t ld, double *out, uint32_t *n_rows);
+
 /* ---- Multi-GPU sharding helpers (host logic) --------------------------- */
 
 /* Contiguous range of units for `rank` of `world_size`, boundaries aligned to `align`

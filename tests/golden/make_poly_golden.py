@@ -61,6 +61,8 @@ def main():
     rw.parse_gates_and_obstacles(g, o)
     n_samples = np.zeros(32, dtype=np.int64)
     samples = np.zeros((32, MAX_SAMPLES, 3))
+    vel = np.zeros((32, MAX_SAMPLES, 3))   # the velocity / acceleration passes of generateTrajectory
+    acc = np.zeros((32, MAX_SAMPLES, 3))   # (trajectory_generator.cpp:71-79)
     times = np.zeros((32, MAX_SAMPLES))
     masks = np.zeros((32, MAX_SAMPLES // 32), dtype=np.uint32)
     first_invalid = np.full(32, -1, dtype=np.int64)
@@ -70,13 +72,17 @@ def main():
         assert n <= MAX_SAMPLES, n
         n_samples[k] = n
         samples[k, :n], times[k, :n] = x, t
+        v, tv, nv = refpoly_py.evaluate_range(coeffs[k], T[k], dt[k], derivative=1)
+        a, ta, na = refpoly_py.evaluate_range(coeffs[k], T[k], dt[k], derivative=2)
+        assert nv == n and na == n and np.array_equal(tv, t) and np.array_equal(ta, t)
+        vel[k, :n], acc[k, :n] = v, a
         max_time[k] = refpoly_py.max_time(coeffs[k], T[k])
         m = rw.check_states_mindist(x, MIN_DISTANCE)
         masks[k, : m.size] = m
         bits = np.unpackbits(m.view(np.uint8), bitorder="little")[:n]
         bad = np.nonzero(bits == 0)[0]
         first_invalid[k] = bad[0] if bad.size else -1
-    out.update(traj_n=n_samples, traj_samples=samples, traj_times=times, traj_masks=masks,
+    out.update(traj_vel=vel, traj_acc=acc, traj_n=n_samples, traj_samples=samples, traj_times=times, traj_masks=masks,
                traj_first_invalid=first_invalid, traj_max_time=max_time,
                min_distance=np.array(MIN_DISTANCE))
 

@@ -121,3 +121,21 @@ def test_gpu_presampled_sweep_equals_reference_golden(config, golden):
         want = golden["traj_masks"][k][: (n + 31) // 32]
         got = gw.check_states_mindist(golden["traj_samples"][k, :n], md)
         assert np.array_equal(got, want)
+
+
+@pytest.mark.gpu
+def test_gpu_trajectory_matrices_equal_reference_golden(golden):
+    """epp_sample_trajectories = the sampling half of poly_traj::generateTrajectory: rows [px vx ax py vy ay pz vz az
+    t + offset], bit-equal to the reference's three evaluateRange passes."""
+    coeffs, T, dt = golden["traj_coeffs"], golden["traj_T"], golden["traj_dt"]
+    mats = epp_b200.sample_trajectories(coeffs, T, dt, time_offsets=1.25, max_rows=512)
+    for k, m in enumerate(mats):
+        n = int(golden["traj_n"][k])
+        assert m.shape == (n, 10), k
+        for d in range(3):
+            assert np.array_equal(m[:, 3 * d], golden["traj_samples"][k, :n, d]), (k, d)
+            assert np.array_equal(m[:, 3 * d + 1], golden["traj_vel"][k, :n, d]), (k, d)
+            assert np.array_equal(m[:, 3 * d + 2], golden["traj_acc"][k, :n, d]), (k, d)
+        assert np.array_equal(m[:, 9], golden["traj_times"][k, :n] + 1.25), k
+    with pytest.raises(epp_b200.EppError):
+        epp_b200.sample_trajectories(coeffs, T, dt, max_rows=64)  # the trajectories have ~200 rows
