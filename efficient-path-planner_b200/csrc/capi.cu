@@ -1040,7 +1040,7 @@ extern "C" int epp_minsnap_dev(const double *d_waypoints, const double *d_durati
                                size_t n_traj, int n_segments, double *d_coeffs, void *stream)
 {
     if (n_traj && (!d_waypoints || !d_durations || !d_coeffs)) return fail(EPP_ERR_INVALID_ARG, "null buffer");
-    if (n_segments < 1 || n_segments > 16) return fail(EPP_ERR_INVALID_ARG, "1 to 16 segments per trajectory");
+    if (n_segments < 1 || n_segments > 128) return fail(EPP_ERR_INVALID_ARG, "1 to 128 segments per trajectory");
     cudaError_t e = launch_minsnap(d_waypoints, d_durations, d_start_vel_acc, n_traj, n_segments, d_coeffs,
                                    (cudaStream_t)stream);
     return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
@@ -1051,7 +1051,7 @@ extern "C" int epp_minsnap(const double *waypoints, const double *durations, con
 {
     if (n_traj == 0) return EPP_OK;
     if (!waypoints || !durations || !coeffs) return fail(EPP_ERR_INVALID_ARG, "null buffer");
-    if (n_segments < 1 || n_segments > 16) return fail(EPP_ERR_INVALID_ARG, "1 to 16 segments per trajectory");
+    if (n_segments < 1 || n_segments > 128) return fail(EPP_ERR_INVALID_ARG, "1 to 128 segments per trajectory");
     int device = 0;
     EPP_CUDA(cudaGetDevice(&device));
     Staging *s;

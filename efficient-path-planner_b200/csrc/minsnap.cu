@@ -13,7 +13,8 @@
 // of duration T is the unit segment under u_r = T^r d_r and b_j = T^j c_j with the cost scaled by T^-7, so
 // H(T) = T^-7 D H1 D with D = diag(T^r) and the constant H1 = A1^-T Q1 A1^-1 (minsnap_constants.h, exact
 // rational arithmetic rounded once): nothing of powers of T is ever inverted.  Rpp is symmetric positive
-// definite of order 4 (K - 1): one warp per trajectory assembles it in shared memory (fixed lane -> row
+// definite of order 4 (K - 1) and block tridiagonal (a free derivative only meets those of the neighbouring
+// vertices), stored as a lower band of width 8: one warp per trajectory assembles it in shared memory (fixed lane -> row
 // assignment, no atomics: results are deterministic), factors it (Cholesky), solves the three dimensions and
 // maps the end-point derivatives of every segment back to coefficients.
 //
@@ -35,7 +36,8 @@ namespace {
 
 constexpr int kMsN = 10;       // coefficients per polynomial
 constexpr int kMsHalf = 5;     // end-point derivatives per vertex: position .. snap
-constexpr int kMsMaxSeg = 16;  // segments per trajectory supported by the shared-memory layout
+constexpr int kMsMaxSeg = 128; // segments per trajectory supported by the shared-memory layout
+constexpr int kMsBand = 8;     // Rpp is block tridiagonal in 4 x 4 blocks: |i - j| <= 7; lower band storage [row][row - col]
 
 __constant__ double c_A1inv[kMsN][kMsN];
 __constant__ double c_H1[kMsN][kMsN];
@@ -61,11 +63,11 @@ __global__ void __launch_bounds__(32) k_minsnap(const double *__restrict__ waypo
     if (t >= n_traj) return;
     const int lane = threadIdx.x;
     const int nP = 4 * (K - 1);
-    // shared: Tp[K][10] powers of T | wp[(K+1)*3] | Rpp[nP*nP] | rhs[3][nP]
+    // shared: Tp[K][10] powers of T | wp[(K+1)*3] | Rpp lower band [nP][8] | rhs[3][nP]
     double *Tp = reinterpret_cast<double *>(ms_smem);
     double *wp = Tp + K * kMsN;
     double *R = wp + 3 * (K + 1);
-    double *rhs = R + nP * nP;
+    double *rhs = R + nP * kMsBand;
     const double *va = start_vel_acc ? start_vel_acc + 6 * t : nullptr;
 
     for (int i = lane; i < 3 * (K + 1); i += 32) wp[i] = waypoints[t * 3 * (size_t)(K + 1) + i];
@@ -77,7 +79,7 @@ __global__ void __launch_bounds__(32) k_minsnap(const double *__restrict__ waypo
             p = p * T;
         }
     }
-    for (int i = lane; i < nP * nP + 3 * nP; i += 32) R[i] = 0.0; // Rpp and rhs are contiguous
+    for (int i = lane; i < nP * kMsBand + 3 * nP; i += 32) R[i] = 0.0; // Rpp and rhs are contiguous
     __syncwarp();
 
     // ---- assemble Rpp and rhs = -Rpf df: lane = local row of the segment's 10 x 10 block, segments in turn
@@ -95,7 +97,7 @@ __global__ void __launch_bounds__(32) k_minsnap(const double *__restrict__ waypo
                     const double h = c_H1[row][col] * srow * tp[rc];
                     const int fj = ms_free_index(vc, rc, K);
                     if (fj >= 0) {
-                        R[fi * nP + fj] += h;
+                        if (fj <= fi) R[fi * kMsBand + (fi - fj)] += h; // lower band only (H1 is symmetric)
                     } else {
                         b0 += h * ms_fixed_value(wp, va, vc, rc, 0, K);
                         b1 += h * ms_fixed_value(wp, va, vc, rc, 1, K);
@@ -110,16 +112,25 @@ __global__ void __launch_bounds__(32) k_minsnap(const double *__restrict__ waypo
         __syncwarp(); // the next segment shares its start vertex's rows with this one's end vertex
     }
 
-    // ---- Cholesky Rpp = L L^T in place (lower triangle), right-looking
+    // ---- banded Cholesky Rpp = L L^T in place, right-looking: column j touches rows j+1 .. j+7 only
+#define MS_L(i, c) R[(i) * kMsBand + ((i) - (c))]
     for (int j = 0; j < nP; ++j) {
-        if (lane == 0) R[j * nP + j] = sqrt(R[j * nP + j]);
+        if (lane == 0) MS_L(j, j) = sqrt(MS_L(j, j));
         __syncwarp();
-        const double ljj = R[j * nP + j];
-        for (int i = j + 1 + lane; i < nP; i += 32) R[i * nP + j] = R[i * nP + j] / ljj;
+        const double ljj = MS_L(j, j);
+        const int last = (j + kMsBand - 1) < (nP - 1) ? (j + kMsBand - 1) : (nP - 1);
+        if (lane >= 1 && j + lane <= last) MS_L(j + lane, j) = MS_L(j + lane, j) / ljj;
         __syncwarp();
-        for (int i = j + 1 + lane; i < nP; i += 32) {
-            const double lij = R[i * nP + j];
-            for (int c = j + 1; c <= i; ++c) R[i * nP + c] -= lij * R[c * nP + j];
+        // trailing update: lanes over the (i, c) pairs j < c <= i <= last (at most 28)
+        const int rows = last - j;
+        if (lane < rows * (rows + 1) / 2) {
+            int a = 0, rem = lane; // a-th row below j, rem-th column in it
+            while (rem > a) {
+                rem -= a + 1;
+                ++a;
+            }
+            const int i = j + 1 + a, c = j + 1 + rem;
+            MS_L(i, c) -= MS_L(i, j) * MS_L(c, j);
         }
         __syncwarp();
     }
@@ -128,15 +139,17 @@ __global__ void __launch_bounds__(32) k_minsnap(const double *__restrict__ waypo
         double *b = rhs + lane * nP;
         for (int i = 0; i < nP; ++i) {
             double s = b[i];
-            for (int c = 0; c < i; ++c) s -= R[i * nP + c] * b[c];
-            b[i] = s / R[i * nP + i];
+            for (int c = (i - (kMsBand - 1)) > 0 ? (i - (kMsBand - 1)) : 0; c < i; ++c) s -= MS_L(i, c) * b[c];
+            b[i] = s / MS_L(i, i);
         }
         for (int i = nP - 1; i >= 0; --i) {
             double s = b[i];
-            for (int c = i + 1; c < nP; ++c) s -= R[c * nP + i] * b[c];
-            b[i] = s / R[i * nP + i];
+            const int last = (i + kMsBand - 1) < (nP - 1) ? (i + kMsBand - 1) : (nP - 1);
+            for (int c = i + 1; c <= last; ++c) s -= MS_L(c, i) * b[c];
+            b[i] = s / MS_L(i, i);
         }
     }
+#undef MS_L
     __syncwarp();
 
     // ---- coefficients: lanes over (segment, dimension); c_j = (A1inv (D d))_j / T^j
@@ -291,7 +304,7 @@ cudaError_t launch_minsnap(const double *d_waypoints, const double *d_durations,
         g_ms_constants_ready[device] = true;
     }
     const int K = n_segments, nP = 4 * (K - 1);
-    const size_t smem = sizeof(double) * ((size_t)K * kMsN + 3 * (K + 1) + (size_t)nP * nP + 3 * nP);
+    const size_t smem = sizeof(double) * ((size_t)K * kMsN + 3 * (K + 1) + (size_t)nP * kMsBand + 3 * nP);
     if (smem > 40 * 1024) {
         err = cudaFuncSetAttribute(k_minsnap, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (err != cudaSuccess) return err;

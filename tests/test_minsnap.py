@@ -65,7 +65,7 @@ def test_oracle_properties(ms):
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("K", [1, 2, 3, 8, 16])
+@pytest.mark.parametrize("K", [1, 2, 3, 8, 16, 40])
 def test_gpu_minsnap_equals_oracle(ms, config, K):
     g, o, lo, hi = worlds.track_world(config)
     rng = np.random.default_rng(100 + K)

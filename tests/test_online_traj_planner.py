@@ -1,0 +1,121 @@
+"""The reference's Python surface (src/pybind.cpp:10-27) on the B200 path: module names, class, the six methods with
+their keyword names, error behaviour; and, on the GPU, one full pre-compute + gate update on the config.json track
+(BASELINE.json configs[0]) with every planner decision re-validated by the CPU oracle."""
+import inspect
+
+import numpy as np
+import pytest
+
+import epp_b200
+
+
+def test_module_surface():
+    import online_traj_planner as otp
+    import polynomial_trajectory as pt
+    assert pt.OnlineTrajGenerator is otp.OnlineTrajGenerator
+    g = otp.OnlineTrajGenerator
+    assert list(inspect.signature(g.__init__).parameters)[1:] == [
+        "start", "goal", "nominalGatePositionAndType", "nominalObstaclePosition", "configPath"]
+    assert list(inspect.signature(g.pre_compute_traj).parameters)[1:] == ["takeoffTime"]
+    assert list(inspect.signature(g.update_gate_pos).parameters)[1:] == [
+        "gateId", "newPose", "dronePos", "nextGateWithinRange", "flightTime"]
+    assert list(inspect.signature(g.sample_traj).parameters)[1:] == ["currentTime"]
+    for name in ("get_traj_end_time", "get_planned_traj"):
+        assert callable(getattr(g, name))
+    assert otp.Vector3d([1, 2, 3]).shape == (3,) and otp.MatrixXd([[1, 2], [3, 4]]).shape == (2, 2)
+
+
+@pytest.fixture(scope="module")
+def generator(config):
+    import online_traj_planner as otp
+    t = config["track"]
+    return otp.OnlineTrajGenerator(start=otp.Vector3d(t["start"]), goal=otp.Vector3d(t["goal"]),
+                                   nominalGatePositionAndType=otp.MatrixXd(t["gates"]),
+                                   nominalObstaclePosition=otp.MatrixXd(t["obstacles"]), configPath=config)
+
+
+def _passes_gates_in_order(gen, traj):
+    pos, row = traj[:, [0, 3, 6]], 0
+    for gate_id in range(gen.gates.shape[0]):
+        while row + 1 < pos.shape[0] and not gen.checkGatePassed(pos[row], pos[row + 1], gate_id):
+            row += 1
+        if row + 1 >= pos.shape[0]:
+            return False
+    return True
+
+
+@pytest.mark.gpu
+def test_pre_compute_and_gate_update_on_the_track(oracle, config, generator):
+    gen = generator
+    with pytest.raises(RuntimeError, match="No trajectory data available."):
+        gen.sample_traj(currentTime=0.0)
+    with pytest.raises(RuntimeError, match="No trajectory data available."):
+        gen.get_traj_end_time()
+    gen.pre_compute_traj(takeoffTime=0.5)
+
+    # every edge the planner kept is valid for the reference's predicate (CPU oracle), canPassGate as planned
+    ow = oracle.OracleWorld(config)
+    ow.parse_gates_and_obstacles(gen.gates, gen.obstacles)
+    assert len(gen.pathSegments) == gen.gates.shape[0] + 1
+    for seg in gen.pathSegments:
+        assert seg.shape[0] >= 2
+        ok = ow.check_segments(seg[:-1], seg[1:], False, threads=1)
+        assert np.unpackbits(ok.view(np.uint8), bitorder="little")[: seg.shape[0] - 1].all()
+    assert np.allclose(gen.pathSegments[0][0], config["track"]["start"])
+    assert np.allclose(gen.pathSegments[-1][-1], config["track"]["goal"])
+
+    traj = gen.get_planned_traj()
+    assert traj.ndim == 2 and traj.shape[1] == 10 and traj.shape[0] > 20
+    assert traj[0, 9] == 0.5 and np.all(np.diff(traj[:, 9]) > 0)
+    dt = config["trajectory_generator_properties"]["sampling_interval"]
+    assert np.allclose(np.diff(traj[:, 9]), dt)
+    assert np.allclose(traj[0, [0, 3, 6]], config["track"]["start"]) and np.allclose(traj[0, [1, 4, 7]], 0.0)
+    assert np.linalg.norm(traj[-1, [0, 3, 6]] - np.asarray(config["track"]["goal"])) < 0.05
+    assert _passes_gates_in_order(gen, traj)
+    assert gen.get_traj_end_time() == traj[-1, 9]
+    k = traj.shape[0] // 2
+    assert np.array_equal(gen.sample_traj(currentTime=traj[k, 9] + 0.01), traj[k])
+
+    # gate 1 is observed 15 cm from its nominal place just after the drone has flown through gate 0 (the reference
+    # re-plans from the drone to gate `gateId`, i.e. it assumes that gate is the next one)
+    pos = traj[:, [0, 3, 6]]
+    r0 = next(i for i in range(pos.shape[0] - 1) if gen.checkGatePassed(pos[i], pos[i + 1], 0)) + 2
+    assert gen.update_gate_pos(gateId=1, newPose=gen.gates[1, :6], dronePos=pos[r0], nextGateWithinRange=False,
+                               flightTime=traj[r0, 9]) is False
+    new_pose = gen.gates[1, :6].copy()
+    new_pose[:2] += [0.12, 0.09]
+    changed = gen.update_gate_pos(gateId=1, newPose=new_pose, dronePos=pos[r0], nextGateWithinRange=True,
+                                  flightTime=traj[r0, 9])
+    assert changed is True
+    assert np.allclose(gen.gates[1, :2], new_pose[:2])
+    new_traj = gen.get_planned_traj()
+    assert np.array_equal(new_traj[: r0 + 1], traj[: r0 + 1])      # the flown part is kept
+    assert np.all(np.diff(new_traj[:, 9]) > -1e-9)
+    assert _passes_gates_in_order(gen, new_traj)                   # gate 0 in the kept part, then the MOVED gate 1, 2, 3
+    assert np.linalg.norm(new_traj[-1, [0, 3, 6]] - np.asarray(config["track"]["goal"])) < 0.05
+    # the same observation again is ignored (src/OnlineTrajGenerator.cpp:131-134)
+    assert gen.update_gate_pos(gateId=1, newPose=new_pose, dronePos=pos[r0], nextGateWithinRange=True,
+                               flightTime=traj[r0, 9]) is False
+
+
+@pytest.mark.gpu
+def test_prune_waypoints_equals_the_reference_loop(oracle, config):
+    """PathPlanner.pruneWaypoints answers its ray checks from one batch; the result equals the reference's loop
+    (src/PathPlanner.cpp:232-265) run one checkRayValid(…, true) at a time on the CPU oracle."""
+    import online_traj_planner as otp
+    t = config["track"]
+    pp = otp.PathPlanner(t["gates"], t["obstacles"], config)
+    ow = oracle.OracleWorld(config)
+    ow.parse_gates_and_obstacles(np.asarray(t["gates"], float), np.asarray(t["obstacles"], float))
+    rng = np.random.default_rng(8)
+    for _ in range(10):
+        w = np.cumsum(rng.normal(size=(12, 3)) * 0.25, axis=0) + [0.0, 0.0, 1.0]
+        want, ref, idx = [w[0]], 0, 2
+        while idx < len(w):
+            ok = ow.check_segments(w[ref][None], w[idx][None], True, threads=1)[0] & 1
+            if not ok:
+                want.append(w[idx - 1])
+                ref = idx - 1
+            idx += 1
+        want.append(w[-1])
+        assert np.array_equal(pp.pruneWaypoints(w), np.array(want))
