@@ -648,6 +648,34 @@ def run_extras(torch, epp_b200, dev):
         lambda: w5.check_segments_dev(a, b, mask=m5), n5 // 4, reps=5)
     out["config5_broadphase"] = epp_b200.BP_NAMES[w5.active_broadphase()]
 
+    # batched min-snap solve, then generate -> sample + check entirely on the device
+    g, o, lo, hi = worlds.track_world(config)
+    rng = np.random.default_rng(4)
+    wp = rng.uniform(lo, hi, size=(n_traj, 9, 3))
+    T = epp_b200.segment_times(wp, 1.0, 2.0)
+    d_wp, d_T8 = torch.from_numpy(wp).to(dev), torch.from_numpy(T).to(dev)
+    d_c8 = epp_b200.minsnap_dev(d_wp, d_T8)
+    out["minsnap_8seg_trajectories_per_s"] = rate(lambda: epp_b200.minsnap_dev(d_wp, d_T8, out=d_c8), n_traj, reps=5)
+    d_dt8 = torch.from_numpy(T.sum(axis=1) / 999.0).to(dev)
+    w1 = epp_b200.World(config)
+    w1.parse_gates_and_obstacles(g, o)
+
+    def gen_and_check():
+        epp_b200.minsnap_dev(d_wp, d_T8, out=d_c8)
+        return w1.check_poly_trajectories_dev(d_c8, d_T8, d_dt8, 0.1, max_samples=1024)
+    ns8 = int(gen_and_check()[2].sum().item())
+    out["config4_minsnap_generate_and_sweep_samples_per_s"] = rate(gen_and_check, ns8, reps=5)
+
+    # config 1: the reference's Python surface end to end on the track (plan through 4 gates, min-snap, sample)
+    import online_traj_planner as otp
+    tr = config["track"]
+    gen = otp.OnlineTrajGenerator(tr["start"], tr["goal"], tr["gates"], tr["obstacles"], config)
+    gen.pre_compute_traj(0.0)  # warm-up (allocations, first launches)
+    t0 = time.perf_counter()
+    gen.pre_compute_traj(0.0)
+    out["config1_pre_compute_traj_ms"] = (time.perf_counter() - t0) * 1e3
+    out["config1_traj_rows"] = int(gen.get_planned_traj().shape[0])
+
     # single-state latency through the OMPL-shaped entry point (epp_is_valid)
     t0 = time.perf_counter()
     for i in range(200):

@@ -1,7 +1,7 @@
 // BatchPlanner.h — batch-native sampling planner that stands where the reference calls OMPL's RRT* /
 // FMT (src/PathPlanner.cpp:106-139).  It asks the validators for whole batches instead of one state /
 // one edge per virtual call:
-//   1. N uniform samples in the world bounds           -> StateValidator::isValidBatch      (1 launch)
+//   1. N uniform samples in the world bounds + N/8 around start and goal -> StateValidator::isValidBatch (1 launch)
 //   2. radius-neighbour edges among the valid samples   -> MotionValidator::checkMotionBatch (1 launch)
 //   3. Dijkstra over the valid edges (host), doubling N until a path exists or the time limit ends
 //   4. vertex reduction: all (i, j) shortcuts of the path -> checkMotionBatch (1 launch), then the

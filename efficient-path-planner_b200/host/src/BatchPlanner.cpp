@@ -69,19 +69,31 @@ bool BatchPlanner::solve(const Vector3d &start, const Vector3d &goal, double tim
     std::size_t n = initialSamples_;
     for (;; n *= 2) {
         ++st.rounds;
-        // 1. samples: index 0 = start, 1 = goal, the rest uniform in the bounds
-        std::vector<double> xyz(3 * (n + 2));
+        // 1. samples: index 0 = start, 1 = goal, n uniform in the bounds, then n/8 in boxes of half-width range and
+        //    range/4 around start and goal (a checkpoint sits 0.21 m behind its gate, often in a slot between the
+        //    gate and an obstacle that uniform samples reach only after several doublings)
+        const std::size_t nt = std::max<std::size_t>(64, n / 8) & ~std::size_t(3);
+        const std::size_t total = n + 2 + nt;
+        std::vector<double> xyz(3 * total);
         for (int d = 0; d < 3; ++d) {
             xyz[d] = start(d);
             xyz[3 + d] = goal(d);
         }
         for (std::size_t i = 0; i < n; ++i)
             for (unsigned d = 0; d < 3; ++d) xyz[3 * (i + 2) + d] = lo_(d) + u01(seed_ + st.rounds, i, d) * ext[d];
-        std::vector<uint32_t> vmask(World::maskWords(n + 2));
-        sv_.isValidBatch(xyz.data(), n + 2, vmask.data());
+        for (std::size_t j = 0; j < nt; ++j) {
+            const Vector3d &c = (j & 1) ? goal : start;
+            const double half = (j & 2) ? 0.25 * range_ : range_;
+            for (unsigned d = 0; d < 3; ++d) {
+                const double x = c(d) + (2.0 * u01(seed_ + st.rounds, n + j, d) - 1.0) * half;
+                xyz[3 * (n + 2 + j) + d] = std::min(std::max(x, lo_(d)), hi_(d));
+            }
+        }
+        std::vector<uint32_t> vmask(World::maskWords(total));
+        sv_.isValidBatch(xyz.data(), total, vmask.data());
         std::vector<double> pts;
-        pts.reserve(3 * (n + 2));
-        for (std::size_t i = 0; i < n + 2; ++i)
+        pts.reserve(3 * total);
+        for (std::size_t i = 0; i < total; ++i)
             if (bit(vmask, i)) pts.insert(pts.end(), xyz.begin() + 3 * i, xyz.begin() + 3 * i + 3);
         const std::size_t m = pts.size() / 3;
         st.samples += n;
