@@ -669,6 +669,8 @@ def run_extras(torch, epp_b200, dev):
     # config 1: the reference's Python surface end to end on the track (plan through 4 gates, min-snap, sample)
     import online_traj_planner as otp
     tr = config["track"]
+    import tempfile
+    otp.OnlineTrajGenerator.path_segments_folder = os.path.join(tempfile.mkdtemp(prefix="epp_bench_"), "path_segments")
     gen = otp.OnlineTrajGenerator(tr["start"], tr["goal"], tr["gates"], tr["obstacles"], config)
     gen.pre_compute_traj(0.0)  # warm-up (allocations, first launches)
     t0 = time.perf_counter()

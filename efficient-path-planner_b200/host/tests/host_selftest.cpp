@@ -12,6 +12,7 @@
 
 #include "epp/BatchPlanner.h"
 #include "epp/PathPlanner.h"
+#include "epp/PathWriter.h"
 
 namespace ob = ompl::base;
 
@@ -197,8 +198,30 @@ static void gpu(const std::string &cfgPath)
     CHECK(pruned.size() <= path.size() && pruned.size() >= 2);
 }
 
+// PathWriter dumps of a fixed call sequence; tests/test_host_cpp.py compares the files byte for byte with the Python
+// PathWriter's (which is itself checked against the reference's own PathWriter.cpp, tests/test_path_writer.py).
+static int writerDumps(const char *folder)
+{
+    PathWriter w(folder);
+    const double gates[2][7] = {{0.45, -1.0, 0, 0, 0, 2.35, 1}, {1.0, -1.55, 0, 0, 0, -0.78, 0}};
+    const double obstacle[6] = {1.0, -0.5, 0, 0, 0, 0};
+    w.updateGatePos(0, epp::VectorXd(gates[0], 7));
+    w.updateGatePos(1, epp::VectorXd(gates[1], 7));
+    w.updateObstaclePos(0, epp::VectorXd(obstacle, 6));
+    std::vector<epp::Vector3d> pts = {epp::Vector3d(1.0, 1.0, 0.05), epp::Vector3d(1e-7, -123456.789, 1e6),
+                                      epp::Vector3d(1.0 / 3.0, 2e10, -0.0), epp::Vector3d(-0.5, 0.29, 1.0000004)};
+    w.writeCheckpoints(pts);
+    w.writePath(pts);
+    pts.pop_back();
+    w.writePath(pts);
+    const double moved[7] = {0.123456789, -0.09, 0, 0, 0, 1e-3, 1};
+    w.updateGatePos(1, epp::VectorXd(moved, 7));
+    return 0;
+}
+
 int main(int argc, char **argv)
 {
+    if (argc == 3 && !std::strcmp(argv[1], "--writer")) return writerDumps(argv[2]);
     if (argc < 3) {
         std::fprintf(stderr, "usage: %s <config.json> --no-gpu|--gpu\n", argv[0]);
         return 2;

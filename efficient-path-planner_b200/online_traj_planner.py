@@ -221,7 +221,68 @@ def generate_trajectory(waypoints, v_max, a_max, sampling_interval, start_time_o
                                max_rows=(rows + 31) // 32 * 32)[0]
 
 
+def _cxx_double(x):
+    """operator<<(ostream&, double) with the stream defaults: %g at precision 6."""
+    return "%g" % float(x)
+
+
+class PathWriter:
+    """The reference's debug dumps for its plotting scripts (src/PathWriter.cpp:7-113): ``path_<k>.txt`` and
+    ``checkpoints.txt`` hold one "x y z " line per point, ``gates.txt`` / ``obstacles.txt`` grow by one
+    "id: <i> info: <row>" line per update with the row in Eigen's default stream format (every coefficient
+    right-aligned to the widest one, one space between).  As in the reference, an existing folder is emptied of its
+    regular files on construction.  ``folderPath=None`` writes nothing."""
+
+    def __init__(self, folderPath):
+        import os
+        self.folderPath, self.write_count = folderPath, 0
+        if folderPath is None:
+            return
+        if not os.path.exists(folderPath):
+            os.makedirs(folderPath)
+            print("Folder created: " + folderPath)
+        else:
+            for name in os.listdir(folderPath):
+                full = os.path.join(folderPath, name)
+                if os.path.isfile(full) and not os.path.islink(full):
+                    os.remove(full)
+
+    def _points(self, fileName, points):
+        if self.folderPath is None:
+            return
+        import os
+        with open(os.path.join(self.folderPath, fileName), "w") as f:
+            for pt in points:
+                f.write("".join(_cxx_double(pt[k]) + " " for k in range(3)) + "\n")
+
+    def _row(self, fileName, ident, row):
+        if self.folderPath is None:
+            return
+        import os
+        cells = [_cxx_double(v) for v in np.asarray(row, float).ravel()]
+        width = max(len(c) for c in cells) if cells else 0
+        with open(os.path.join(self.folderPath, fileName), "a") as f:
+            f.write("id: %d info: %s\n" % (ident, " ".join(c.rjust(width) for c in cells)))
+
+    def writePath(self, path):
+        self._points("path_%d.txt" % self.write_count, path)
+        self.write_count += 1
+
+    def updateGatePos(self, gateId, gateInfo):
+        self._row("gates.txt", gateId, gateInfo)
+
+    def updateObstaclePos(self, obstacleId, pose):
+        self._row("obstacles.txt", obstacleId, pose)
+
+    def writeCheckpoints(self, checkpoints):
+        self._points("checkpoints.txt", checkpoints)
+
+
 class OnlineTrajGenerator:
+    #: folder of the PathWriter dumps (include/OnlineTrajGenerator.h:132); set to None before constructing a
+    #: generator to write nothing
+    path_segments_folder = "path_segments"
+
     def __init__(self, start, goal, nominalGatePositionAndType, nominalObstaclePosition, configPath):
         self.config = load_config(configPath) if isinstance(configPath, str) else configPath
         self.pp = self.config["path_planner_properties"]
@@ -229,12 +290,18 @@ class OnlineTrajGenerator:
         self.gates = np.array(nominalGatePositionAndType, dtype=np.float64).reshape(-1, 7)
         self.obstacles = np.array(nominalObstaclePosition, dtype=np.float64).reshape(-1, 6)
         self.pathPlanner = PathPlanner(self.gates, self.obstacles, self.config)
+        self.pathWriter = PathWriter(self.path_segments_folder)
+        for i, gate in enumerate(self.gates):                                 # src/OnlineTrajGenerator.cpp:20-30
+            self.pathWriter.updateGatePos(i, gate)
+        for i, obstacle in enumerate(self.obstacles):
+            self.pathWriter.updateObstaclePos(i, obstacle)
         self.checkpoints = [np.asarray(start, float).reshape(3)]
         for gate in self.gates:                                               # src/OnlineTrajGenerator.cpp:32-46
             center, normal = self.getGateCenterAndNormal(gate)
             off = self.pp["checkpoint_gate_offset"]
             self.checkpoints += [center - off * normal, center + off * normal]
         self.checkpoints.append(np.asarray(goal, float).reshape(3))
+        self.pathWriter.writeCheckpoints(self.checkpoints)
         self.pathSegments = []
         self.plannedTraj = np.zeros((0, 10))
         self.gatesObservedWithinRange = set()
@@ -277,6 +344,7 @@ class OnlineTrajGenerator:
                 raise RuntimeError("Path not found")
             self.pathSegments.append(path)
         self.prunedPath = self.pathPlanner.includeGates2(self.pathSegments)
+        self.pathWriter.writePath(self.prunedPath)
         self.plannedTraj = self._generate(self.prunedPath, takeoffTime, np.zeros(3), np.zeros(3))
 
     def update_gate_pos(self, gateId, newPose, dronePos, nextGateWithinRange, flightTime):   # :123-226
@@ -288,6 +356,7 @@ class OnlineTrajGenerator:
         self.gatesObservedWithinRange.add(gateId)
         self.gates[gateId, :6] = np.asarray(newPose, float).reshape(6)
         self.pathPlanner.parseGatesAndObstacles(self.gates, self.obstacles)
+        self.pathWriter.updateGatePos(gateId, self.gates[gateId])             # :147
         traj = self.plannedTraj
         startIdx = int(np.argmin(np.abs(traj[:, -1] - flightTime)))
         cpNext = min(2 * gateId + 3, len(self.checkpoints) - 1)
@@ -315,6 +384,7 @@ class OnlineTrajGenerator:
         center, normal = self.getGateCenterAndNormal(self.gates[gateId])
         off = self.pp["checkpoint_gate_offset"]
         self.checkpoints[pre], self.checkpoints[post] = center - off * normal, center + off * normal
+        self.pathWriter.writeCheckpoints(self.checkpoints)                    # :277
         advanced = flightTime
         if self.pp.get("advance_for_calculation", True):
             advanced += self.pp["time_limit_online"] + 0.01
@@ -335,6 +405,7 @@ class OnlineTrajGenerator:
             raise RuntimeError("Post segment path not found. Exiting")
         self.pathSegments[gateId], self.pathSegments[gateId + 1] = pre_path, post_path
         filled = self.pathPlanner.includeGates2(self.pathSegments[gateId:])
+        self.pathWriter.writePath(filled)                                     # :369
         part_post = self._generate(filled, advanced, v, a)
         self.plannedTraj = np.vstack([part_pre, part_post])
 

@@ -140,3 +140,39 @@ class RefWorld:
         lib().ref_check_segments(self._h, a.ctypes.data, b.ctypes.data, n, int(can_pass_gate), mask.ctypes.data,
                                  threads, self.via)
         return mask
+
+
+class RefPathWriter:
+    """The reference's own PathWriter (src/PathWriter.cpp, unmodified; Eigen's stream format restated in the shim)."""
+
+    def __init__(self, folder):
+        L = lib()
+        L.ref_writer_create.restype = _vp
+        L.ref_writer_create.argtypes = [C.c_char_p]
+        L.ref_writer_destroy.argtypes = [_vp]
+        L.ref_writer_write_path.argtypes = [_vp, _vp, C.c_size_t]
+        L.ref_writer_write_checkpoints.argtypes = [_vp, _vp, C.c_size_t]
+        L.ref_writer_update_gate.argtypes = [_vp, C.c_int, _vp, C.c_int]
+        L.ref_writer_update_obstacle.argtypes = [_vp, C.c_int, _vp, C.c_int]
+        self._h = L.ref_writer_create(os.fsencode(folder))
+
+    def __del__(self):
+        if getattr(self, "_h", None):
+            lib().ref_writer_destroy(self._h)
+            self._h = None
+
+    def writePath(self, path):
+        p = _f64(path, (-1, 3))
+        lib().ref_writer_write_path(self._h, p.ctypes.data, p.shape[0])
+
+    def writeCheckpoints(self, checkpoints):
+        p = _f64(checkpoints, (-1, 3))
+        lib().ref_writer_write_checkpoints(self._h, p.ctypes.data, p.shape[0])
+
+    def updateGatePos(self, gateId, row):
+        r = _f64(row, (-1,))
+        lib().ref_writer_update_gate(self._h, int(gateId), r.ctypes.data, r.shape[0])
+
+    def updateObstaclePos(self, obstacleId, row):
+        r = _f64(row, (-1,))
+        lib().ref_writer_update_obstacle(self._h, int(obstacleId), r.ctypes.data, r.shape[0])

@@ -17,6 +17,7 @@
 #include "Object.h"
 #include "StateValidator.h"
 #include "World.h"
+#include "PathWriter.h"
 #include <ompl/base/spaces/RealVectorStateSpace.h>
 
 namespace ob = ompl::base;
@@ -268,5 +269,29 @@ void ref_check_segments(ref_world *w, const double *a, const double *b, size_t n
         }
     });
 }
+
+// ---- PathWriter (src/PathWriter.cpp, compiled unmodified): the debug dumps, for the format tests of N4 ----------
+struct ref_writer {
+    PathWriter pw;
+    explicit ref_writer(const char *folder) : pw(folder) {}
+};
+ref_writer *ref_writer_create(const char *folder) { return new ref_writer(folder); }
+void ref_writer_destroy(ref_writer *w) { delete w; }
+static std::vector<Eigen::Vector3d> points_of(const double *xyz, size_t n)
+{
+    std::vector<Eigen::Vector3d> v;
+    for (size_t i = 0; i < n; ++i) v.push_back(Eigen::Vector3d(xyz[3 * i], xyz[3 * i + 1], xyz[3 * i + 2]));
+    return v;
+}
+static Eigen::VectorXd vector_of(const double *x, int n)
+{
+    Eigen::VectorXd v(n);
+    for (int i = 0; i < n; ++i) v(i) = x[i];
+    return v;
+}
+void ref_writer_write_path(ref_writer *w, const double *xyz, size_t n) { w->pw.writePath(points_of(xyz, n)); }
+void ref_writer_write_checkpoints(ref_writer *w, const double *xyz, size_t n) { w->pw.writeCheckpoints(points_of(xyz, n)); }
+void ref_writer_update_gate(ref_writer *w, int id, const double *row, int n) { w->pw.updateGatePos(id, vector_of(row, n)); }
+void ref_writer_update_obstacle(ref_writer *w, int id, const double *row, int n) { w->pw.updateObstaclePos(id, vector_of(row, n)); }
 
 } // extern "C"

@@ -21,6 +21,7 @@ w = epp_b200.World(config); w.parse_gates_and_obstacles(np.asarray(tr["gates"],f
 w.check_states(pts, False)
 probe("after cuda init")
 import online_traj_planner as otp
+otp.OnlineTrajGenerator.path_segments_folder = None
 gen = otp.OnlineTrajGenerator(tr["start"], tr["goal"], tr["gates"], tr["obstacles"], config)
 gen.pre_compute_traj(0.0)
 pp = gen.pathPlanner

@@ -4,6 +4,7 @@ import cProfile, ctypes, pstats, sys, time
 sys.path.insert(0, ".")
 import epp_b200, online_traj_planner as otp
 config = epp_b200.load_config(); tr = config["track"]
+otp.OnlineTrajGenerator.path_segments_folder = None
 gen = otp.OnlineTrajGenerator(tr["start"], tr["goal"], tr["gates"], tr["obstacles"], config)
 gen.pre_compute_traj(0.0)
 def timed(tag):

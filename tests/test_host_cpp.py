@@ -12,12 +12,39 @@ HOST = os.path.join(ROOT, "efficient-path-planner_b200", "host")
 CONFIG = os.path.join(ROOT, "efficient-path-planner_b200", "config", "config.json")
 
 
-def _selftest(mode):
+def _exe():
     exe = os.path.join(HOST, "host_selftest")
     if not os.path.exists(exe):
         subprocess.check_call(["make", "-s", "-C", os.path.join(ROOT, "efficient-path-planner_b200", "csrc")])
         subprocess.check_call(["make", "-s", "-C", HOST])
-    return subprocess.run([exe, CONFIG, mode], capture_output=True, text=True, timeout=300)
+    return exe
+
+
+def _selftest(mode):
+    return subprocess.run([_exe(), CONFIG, mode], capture_output=True, text=True, timeout=300)
+
+
+def test_cpp_path_writer_dumps_equal_the_python_writer(tmp_path):
+    """host/src/PathWriter.cpp and online_traj_planner.PathWriter (checked against the reference's own PathWriter.cpp in
+    tests/test_path_writer.py) write the same bytes for the call sequence of host_selftest --writer."""
+    import online_traj_planner as otp
+    r = subprocess.run([_exe(), "--writer", str(tmp_path / "cpp")], capture_output=True, text=True, timeout=60)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert "Folder created: " + str(tmp_path / "cpp") in r.stdout
+    w = otp.PathWriter(str(tmp_path / "py"))
+    w.updateGatePos(0, [0.45, -1.0, 0, 0, 0, 2.35, 1])
+    w.updateGatePos(1, [1.0, -1.55, 0, 0, 0, -0.78, 0])
+    w.updateObstaclePos(0, [1.0, -0.5, 0, 0, 0, 0])
+    pts = [[1.0, 1.0, 0.05], [1e-7, -123456.789, 1e6], [1.0 / 3.0, 2e10, -0.0], [-0.5, 0.29, 1.0000004]]
+    w.writeCheckpoints(pts)
+    w.writePath(pts)
+    w.writePath(pts[:-1])
+    w.updateGatePos(1, [0.123456789, -0.09, 0, 0, 0, 1e-3, 1])
+    names = sorted(os.listdir(tmp_path / "py"))
+    assert names == ["checkpoints.txt", "gates.txt", "obstacles.txt", "path_0.txt", "path_1.txt"]
+    assert sorted(os.listdir(tmp_path / "cpp")) == names
+    for name in names:
+        assert (tmp_path / "cpp" / name).read_bytes() == (tmp_path / "py" / name).read_bytes(), name
 
 
 def test_host_layer_api_and_errors_without_gpu():

@@ -26,9 +26,10 @@ def test_module_surface():
 
 
 @pytest.fixture(scope="module")
-def generator(config):
+def generator(config, tmp_path_factory):
     import online_traj_planner as otp
     t = config["track"]
+    otp.OnlineTrajGenerator.path_segments_folder = str(tmp_path_factory.mktemp("dumps") / "path_segments")
     return otp.OnlineTrajGenerator(start=otp.Vector3d(t["start"]), goal=otp.Vector3d(t["goal"]),
                                    nominalGatePositionAndType=otp.MatrixXd(t["gates"]),
                                    nominalObstaclePosition=otp.MatrixXd(t["obstacles"]), configPath=config)
@@ -93,6 +94,13 @@ def test_pre_compute_and_gate_update_on_the_track(oracle, config, generator):
     assert np.all(np.diff(new_traj[:, 9]) > -1e-9)
     assert _passes_gates_in_order(gen, new_traj)                   # gate 0 in the kept part, then the MOVED gate 1, 2, 3
     assert np.linalg.norm(new_traj[-1, [0, 3, 6]] - np.asarray(config["track"]["goal"])) < 0.05
+    # the PathWriter dumps of the run (src/OnlineTrajGenerator.cpp:23,29,47,90,147,277,369)
+    import os
+    folder = gen.pathWriter.folderPath
+    assert sorted(os.listdir(folder)) == ["checkpoints.txt", "gates.txt", "obstacles.txt", "path_0.txt", "path_1.txt"]
+    assert len(open(os.path.join(folder, "gates.txt")).readlines()) == gen.gates.shape[0] + 1
+    assert len(open(os.path.join(folder, "checkpoints.txt")).readlines()) == 2 * gen.gates.shape[0] + 2
+    assert np.allclose(np.loadtxt(os.path.join(folder, "path_0.txt")), gen.prunedPath, atol=1e-4, rtol=1e-5)
     # the same observation again is ignored (src/OnlineTrajGenerator.cpp:131-134)
     assert gen.update_gate_pos(gateId=1, newPose=new_pose, dronePos=pos[r0], nextGateWithinRange=True,
                                flightTime=traj[r0, 9]) is False
