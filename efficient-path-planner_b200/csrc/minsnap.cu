@@ -19,9 +19,9 @@
 // maps the end-point derivatives of every segment back to coefficients.
 //
 // Floating point: binary64, no FMA contraction (the TU is built with -fmad=false like the rest of the library).
-// This is a floating-point kernel: parity is by tolerance against oracle/minsnap_np.py (a numpy restatement of
-// the reference's unscaled formulation), stated in tests/test_minsnap.py; the reference's solver itself (Eigen)
-// cannot be built in this image.
+// This is a floating-point kernel: parity is by tolerance (1e-9 m along every segment, tests/test_minsnap.py) against
+// the reference's own PolynomialOptimization<10> code compiled over stand-in linear algebra (oracle/_ref, golden
+// vectors) and against oracle/minsnap_np.py, a numpy restatement of the same unscaled formulation.
 #include <cuda_runtime.h>
 
 #include <cstdint>

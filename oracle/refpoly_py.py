@@ -73,3 +73,40 @@ def segment_times(waypoints, v_max, a_max):
     out = np.zeros(w.shape[0] - 1)
     lib().refpoly_segment_times(_p(w), w.shape[0], 3, float(v_max), float(a_max), _p(out))
     return out
+
+
+def has_minsnap():
+    """False for a prebuilt oracle/_ref that predates the min-snap entry points."""
+    return available() and hasattr(lib(), "refpoly_minsnap")
+
+
+def minsnap(waypoints, times, v0=None, a0=None):
+    """The reference's PolynomialOptimization<10> (setupFromVertices + solveLinear, unmodified) on the vertex pattern
+    of poly_traj::generateTrajectory, for GIVEN segment times.  Returns coefficients [K][3][10]."""
+    L = lib()
+    L.refpoly_minsnap.argtypes = [_dp, C.c_int, _dp, _dp, _dp, _dp]
+    wp = _f64(np.asarray(waypoints, float).reshape(-1, 3))
+    t = _f64(times)
+    v = _f64(np.zeros(3) if v0 is None else v0)
+    a = _f64(np.zeros(3) if a0 is None else a0)
+    out = np.zeros((wp.shape[0] - 1, 3, 10))
+    rc = L.refpoly_minsnap(_p(wp), wp.shape[0], _p(t), _p(v), _p(a), _p(out))
+    if rc:
+        raise RuntimeError("refpoly_minsnap failed")
+    return out
+
+
+def generate_trajectory(waypoints, v_max, a_max, dt, offset=0.0, v0=None, a0=None, max_rows=1 << 16):
+    """poly_traj::generateTrajectory (trajectory_generator.cpp:12-100), unmodified: N x 10 rows."""
+    L = lib()
+    L.refpoly_generate_trajectory.restype = C.c_long
+    L.refpoly_generate_trajectory.argtypes = [_dp, C.c_int, C.c_double, C.c_double, C.c_double, C.c_double, _dp, _dp,
+                                              _dp, C.c_long]
+    wp = _f64(np.asarray(waypoints, float).reshape(-1, 3))
+    v = _f64(np.zeros(3) if v0 is None else v0)
+    a = _f64(np.zeros(3) if a0 is None else a0)
+    rows = np.zeros((max_rows, 10))
+    n = L.refpoly_generate_trajectory(_p(wp), wp.shape[0], v_max, a_max, dt, offset, _p(v), _p(a), _p(rows), max_rows)
+    if n < 0:
+        raise RuntimeError("refpoly_generate_trajectory failed")
+    return rows[:n].copy()

@@ -39,6 +39,7 @@ T &&check_not_null(T &&p, const char *what)
 
 #define LOG(severity) ::shim_glog::Sink()
 #define VLOG(level) ::shim_glog::Sink()
+#define DLOG(severity) ::shim_glog::Sink()
 #define CHECK(cond) \
     if (cond) {     \
     } else          \

@@ -10,6 +10,8 @@
 #include <vector>
 
 #include "mav_trajectory_generation/polynomial.h"
+#include "mav_trajectory_generation/polynomial_optimization_linear.h"
+#include "poly_traj/trajectory_generator.h"
 #include "mav_trajectory_generation/rpoly/rpoly_ak1.h"
 #include "mav_trajectory_generation/segment.h"
 #include "mav_trajectory_generation/trajectory.h"
@@ -108,6 +110,69 @@ void refpoly_segment_times(const double *waypoints, int n, int D, double v_max, 
     }
     const std::vector<double> t = mtg::estimateSegmentTimes(vertices, v_max, a_max);
     for (size_t i = 0; i < t.size(); ++i) out[i] = t[i];
+}
+
+} // extern "C"
+
+// ---- the linear min-snap solve ------------------------------------------------------------
+// The reference's OWN formulation code (PolynomialOptimization<10>::setupFromVertices / solveLinear, compiled
+// unmodified from polynomial_optimization_linear_impl.h) over the stand-in linear algebra of shim_poly/Eigen.
+extern "C" {
+
+// poly_traj::generateTrajectory exactly as OnlineTrajGenerator calls it (trajectory_generator.cpp:12-100).
+// rows: row-major n x 10, capacity `cap` rows.  Returns the row count or -1.
+long refpoly_generate_trajectory(const double *waypoints, int n_wp, double v_max, double a_max, double dt, double offset,
+                                 const double *vel3, const double *acc3, double *rows, long cap)
+{
+    std::vector<Eigen::Vector3d> wp;
+    for (int i = 0; i < n_wp; ++i) wp.push_back(Eigen::Vector3d(waypoints[3 * i], waypoints[3 * i + 1], waypoints[3 * i + 2]));
+    Eigen::MatrixXd result;
+    if (!poly_traj::generateTrajectory(wp, v_max, a_max, dt, offset, Eigen::Vector3d(vel3[0], vel3[1], vel3[2]),
+                                       Eigen::Vector3d(acc3[0], acc3[1], acc3[2]), result))
+        return -1;
+    if (result.rows() > cap) return -1;
+    for (long r = 0; r < (long)result.rows(); ++r)
+        for (int c = 0; c < 10; ++c) rows[10 * r + c] = result(r, c);
+    return (long)result.rows();
+}
+
+// Coefficients for GIVEN segment times: the vertex pattern of generateTrajectory (start: position, velocity,
+// acceleration given, jerk = snap = 0; interior: position; end: position, derivatives 0) handed to the reference's
+// optimiser.  coeffs: [K][3][10].
+int refpoly_minsnap(const double *waypoints, int n_wp, const double *times, const double *vel3, const double *acc3,
+                    double *coeffs)
+{
+    const int D = 3, snap = mtg::derivative_order::SNAP;
+    mtg::Vertex::Vector vertices;
+    mtg::Vertex start(D);
+    Eigen::VectorXd sc(3 * D);
+    for (int d = 0; d < D; ++d) {
+        sc[d] = waypoints[d];
+        sc[D + d] = vel3[d];
+        sc[2 * D + d] = acc3[d];
+    }
+    start.makeStartOrEnd(sc, snap);
+    vertices.push_back(start);
+    for (int i = 1; i + 1 < n_wp; ++i) {
+        mtg::Vertex v(D);
+        v.addConstraint(mtg::derivative_order::POSITION, Eigen::Vector3d(waypoints[3 * i], waypoints[3 * i + 1], waypoints[3 * i + 2]));
+        vertices.push_back(v);
+    }
+    mtg::Vertex end(D);
+    end.makeStartOrEnd(Eigen::Vector3d(waypoints[3 * (n_wp - 1)], waypoints[3 * (n_wp - 1) + 1], waypoints[3 * (n_wp - 1) + 2]), snap);
+    vertices.push_back(end);
+    std::vector<double> t(times, times + (n_wp - 1));
+    mtg::PolynomialOptimization<10> opt(D);
+    if (!opt.setupFromVertices(vertices, t, snap)) return -1;
+    if (!opt.solveLinear()) return -1;
+    mtg::Segment::Vector segments;
+    opt.getSegments(&segments);
+    for (int k = 0; k < n_wp - 1; ++k)
+        for (int d = 0; d < D; ++d) {
+            const Eigen::VectorXd c = segments[k][d].getCoefficients(0);
+            for (int j = 0; j < 10; ++j) coeffs[(k * D + d) * 10 + j] = c[j];
+        }
+    return 0;
 }
 
 } // extern "C"

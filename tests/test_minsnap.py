@@ -1,12 +1,17 @@
-"""Min-snap trajectory generation: the batched CUDA solve against oracle/minsnap_np.py, a
-numpy restatement of the reference's PolynomialOptimization<10>::solveLinear in its own unscaled coordinates.
+"""Min-snap trajectory generation: the batched CUDA solve against
+  * tests/golden/minsnap_golden.npz — outputs of THE REFERENCE'S OWN PolynomialOptimization<10>::setupFromVertices /
+    solveLinear and poly_traj::generateTrajectory, compiled unmodified into oracle/_ref/libepp_refpoly.so
+    (tests/golden/make_minsnap_golden.py); only the linear algebra underneath that code (Eigen's fixed-size and sparse
+    matrices, SparseQR) is a stand-in, so these pin the formulation to rounding, not Eigen's bits;
+  * oracle/minsnap_np.py — a numpy restatement of the same formulation in its unscaled coordinates, itself checked
+    against the golden vectors and the live reference here.
 
-FLOATING-POINT PATH — tolerance, stated here: positions along the trajectory agree to 1e-9 m (the restatement
-inverts matrices of powers of T in double and is itself only ~1e-10 accurate), boundary values and continuity of
-the derivatives hold to 1e-9 in units scaled by the segment time.  The reference's solver (Eigen SparseQR) cannot
-be built in this image, so this row's parity is against the restatement only ("unpinned").
-What IS bit-exact: the segment-time heuristic against the reference's own vertex.cpp (golden), the run-to-run
-determinism of the kernel, and everything downstream of the coefficients (sampler + World check)."""
+FLOATING-POINT PATH — tolerance, stated here: positions along the trajectory agree to 1e-9 m (the unscaled formulation
+inverts matrices of powers of T in double and is itself only ~1e-10 accurate), velocities to 1e-8 m/s, accelerations to
+1e-7 m/s^2; boundary values and continuity of the derivatives hold to 1e-9 in units scaled by the segment time.
+What IS bit-exact: the segment-time heuristic and the sampling times against the reference's own vertex.cpp /
+trajectory.cpp (golden), the run-to-run determinism of the kernel, and everything downstream of the coefficients
+(sampler + World check)."""
 import os
 
 import numpy as np
@@ -25,6 +30,20 @@ def ms():
     return minsnap_np
 
 
+@pytest.fixture(scope="module")
+def golden():
+    return np.load(os.path.join(HERE, "golden", "minsnap_golden.npz"))
+
+
+def worst_position_gap(ms, a, b, T, taus=np.linspace(0.0, 1.0, 17)):
+    worst = 0.0
+    for k in range(len(T)):
+        for d in range(3):
+            for tau in taus:
+                worst = max(worst, abs(ms.evaluate(a[k, d], tau * T[k]) - ms.evaluate(b[k, d], tau * T[k])))
+    return worst
+
+
 def random_problem(rng, n, K, lo, hi):
     wp = rng.uniform(lo, hi, size=(n, K + 1, 3))
     T = epp_b200.segment_times(wp, 1.0, 2.0)
@@ -37,6 +56,29 @@ def test_segment_times_equal_reference_golden():
     z = np.load(os.path.join(HERE, "golden", "poly_golden.npz"))
     got = epp_b200.segment_times(z["nfabian_waypoints"], 1.0, 2.0)
     assert np.array_equal(got, z["nfabian_times"])
+
+
+def test_oracle_equals_reference_golden(ms, golden):
+    """numpy restatement vs the reference's own solver, 15 problems of 1..64 segments."""
+    for p, K in enumerate(golden["K"]):
+        wp, T, va = golden["waypoints"][p, : K + 1], golden["times"][p, :K], golden["start_vel_acc"][p]
+        mine = ms.solve(wp, T, va[:3], va[3:])
+        assert worst_position_gap(ms, mine, golden["coeffs"][p, :K], T) < TOL, (p, K)
+
+
+def test_live_reference_solver_equals_oracle(ms):
+    refpoly = pytest.importorskip("refpoly_py")
+    if not refpoly.has_minsnap():
+        pytest.skip("oracle/_ref/libepp_refpoly.so without the min-snap entry points (needs /root/reference)")
+    rng = np.random.default_rng(31)
+    for K in (1, 2, 4, 7, 11, 20):
+        wp = rng.uniform(-2, 2, size=(K + 1, 3))
+        T = rng.uniform(0.5, 3.0, size=K)
+        v0, a0 = rng.normal(size=3) * 0.4, rng.normal(size=3) * 0.4
+        ref = refpoly.minsnap(wp, T, v0, a0)
+        # violent random problems (3 m in 0.7 s: coefficients of 1e2) lose digits in BOTH unscaled solves: the gap is
+        # bounded relative to the largest coefficient
+        assert worst_position_gap(ms, ms.solve(wp, T, v0, a0), ref, T) < TOL * max(1.0, np.abs(ref).max()), K
 
 
 def test_oracle_properties(ms):
@@ -92,6 +134,32 @@ def test_gpu_minsnap_equals_oracle(ms, config, K):
     at_rest = epp_b200.minsnap(wp, T)  # start at rest
     for d in range(3):
         assert at_rest[0, 0, d, 1] == 0.0 and at_rest[0, 0, d, 2] == 0.0
+
+
+@pytest.mark.gpu
+def test_gpu_minsnap_equals_reference_golden(ms, golden):
+    """The CUDA solve vs the reference's own PolynomialOptimization<10> on the committed problems (1..64 segments)."""
+    for p, K in enumerate(golden["K"]):
+        wp, T, va = golden["waypoints"][p, : K + 1], golden["times"][p, :K], golden["start_vel_acc"][p]
+        got = epp_b200.minsnap(wp[None], T[None], va[None])[0]
+        assert worst_position_gap(ms, got, golden["coeffs"][p, :K], T) < TOL, (p, K)
+
+
+@pytest.mark.gpu
+def test_gpu_generate_trajectory_equals_reference_golden(golden):
+    """generate_trajectory (segment times -> k_minsnap -> k_sample_poly) vs poly_traj::generateTrajectory's N x 10
+    matrix: same row count, time column bit-equal, positions / velocities / accelerations within the stated tolerances."""
+    import online_traj_planner as otp
+    for g in range(int(golden["gen_count"])):
+        wp, want = golden["gen%d_waypoints" % g], golden["gen%d_rows" % g]
+        v_max, a_max, dt, off = golden["gen_params"][g]
+        va = golden["gen_start_vel_acc"][g]
+        got = otp.generate_trajectory(wp, v_max, a_max, dt, off, va[:3], va[3:])
+        assert got.shape == want.shape, g
+        assert np.array_equal(got[:, 9], want[:, 9]), g
+        assert np.abs(got[:, [0, 3, 6]] - want[:, [0, 3, 6]]).max() < TOL, g
+        assert np.abs(got[:, [1, 4, 7]] - want[:, [1, 4, 7]]).max() < 1e-8, g
+        assert np.abs(got[:, [2, 5, 8]] - want[:, [2, 5, 8]]).max() < 1e-7, g
 
 
 @pytest.mark.gpu
