@@ -601,8 +601,10 @@ __device__ __forceinline__ bool rec_hit(const double *__restrict__ r, const P3 &
     return in & (fabs(lx) <= r[13]) & (fabs(ly) <= r[14]) & (fabs(d2) <= r[15]);
 }
 
-template <int BP, int S, bool RS, bool GA>
-__device__ __forceinline__ void warp_states_step(const PointWorld<BP> &world, const WorldView &wv,
+// SOA: the slot holds three runs of S*32 doubles (x, y, z columns of a trajectory matrix) instead of xyz triples.
+// Returns, in lanes < S, the INVALID bits of the lane's word (0 elsewhere); mask_out may be null.
+template <int BP, int S, bool RS, bool GA, bool SOA = false>
+__device__ __forceinline__ uint32_t warp_states_step(const PointWorld<BP> &world, const WorldView &wv,
                                                  const double *__restrict__ rec, const double *__restrict__ pts,
                                                  int units, int mode, bool cpg, double md, unsigned char *queue,
                                                  uint32_t *inv, uint32_t *__restrict__ mask_out, int lane,
@@ -623,7 +625,8 @@ __device__ __forceinline__ void warp_states_step(const PointWorld<BP> &world, co
         const int unit = u * 32 + lane;
         bool has = false;
         if (unit < units) {
-            const P3 p = {pts[3 * unit], pts[3 * unit + 1], pts[3 * unit + 2]};
+            const P3 p = SOA ? P3{pts[unit], pts[S * 32 + unit], pts[2 * S * 32 + unit]}
+                             : P3{pts[3 * unit], pts[3 * unit + 1], pts[3 * unit + 2]};
             has = dbg == 2 ? (p.x + p.y + p.z == 12345.0) : world.has_candidates(wv, p);
         }
         const uint32_t b = __ballot_sync(0xffffffffu, has);
@@ -635,7 +638,8 @@ __device__ __forceinline__ void warp_states_step(const PointWorld<BP> &world, co
         // ---- phase 2: one queued state per lane, exact tests with early exit
         for (int q = lane; q < queued; q += 32) {
             const int unit = queue[q];
-            const P3 p = {pts[3 * unit], pts[3 * unit + 1], pts[3 * unit + 2]};
+            const P3 p = SOA ? P3{pts[unit], pts[S * 32 + unit], pts[2 * S * 32 + unit]}
+                             : P3{pts[3 * unit], pts[3 * unit + 1], pts[3 * unit + 2]};
             const bool hit = world.any(wv, p, [&](int k) -> bool {
                 if (RS) return rec_hit(rec + k * kRecDoubles, p);
                 return point_candidate_invalid(wv.aabb, wv.obb, k, p, mode, cpg, md);
@@ -645,11 +649,13 @@ __device__ __forceinline__ void warp_states_step(const PointWorld<BP> &world, co
         __syncwarp();
     }
     // ---- verdicts: bit = valid; bits of units beyond `units` stay 0
+    uint32_t bad = 0u;
     if (lane < S && lane * 32 < units) {
         const int live = units - 32 * lane;
         const uint32_t active = live >= 32 ? 0xffffffffu : ((1u << live) - 1u);
         const uint32_t verdict = ~inv[lane] & active;
-        mask_out[lane] = verdict;
+        bad = inv[lane] & active;
+        if (mask_out) mask_out[lane] = verdict;
         if (GA && stage_words) {
             stage_words[lane] = verdict; // sent with its group (k_states_warp)
         } else if (GA && !(gv.debug & 2)) { // the same word, with this call's number, into every peer's row of this rank
@@ -659,7 +665,20 @@ __device__ __forceinline__ void warp_states_step(const PointWorld<BP> &world, co
         inv[lane] = 0u;
     }
     __syncwarp();
+    return bad;
 }
+
+// Trajectory-matrix form of the warp-pipelined kernel (K3a): the units are the rows of n_traj column-major matrices,
+// position = columns 0, 3, 6 (src/PathPlanner.cpp:272-273).  Every trajectory is cut into cpt chunks of S*32 rows;
+// its mask words live at sample_mask + t * wpt.
+struct TrajArgs {
+    const double *mats;
+    size_t rows, ld, traj_stride;
+    uint32_t wpt, cpt;       // mask words and chunks per trajectory
+    int aligned;             // columns start on 16 B and ld / traj_stride are even: cp.async.bulk can move them
+    uint32_t *sample_mask;   // may be null
+    long long *first_row;    // LLONG_MAX on entry; atomicMin of the first invalid row per trajectory
+};
 
 // Block = 1 producer warp + up to 31 consumer warps, one block per SM by default.  Block b owns words
 // [b*wpb + min(b, rem), +wpb + (b < rem)) (the host passes wpb = words / blocks and rem = words % blocks, so no
@@ -684,13 +703,16 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
     asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_addr(bar)) : "memory");
 }
 
-template <int BP, int S, bool RS, bool GA>
+// TR: trajectory-matrix form (TrajArgs above); wpb / rem then count CHUNKS, xyz / n / mask are unused.
+template <int BP, int S, bool RS, bool GA, bool TR = false>
 __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const double *__restrict__ xyz, size_t n, int mode,
                                                       int can_pass_gate, double min_distance, int aabb_in_smem,
                                                       int log2_slots, uint32_t table_bytes, uint32_t rec_bytes,
                                                       uint32_t wpb, uint32_t rem, uint32_t *__restrict__ mask,
-                                                      const __grid_constant__ GatherView gv, uint32_t ga_group)
+                                                      const __grid_constant__ GatherView gv, uint32_t ga_group,
+                                                      const __grid_constant__ TrajArgs ta)
 {
+    static_assert(!(TR && GA), "the trajectory form has no fused exchange");
     __shared__ uint32_t s_seq, s_hdr, s_cnt[kMaxRanks]; // GA: call number; header state (0 none, 1 claimed, 2 read)
     __shared__ __align__(8) uint64_t s_full[kMaxSlots];
     __shared__ __align__(8) uint64_t s_empty[kMaxSlots];
@@ -715,11 +737,23 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
 
     const uint32_t b0 = blockIdx.x * wpb + (blockIdx.x < rem ? blockIdx.x : rem);
     const uint32_t b1 = b0 + wpb + (blockIdx.x < rem ? 1u : 0u);
-    const uint32_t chunks = (b1 - b0 + S - 1) / S;
+    const uint32_t chunks = TR ? (b1 - b0) : (b1 - b0 + S - 1) / S;
     const uint32_t words_total = (uint32_t)((n + 31) / 32);
-    const bool aligned = (reinterpret_cast<uintptr_t>(xyz) & 15u) == 0;
+    const bool aligned = TR ? ta.aligned != 0 : (reinterpret_cast<uintptr_t>(xyz) & 15u) == 0;
+    // TR: trajectory and first row of chunk i of this block
+    auto traj_of = [&](uint32_t i, uint32_t &t, uint32_t &j) {
+        const uint32_t gi = b0 + i;
+        t = gi / ta.cpt;
+        j = gi - t * ta.cpt;
+    };
     // states in chunk i of this block
     auto chunk_units = [&](uint32_t i) -> int {
+        if (TR) {
+            uint32_t t, j;
+            traj_of(i, t, j);
+            const size_t left = ta.rows - (size_t)j * (S * 32);
+            return left < (size_t)(S * 32) ? (int)left : S * 32;
+        }
         const uint32_t cw = b0 + i * S;
         const uint32_t sw = (b1 - cw) < (uint32_t)S ? (b1 - cw) : (uint32_t)S;
         int units = (int)(sw * 32u);
@@ -796,7 +830,17 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
             const int units = chunk_units(i);
             if (by_tma(units)) {
                 mbar_expect_tx(&s_full[slot], (uint32_t)units * 24u);
-                bulk_g2s(ring + slot * kSlotBytes, xyz + (size_t)(b0 + i * S) * 96, (uint32_t)units * 24u, &s_full[slot]);
+                if (TR) {
+                    uint32_t t, j;
+                    traj_of(i, t, j);
+                    const double *col = ta.mats + (size_t)t * ta.traj_stride + (size_t)j * (S * 32);
+#pragma unroll
+                    for (int d = 0; d < 3; ++d)
+                        bulk_g2s(ring + slot * kSlotBytes + d * (S * 32 * 8), col + (size_t)(3 * d) * ta.ld,
+                                 (uint32_t)units * 8u, &s_full[slot]);
+                } else {
+                    bulk_g2s(ring + slot * kSlotBytes, xyz + (size_t)(b0 + i * S) * 96, (uint32_t)units * 24u, &s_full[slot]);
+                }
             } else {
                 mbar_arrive(&s_full[slot]); // the consumer loads this chunk with its lanes
             }
@@ -863,16 +907,35 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
             } while (done < round);
         }
         mbar_wait(&s_full[slot], round & 1u);
+        uint32_t tr_t = 0, tr_j = 0;
+        if (TR) traj_of(i, tr_t, tr_j);
         if (!by_tma(units)) {
-            const double *src = xyz + (size_t)(b0 + i * S) * 96;
-            for (int e = lane; e < 3 * units; e += 32) pts[e] = __ldg(src + e);
+            if (TR) {
+                const double *col = ta.mats + (size_t)tr_t * ta.traj_stride + (size_t)tr_j * (S * 32);
+#pragma unroll
+                for (int d = 0; d < 3; ++d)
+                    for (int u = lane; u < units; u += 32) pts[d * (S * 32) + u] = __ldg(col + (size_t)(3 * d) * ta.ld + u);
+            } else {
+                const double *src = xyz + (size_t)(b0 + i * S) * 96;
+                for (int e = lane; e < 3 * units; e += 32) pts[e] = __ldg(src + e);
+            }
             __syncwarp();
         }
         EPP_TRACE_EV(g, 4 + 2 * tstep);
         const bool staged = GA && ga_group != 0u;
-        warp_states_step<BP, S, RS, GA>(world, wv, rec, pts, units, mode, cpg, min_distance, queue, inv,
-                                        mask + b0 + i * S, lane, gv, seq, ll_row + b0 + i * S,
-                                        staged ? ga_words + i * S : nullptr);
+        if (TR) {
+            uint32_t *mo = ta.sample_mask ? ta.sample_mask + (size_t)tr_t * ta.wpt + tr_j * S : nullptr;
+            const uint32_t bad = warp_states_step<BP, S, RS, false, true>(world, wv, rec, pts, units, mode, cpg, min_distance,
+                                                                          queue, inv, mo, lane, gv, 0u, 0u, nullptr);
+            // first invalid row of the chunk -> atomicMin into the trajectory's slot (rows < 2^32 - 1, host-checked)
+            const uint32_t cand = bad ? tr_j * (S * 32) + (uint32_t)lane * 32u + (uint32_t)(__ffs(bad) - 1) : 0xffffffffu;
+            const uint32_t first = __reduce_min_sync(0xffffffffu, cand);
+            if (lane == 0 && first != 0xffffffffu) atomicMin(ta.first_row + tr_t, (long long)first);
+        } else {
+            warp_states_step<BP, S, RS, GA>(world, wv, rec, pts, units, mode, cpg, min_distance, queue, inv,
+                                            mask + b0 + i * S, lane, gv, seq, ll_row + b0 + i * S,
+                                            staged ? ga_words + i * S : nullptr);
+        }
         if (staged) {
             // count the chunk into its group; the warp that completes a group sends it
             const uint32_t grp = i / ga_group, g0 = grp * ga_group;
@@ -1383,13 +1446,19 @@ extern "C" int epp_debug_trace_copy(unsigned long long *host, size_t n, int clea
     default: { constexpr int BP = EPP_BP_GRID; __VA_ARGS__; } break;             \
     }
 
-template <int BP, int S, bool RS, bool GA>
+// TR: the units are the rows of ta's matrices (n = trajectories * rows is only used for the size checks).
+template <int BP, int S, bool RS, bool GA, bool TR = false>
 cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const double *d_xyz, size_t n, int mode,
                                int can_pass_gate, double min_distance, bool in_smem, size_t table_bytes, int stages,
-                               uint32_t *d_mask, cudaStream_t stream, bool &launched, const GatherView &gv)
+                               uint32_t *d_mask, cudaStream_t stream, bool &launched, const GatherView &gv,
+                               TrajArgs ta = TrajArgs(), size_t n_traj = 0)
 {
     launched = false;
-    const size_t words = (n + 31) / 32;
+    if (TR) {
+        ta.wpt = (uint32_t)((ta.rows + 31) / 32);
+        ta.cpt = (uint32_t)((ta.rows + S * 32 - 1) / (S * 32));
+    }
+    const size_t words = TR ? n_traj * ta.cpt * S : (n + 31) / 32;
     if (words >= 0xfff00000ull) return cudaSuccess;
     const size_t rec_bytes = RS ? ((size_t)wv.M * kRecDoubles * 8 + 127) / 128 * 128 : 0;
     const size_t warp_bytes = S * 32 + 32, slot_bytes = (size_t)S * kWordBytes;
@@ -1427,7 +1496,9 @@ cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const 
     // the records from global memory instead (the caller retries with RS = false)
     if (RS && cons * 32 < wv.M) return cudaSuccess;
     const size_t smem = fixed + (slot_bytes << log2_slots);
-    cudaError_t err = cudaFuncSetAttribute(k_states_warp<BP, S, RS, GA>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    // ownership is handed out in words for state batches and in whole chunks for trajectory matrices
+    const size_t own_units = TR ? chunks_total : words;
+    cudaError_t err = cudaFuncSetAttribute(k_states_warp<BP, S, RS, GA, TR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
     cudaLaunchConfig_t lc = {};
     lc.gridDim = dim3((unsigned)grid);
@@ -1439,9 +1510,10 @@ cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const 
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     lc.attrs = attr;
     lc.numAttrs = cfg.states_pdl ? 1 : 0;
-    err = cudaLaunchKernelEx(&lc, k_states_warp<BP, S, RS, GA>, wv, d_xyz, n, mode | (cfg.states_debug << 8),
+    err = cudaLaunchKernelEx(&lc, k_states_warp<BP, S, RS, GA, TR>, wv, d_xyz, n, mode | (cfg.states_debug << 8),
                              can_pass_gate, min_distance, in_smem ? 1 : 0, log2_slots, (uint32_t)table_bytes,
-                             (uint32_t)rec_bytes, (uint32_t)(words / grid), (uint32_t)(words % grid), d_mask, gv, ga_group);
+                             (uint32_t)rec_bytes, (uint32_t)(own_units / grid), (uint32_t)(own_units % grid), d_mask, gv,
+                             ga_group, ta);
     if (err != cudaSuccess) return err;
     launched = true;
     return cudaGetLastError();
@@ -1572,7 +1644,7 @@ cudaError_t launch_segments(const LaunchCfg &cfg, const WorldView &wv, int bp, c
     return err;
 }
 
-cudaError_t launch_trajectories(const LaunchCfg &, const WorldView &wv, int bp, const double *d_mats, size_t n_traj,
+cudaError_t launch_trajectories(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_mats, size_t n_traj,
                                 size_t rows, size_t ld, size_t traj_stride, double min_distance, uint32_t *d_traj_valid,
                                 uint32_t *d_sample_mask, int64_t *d_first_invalid, long long *d_first_scratch,
                                 cudaStream_t stream)
@@ -1582,7 +1654,44 @@ cudaError_t launch_trajectories(const LaunchCfg &, const WorldView &wv, int bp, 
     g_launches++;
     cudaError_t err = cudaGetLastError();
     if (err != cudaSuccess) return err;
-    if (rows > 0) {
+    bool done = false;
+    if (rows > 0 && rows < 0xfffffff0ull && n_traj * rows >= (size_t)cfg.states_warp_min_n && cfg.traj_variant != 1) {
+        // warp-pipelined form (k_states_warp in its trajectory mode): columns 0, 3, 6 arrive by cp.async.bulk
+        bool in_smem;
+        const size_t smem = point_smem_bytes(wv, bp, in_smem);
+        const size_t table_bytes = (smem + 127) / 128 * 128;
+        const int rec_max = cfg.states_rec_smem_max > 0 ? (cfg.states_rec_smem_max < 992 ? cfg.states_rec_smem_max : 992) : kRecSmemMax;
+        bool rs = wv.M <= rec_max && wv.zrot && cfg.states_rec_smem != 0;
+        const int wbp = (bp == EPP_BP_BITS && wv.W == 1 && cfg.states_bits1 != 0) ? kBpBits1 : bp;
+        TrajArgs ta = {};
+        ta.mats = d_mats;
+        ta.rows = rows;
+        ta.ld = ld;
+        ta.traj_stride = traj_stride;
+        ta.aligned = ((reinterpret_cast<uintptr_t>(d_mats) & 15u) == 0 && (ld & 1) == 0 && (traj_stride & 1) == 0) ? 1 : 0;
+        ta.sample_mask = d_sample_mask;
+        ta.first_row = d_first_scratch;
+        const GatherView no_gather = {};
+#define EPP_LAUNCH_TRAJ(RS_)                                                                                                \
+    err = launch_states_warp<BP, 4, RS_, false, true>(cfg, wv, nullptr, n_traj * rows, kModeMinDist, 0, min_distance, in_smem, \
+                                                      table_bytes, 0, nullptr, stream, done, no_gather, ta, n_traj)
+        for (int attempt = 0; attempt < 2 && !done && err == cudaSuccess; ++attempt) {
+            if (attempt == 1) {
+                if (!rs) break;
+                rs = false;
+            }
+            if (wbp == kBpBits1) {
+                constexpr int BP = kBpBits1;
+                if (rs) EPP_LAUNCH_TRAJ(true); else EPP_LAUNCH_TRAJ(false);
+            } else {
+                EPP_DISPATCH_BP(bp, { if (rs) EPP_LAUNCH_TRAJ(true); else EPP_LAUNCH_TRAJ(false); });
+            }
+        }
+#undef EPP_LAUNCH_TRAJ
+        if (err != cudaSuccess) return err;
+        if (done) g_launches++;
+    }
+    if (rows > 0 && !done) {
         bool in_smem;
         const size_t smem = point_smem_bytes(wv, bp, in_smem);
         const size_t row_tiles = (rows + kBlock - 1) / kBlock;

@@ -186,6 +186,56 @@ def test_presampled_trajectories(oracle, config, bp):
     assert (v11[0] & 3) == (valid[0] & 3)
 
 
+@pytest.mark.parametrize("shape", [(9, 1000, 10), (200, 31, 10), (40, 129, 11), (3, 4099, 10), (70, 64, 10)],
+                         ids=lambda s: "x".join(map(str, s)))
+def test_presampled_trajectories_warp_form(oracle, config, track, shape):
+    """K3a's warp-pipelined form (batches of >= 4096 rows: columns 0, 3, 6 by cp.async.bulk into the K1 ring) against
+    the oracle and against the direct form (tuning knob traj_variant=1): ragged last chunks, odd row counts, padded
+    leading dimensions, a base address that is only 8 B aligned, 10 and 11 columns, with and without sample masks."""
+    import torch
+    g, o, lo, hi = track
+    ow, gw = build_pair(oracle, epp_b200, config, g, o, epp_b200.BP_AUTO)
+    n_traj, rows, cols = shape
+    trajs = np.zeros((n_traj, rows, cols))
+    for t in range(n_traj):
+        xyz = worlds.gen_states(900 + t, 0, rows, lo, hi)
+        if t % 4 == 0:
+            xyz[:, 2] = 1.9          # above the gates: collision free
+        if t % 4 == 1:
+            xyz[: rows - 1 - (t % 7), 2] = 1.9   # only the last rows can collide
+        trajs[t, :, :10] = worlds.traj_matrix_from_positions(xyz, np.arange(rows) * 0.05)
+    want = [ow.check_trajectory(trajs[t, :, :10], 0.1) for t in range(n_traj)]
+    try:
+        results = {}
+        for variant in (0, 1):
+            epp_b200.set_tuning("traj_variant", variant)
+            results[variant] = gw.check_trajectories(trajs, 0.1)
+    finally:
+        epp_b200.set_tuning("traj_variant", 0)
+    for variant, (valid, smask, first) in results.items():
+        for t in range(n_traj):
+            ok, m, f = want[t]
+            assert bool(valid[t >> 5] >> (t & 31) & 1) is ok, (variant, t)
+            assert np.array_equal(smask[t], m), (variant, t)
+            assert first[t] == f, (variant, t)
+    assert 0 < sum(w[0] for w in want) < n_traj
+    # device buffers: leading dimension rows + pad, matrices 8 B (not 16 B) aligned, no sample masks wanted
+    for pad, shift in ((0, 0), (3, 0), (2, 1), (0, 1)):
+        ld = rows + pad
+        stride = ld * cols + (pad & 1)
+        host = np.full(n_traj * stride + 2, np.nan)
+        for t in range(n_traj):
+            for c in range(cols):
+                host[shift + t * stride + c * ld: shift + t * stride + c * ld + rows] = trajs[t, :, c]
+        dev = torch.from_numpy(host).cuda()
+        v, sm, f = gw.check_trajectories_dev(dev[shift:], n_traj, rows, ld, stride, cols, 0.1, want_samples=(pad != 3))
+        torch.cuda.synchronize()
+        assert np.array_equal(v.cpu().numpy().view(np.uint32), results[1][0]), (pad, shift)
+        assert np.array_equal(f.cpu().numpy(), results[1][2]), (pad, shift)
+        if sm is not None:
+            assert np.array_equal(sm.cpu().numpy().view(np.uint32), results[1][1]), (pad, shift)
+
+
 @pytest.mark.parametrize("bp", BPS, ids=BP_IDS)
 def test_fused_polynomial_sweep(oracle, config, bp):
     """Config 4 (fused form) at reduced size: coefficients -> sampler -> Horner -> world check."""
