@@ -12,7 +12,9 @@
 
 #include "epp/BatchPlanner.h"
 #include "epp/PathPlanner.h"
+#include "epp/OnlineTrajGenerator.h"
 #include "epp/PathWriter.h"
+#include "epp/TrajectoryGenerator.h"
 
 namespace ob = ompl::base;
 
@@ -24,6 +26,8 @@ static int failures = 0;
             ++failures;                                                        \
         }                                                                      \
     } while (0)
+
+#define CHECK_THROWS(expr, text) CHECK(thrown([&] { (void)(expr); }).find(text) != std::string::npos)
 
 template <class F>
 static std::string thrown(F f)
@@ -196,6 +200,63 @@ static void gpu(const std::string &cfgPath)
     }
     const std::vector<epp::Vector3d> pruned = track.pruneWaypoints(path);
     CHECK(pruned.size() <= path.size() && pruned.size() >= 2);
+
+    // poly_traj::generateTrajectory through the C ABI: interpolation, start state, rest at the end, time column
+    {
+        const std::vector<epp::Vector3d> wp = {epp::Vector3d(0, 0, 1), epp::Vector3d(1, 0.5, 1.2), epp::Vector3d(1.5, -0.5, 0.8),
+                                               epp::Vector3d(0.2, -1.0, 1.0)};
+        epp::MatrixXd traj;
+        CHECK(poly_traj::generateTrajectory(wp, 2.0, 2.0, 0.05, 0.5, epp::Vector3d(0.1, 0, 0), epp::Vector3d(0, 0, 0), traj));
+        CHECK(traj.cols() == 10 && traj.rows() > 20);
+        CHECK(traj(0, 9) == 0.5 && traj(0, 0) == 0.0 && traj(0, 6) == 1.0 && std::fabs(traj(0, 1) - 0.1) < 1e-12);
+        const std::size_t e = traj.rows() - 1;
+        CHECK(std::fabs(traj(e, 0) - 0.2) < 0.05 && std::fabs(traj(e, 3) + 1.0) < 0.05 && std::fabs(traj(e, 1)) < 0.2);
+        for (std::size_t r = 1; r < (std::size_t)traj.rows(); ++r) CHECK(std::fabs(traj(r, 9) - traj(r - 1, 9) - 0.05) < 1e-9);
+        CHECK_THROWS(poly_traj::generateTrajectory({wp[0]}, 2.0, 2.0, 0.05, 0.0, wp[0], wp[0], traj), "At least two waypoints");
+    }
+
+    // OnlineTrajGenerator on the track of config.json: pre-compute, sample, gate update with re-plan
+    {
+        OnlineTrajGenerator gen(epp::Vector3d(1, 1, 0.05), epp::Vector3d(0, -2, 0.5), tg, to, cfgPath);
+        CHECK_THROWS(gen.sampleTraj(0.0), "No trajectory data available.");
+        CHECK_THROWS(gen.getTrajEndTime(), "No trajectory data available.");
+        CHECK(gen.getCheckpoints().size() == 2 * 4 + 2);
+        gen.preComputeTraj(0.5);
+        const epp::MatrixXd traj = gen.getPlannedTraj();
+        CHECK(traj.cols() == 10 && traj.rows() > 20 && traj(0, 9) == 0.5);
+        CHECK(gen.getTrajEndTime() == traj(traj.rows() - 1, 9));
+        CHECK(gen.getPathSegments().size() == 5);
+        for (const std::vector<epp::Vector3d> &seg : gen.getPathSegments())
+            for (std::size_t i = 1; i < seg.size(); ++i) CHECK(gen.planner().worldPtr->checkRayValid(seg[i - 1], seg[i], false));
+        auto pos = [](const epp::MatrixXd &t, std::size_t r) { return epp::Vector3d(t(r, 0), t(r, 3), t(r, 6)); };
+        auto gatesInOrder = [&](const epp::MatrixXd &t) {
+            std::size_t row = 0;
+            for (int g = 0; g < 4; ++g) {
+                while (row + 1 < (std::size_t)t.rows() && !gen.checkGatePassed(pos(t, row), pos(t, row + 1), g)) ++row;
+                if (row + 1 >= (std::size_t)t.rows()) return false;
+            }
+            return true;
+        };
+        CHECK(gatesInOrder(traj));
+        const std::size_t mid = traj.rows() / 2;
+        const epp::VectorXd s = gen.sampleTraj(traj(mid, 9) + 0.01);
+        CHECK(s.size() == 10 && s(9) == traj(mid, 9) && s(0) == traj(mid, 0));
+        // just after gate 0 the drone sees gate 1 fifteen centimetres off its nominal place
+        std::size_t r0 = 0;
+        while (r0 + 1 < (std::size_t)traj.rows() && !gen.checkGatePassed(pos(traj, r0), pos(traj, r0 + 1), 0)) ++r0;
+        r0 += 2;
+        epp::VectorXd pose{1.0 + 0.12, -1.55 + 0.09, 0, 0, 0, -0.78};
+        CHECK(gen.updateGatePos(1, pose, pos(traj, r0), false, traj(r0, 9)) == false);
+        CHECK(gen.updateGatePos(1, pose, pos(traj, r0), true, traj(r0, 9)) == true);
+        const epp::MatrixXd moved = gen.getPlannedTraj();
+        bool kept = true;
+        for (std::size_t r = 0; r <= r0; ++r)
+            for (std::size_t c = 0; c < 10; ++c) kept = kept && moved(r, c) == traj(r, c);
+        CHECK(kept);
+        CHECK(gatesInOrder(moved));
+        CHECK(gen.updateGatePos(1, pose, pos(traj, r0), true, traj(r0, 9)) == false); // seen once: ignored
+        std::printf("generator: %zu rows, %zu after the gate update\n", (std::size_t)traj.rows(), (std::size_t)moved.rows());
+    }
 }
 
 // PathWriter dumps of a fixed call sequence; tests/test_host_cpp.py compares the files byte for byte with the Python

@@ -1,5 +1,6 @@
 """The C++ host layer above the C ABI (efficient-path-planner_b200/host): World, StateValidator,
-MotionValidator, PathPlanner::checkTrajectoryValidity, BatchPlanner — built by host/Makefile and
+MotionValidator, PathPlanner::checkTrajectoryValidity, BatchPlanner, poly_traj::generateTrajectory, OnlineTrajGenerator,
+PathWriter — built by host/Makefile and
 exercised by host_selftest the way the reference's own code uses these classes
 (src/PathPlanner.cpp:27-58, src/StateValidator.cpp, src/MotionValidator.cpp)."""
 import os
@@ -21,7 +22,9 @@ def _exe():
 
 
 def _selftest(mode):
-    return subprocess.run([_exe(), CONFIG, mode], capture_output=True, text=True, timeout=300)
+    import tempfile
+    env = dict(os.environ, EPP_PATH_SEGMENTS_DIR=os.path.join(tempfile.mkdtemp(prefix="epp_host_"), "path_segments"))
+    return subprocess.run([_exe(), CONFIG, mode], capture_output=True, text=True, timeout=300, env=env)
 
 
 def test_cpp_path_writer_dumps_equal_the_python_writer(tmp_path):
