@@ -236,6 +236,39 @@ def test_presampled_trajectories_warp_form(oracle, config, track, shape):
             assert np.array_equal(sm.cpu().numpy().view(np.uint32), results[1][1]), (pad, shift)
 
 
+def test_presampled_trajectories_warp_form_ring_wrap(oracle, config, track):
+    """2 000 x 1 001 rows: every block takes ~110 chunks through a ring of at most 64 slots (several wraps), the last
+    chunk of every trajectory is ragged and odd.  Warp form == direct form on all of it, == oracle on a subsample."""
+    import torch
+    g, o, lo, hi = track
+    ow, gw = build_pair(oracle, epp_b200, config, g, o, epp_b200.BP_AUTO)
+    n_traj, rows = 2000, 1001
+    xyz = epp_b200.gen_states_dev(worlds.SEED_TRAJ, 0, n_traj * rows, lo, hi).view(n_traj, rows, 3)
+    xyz[::3, :, 2] = 1.9                       # a third of the trajectories fly above everything
+    mats = torch.zeros((n_traj, 10, rows + 1), dtype=torch.float64, device="cuda")   # ld = rows + 1 (even)
+    for c in range(3):
+        mats[:, 3 * c, :rows] = xyz[:, :, c]
+    got = {}
+    try:
+        for variant in (0, 1):
+            epp_b200.set_tuning("traj_variant", variant)
+            v, sm, f = gw.check_trajectories_dev(mats, n_traj, rows, rows + 1, 10 * (rows + 1), 10, 0.1)
+            torch.cuda.synchronize()
+            got[variant] = (v.cpu().numpy().view(np.uint32), sm.cpu().numpy().view(np.uint32), f.cpu().numpy())
+    finally:
+        epp_b200.set_tuning("traj_variant", 0)
+    for a, b in zip(got[0], got[1]):
+        assert np.array_equal(a, b)
+    host = xyz.cpu().numpy()
+    for t in (0, 1, 2, 777, 1999):
+        m = ow.check_states_mindist(host[t], 0.1)
+        assert np.array_equal(got[0][1][t], m)
+        bad = np.flatnonzero(~np.unpackbits(m.view(np.uint8), bitorder="little")[:rows].astype(bool))
+        assert got[0][2][t] == (bad[0] if bad.size else -1)
+    nvalid = int(np.unpackbits(got[0][0].view(np.uint8), bitorder="little")[:n_traj].sum())
+    assert 0 < nvalid < n_traj
+
+
 @pytest.mark.parametrize("bp", BPS, ids=BP_IDS)
 def test_fused_polynomial_sweep(oracle, config, bp):
     """Config 4 (fused form) at reduced size: coefficients -> sampler -> Horner -> world check."""
