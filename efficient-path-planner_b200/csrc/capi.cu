@@ -52,6 +52,7 @@ Knob g_knobs[] = {
     {"states_blocks_per_sm", {8}},       // direct form of K1: persistent blocks per SM
     {"segments_blocks_per_sm", {4}},
     {"segments_variant", {0}},           // 0: auto (records in shared memory when they fit), 1: records in global memory
+    {"segments_block", {0}},             // k_segments_rs threads per block: 256, 512, 1024; 0 = by batch size
     {"traj_variant", {0}},               // pre-sampled trajectories: 0 auto (warp-pipelined), 1 direct form only
     {"states_variant", {0}},             // 0: auto, 1: direct, 3: warp-pipelined
     {"states_per_thread", {0}},          // warp form: mask words per chunk (4 default, 8)
@@ -244,6 +245,7 @@ LaunchCfg launch_cfg(const DeviceEpoch &ep)
     c.segments_blocks_per_sm = knob_value("segments_blocks_per_sm");
     c.segments_variant = knob_value("segments_variant");
     c.traj_variant = knob_value("traj_variant");
+    c.segments_block = knob_value("segments_block");
     c.states_variant = knob_value("states_variant");
     c.states_per_thread = knob_value("states_per_thread");
     c.states_warp_blocks_per_sm = knob_value("states_warp_blocks_per_sm");

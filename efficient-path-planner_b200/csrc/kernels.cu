@@ -1055,8 +1055,8 @@ __device__ __forceinline__ bool ray_rec_invalid(const double *__restrict__ r, co
     return 0.0 <= t_min && t_min <= 1.0 && 0.0 <= t_max && t_max <= 1.0;
 }
 
-template <int BP>
-__global__ void __launch_bounds__(kBlock, 4) k_segments_rs(WorldView wv, const double *__restrict__ pa,
+template <int BP, int TB>
+__global__ void __launch_bounds__(TB, TB >= 1024 ? 1 : (TB >= 512 ? 2 : 4)) k_segments_rs(WorldView wv, const double *__restrict__ pa,
                                                             const double *__restrict__ pb, size_t n, int can_pass_gate,
                                                             uint32_t table_bytes, uint32_t *__restrict__ mask)
 {
@@ -1087,10 +1087,10 @@ __global__ void __launch_bounds__(kBlock, 4) k_segments_rs(WorldView wv, const d
         r[19] = r[20] = 0.0;
     }
     __syncthreads();
-    const size_t tiles = (n + kBlock - 1) / kBlock;
+    const size_t tiles = (n + TB - 1) / TB;
     size_t tile = blockIdx.x;
     if (tile >= tiles) return;
-    size_t i = tile * kBlock + threadIdx.x;
+    size_t i = tile * TB + threadIdx.x;
     P3 a = {0.0, 0.0, 0.0}, b = {0.0, 0.0, 0.0};
     if (i < n) {
         a = {__ldg(pa + 3 * i), __ldg(pa + 3 * i + 1), __ldg(pa + 3 * i + 2)};
@@ -1098,7 +1098,7 @@ __global__ void __launch_bounds__(kBlock, 4) k_segments_rs(WorldView wv, const d
     }
     for (;;) {
         const size_t next_tile = tile + gridDim.x;
-        const size_t ni = next_tile * kBlock + threadIdx.x;
+        const size_t ni = next_tile * TB + threadIdx.x;
         P3 na = {0.0, 0.0, 0.0}, nb = {0.0, 0.0, 0.0};
         if (next_tile < tiles && ni < n) {
             na = {__ldg(pa + 3 * ni), __ldg(pa + 3 * ni + 1), __ldg(pa + 3 * ni + 2)};
@@ -1618,15 +1618,29 @@ cudaError_t launch_segments(const LaunchCfg &cfg, const WorldView &wv, int bp, c
         // persistent blocks: as many per SM as the shared memory holds at once (a second wave would start late)
         int bps = (int)((size_t)(227 * 1024) / (total + 1024));
         bps = bps < 1 ? 1 : (bps > cfg.segments_blocks_per_sm ? cfg.segments_blocks_per_sm : bps);
-        const unsigned grid_rs = persistent_grid(cfg, tiles, bps);
+        // threads per block (tuning knob segments_block): the records are per block, so bigger blocks put more warps
+        // behind the same shared memory (3 x 256 threads fit an SM with 71 KB each, 2 x 512 or 1 x 1024 hold 32 warps)
+        // 0 = auto: the biggest block that still gives every SM a tile
+        int tb = cfg.segments_block;
+        if (tb <= 0) tb = n >= (size_t)cfg.sm_count * 1024 ? 1024 : (n >= (size_t)cfg.sm_count * 512 ? 512 : 256);
+        tb = tb >= 1024 ? 1024 : (tb >= 512 ? 512 : 256);
+#define EPP_LAUNCH_SEG_RS(TB_)                                                                                        \
+    {                                                                                                                 \
+        const int bps_tb = bps < 1024 / TB_ ? bps : 1024 / TB_; /* 64 registers per thread: 1024 threads per SM */    \
+        const unsigned grid_tb = persistent_grid(cfg, (n + TB_ - 1) / TB_, bps_tb);                                   \
+        err = ensure_smem(k_segments_rs<BP, TB_>, total);                                                             \
+        if (err == cudaSuccess) {                                                                                     \
+            k_segments_rs<BP, TB_><<<grid_tb, TB_, total, stream>>>(wv, d_a, d_b, n, can_pass_gate,                    \
+                                                                   (uint32_t)table_bytes, d_mask);                     \
+            err = cudaGetLastError();                                                                                 \
+        }                                                                                                             \
+    }
         EPP_DISPATCH_BP(bp, {
-            err = ensure_smem(k_segments_rs<BP>, total);
-            if (err == cudaSuccess) {
-                k_segments_rs<BP><<<grid_rs, kBlock, total, stream>>>(wv, d_a, d_b, n, can_pass_gate,
-                                                                     (uint32_t)table_bytes, d_mask);
-                err = cudaGetLastError();
-            }
+            if (tb == 1024) EPP_LAUNCH_SEG_RS(1024)
+            else if (tb == 512) EPP_LAUNCH_SEG_RS(512)
+            else EPP_LAUNCH_SEG_RS(256)
         });
+#undef EPP_LAUNCH_SEG_RS
         g_launches++;
         if (err == cudaSuccess && gv) err = launch_gather_push(cfg, *gv, stream);
         return err;

@@ -21,6 +21,7 @@ struct LaunchCfg {
     int states_warp_log2_slots = 0; // cap on log2(ring slots per block); 0: as many as fit (<= 64)
     int states_warp_min_n = 4096;   // auto: batches from this size up take the warp-pipelined form
     int states_debug = 0;           // profiling only: 1 skips phase 2 of the warp form, 2 also phase 1 (wrong masks)
+    int segments_block = 0;         // k_segments_rs: threads per block (256, 512, 1024; 0 = by batch size)
     int traj_variant = 0;           // pre-sampled trajectories: 0 auto (warp-pipelined form), 1 direct form only
     int states_pdl = 1;             // warp form: programmatic dependent launch (prologue overlaps the previous kernel's tail)
     int states_bits1 = 1;           // warp form: single-word candidate masks for worlds of <= 32 OBBs

@@ -601,6 +601,14 @@ def test_gather_segments_and_mindist_logical_ranks(oracle, config):
         lo_, hi_ = epp_b200.shard_range(n, r, world_size, 1024)
         gth.check_states(gw, d_a[lo_:hi_], 1, min_distance=0.3)
 
+    # The two ranks' ranges differ in size and may take different block sizes of K2.  CUDA loads a kernel lazily at
+    # its first launch and that load waits for running kernels — here the other logical rank's push kernel, which is
+    # waiting for this one (only an issue with several ranks inside ONE process): launch every form once beforehand.
+    for block in (256, 512, 1024):
+        epp_b200.set_tuning("segments_block", block)
+        gw.check_segments_dev(d_a[:4096], d_b[:4096])
+    epp_b200.set_tuning("segments_block", 0)
+    torch.cuda.synchronize()
     _run_logical_ranks(gathers, seg)
     _run_logical_ranks(gathers, md)
     for gth in gathers:
@@ -659,7 +667,7 @@ def test_segments_smem_record_form_equals_global_record_form(oracle, config, bp)
     cfgf = filling_config(config)
     ow, gw = build_pair(oracle, epp_b200, cfgf, g, o, broadphase=bp)
     rng = np.random.default_rng(99)
-    for n in (1, 31, 33, 4097, 70_001):
+    for n in (1, 31, 33, 4097, 70_001, 160_003):
         a, b = worlds.gen_segments(worlds.SEED_SEGMENTS, 1000 + n, n, lo, hi, 1.0)
         b[::17] = a[::17]  # zero-length segments
         extra_a, extra_b = adversarial_segments(gw.obbs(), rng, lo, hi, per_obb=2)
@@ -669,14 +677,16 @@ def test_segments_smem_record_form_equals_global_record_form(oracle, config, bp)
         for cpg in (False, True):
             want = ow.check_segments(a, b, cpg, threads=8)
             got = {}
-            for variant in (0, 1):
-                epp_b200.set_tuning("segments_variant", variant)
+            for variant, block in ((0, 0), (0, 256), (0, 512), (0, 1024), (1, 0)):   # block: threads per block of the
+                epp_b200.set_tuning("segments_variant", variant)                    # shared-memory form, 0 = by batch size
+                epp_b200.set_tuning("segments_block", block)
                 try:
-                    got[variant] = gw.check_segments_dev(d_a, d_b, can_pass_gate=cpg).cpu().numpy().view(np.uint32)
+                    got[variant, block] = gw.check_segments_dev(d_a, d_b, can_pass_gate=cpg).cpu().numpy().view(np.uint32)
                 finally:
                     epp_b200.set_tuning("segments_variant", 0)
-            assert mismatches(got[0], want) == 0, (n, cpg)
-            assert mismatches(got[1], want) == 0, (n, cpg)
+                    epp_b200.set_tuning("segments_block", 0)
+            for key, words in got.items():
+                assert mismatches(words, want) == 0, (n, cpg, key)
 
 
 @pytest.mark.parametrize("bp", BPS, ids=BP_IDS)
