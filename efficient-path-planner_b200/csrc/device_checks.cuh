@@ -28,7 +28,7 @@ struct WorldView {
     const uint32_t *bits_max_ge;
     int nb;
     int W;
-    int Ws; // row stride of the bits tables in words (W | 1)
+    int Ws; // row stride of the bits tables in words (W = 1: 1; else (W + 1) | 1 with a summary word at index W)
     KeyBins kb;
     int zrot; // every OBB rotation is a rotation about z (rot[2,5,6,7] == 0, rot[8] == 1)
     // EPP_BP_GRID

@@ -114,10 +114,8 @@ struct PointWorld<EPP_BP_BITS> {
             }
             return false;
         }
-        // two passes, as in RayWorld<EPP_BP_BITS>::any: non-zero words first (converged), then their candidates
-        uint32_t nz = 0u;
-        for (int w = 0; w < W; ++w)
-            if (tx[w] & ty[w] & tz[w]) nz |= 1u << w;
+        // word W of a row summarises which of its words are non-zero: three reads bound the words worth a look
+        uint32_t nz = tx[W] & ty[W] & tz[W];
         while (nz) {
             const int w = __ffs(nz) - 1;
             nz &= nz - 1;
@@ -137,32 +135,17 @@ struct PointWorld<EPP_BP_BITS> {
         const uint32_t *ty = inside + (nb + dev_key_bin(p.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb)) * Ws;
         const uint32_t *tz = inside + (2 * nb + dev_key_bin(p.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb)) * Ws;
         if (W == 1) return (tx[0] & ty[0] & tz[0]) != 0u;
-        uint32_t m = 0u;
-        for (int w = 0; w < W; ++w) m |= tx[w] & ty[w] & tz[w];
-        return m != 0u;
-    }
-    // Single pass over the words: for callers whose lanes hold NEIGHBOURING units (rows of one trajectory, samples of
-    // one polynomial) and therefore walk the same words together; the two passes of any() cost them ~5 %.
-    template <class F>
-    __device__ __forceinline__ bool any_seq(const WorldView &wv, const P3 &p, F test) const
-    {
-        const int nb = wv.nb, W = wv.W, Ws = wv.Ws;
-        const uint32_t *tx = inside + dev_key_bin(p.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb) * Ws;
-        const uint32_t *ty = inside + (nb + dev_key_bin(p.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb)) * Ws;
-        const uint32_t *tz = inside + (2 * nb + dev_key_bin(p.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb)) * Ws;
-        for (int w = 0; w < W; ++w) {
-            uint32_t m = tx[w] & ty[w] & tz[w];
-            while (m) {
-                const int k = (w << 5) + __ffs(m) - 1;
-                m &= m - 1;
-                if (test(k)) return true;
-            }
+        uint32_t nz = tx[W] & ty[W] & tz[W]; // summaries (see any())
+        while (nz) {
+            const int w = __ffs(nz) - 1;
+            nz &= nz - 1;
+            if (tx[w] & ty[w] & tz[w]) return true;
         }
         return false;
     }
     __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &p, int mode, bool cpg, double md) const
     {
-        return any_seq(wv, p, [&](int k) { return point_candidate_invalid(wv.aabb, wv.obb, k, p, mode, cpg, md); });
+        return any(wv, p, [&](int k) { return point_candidate_invalid(wv.aabb, wv.obb, k, p, mode, cpg, md); });
     }
 };
 
@@ -283,7 +266,7 @@ struct RayWorld<EPP_BP_BRUTE> {
 };
 
 // candidates = AND over axes of max_ge[bin(rayMin)] & min_le[bin(rayMax)].  Rows have an ODD stride of
-// Ws = W | 1 words (built that way on the host): lanes look up unrelated bins, and with the natural stride of W = 8 words every row
+// Ws words (W + a summary word, padded to odd; built that way on the host): lanes look up unrelated bins, and with the natural stride of W = 8 words every row
 // starts in one of four banks (ncu: 10.5 M bank-conflict cycles per 1 M segments, 40 % of the kernel's cycles).
 template <>
 struct RayWorld<EPP_BP_BITS> {

@@ -328,7 +328,9 @@ void build_bits(const std::vector<AabbRec> &aabbs, int bins_per_axis, BitsTables
 {
     const int M = static_cast<int>(aabbs.size());
     out.W = std::max(1, (M + 31) / 32);
-    out.Ws = out.W | 1;
+    // Row = W words + (W > 1) one SUMMARY word at index W (bit w set iff word w of the row is non-zero: point queries AND
+    // three summaries instead of scanning W words), padded to an odd stride (rows of unrelated bins in different banks).
+    out.Ws = out.W == 1 ? 1 : ((out.W + 1) | 1);
     double lo[3], hi[3];
     world_extent(aabbs, lo, hi);
     for (int a = 0; a < 3; ++a)
@@ -352,6 +354,14 @@ void build_bits(const std::vector<AabbRec> &aabbs, int bins_per_axis, BitsTables
                 if (b1 >= b) out.max_ge[at] |= bit;
             }
         }
+    if (out.W > 1)
+        for (size_t row = 0; row < static_cast<size_t>(3) * out.nb; ++row)
+            for (std::vector<uint32_t> *t : {&out.inside, &out.min_le, &out.max_ge}) {
+                uint32_t summary = 0u;
+                for (int w = 0; w < out.W; ++w)
+                    if ((*t)[row * out.Ws + w]) summary |= 1u << w;
+                (*t)[row * out.Ws + out.W] = summary;
+            }
 }
 
 void build_grid(const std::vector<AabbRec> &aabbs, std::vector<ObbRec> &obbs, long max_cells,

@@ -65,7 +65,7 @@ int host_key_bin(double x, double off, int32_t h0, int32_t shift, int32_t n);
 struct BitsTables {
     int nb = 0; // bins per axis
     int W = 0;  // 32-bit words per bin = ceil(M / 32)
-    int Ws = 0; // row stride in words = W | 1: odd, so rows of unrelated bins start in different shared-memory banks
+    int Ws = 0; // row stride in words: 1 for W = 1, else (W + 1) | 1 — W words, a summary word at index W, odd stride
     KeyBins bins{};
     std::vector<uint32_t> inside; // k set iff bin(min_k) <= b <= bin(max_k)
     std::vector<uint32_t> min_le; // k set iff bin(min_k) <= b
