@@ -86,6 +86,8 @@ SIGNATURES = {
     "epp_shard_range": (C.c_int, [C.c_size_t, C.c_int, C.c_int, C.c_size_t,
                                   C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
     "epp_mask_summary_dev": (C.c_int, [_vp, C.c_size_t, C.c_uint64, _vp, _vp]),
+    "epp_measure_fp64_nofma": (C.c_int, [C.c_int, C.c_int, _vp, _dp, _dp]),
+    "epp_count_candidates_dev": (C.c_int, [_vp, _vp, _vp, C.c_size_t, _vp, _vp]),
     "epp_gen_states_dev": (C.c_int, [C.c_uint64, C.c_uint64, C.c_size_t, _dp, _dp, _vp, _vp]),
     "epp_gen_segments_dev": (C.c_int, [C.c_uint64, C.c_uint64, C.c_size_t, _dp, _dp, C.c_double,
                                        _vp, _vp, _vp]),
@@ -374,9 +376,11 @@ class World:
         valid, _, _ = self.check_trajectories(np.asarray(trajectory)[None], minDistance, False)
         return bool(valid[0] & 1)
 
-    def check_poly_trajectories(self, coeffs, durations, dt, min_distance, max_samples=1024,
+    def check_poly_trajectories(self, coeffs, durations, dt, min_distance, max_samples=None,
                                 want_samples=True):
-        """coeffs (n_traj, K, 3, N), durations (n_traj, K), dt scalar or (n_traj,)."""
+        """coeffs (n_traj, K, 3, N), durations (n_traj, K), dt scalar or (n_traj,).  max_samples (rows reserved per
+        trajectory) defaults to what the longest trajectory needs; a trajectory that would produce more rows than
+        max_samples is reported invalid with first row = max_samples, never silently valid."""
         self._sync()
         c = _f64(coeffs)
         d = _f64(durations)
@@ -384,6 +388,8 @@ class World:
             c, d = c[None], d[None]
         n_traj, K, _, N = c.shape
         dts = np.ascontiguousarray(np.broadcast_to(np.asarray(dt, dtype=np.float64), (n_traj,)))
+        if max_samples is None:
+            max_samples = poly_max_samples(d, dts)
         max_samples = (int(max_samples) + 31) // 32 * 32
         valid = np.zeros(mask_words(n_traj), dtype=np.uint32)
         smask = np.zeros((n_traj, max_samples // 32), dtype=np.uint32) if want_samples else None
@@ -424,6 +430,18 @@ class World:
                                           mask.data_ptr(), self._stream()))
         return mask
 
+    def count_candidates_dev(self, a, b=None):
+        """(mean broad-phase candidates visited, mean candidates passing the exact stored-AABB test) per unit of a
+        device batch of points (b None) or segments."""
+        import torch
+        self._sync()
+        n = a.numel() // 3
+        out = torch.zeros(2, dtype=torch.int64, device=a.device)
+        _chk(lib().epp_count_candidates_dev(self._h, a.data_ptr(), b.data_ptr() if b is not None else None, n,
+                                            out.data_ptr(), self._stream()))
+        v, h = out.cpu().numpy().view(np.uint64)
+        return float(v) / max(n, 1), float(h) / max(n, 1)
+
     def check_trajectories_dev(self, mats, n_traj, rows, ld, traj_stride, cols, min_distance,
                                want_samples=True):
         import torch
@@ -438,12 +456,14 @@ class World:
                                               first.data_ptr(), self._stream()))
         return valid, smask, first
 
-    def check_poly_trajectories_dev(self, coeffs, durations, dt, min_distance, max_samples=1024,
+    def check_poly_trajectories_dev(self, coeffs, durations, dt, min_distance, max_samples=None,
                                     want_samples=True):
         import torch
         self._sync()
         n_traj, K, _, N = coeffs.shape
         dev = coeffs.device
+        if max_samples is None:  # one device -> host read; pass max_samples to stay asynchronous
+            max_samples = poly_max_samples(durations, dt)
         max_samples = (int(max_samples) + 31) // 32 * 32
         valid = torch.empty(mask_words(n_traj), dtype=torch.int32, device=dev)
         smask = torch.empty((n_traj, max_samples // 32), dtype=torch.int32, device=dev) if want_samples else None
@@ -589,6 +609,18 @@ def sample_trajectories(coeffs, durations, dt, time_offsets=None, max_rows=1024)
     return [np.ascontiguousarray(out[i, :, : rows[i]].T) for i in range(n)]
 
 
+def sample_trajectories_dev(coeffs, durations, dt, ld=1024, time_offsets=None):
+    """Device form of sample_trajectories: torch tensors in, (n, 10, ld) column-major matrices + row counts out."""
+    import torch
+    n, K, _, N = coeffs.shape
+    out = torch.zeros((n, 10, ld), dtype=torch.float64, device=coeffs.device)
+    rows = torch.zeros(n, dtype=torch.int32, device=coeffs.device)
+    _chk(lib().epp_sample_trajectories_dev(coeffs.data_ptr(), durations.data_ptr(), dt.data_ptr(),
+                                           time_offsets.data_ptr() if time_offsets is not None else None, n, K, N, ld,
+                                           out.data_ptr(), rows.data_ptr(), torch.cuda.current_stream().cuda_stream))
+    return out, rows
+
+
 def gen_states_dev(seed, first, n, lo, hi, out=None, device="cuda"):
     import torch
     if out is None:
@@ -618,6 +650,24 @@ def mask_summary_dev(mask, first_word=0):
                                     torch.cuda.current_stream().cuda_stream))
     pop, x = out.cpu().numpy().view(np.uint64)
     return int(pop), int(x)
+
+
+def poly_max_samples(durations, dt):
+    """Rows to reserve per trajectory for evaluateRange(0, sum(durations), dt): the running sums of the sampler
+    (trajectory.cpp:121-140) can emit a few rows more than sum / dt, hence the margin."""
+    worst = float((durations.sum(1) / dt).max()) if durations.shape[0] else 0.0
+    if not np.isfinite(worst):
+        raise ValueError("dt must be positive and durations finite")
+    return int(worst * (1.0 + 1e-9)) + 8
+
+
+def measure_fp64_nofma(iters=4096, reps=5):
+    """(thread-level non-fused FP64 instructions per second, ms per launch) of the current device."""
+    import torch
+    rate, ms = C.c_double(0.0), C.c_double(0.0)
+    _chk(lib().epp_measure_fp64_nofma(int(iters), int(reps), torch.cuda.current_stream().cuda_stream,
+                                      C.byref(rate), C.byref(ms)))
+    return rate.value, ms.value
 
 
 def _mix64(seed, counter):

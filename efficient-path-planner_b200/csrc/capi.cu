@@ -51,7 +51,10 @@ struct Knob {
 Knob g_knobs[] = {
     {"states_blocks_per_sm", {8}},       // direct form of K1: persistent blocks per SM
     {"segments_blocks_per_sm", {4}},
-    {"segments_variant", {0}},           // 0: auto (records in shared memory when they fit), 1: records in global memory
+    {"segments_variant", {0}},           // 0: auto, 1: direct form with records in global memory, 2: warp-pipelined, 3: direct forms only
+    {"segments_warp_min_n", {32768}},
+    {"segments_warp_threads", {1024}},
+    {"segments_warp_slots", {0}},
     {"segments_block", {0}},             // k_segments_rs threads per block: 256, 512, 1024; 0 = by batch size
     {"traj_variant", {0}},               // pre-sampled trajectories: 0 auto (warp-pipelined), 1 direct form only
     {"states_variant", {0}},             // 0: auto, 1: direct, 3: warp-pipelined
@@ -71,6 +74,7 @@ Knob g_knobs[] = {
     {"sm_limit", {0}},                   // 0: all SMs; > 0: size grids for this many SMs (several ranks on one GPU in tests)
     {"bits_bins", {0}},                  // 0: by world size
     {"grid_max_cells", {1 << 22}},
+    {"grid_occ_kb", {72}},               // shared-memory budget of the grid's occupancy bitmap
     {"bits_max_obbs", {1024}},
 };
 
@@ -82,6 +86,8 @@ std::atomic<int> *knob(const char *name)
 }
 
 int knob_value(const char *name) { return knob(name)->load(); }
+
+constexpr int kBitsMaxObbs = 1024;
 
 // One immutable committed world on one device.
 struct DeviceEpoch {
@@ -244,6 +250,9 @@ LaunchCfg launch_cfg(const DeviceEpoch &ep)
     c.states_blocks_per_sm = knob_value("states_blocks_per_sm");
     c.segments_blocks_per_sm = knob_value("segments_blocks_per_sm");
     c.segments_variant = knob_value("segments_variant");
+    c.segments_warp_min_n = knob_value("segments_warp_min_n");
+    c.segments_warp_threads = knob_value("segments_warp_threads");
+    c.segments_warp_slots = knob_value("segments_warp_slots");
     c.traj_variant = knob_value("traj_variant");
     c.segments_block = knob_value("segments_block");
     c.states_variant = knob_value("states_variant");
@@ -510,9 +519,12 @@ extern "C" int epp_world_commit(epp_world *w)
     const int M = (int)aabbs.size();
 
     int bp = w->bp_request;
-    const int bits_max = knob_value("bits_max_obbs");
+    // A bits row is summarised by ONE 32-bit word (bit w = word w of the row is non-zero) and the ray walk keeps its
+    // non-zero words in a 32-bit set: rows of more than 32 words (1024 OBBs) cannot be represented.
+    const int bits_max = std::min(knob_value("bits_max_obbs"), kBitsMaxObbs);
     if (bp == EPP_BP_AUTO) bp = (M <= bits_max) ? EPP_BP_BITS : EPP_BP_GRID;
-    if (bp == EPP_BP_BITS && M > 4096) return fail(EPP_ERR_INVALID_ARG, "EPP_BP_BITS supports at most 4096 OBBs");
+    if (bp == EPP_BP_BITS && M > kBitsMaxObbs)
+        return fail(EPP_ERR_INVALID_ARG, "EPP_BP_BITS supports at most 1024 OBBs (use EPP_BP_GRID or EPP_BP_AUTO)");
 
     BitsTables bits;
     GridTables grid;
@@ -522,7 +534,8 @@ extern "C" int epp_world_commit(epp_world *w)
         if (nb <= 0) nb = W == 1 ? 256 : (W <= 8 ? 128 : (W <= 32 ? 64 : 32));
         build_bits(aabbs, nb, bits);
     }
-    if (bp == EPP_BP_GRID) build_grid(aabbs, obbs, knob_value("grid_max_cells"), grid);
+    if (bp == EPP_BP_GRID)
+        build_grid(aabbs, obbs, knob_value("grid_max_cells"), grid, (long)knob_value("grid_occ_kb") * 1024);
 
     // One blob: [aabb][obb][bits inside|min_le|max_ge][cell_start][cell_items], 256 B aligned parts.
     struct Part {
@@ -534,7 +547,7 @@ extern "C" int epp_world_commit(epp_world *w)
         {aabbs.data(), aabbs.size() * sizeof(AabbRec), 0},      {obbs.data(), obbs.size() * sizeof(ObbRec), 0},
         {bits.inside.data(), bits.inside.size() * 4, 0},        {bits.min_le.data(), bits.min_le.size() * 4, 0},
         {bits.max_ge.data(), bits.max_ge.size() * 4, 0},        {grid.cell_start.data(), grid.cell_start.size() * 4, 0},
-        {grid.cell_items.data(), grid.cell_items.size() * 4, 0}};
+        {grid.cell_items.data(), grid.cell_items.size() * 4, 0}, {grid.occ.data(), grid.occ.size() * 4, 0}};
     size_t total = 0;
     for (Part &p : parts) {
         p.off = total;
@@ -566,6 +579,11 @@ extern "C" int epp_world_commit(epp_world *w)
     v.cell_start = (const uint32_t *)(base + parts[5].off);
     v.cell_items = (const uint32_t *)(base + parts[6].off);
     v.gbins = grid.bins;
+    v.occ = (const uint32_t *)(base + parts[7].off);
+    v.occ_bytes = (uint32_t)align_up(grid.occ.size() * 4, 16); // parts are padded to 256 B
+    v.occ_n0 = grid.occ_n[0];
+    v.occ_n1 = grid.occ_n[1];
+    for (int a = 0; a < 3; ++a) v.occ_shift[a] = grid.occ_shift[a];
     ep->bp = bp;
     ep->epoch = ++w->epoch;
     w->current = ep; // the previous epoch is released when its last in-flight user drops it
@@ -1152,6 +1170,19 @@ extern "C" int epp_mask_summary_dev(const uint32_t *d_mask, size_t n_words, uint
     EPP_CUDA(cudaGetDevice(&device));
     EPP_CUDA(cudaDeviceGetAttribute(&cfg.sm_count, cudaDevAttrMultiProcessorCount, device));
     cudaError_t e = launch_mask_summary(cfg, d_mask, n_words, first_word, d_popcount_xor, (cudaStream_t)stream);
+    return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
+}
+
+extern "C" int epp_count_candidates_dev(epp_world *w, const double *d_a, const double *d_b, size_t n,
+                                       uint64_t *d_visited_hits, void *stream)
+{
+    std::shared_ptr<DeviceEpoch> ep;
+    int rc = snapshot(w, ep);
+    if (rc) return rc;
+    if (!d_visited_hits || (n && !d_a)) return fail(EPP_ERR_INVALID_ARG, "null buffer");
+    DeviceGuard guard;
+    EPP_CUDA(guard.enter(ep->device));
+    cudaError_t e = launch_count_candidates(launch_cfg(*ep), ep->view, ep->bp, d_a, d_b, n, d_visited_hits, (cudaStream_t)stream);
     return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
 }
 

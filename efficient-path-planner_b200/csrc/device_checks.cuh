@@ -35,6 +35,11 @@ struct WorldView {
     const uint32_t *cell_start;
     const uint32_t *cell_items;
     AxisBins gbins;
+    // occupancy bitmap over coarse cells (GridTables::occ): bit (z' * occ_n1 + y') * occ_n0 + x', c' = c >> occ_shift
+    const uint32_t *occ;
+    uint32_t occ_bytes; // multiple of 16
+    int occ_n0, occ_n1;
+    int occ_shift[3];
 };
 
 struct P3 {

@@ -186,21 +186,35 @@ struct PointWorld<kBpBits1> {
     }
 };
 
-// Uniform grid: candidates = CSR list of the cell holding p.
+// Uniform grid: candidates = CSR list of the cell holding p.  The warp-pipelined form first asks an occupancy
+// bitmap over (coarsened) cells that lives in shared memory: in a 10 000-OBB world spread over 400 x 400 m a few
+// per cent of the states are in an occupied cell, the rest never touch global memory for the broad phase (with
+// cell_start read per state the kernel was bound by L2 traffic: 2.3 sectors per 24-byte state).
+__device__ __forceinline__ size_t occ_bit(const WorldView &wv, int bx, int by, int bz)
+{
+    return ((size_t)(bz >> wv.occ_shift[2]) * wv.occ_n1 + (by >> wv.occ_shift[1])) * wv.occ_n0 + (bx >> wv.occ_shift[0]);
+}
+
 template <>
 struct PointWorld<EPP_BP_GRID> {
-    __device__ void init(const WorldView &, bool) {}
-    __device__ static uint32_t table(const WorldView &, bool, const void *&src)
+    const uint32_t *occ; // warp form: the bitmap's copy in shared memory
+    __device__ void init(const WorldView &wv, bool) { occ = wv.occ; }
+    __device__ static uint32_t table(const WorldView &wv, bool, const void *&src)
     {
-        src = nullptr;
-        return 0u;
+        src = wv.occ;
+        return wv.occ_bytes;
     }
-    __device__ void bind(const WorldView &, bool) {}
+    __device__ void bind(const WorldView &, bool) { occ = reinterpret_cast<const uint32_t *>(g_smem); }
+    __device__ __forceinline__ static void cell_of(const WorldView &wv, const P3 &p, int &bx, int &by, int &bz)
+    {
+        bx = dev_bin(p.x, wv.gbins.lo[0], wv.gbins.inv[0], wv.gbins.n[0]);
+        by = dev_bin(p.y, wv.gbins.lo[1], wv.gbins.inv[1], wv.gbins.n[1]);
+        bz = dev_bin(p.z, wv.gbins.lo[2], wv.gbins.inv[2], wv.gbins.n[2]);
+    }
     __device__ __forceinline__ static void cell_range(const WorldView &wv, const P3 &p, uint32_t &s, uint32_t &e)
     {
-        const int bx = dev_bin(p.x, wv.gbins.lo[0], wv.gbins.inv[0], wv.gbins.n[0]);
-        const int by = dev_bin(p.y, wv.gbins.lo[1], wv.gbins.inv[1], wv.gbins.n[1]);
-        const int bz = dev_bin(p.z, wv.gbins.lo[2], wv.gbins.inv[2], wv.gbins.n[2]);
+        int bx, by, bz;
+        cell_of(wv, p, bx, by, bz);
         const size_t cell = ((size_t)bz * wv.gbins.n[1] + by) * wv.gbins.n[0] + bx;
         s = __ldg(wv.cell_start + cell);
         e = __ldg(wv.cell_start + cell + 1);
@@ -214,11 +228,13 @@ struct PointWorld<EPP_BP_GRID> {
             if (test((int)__ldg(wv.cell_items + j))) return true;
         return false;
     }
+    // bitmap only (a superset test: the coarse cell may be occupied where the point's own cell is empty)
     __device__ __forceinline__ bool has_candidates(const WorldView &wv, const P3 &p) const
     {
-        uint32_t s, e;
-        cell_range(wv, p, s, e);
-        return e != s;
+        int bx, by, bz;
+        cell_of(wv, p, bx, by, bz);
+        const size_t b = occ_bit(wv, bx, by, bz);
+        return (occ[b >> 5] >> (b & 31)) & 1u;
     }
     __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &p, int mode, bool cpg, double md) const
     {
@@ -328,17 +344,54 @@ struct RayWorld<EPP_BP_BITS> {
 };
 
 // Cells overlapped by the ray box; a candidate listed in several of them is evaluated only
-// in the first cell of (ray cells) x (candidate cells).
+// in the first cell of (ray cells) x (candidate cells).  has_candidates() asks the occupancy bitmap (PointWorld<GRID>
+// above) about the coarse cells under the ray box first: rows of x-bits, at most two words per (y, z) row.
 template <>
 struct RayWorld<EPP_BP_GRID> {
-    __device__ void init(const WorldView &, bool) {}
+    const uint32_t *occ;
+    __device__ void init(const WorldView &wv, bool) { occ = wv.occ; }
+    __device__ void bind(const WorldView &) { occ = reinterpret_cast<const uint32_t *>(g_smem); }
+    __device__ __forceinline__ static void cells_of(const WorldView &wv, const P3 &mn, const P3 &mx, int &x0, int &x1,
+                                                    int &y0, int &y1, int &z0, int &z1)
+    {
+        const AxisBins &g = wv.gbins;
+        x0 = dev_bin(mn.x, g.lo[0], g.inv[0], g.n[0]), x1 = dev_bin(mx.x, g.lo[0], g.inv[0], g.n[0]);
+        y0 = dev_bin(mn.y, g.lo[1], g.inv[1], g.n[1]), y1 = dev_bin(mx.y, g.lo[1], g.inv[1], g.n[1]);
+        z0 = dev_bin(mn.z, g.lo[2], g.inv[2], g.n[2]), z1 = dev_bin(mx.z, g.lo[2], g.inv[2], g.n[2]);
+    }
+    template <bool GLOBAL>
+    __device__ __forceinline__ bool has_candidates_t(const WorldView &wv, const P3 &mn, const P3 &mx) const
+    {
+        int x0, x1, y0, y1, z0, z1;
+        cells_of(wv, mn, mx, x0, x1, y0, y1, z0, z1);
+        x0 >>= wv.occ_shift[0], x1 >>= wv.occ_shift[0];
+        y0 >>= wv.occ_shift[1], y1 >>= wv.occ_shift[1];
+        z0 >>= wv.occ_shift[2], z1 >>= wv.occ_shift[2];
+        for (int z = z0; z <= z1; ++z)
+            for (int y = y0; y <= y1; ++y) {
+                size_t s = ((size_t)z * wv.occ_n1 + y) * wv.occ_n0 + x0;
+                int len = x1 - x0 + 1;
+                while (len > 0) {
+                    const int off = (int)(s & 31), take = (32 - off) < len ? (32 - off) : len;
+                    const uint32_t m = (take == 32 ? 0xffffffffu : ((1u << take) - 1u)) << off;
+                    const uint32_t w = GLOBAL ? __ldg(occ + (s >> 5)) : occ[s >> 5];
+                    if (w & m) return true;
+                    s += take;
+                    len -= take;
+                }
+            }
+        return false;
+    }
+    __device__ __forceinline__ bool has_candidates(const WorldView &wv, const P3 &mn, const P3 &mx) const
+    {
+        return has_candidates_t<false>(wv, mn, mx);
+    }
     template <typename F>
     __device__ __forceinline__ bool any(const WorldView &wv, const P3 &mn, const P3 &mx, F f) const
     {
         const AxisBins &g = wv.gbins;
-        const int x0 = dev_bin(mn.x, g.lo[0], g.inv[0], g.n[0]), x1 = dev_bin(mx.x, g.lo[0], g.inv[0], g.n[0]);
-        const int y0 = dev_bin(mn.y, g.lo[1], g.inv[1], g.n[1]), y1 = dev_bin(mx.y, g.lo[1], g.inv[1], g.n[1]);
-        const int z0 = dev_bin(mn.z, g.lo[2], g.inv[2], g.n[2]), z1 = dev_bin(mx.z, g.lo[2], g.inv[2], g.n[2]);
+        int x0, x1, y0, y1, z0, z1;
+        cells_of(wv, mn, mx, x0, x1, y0, y1, z0, z1);
         for (int z = z0; z <= z1; ++z)
             for (int y = y0; y <= y1; ++y) {
                 const size_t row = ((size_t)z * g.n[1] + y) * g.n[0];
@@ -359,6 +412,7 @@ struct RayWorld<EPP_BP_GRID> {
     {
         P3 mn, mx;
         ray_box(a, b, mn, mx);
+        if (!has_candidates_t<true>(wv, mn, mx)) return false; // direct form: the bitmap is read from global memory
         return any(wv, mn, mx, [&](int k) -> bool { return ray_candidate_invalid(wv.aabb, wv.obb, k, a, b, mn, mx, cpg); });
     }
 };
@@ -1089,14 +1143,9 @@ __device__ __forceinline__ bool ray_rec_invalid(const double *__restrict__ r, co
     return 0.0 <= t_min && t_min <= 1.0 && 0.0 <= t_max && t_max <= 1.0;
 }
 
-template <int BP, int TB>
-__global__ void __launch_bounds__(TB, TB >= 1024 ? 1 : (TB >= 512 ? 2 : 4)) k_segments_rs(WorldView wv, const double *__restrict__ pa,
-                                                            const double *__restrict__ pb, size_t n, int can_pass_gate,
-                                                            uint32_t table_bytes, uint32_t *__restrict__ mask)
+// The call's rules folded into one kRayRec-double record per OBB (layout above), by all threads of the block.
+__device__ __forceinline__ void fold_ray_records(const WorldView &wv, double *rec, bool can_pass_gate)
 {
-    RayWorld<BP> world;
-    world.init(wv, false);
-    double *rec = reinterpret_cast<double *>(g_smem + table_bytes);
     for (int k = threadIdx.x; k < wv.M; k += blockDim.x) {
         const AabbRec *ab = wv.aabb + k;
         const ObbRec *o = wv.obb + k;
@@ -1120,6 +1169,17 @@ __global__ void __launch_bounds__(TB, TB >= 1024 ? 1 : (TB >= 512 ? 2 : 4)) k_se
         r[12] = __ldg(&o->rot[4]);
         r[19] = r[20] = 0.0;
     }
+}
+
+template <int BP, int TB>
+__global__ void __launch_bounds__(TB, TB >= 1024 ? 1 : (TB >= 512 ? 2 : 4)) k_segments_rs(WorldView wv, const double *__restrict__ pa,
+                                                            const double *__restrict__ pb, size_t n, int can_pass_gate,
+                                                            uint32_t table_bytes, uint32_t *__restrict__ mask)
+{
+    RayWorld<BP> world;
+    world.init(wv, false);
+    double *rec = reinterpret_cast<double *>(g_smem + table_bytes);
+    fold_ray_records(wv, rec, can_pass_gate != 0);
     __syncthreads();
     const size_t tiles = (n + TB - 1) / TB;
     size_t tile = blockIdx.x;
@@ -1151,6 +1211,212 @@ __global__ void __launch_bounds__(TB, TB >= 1024 ? 1 : (TB >= 512 ? 2 : 4)) k_se
         i = ni;
         a = na;
         b = nb;
+    }
+}
+
+// ---- K2 (warp-pipelined form): end points through a cp.async.bulk ring ---------------------------------------
+//
+// The direct forms above fetch a segment's six coordinates with scalar loads at a 24-byte stride (ncu: 3.5 L1 sectors
+// per algorithmic sector) and, on the grid broad phase, walk cell lists of very different lengths lane by lane.  This
+// form has K1's structure: block = 1 producer warp + up to 31 consumer warps per SM; the block's mask words are cut into
+// chunks of kSegS words (64 segments); the producer brings a chunk's two end-point runs (2 x 1536 B) into a ring slot
+// with two bulk copies on one mbarrier; consumers take chunk numbers from a shared counter.
+//   bits / brute: every lane evaluates its kSegS segments from shared memory (records folded as in k_segments_rs for
+//                 worlds of <= 256 z-rotated OBBs) — three lanes in four have candidates there, compaction would not pay;
+//   grid:         phase 1 asks the occupancy bitmap (shared memory) whether any coarse cell under the ray box is
+//                 occupied and compacts those segments (~1 in 8 in the 10 000-OBB world) into a per-warp queue,
+//                 phase 2 walks their cell lists one queued segment per lane.
+constexpr int kSegS = 2;
+constexpr int kSegSlotBytes = kSegS * 2 * kWordBytes; // both end points of kSegS * 32 segments
+constexpr int kSegMaxSlots = 64;
+
+template <int BP, bool RS>
+__global__ void __launch_bounds__(1024, 1) k_segments_warp(WorldView wv, const double *__restrict__ pa,
+                                                          const double *__restrict__ pb, size_t n, int can_pass_gate,
+                                                          int aabb_in_smem, uint32_t slots, uint32_t table_bytes,
+                                                          uint32_t rec_bytes, uint32_t wpb, uint32_t rem,
+                                                          uint32_t *__restrict__ mask)
+{
+    constexpr int S = kSegS;
+    __shared__ __align__(8) uint64_t s_full[kSegMaxSlots];
+    __shared__ __align__(8) uint64_t s_empty[kSegMaxSlots];
+    __shared__ __align__(8) uint64_t s_table;
+    __shared__ uint32_t s_next;
+    __shared__ uint32_t s_rounds_done[kSegMaxSlots];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const uint32_t consumers = (blockDim.x >> 5) - 1u;
+    const bool cpg = can_pass_gate != 0;
+    double *rec = reinterpret_cast<double *>(g_smem + table_bytes);
+    unsigned char *ring = g_smem + table_bytes + rec_bytes;
+    unsigned char *areas = ring + slots * kSegSlotBytes;
+
+    const uint32_t b0 = blockIdx.x * wpb + (blockIdx.x < rem ? blockIdx.x : rem);
+    const uint32_t b1 = b0 + wpb + (blockIdx.x < rem ? 1u : 0u);
+    const uint32_t chunks = (b1 - b0 + S - 1) / S;
+    const uint32_t words_total = (uint32_t)((n + 31) / 32);
+    const bool aligned = ((reinterpret_cast<uintptr_t>(pa) | reinterpret_cast<uintptr_t>(pb)) & 15u) == 0;
+    auto chunk_units = [&](uint32_t i) -> int {
+        const uint32_t cw = b0 + i * S;
+        const uint32_t sw = (b1 - cw) < (uint32_t)S ? (b1 - cw) : (uint32_t)S;
+        int units = (int)(sw * 32u);
+        if (cw + sw == words_total) units = (int)(n - (size_t)cw * 32u);
+        return units;
+    };
+    auto by_tma = [&](int units) -> bool { return aligned && (units & 1) == 0; };
+
+    RayWorld<BP> world;
+    if constexpr (BP == EPP_BP_GRID) {
+        if (threadIdx.x == 0) {
+            s_next = 0u;
+            mbar_init(&s_table, 1);
+            mbar_init_fence();
+            mbar_expect_tx(&s_table, wv.occ_bytes);
+            bulk_g2s(g_smem, wv.occ, wv.occ_bytes, &s_table);
+        }
+    } else {
+        if (threadIdx.x == 0) s_next = 0u;
+        world.init(wv, aabb_in_smem != 0); // tables (bits) / stored AABBs (brute) by all threads; ends with a barrier
+    }
+    if (RS) fold_ray_records(wv, rec, cpg);
+    if (threadIdx.x >= 32) {
+        for (uint32_t s = threadIdx.x - 32; s < slots; s += blockDim.x - 32) {
+            mbar_init(&s_full[s], 1);
+            mbar_init(&s_empty[s], 1);
+            s_rounds_done[s] = 0u;
+        }
+        if (threadIdx.x - 32 < slots) mbar_init_fence();
+    }
+    __syncthreads();
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+
+    if (warp == 0) {
+        // ---- producer: waves of min(32, slots) chunks; slots is <= 32 or a multiple of 32 (launcher), so a slot is
+        // always armed by the same lane, in program order
+        const uint32_t wave = slots < 32u ? slots : 32u;
+        for (uint32_t base = 0; base < chunks; base += wave) {
+            const uint32_t i = base + (uint32_t)lane;
+            if ((uint32_t)lane >= wave || i >= chunks) continue;
+            const uint32_t slot = i % slots, round = i / slots;
+            if (round > 0) mbar_wait(&s_empty[slot], (round - 1u) & 1u);
+            const int units = chunk_units(i);
+            if (by_tma(units)) {
+                unsigned char *dst = ring + slot * kSegSlotBytes;
+                const size_t off = (size_t)(b0 + i * S) * 96;
+                mbar_expect_tx(&s_full[slot], (uint32_t)units * 48u);
+                bulk_g2s(dst, pa + off, (uint32_t)units * 24u, &s_full[slot]);
+                bulk_g2s(dst + S * kWordBytes, pb + off, (uint32_t)units * 24u, &s_full[slot]);
+            } else {
+                mbar_arrive(&s_full[slot]);
+            }
+        }
+        return;
+    }
+
+    // ---- consumers
+    const uint32_t c = (uint32_t)warp - 1u;
+    unsigned char *queue = areas + c * (S * 32u + 32u);
+    uint32_t *inv = reinterpret_cast<uint32_t *>(queue + S * 32);
+    if (lane < 8) inv[lane] = 0u;
+    if constexpr (BP == EPP_BP_GRID) {
+        world.bind(wv);
+        mbar_wait(&s_table, 0);
+    }
+    __syncwarp();
+    const uint32_t lt = (1u << lane) - 1u;
+
+    for (;;) {
+        uint32_t i = 0;
+        if (lane == 0) i = atomicAdd(&s_next, 1u);
+        i = __shfl_sync(0xffffffffu, i, 0);
+        if (i >= chunks) break;
+        const uint32_t slot = i % slots, round = i / slots;
+        const int units = chunk_units(i);
+        double *A = reinterpret_cast<double *>(ring + slot * kSegSlotBytes);
+        double *B = A + S * 96;
+        if (round > 0) { // see k_states_warp: the parity wait below is only meaningful once round - 1 has been consumed
+            uint32_t done;
+            do {
+                asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(done) : "r"(smem_addr(&s_rounds_done[slot])) : "memory");
+            } while (done < round);
+        }
+        mbar_wait(&s_full[slot], round & 1u);
+        if (!by_tma(units)) {
+            const size_t off = (size_t)(b0 + i * S) * 96;
+            for (int e = lane; e < 3 * units; e += 32) {
+                A[e] = __ldg(pa + off + e);
+                B[e] = __ldg(pb + off + e);
+            }
+            __syncwarp();
+        }
+        uint32_t *mo = mask + b0 + i * S;
+        if constexpr (BP == EPP_BP_GRID) {
+            // phase 1: which of my segments have an occupied coarse cell under their box
+            int queued = 0;
+#pragma unroll
+            for (int u = 0; u < S; ++u) {
+                const int unit = u * 32 + lane;
+                bool has = false;
+                if (unit < units) {
+                    const P3 a = {A[3 * unit], A[3 * unit + 1], A[3 * unit + 2]};
+                    const P3 b = {B[3 * unit], B[3 * unit + 1], B[3 * unit + 2]};
+                    P3 mn, mx;
+                    ray_box(a, b, mn, mx);
+                    has = world.has_candidates(wv, mn, mx);
+                }
+                const uint32_t bal = __ballot_sync(0xffffffffu, has);
+                if (has) queue[queued + __popc(bal & lt)] = (unsigned char)unit;
+                queued += __popc(bal);
+            }
+            if (queued != 0) {
+                __syncwarp();
+                // phase 2: one queued segment per lane through the cell lists
+                for (int q = lane; q < queued; q += 32) {
+                    const int unit = queue[q];
+                    const P3 a = {A[3 * unit], A[3 * unit + 1], A[3 * unit + 2]};
+                    const P3 b = {B[3 * unit], B[3 * unit + 1], B[3 * unit + 2]};
+                    P3 mn, mx;
+                    ray_box(a, b, mn, mx);
+                    const bool hit = world.any(wv, mn, mx, [&](int k) -> bool {
+                        return ray_candidate_invalid(wv.aabb, wv.obb, k, a, b, mn, mx, cpg);
+                    });
+                    if (hit) atomicOr(&inv[unit >> 5], 1u << (unit & 31));
+                }
+                __syncwarp();
+            }
+            if (lane < S && lane * 32 < units) {
+                const int live = units - 32 * lane;
+                const uint32_t active = live >= 32 ? 0xffffffffu : ((1u << live) - 1u);
+                mo[lane] = ~inv[lane] & active;
+                inv[lane] = 0u;
+            }
+            __syncwarp();
+        } else {
+            uint32_t mine = 0u;
+#pragma unroll
+            for (int u = 0; u < S; ++u) {
+                const int unit = u * 32 + lane;
+                bool valid = false;
+                if (unit < units) {
+                    const P3 a = {A[3 * unit], A[3 * unit + 1], A[3 * unit + 2]};
+                    const P3 b = {B[3 * unit], B[3 * unit + 1], B[3 * unit + 2]};
+                    P3 mn, mx;
+                    ray_box(a, b, mn, mx);
+                    valid = !world.any(wv, mn, mx, [&](int k) -> bool {
+                        if (RS) return ray_rec_invalid(rec + k * kRayRec, a, b, mn, mx);
+                        return ray_candidate_invalid(wv.aabb, wv.obb, k, a, b, mn, mx, cpg);
+                    });
+                }
+                const uint32_t w = __ballot_sync(0xffffffffu, valid);
+                if (lane == u) mine = w;
+            }
+            if (lane < S && lane * 32 < units) mo[lane] = mine;
+            __syncwarp();
+        }
+        if (lane == 0) {
+            mbar_arrive(&s_empty[slot]);
+            asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(smem_addr(&s_rounds_done[slot])), "r"(round + 1u) : "memory");
+        }
     }
 }
 
@@ -1207,8 +1473,9 @@ __global__ void k_traj_finalize(long long *first_row, int64_t *first_out, size_t
 
 // ---- K3b: fused polynomial sweep --------------------------------------------------------------
 
-constexpr int kPolyWarps = 4;
-constexpr int kPolyPitch = 33; // odd pitch: conflict-free column writes and row reads
+constexpr int kPolyThreads = 256;  // 1 producer warp + 7 consumer warps
+constexpr int kPolyRing = 4;       // rounds of parked samples per block
+constexpr int kPolyPitch = 33;     // odd pitch: conflict-free column writes and row reads
 
 // Polynomial::evaluate(t, 0) (polynomial.h:136-150): Horner from the top coefficient.
 __device__ __forceinline__ double horner(const double *__restrict__ c, int n, double t)
@@ -1218,115 +1485,200 @@ __device__ __forceinline__ double horner(const double *__restrict__ c, int n, do
     return r;
 }
 
-// A warp owns G trajectories (G = 1..32, chosen by the launcher so that the batch fills the GPU: 10 000
-// trajectories at G = 32 are only 313 warps, two per SM).  Phase 1: lane l < G advances the reference's
-// sequential sampler (trajectory.cpp:121-140: running sums, not k*dt) of ITS trajectory by up to 32 samples
-// and parks (segment, time_in_segment) in shared memory.  Phase 2: for each of the G trajectories in turn,
-// the 32 lanes evaluate its 32 parked samples (Horner x 3 + world check) and ballot them into one mask word.
-template <int BP>
-__global__ void __launch_bounds__(kPolyWarps * 32) k_poly_traj(WorldView wv, const double *__restrict__ coeffs,
-                                                               const double *__restrict__ durations,
-                                                               const double *__restrict__ dts, size_t n_traj,
-                                                               int n_segments, int n_coeffs, double min_distance,
-                                                               size_t max_samples, int aabb_in_smem, int G,
-                                                               uint32_t table_bytes,
-                                                               uint32_t *__restrict__ sample_mask,
-                                                               uint32_t *__restrict__ n_samples_out,
-                                                               long long *__restrict__ first_row)
+// N = 10 (trajectory_generator.cpp:17), the only degree the reference builds: fully unrolled, coefficients fetched
+// two at a time (a segment's 30 coefficients start on a 16-byte boundary when the batch does).
+__device__ __forceinline__ double horner10(const double *__restrict__ c, double t)
 {
+    const double2 *c2 = reinterpret_cast<const double2 *>(c);
+    const double2 c89 = __ldg(c2 + 4), c67 = __ldg(c2 + 3), c45 = __ldg(c2 + 2), c23 = __ldg(c2 + 1), c01 = __ldg(c2);
+    double r = c89.y;
+    r = dadd(dmul(r, t), c89.x);
+    r = dadd(dmul(r, t), c67.y);
+    r = dadd(dmul(r, t), c67.x);
+    r = dadd(dmul(r, t), c45.y);
+    r = dadd(dmul(r, t), c45.x);
+    r = dadd(dmul(r, t), c23.y);
+    r = dadd(dmul(r, t), c23.x);
+    r = dadd(dmul(r, t), c01.y);
+    r = dadd(dmul(r, t), c01.x);
+    return r;
+}
+
+// A block owns G <= 32 trajectories.  Its PRODUCER warp runs the reference's sequential sampler
+// (trajectory.cpp:121-140: running sums tin += dt, acc += dt — k * dt would change bits), lane l on trajectory l, 32
+// samples per trajectory and round, and parks (segment, time in segment) in a ring of kPolyRing rounds in shared memory.
+// The CONSUMER warps take (round, trajectory) items from a shared counter and evaluate the 32 parked samples of the
+// item, one per lane (3 Horner chains + the world check), into one mask word.  Round 1 had the sampler and the
+// evaluation in the same warp: with the G = 2 trajectories per warp that filled the GPU, 2 of 32 lanes worked in the
+// sampler and it was a third of all issued instructions (ncu r02_a); with G = 32 there were 313 warps in all.
+// A trajectory with more than max_samples samples is reported INVALID with first row max_samples (the first row that
+// was not checked) unless an earlier row is invalid — never silently valid.
+template <int BP, bool N10>
+__global__ void __launch_bounds__(kPolyThreads) k_poly_traj(WorldView wv, const double *__restrict__ coeffs,
+                                                            const double *__restrict__ durations,
+                                                            const double *__restrict__ dts, size_t n_traj,
+                                                            int n_segments, int n_coeffs, double min_distance,
+                                                            size_t max_samples, int aabb_in_smem, int G,
+                                                            uint32_t table_bytes,
+                                                            uint32_t *__restrict__ sample_mask,
+                                                            uint32_t *__restrict__ n_samples_out,
+                                                            long long *__restrict__ first_row)
+{
+    __shared__ uint32_t s_next, s_produced, s_total, s_done[kPolyRing];
     PointWorld<BP> world;
+    if (threadIdx.x == 0) {
+        s_next = 0u;
+        s_produced = 0u;
+        s_total = 0xffffffffu;
+        for (int r = 0; r < kPolyRing; ++r) s_done[r] = 0u;
+    }
     world.init(wv, aabb_in_smem != 0);
+    __syncthreads();
 
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
-    // shared memory behind the broad-phase table: per warp G rows of parked times, then G rows of segment numbers
-    double *s_t = reinterpret_cast<double *>(g_smem + table_bytes) + (size_t)warp * G * kPolyPitch;
-    unsigned short *s_seg = reinterpret_cast<unsigned short *>(g_smem + table_bytes + (size_t)kPolyWarps * G * kPolyPitch * 8) +
-                            (size_t)warp * G * kPolyPitch;
-    const size_t traj0 = ((size_t)blockIdx.x * kPolyWarps + warp) * (size_t)G;
-    if (traj0 >= n_traj) return;
-    const size_t my = traj0 + lane;
-    const bool have = lane < G && my < n_traj;
+    const size_t traj0 = (size_t)blockIdx.x * (size_t)G;
+    const uint32_t Gb = (uint32_t)((n_traj - traj0) < (size_t)G ? (n_traj - traj0) : (size_t)G); // trajectories of this block
     const size_t words_per_traj = max_samples / 32;
+    // ring behind the broad-phase table: per round G rows of parked times, G rows of segment numbers, G counts
+    const size_t round_bytes = (size_t)G * kPolyPitch * 10 + (size_t)G * 4;
+    auto ring_t = [&](uint32_t slot) { return reinterpret_cast<double *>(g_smem + table_bytes + slot * round_bytes); };
+    auto ring_seg = [&](uint32_t slot) {
+        return reinterpret_cast<unsigned short *>(g_smem + table_bytes + slot * round_bytes + (size_t)G * kPolyPitch * 8);
+    };
+    auto ring_cnt = [&](uint32_t slot) {
+        return reinterpret_cast<uint32_t *>(g_smem + table_bytes + slot * round_bytes + (size_t)G * kPolyPitch * 10);
+    };
 
-    // Sampler state of my trajectory: evaluateRange(0, maxTime, dt), trajectory.cpp:95-119.
-    const double *dur = durations + my * n_segments;
-    double t_end = 0.0, dt = 0.0, acc = 0.0, tin = 0.0, seg_T = 0.0;
-    int seg = 0;
-    bool done = !have;
-    if (have) {
-        dt = __ldg(dts + my);
-        for (int k = 0; k < n_segments; ++k) t_end = dadd(t_end, __ldg(dur + k)); // trajectory.h:64-71
-        // start-segment search with t_start = 0 (:99-114)
-        double a = 0.0;
-        int k = 0;
-        for (k = 0; k < n_segments; ++k) {
-            a = dadd(a, __ldg(dur + k));
-            if (a > 0.0) break;
-        }
-        if (0.0 > a || k >= n_segments) {
-            done = true;
-        } else {
-            seg = k;
-            seg_T = __ldg(dur + seg);
-            acc = dsub(a, seg_T);      // :117
-            tin = dsub(0.0, acc);      // :118
-        }
-    }
-    uint32_t emitted_total = 0;
-
-    for (size_t chunk = 0; chunk < words_per_traj; ++chunk) {
-        // ---- phase 1: up to 32 samples of my trajectory
-        int cnt = 0;
-        while (!done && cnt < 32) {
-            if (!(acc < t_end)) { // :121
-                done = true;
-                break;
+    if (warp == 0) {
+        // ---- producer: sampler state of my trajectory, evaluateRange(0, maxTime, dt), trajectory.cpp:95-119
+        const size_t my = traj0 + lane;
+        const bool have = (uint32_t)lane < Gb;
+        const double *dur = durations + my * n_segments;
+        double t_end = 0.0, dt = 0.0, acc = 0.0, tin = 0.0, seg_T = 0.0;
+        int seg = 0;
+        bool done = !have;
+        if (have) {
+            dt = __ldg(dts + my);
+            for (int k = 0; k < n_segments; ++k) t_end = dadd(t_end, __ldg(dur + k)); // trajectory.h:64-71
+            // start-segment search with t_start = 0 (:99-114)
+            double a = 0.0;
+            int k = 0;
+            for (k = 0; k < n_segments; ++k) {
+                a = dadd(a, __ldg(dur + k));
+                if (a > 0.0) break;
             }
-            if (tin > seg_T) { // :122-130
-                tin = dsub(tin, seg_T);
-                ++seg;
-                if (seg >= n_segments) {
+            if (0.0 > a || k >= n_segments) {
+                done = true;
+            } else {
+                seg = k;
+                seg_T = __ldg(dur + seg);
+                acc = dsub(a, seg_T);      // :117
+                tin = dsub(0.0, acc);      // :118
+            }
+        }
+        uint32_t emitted_total = 0;
+        // One step of the sampler's loop up to (not including) the emission: returns true when a sample is due.
+        auto advance = [&]() -> bool {
+            while (!done) {
+                if (!(acc < t_end)) { // :121
                     done = true;
                     break;
                 }
-                seg_T = __ldg(dur + seg);
-                continue;
+                if (tin > seg_T) { // :122-130
+                    tin = dsub(tin, seg_T);
+                    ++seg;
+                    if (seg >= n_segments) {
+                        done = true;
+                        break;
+                    }
+                    seg_T = __ldg(dur + seg);
+                    continue;
+                }
+                return true;
             }
-            s_t[lane * kPolyPitch + cnt] = tin; // :132
-            s_seg[lane * kPolyPitch + cnt] = (unsigned short)seg;
-            ++cnt;
-            tin = dadd(tin, dt); // :138-139
-            acc = dadd(acc, dt);
+            return false;
+        };
+        uint32_t round = 0;
+        for (; round < (uint32_t)words_per_traj; ++round) {
+            const uint32_t slot = round % kPolyRing;
+            if (round >= (uint32_t)kPolyRing) { // all Gb items of the slot's previous round have been evaluated
+                const uint32_t need = Gb * (round / kPolyRing);
+                uint32_t d;
+                do {
+                    asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(d) : "r"(smem_addr(&s_done[slot])) : "memory");
+                } while (d < need);
+            }
+            double *st = ring_t(slot) + lane * kPolyPitch;
+            unsigned short *sg = ring_seg(slot) + lane * kPolyPitch;
+            int cnt = 0;
+            while (cnt < 32 && advance()) {
+                st[cnt] = tin; // :132
+                sg[cnt] = (unsigned short)seg;
+                ++cnt;
+                tin = dadd(tin, dt); // :138-139
+                acc = dadd(acc, dt);
+            }
+            if (have) ring_cnt(slot)[lane] = (uint32_t)cnt;
+            emitted_total += (uint32_t)cnt;
+            if (__ballot_sync(0xffffffffu, cnt > 0) == 0u) break; // every trajectory of the block has ended
+            __syncwarp();
+            if (lane == 0)
+                asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(smem_addr(&s_produced)), "r"(round + 1u) : "memory");
         }
-        emitted_total += (uint32_t)cnt;
-        __syncwarp();
-        if (__ballot_sync(0xffffffffu, cnt > 0) == 0) break;
+        if (lane == 0) asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(smem_addr(&s_total)), "r"(round) : "memory");
+        if (have) {
+            if (advance()) atomicMin(first_row + my, (long long)max_samples); // truncated: rows beyond max_samples unchecked
+            if (n_samples_out) n_samples_out[my] = emitted_total;
+        }
+        return;
+    }
 
-        // ---- phase 2: evaluate trajectory j's parked samples, one per lane
-        for (int j = 0; j < G; ++j) {
-            const int cj = __shfl_sync(0xffffffffu, cnt, j);
-            if (cj == 0) continue;
+    // ---- consumers
+    for (;;) {
+        uint32_t i = 0;
+        if (lane == 0) i = atomicAdd(&s_next, 1u);
+        i = __shfl_sync(0xffffffffu, i, 0);
+        const uint32_t round = i / Gb, j = i - round * Gb;
+        bool gone = false;
+        for (;;) { // wait for the round, or learn that it will never come
+            uint32_t p, t;
+            asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(p) : "r"(smem_addr(&s_produced)) : "memory");
+            if (p > round) break;
+            asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(t) : "r"(smem_addr(&s_total)) : "memory");
+            if (t <= round) {
+                gone = true;
+                break;
+            }
+        }
+        if (gone) break;
+        const uint32_t slot = round % kPolyRing;
+        const int cj = (int)ring_cnt(slot)[j];
+        if (cj != 0) {
             const size_t tj = traj0 + j;
             bool valid = false;
             if (lane < cj) {
-                const double t = s_t[j * kPolyPitch + lane];
-                const int sg = s_seg[j * kPolyPitch + lane];
+                const double t = ring_t(slot)[j * kPolyPitch + lane];
+                const int sg = ring_seg(slot)[j * kPolyPitch + lane];
                 const double *c = coeffs + ((tj * n_segments + sg) * 3) * (size_t)n_coeffs; // segment.cpp:51-58
-                const P3 p = {horner(c, n_coeffs, t), horner(c + n_coeffs, n_coeffs, t),
-                              horner(c + 2 * n_coeffs, n_coeffs, t)};
+                const P3 p = N10 ? P3{horner10(c, t), horner10(c + 10, t), horner10(c + 20, t)}
+                                 : P3{horner(c, n_coeffs, t), horner(c + n_coeffs, n_coeffs, t),
+                                      horner(c + 2 * n_coeffs, n_coeffs, t)};
                 valid = !world.invalid(wv, p, kModeMinDist, false, min_distance);
             }
             const uint32_t word = __ballot_sync(0xffffffffu, valid);
             if (lane == 0) {
-                if (sample_mask) sample_mask[tj * words_per_traj + chunk] = word;
+                if (sample_mask) sample_mask[tj * words_per_traj + round] = word;
                 const uint32_t active = cj >= 32 ? 0xffffffffu : ((1u << cj) - 1u);
                 const uint32_t bad = active & ~word;
-                if (bad) atomicMin(first_row + tj, (long long)(chunk * 32 + (size_t)(__ffs(bad) - 1)));
+                if (bad) atomicMin(first_row + tj, (long long)((size_t)round * 32 + (size_t)(__ffs(bad) - 1)));
             }
         }
         __syncwarp();
+        if (lane == 0) {
+            __threadfence_block();
+            atomicAdd(&s_done[slot], 1u);
+        }
     }
-    if (have && n_samples_out) n_samples_out[my] = emitted_total;
 }
 
 __global__ void k_fill_u32(uint32_t *p, size_t n, uint32_t v)
@@ -1407,6 +1759,49 @@ __global__ void k_mask_summary(const uint32_t *__restrict__ mask, size_t n_words
     if ((threadIdx.x & 31) == 0) {
         atomicAdd(out, pop);
         atomicXor(out + 1, x);
+    }
+}
+
+// ---- broad-phase statistics (bench.py: measured M_visited and k of SURVEY.md 8(d)'s ops-per-check formula) -----------
+
+// out[0] += broad-phase candidates visited, out[1] += candidates whose stored AABB passes the reference's exact test
+// (strict containment for points, closed box/box for segments: the R-tree hits of src/World.cpp:83,143).
+template <int BP>
+__global__ void __launch_bounds__(kBlock) k_count_candidates(WorldView wv, const double *__restrict__ pa,
+                                                             const double *__restrict__ pb, size_t n, int aabb_in_smem,
+                                                             unsigned long long *out)
+{
+    PointWorld<BP> pw;
+    RayWorld<BP> rw;
+    if (pb) rw.init(wv, aabb_in_smem != 0);
+    else pw.init(wv, aabb_in_smem != 0);
+    unsigned long long visited = 0, hits = 0;
+    for (size_t i = (size_t)blockIdx.x * kBlock + threadIdx.x; i < n; i += (size_t)gridDim.x * kBlock) {
+        const P3 a = {__ldg(pa + 3 * i), __ldg(pa + 3 * i + 1), __ldg(pa + 3 * i + 2)};
+        if (pb) {
+            const P3 b = {__ldg(pb + 3 * i), __ldg(pb + 3 * i + 1), __ldg(pb + 3 * i + 2)};
+            P3 mn, mx;
+            ray_box(a, b, mn, mx);
+            rw.any(wv, mn, mx, [&](int k) -> bool {
+                ++visited;
+                if (boxes_touch(wv.aabb + k, mn, mx)) ++hits;
+                return false;
+            });
+        } else {
+            pw.any(wv, a, [&](int k) -> bool {
+                ++visited;
+                if (within_strict(wv.aabb + k, a)) ++hits;
+                return false;
+            });
+        }
+    }
+    for (int o = 16; o; o >>= 1) {
+        visited += __shfl_xor_sync(0xffffffffu, visited, o);
+        hits += __shfl_xor_sync(0xffffffffu, hits, o);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        atomicAdd(out, visited);
+        atomicAdd(out + 1, hits);
     }
 }
 
@@ -1584,7 +1979,7 @@ cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, con
     cudaError_t err = cudaSuccess;
     // Warp-pipelined form: any alignment, any n; worth its prologue from a few thousand states up.
     if ((cfg.states_variant == 3 || (cfg.states_variant == 0 && n >= (size_t)cfg.states_warp_min_n))) {
-        const size_t table_bytes = (smem + 127) / 128 * 128;
+        const size_t table_bytes = ((bp == EPP_BP_GRID ? (size_t)wv.occ_bytes : smem) + 127) / 128 * 128;
         const int stages = 0; // ring depth comes from the shared-memory budget
         const int S = cfg.states_per_thread == 8 ? 8 : 4;
         const int rec_max = cfg.states_rec_smem_max > 0 ? (cfg.states_rec_smem_max < 992 ? cfg.states_rec_smem_max : 992) : kRecSmemMax;
@@ -1637,6 +2032,52 @@ cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, con
     return err;
 }
 
+template <int BP, bool RS>
+cudaError_t launch_segments_warp(const LaunchCfg &cfg, const WorldView &wv, const double *d_a, const double *d_b, size_t n,
+                                 int can_pass_gate, size_t table_bytes, bool in_smem, uint32_t *d_mask,
+                                 cudaStream_t stream, bool &launched)
+{
+    launched = false;
+    const size_t words = (n + 31) / 32;
+    if (words >= 0xfff00000ull) return cudaSuccess;
+    const size_t rec_bytes = RS ? ((size_t)wv.M * kRayRec * 8 + 127) / 128 * 128 : 0;
+    const size_t chunks_total = (words + kSegS - 1) / kSegS;
+    const size_t grid = chunks_total < (size_t)cfg.sm_count ? chunks_total : (size_t)cfg.sm_count;
+    const size_t chunks_per_block = (chunks_total + grid - 1) / grid;
+    int cons = (cfg.segments_warp_threads > 0 ? cfg.segments_warp_threads / 32 : kMaxWarps) - 1;
+    cons = cons < 1 ? 1 : (cons > kMaxWarps - 1 ? kMaxWarps - 1 : cons);
+    if ((size_t)cons > chunks_per_block) cons = (int)chunks_per_block;
+    const size_t budget = (size_t)(228 * 1024) - 1024 - 4096;
+    const size_t fixed = table_bytes + rec_bytes + (size_t)cons * (kSegS * 32 + 32);
+    if (fixed + 2 * (size_t)kSegSlotBytes > budget) return cudaSuccess;
+    size_t slots = (budget - fixed) / kSegSlotBytes;
+    if (slots > chunks_per_block) slots = chunks_per_block < 2 ? 2 : chunks_per_block;
+    if (cfg.segments_warp_slots > 0 && (size_t)cfg.segments_warp_slots < slots) slots = cfg.segments_warp_slots;
+    // a slot must always be armed by the same producer lane: <= 32 slots, or a multiple of 32
+    slots = slots >= (size_t)kSegMaxSlots ? (size_t)kSegMaxSlots : (slots > 32 ? 32 : slots);
+    if (slots < 2) slots = 2;
+    if ((size_t)cons > slots) cons = (int)slots; // in-order hand-out needs slots >= consumers (see k_states_warp)
+    const size_t smem = fixed + slots * kSegSlotBytes;
+    cudaError_t err = cudaFuncSetAttribute(k_segments_warp<BP, RS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (err != cudaSuccess) return err;
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3((unsigned)grid);
+    lc.blockDim = dim3((unsigned)(cons + 1) * 32);
+    lc.dynamicSmemBytes = smem;
+    lc.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = attr;
+    lc.numAttrs = cfg.states_pdl ? 1 : 0;
+    err = cudaLaunchKernelEx(&lc, k_segments_warp<BP, RS>, wv, d_a, d_b, n, can_pass_gate, in_smem ? 1 : 0, (uint32_t)slots,
+                             (uint32_t)table_bytes, (uint32_t)rec_bytes, (uint32_t)(words / grid), (uint32_t)(words % grid),
+                             d_mask);
+    if (err != cudaSuccess) return err;
+    launched = true;
+    return cudaGetLastError();
+}
+
 cudaError_t launch_segments(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_a, const double *d_b,
                             size_t n, int can_pass_gate, uint32_t *d_mask, cudaStream_t stream, const GatherView *gv)
 {
@@ -1645,6 +2086,24 @@ cudaError_t launch_segments(const LaunchCfg &cfg, const WorldView &wv, int bp, c
     const size_t smem = ray_smem_bytes(wv, bp, in_smem);
     cudaError_t err = cudaSuccess;
     const size_t tiles = (n + kBlock - 1) / kBlock;
+    if (cfg.segments_variant == 2 || (cfg.segments_variant == 0 && n >= (size_t)cfg.segments_warp_min_n)) {
+        // warp-pipelined form: end points through the cp.async.bulk ring
+        const bool rs = wv.zrot && wv.M <= kRayRecMax && bp != EPP_BP_GRID;
+        bool in_smem_w = in_smem && !rs;
+        size_t table_bytes = bp == EPP_BP_GRID ? (size_t)wv.occ_bytes : ((rs && bp == EPP_BP_BRUTE) ? 0 : smem);
+        table_bytes = (table_bytes + 127) / 128 * 128;
+        bool launched = false;
+        EPP_DISPATCH_BP(bp, {
+            if (rs) err = launch_segments_warp<BP, true>(cfg, wv, d_a, d_b, n, can_pass_gate, table_bytes, in_smem_w, d_mask, stream, launched);
+            else err = launch_segments_warp<BP, false>(cfg, wv, d_a, d_b, n, can_pass_gate, table_bytes, in_smem_w, d_mask, stream, launched);
+        });
+        if (err != cudaSuccess) return err;
+        if (launched) {
+            g_launches++;
+            if (gv) err = launch_gather_push(cfg, *gv, stream);
+            return err;
+        }
+    }
     if (cfg.segments_variant != 1 && wv.zrot && wv.M <= kRayRecMax) {
         // records in shared memory (the broad-phase table of the brute form is the records themselves)
         const size_t table_bytes = bp == EPP_BP_BRUTE ? 0 : (smem + 127) / 128 * 128;
@@ -1707,7 +2166,7 @@ cudaError_t launch_trajectories(const LaunchCfg &cfg, const WorldView &wv, int b
         // warp-pipelined form (k_states_warp in its trajectory mode): columns 0, 3, 6 arrive by cp.async.bulk
         bool in_smem;
         const size_t smem = point_smem_bytes(wv, bp, in_smem);
-        const size_t table_bytes = (smem + 127) / 128 * 128;
+        const size_t table_bytes = ((bp == EPP_BP_GRID ? (size_t)wv.occ_bytes : smem) + 127) / 128 * 128;
         const int rec_max = cfg.states_rec_smem_max > 0 ? (cfg.states_rec_smem_max < 992 ? cfg.states_rec_smem_max : 992) : kRecSmemMax;
         bool rs = wv.M <= rec_max && wv.zrot && cfg.states_rec_smem != 0;
         const int wbp = (bp == EPP_BP_BITS && wv.W == 1 && cfg.states_bits1 != 0) ? kBpBits1 : bp;
@@ -1780,24 +2239,26 @@ cudaError_t launch_poly_trajectories(const LaunchCfg &cfg, const WorldView &wv, 
     }
     bool in_smem;
     const size_t smem = point_smem_bytes(wv, bp, in_smem);
-    // trajectories per warp: 32 for big batches, fewer while the batch would leave SMs without warps
+    // trajectories per block (= lanes of its producer warp that work): 32 for big batches, fewer while the batch would
+    // leave SMs without blocks (the sampler is latency-bound, so idle producer lanes cost nothing but their warp)
     int G = cfg.poly_traj_per_warp;
     if (G <= 0) {
         G = 32;
-        while (G > 1 && n_traj / (size_t)G < (size_t)cfg.sm_count * 24) G >>= 1;
+        while (G > 4 && n_traj / (size_t)G < (size_t)cfg.sm_count * 6) G >>= 1;
     }
-    G = G > 32 ? 32 : G;
-    const size_t per_block = (size_t)kPolyWarps * (size_t)G;
-    const unsigned grid = (unsigned)((n_traj + per_block - 1) / per_block);
+    G = G > 32 ? 32 : (G < 1 ? 1 : G);
+    const unsigned grid = (unsigned)((n_traj + G - 1) / G);
     const size_t table_bytes = (smem + 127) / 128 * 128;
-    const size_t total = table_bytes + (size_t)kPolyWarps * G * kPolyPitch * (8 + 2);
+    const size_t total = table_bytes + (size_t)kPolyRing * ((size_t)G * kPolyPitch * 10 + (size_t)G * 4);
+    // 16-byte coefficient loads need a 16 B-aligned batch (a segment's 3 x 10 coefficients are 240 B)
+    const bool n10 = n_coeffs == 10 && (reinterpret_cast<uintptr_t>(d_coeffs) & 15u) == 0;
     EPP_DISPATCH_BP(bp, {
-        err = ensure_smem(k_poly_traj<BP>, total);
+        auto kern = n10 ? k_poly_traj<BP, true> : k_poly_traj<BP, false>;
+        err = ensure_smem(kern, total);
         if (err == cudaSuccess) {
-            k_poly_traj<BP><<<grid, kPolyWarps * 32, total, stream>>>(wv, d_coeffs, d_durations, d_dt, n_traj, n_segments,
-                                                                      n_coeffs, min_distance, max_samples, in_smem ? 1 : 0, G,
-                                                                      (uint32_t)table_bytes, d_sample_mask, d_n_samples,
-                                                                      d_first_scratch);
+            kern<<<grid, kPolyThreads, total, stream>>>(wv, d_coeffs, d_durations, d_dt, n_traj, n_segments, n_coeffs,
+                                                        min_distance, max_samples, in_smem ? 1 : 0, G, (uint32_t)table_bytes,
+                                                        d_sample_mask, d_n_samples, d_first_scratch);
             err = cudaGetLastError();
         }
     });
@@ -1807,6 +2268,25 @@ cudaError_t launch_poly_trajectories(const LaunchCfg &cfg, const WorldView &wv, 
                                                                          d_traj_valid);
     g_launches++;
     return cudaGetLastError();
+}
+
+cudaError_t launch_count_candidates(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_a, const double *d_b,
+                                    size_t n, uint64_t *d_out, cudaStream_t stream)
+{
+    cudaError_t err = cudaMemsetAsync(d_out, 0, 2 * sizeof(uint64_t), stream);
+    if (err != cudaSuccess || n == 0) return err;
+    bool in_smem;
+    const size_t smem = d_b ? ray_smem_bytes(wv, bp, in_smem) : point_smem_bytes(wv, bp, in_smem);
+    const unsigned grid = persistent_grid(cfg, (n + kBlock - 1) / kBlock, 4);
+    EPP_DISPATCH_BP(bp, {
+        err = ensure_smem(k_count_candidates<BP>, smem);
+        if (err == cudaSuccess) {
+            k_count_candidates<BP><<<grid, kBlock, smem, stream>>>(wv, d_a, d_b, n, in_smem ? 1 : 0, (unsigned long long *)d_out);
+            err = cudaGetLastError();
+        }
+    });
+    g_launches++;
+    return err;
 }
 
 cudaError_t launch_gen_states(uint64_t seed, uint64_t first, size_t n, const double lo[3], const double hi[3],

@@ -14,7 +14,10 @@ struct LaunchCfg {
     int sm_count = 148;
     int states_blocks_per_sm = 8;   // 0: one block per tile (non-persistent)
     int segments_blocks_per_sm = 4; // 0: one block per tile
-    int segments_variant = 0;       // 0: auto (records in shared memory for worlds of <= 256 z-rotated OBBs), 1: records in global memory
+    int segments_variant = 0;       // 0: auto (warp-pipelined from segments_warp_min_n segments up, else direct), 1: direct with records in global memory, 2: warp-pipelined, 3: direct forms only
+    int segments_warp_min_n = 32768;
+    int segments_warp_threads = 1024;
+    int segments_warp_slots = 0;    // cap on the ring slots per block (0: as many as fit, <= 64)
     int states_variant = 0;         // 0: auto (warp-pipelined from states_warp_min_n states up), 1: direct, 3: warp-pipelined
     int states_warp_blocks_per_sm = 1;
     int states_warp_threads = 1024; // block size of the warp-pipelined form
@@ -87,6 +90,10 @@ cudaError_t launch_gen_states(uint64_t seed, uint64_t first, size_t n, const dou
                               double *d_xyz, cudaStream_t stream);
 cudaError_t launch_gen_segments(uint64_t seed, uint64_t first, size_t n, const double lo[3], const double hi[3],
                                 double max_len, double *d_a, double *d_b, cudaStream_t stream);
+// d_out[0] = broad-phase candidates visited over the batch, d_out[1] = those passing the exact stored-AABB test
+// (d_b == nullptr: points, else segments).
+cudaError_t launch_count_candidates(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_a, const double *d_b,
+                                    size_t n, uint64_t *d_out, cudaStream_t stream);
 cudaError_t launch_mask_summary(const LaunchCfg &cfg, const uint32_t *d_mask, size_t n_words, uint64_t first_word,
                                 uint64_t *d_out, cudaStream_t stream);
 

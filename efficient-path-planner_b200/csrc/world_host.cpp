@@ -365,7 +365,7 @@ void build_bits(const std::vector<AabbRec> &aabbs, int bins_per_axis, BitsTables
 }
 
 void build_grid(const std::vector<AabbRec> &aabbs, std::vector<ObbRec> &obbs, long max_cells,
-                GridTables &out)
+                GridTables &out, long occ_budget_bytes)
 {
     const size_t M = aabbs.size();
     double lo[3], hi[3];
@@ -424,6 +424,37 @@ void build_grid(const std::vector<AabbRec> &aabbs, std::vector<ObbRec> &obbs, lo
             for (int y = b0[3 * k + 1]; y <= b1[3 * k + 1]; ++y)
                 for (int x = b0[3 * k]; x <= b1[3 * k]; ++x)
                     out.cell_items[cursor[cell_id(x, y, z)]++] = static_cast<uint32_t>(k);
+
+    // Occupancy bitmap over coarsened cells: fold z first (worlds of this planner are flat: 400 x 400 x 4 m), then
+    // x and y together, until the map fits its shared-memory budget.
+    for (int a = 0; a < 3; ++a) {
+        out.occ_shift[a] = 0;
+        out.occ_n[a] = n[a];
+    }
+    auto occ_bits = [&]() { return static_cast<double>(out.occ_n[0]) * out.occ_n[1] * out.occ_n[2]; };
+    auto coarsen = [&](int a) {
+        ++out.occ_shift[a];
+        out.occ_n[a] = ((n[a] - 1) >> out.occ_shift[a]) + 1;
+    };
+    const double budget_bits = 8.0 * static_cast<double>(std::max(16l, occ_budget_bytes));
+    while (occ_bits() > budget_bits) {
+        if (out.occ_n[2] > 2) coarsen(2);
+        else if (out.occ_n[0] > 1 || out.occ_n[1] > 1) {
+            coarsen(0);
+            coarsen(1);
+        } else coarsen(2);
+    }
+    const size_t bits = static_cast<size_t>(occ_bits());
+    out.occ.assign((bits + 31) / 32 + 4, 0u); // + slack: range queries read one word past the last bit
+    for (int z = 0; z < n[2]; ++z)
+        for (int y = 0; y < n[1]; ++y)
+            for (int x = 0; x < n[0]; ++x) {
+                const size_t c = cell_id(x, y, z);
+                if (out.cell_start[c + 1] == out.cell_start[c]) continue;
+                const size_t b = (static_cast<size_t>(z >> out.occ_shift[2]) * out.occ_n[1] + (y >> out.occ_shift[1])) *
+                                     out.occ_n[0] + (x >> out.occ_shift[0]);
+                out.occ[b >> 5] |= 1u << (b & 31);
+            }
 }
 
 } // namespace epp

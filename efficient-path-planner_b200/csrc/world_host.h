@@ -77,6 +77,12 @@ struct GridTables {
     AxisBins bins{};
     std::vector<uint32_t> cell_start; // ncell + 1
     std::vector<uint32_t> cell_items;
+    // Occupancy bitmap: one bit per COARSE cell (fine cell index >> occ_shift per axis), set iff any fine cell
+    // under it has an item.  Sized to live in shared memory (occ_budget_bytes): a unit whose coarse cells are
+    // all clear has no candidate and never touches cell_start / cell_items.
+    std::vector<uint32_t> occ;
+    int occ_shift[3] = {0, 0, 0};
+    int occ_n[3] = {1, 1, 1}; // coarse cells per axis; bit index = (z * occ_n[1] + y) * occ_n[0] + x
 };
 
 // ---- host world ------------------------------------------------------------------------
@@ -136,7 +142,7 @@ void obb_aabb(const HostObb &o, double inflate, double mn[3], double mx[3]);
 // Broad-phase construction over flattened records.
 void build_bits(const std::vector<AabbRec> &aabbs, int bins_per_axis, BitsTables &out);
 void build_grid(const std::vector<AabbRec> &aabbs, std::vector<ObbRec> &obbs, long max_cells,
-                GridTables &out);
+                GridTables &out, long occ_budget_bytes = 72 * 1024);
 
 const char *status_message(int status);
 

@@ -167,3 +167,38 @@ def traj_matrix_from_positions(xyz, times):
     m = np.zeros((n, 10))
     m[:, 0], m[:, 3], m[:, 6], m[:, 9] = xyz[:, 0], xyz[:, 1], xyz[:, 2], times
     return m
+
+
+def adversarial_states(obbs, n, seed=0x5EED0A2):
+    """n states on, and 1-2 ulp either side of, the faces of the stored AABBs and of the (inflated) OBBs of a world
+    (where a rounding difference between two implementations of the predicates would show).
+
+    obbs: records as returned by World.obbs() (center, half, rot row-major, aabb_min, aabb_max, inflate, filling).
+    State i cycles over (OBB, AABB face | OBB face, axis, side, ulp offset in -2..2); its position on the face comes
+    from the counter-based generator, so the batch is reproducible bit for bit."""
+    M = len(obbs)
+    mn = np.array([o["aabb_min"] for o in obbs], dtype=np.float64)
+    mx = np.array([o["aabb_max"] for o in obbs], dtype=np.float64)
+    c = np.array([o["center"] for o in obbs], dtype=np.float64)
+    R = np.array([o["rot"] for o in obbs], dtype=np.float64).reshape(M, 3, 3)
+    H = np.array([np.asarray(o["half"], float) + (0.0 if o["filling"] else o["inflate"]) for o in obbs])
+    i = np.arange(n, dtype=np.uint64)
+    k = (i % np.uint64(M)).astype(np.int64)
+    j = (i // np.uint64(M)).astype(np.int64)
+    kind, axis, side, ulp = j % 2, (j // 2) % 3, (j // 6) % 2, (j // 12) % 5 - 2
+    u = np.stack([u01(seed, i, d) for d in range(3)], axis=1)
+    rows = np.arange(n)
+    # stored-AABB faces
+    p_box = mn[k] + u * (mx[k] - mn[k])
+    p_box[rows, axis] = np.where(side == 0, mn[k, axis], mx[k, axis])
+    # OBB faces: local point on the face, rotated into the world
+    loc = (2.0 * u - 1.0) * H[k]
+    loc[rows, axis] = np.where(side == 0, -1.0, 1.0) * H[k, axis]
+    p_obb = np.einsum("nij,nj->ni", R[k], loc) + c[k]
+    p = np.where((kind == 0)[:, None], p_box, p_obb)
+    v = p[rows, axis]
+    for step in (1, 2):
+        v = np.where(ulp >= step, np.nextafter(v, np.inf), v)
+        v = np.where(ulp <= -step, np.nextafter(v, -np.inf), v)
+    p[rows, axis] = v
+    return np.ascontiguousarray(p)

@@ -258,6 +258,17 @@ int epp_gen_segments_dev(uint64_t seed, uint64_t first, size_t n, const double l
 
 /* Number of kernels this library has launched on the calling process so far. */
 uint64_t epp_kernel_launch_count(void);
+/* Broad-phase statistics of a device batch against the committed world (d_b NULL: points, else segments):
+ * d_visited_hits[0] = candidates the active broad phase visits, [1] = those whose stored AABB passes the
+ * reference's exact R-tree predicate (src/World.cpp:83 strict containment / :143 closed intersection).  Feeds the
+ * FP64 ops-per-check figure of the roofline (6 * M_visited + 21 * k). */
+int epp_count_candidates_dev(epp_world *w, const double *d_a, const double *d_b /* nullable */, size_t n,
+                             uint64_t *d_visited_hits, void *stream);
+/* Non-fused FP64 issue rate of the current device (thread-level DADD + DMUL instructions per second; 8
+ * independent chains per thread, full occupancy, no DFMA in the SASS): the compute roof of this path, whose
+ * reference arithmetic (src/OBB.cpp:10-91, polynomial.h:136-150) is individually rounded.  Best of `reps`
+ * launches of `iters` loop iterations, timed with CUDA events on `stream`. */
+int epp_measure_fp64_nofma(int iters, int reps, void *stream, double *instr_per_s, double *ms_per_launch);
 /* Tuning knobs (DESIGN.md "Tuning"); unknown keys return EPP_ERR_INVALID_ARG. */
 int epp_set_tuning(const char *key, int value);
 int epp_get_tuning(const char *key, int *value);

@@ -308,6 +308,38 @@ def test_polynomial_sweep_ragged(oracle, config, track):
             assert bool(valid[t >> 5] >> (t & 31) & 1) is ok
 
 
+@pytest.mark.parametrize("G", [0, 1, 4, 32])
+def test_polynomial_sweep_truncation_and_block_shapes(oracle, config, track, G):
+    """A trajectory with more rows than max_samples must not pass as valid on its unchecked tail: it is reported
+    invalid with first row = max_samples unless an earlier row already is; n_samples = rows emitted; the rows that were
+    checked equal the oracle's.  Default max_samples (derived from the durations) checks every row.  All block shapes
+    of the producer / consumer kernel (G trajectories per block) give the same answers."""
+    g, o, lo, hi = track
+    ow, gw = build_pair(oracle, epp_b200, config, g, o)
+    n_traj = 70
+    coeffs, T, dt = worlds.rest_to_rest_trajectories(n_traj, 4, lo, hi, seed=4141, n_samples=300)
+    dt = dt * (1.0 + 0.9 * (np.arange(n_traj) % 7 == 0))  # every 7th trajectory has ~160 rows, the others ~300
+    epp_b200.set_tuning("poly_traj_per_warp", G)
+    try:
+        valid, smask, cnt, first = gw.check_poly_trajectories(coeffs, T, dt, 0.15, max_samples=192)
+        full = gw.check_poly_trajectories(coeffs, T, dt, 0.15)
+    finally:
+        epp_b200.set_tuning("poly_traj_per_warp", 0)
+    truncated = 0
+    for t in range(n_traj):
+        ok, m, n, f = ow.check_poly_traj(coeffs[t], T[t], dt[t], 0.15, max_samples=1024)
+        assert full[2][t] == n and np.array_equal(full[1][t], m[: full[1].shape[1]]) and full[3][t] == f
+        assert bool(full[0][t >> 5] >> (t & 31) & 1) is ok
+        got_ok = bool(valid[t >> 5] >> (t & 31) & 1)
+        if n <= 192:
+            assert cnt[t] == n and np.array_equal(smask[t], m[:6]) and first[t] == f and got_ok is ok
+        else:
+            truncated += 1
+            assert cnt[t] == 192 and np.array_equal(smask[t], m[:6]) and not got_ok
+            assert first[t] == (f if 0 <= f < 192 else 192)
+    assert 0 < truncated < n_traj
+
+
 def test_device_buffers_and_generators(oracle, config, track):
     """_dev entry points on torch buffers + on-device generators bit-identical to the host twins."""
     import torch
@@ -376,7 +408,7 @@ def test_config5_cluttered_subsample(oracle, config):
     got = gw.check_segments_dev(d_a, d_b).cpu().numpy().view(np.uint32)
     h_a, h_b = oracle.gen_segments(worlds.SEED_CLUTTER, first, ne, lo, hi, 1.0)
     assert mismatches(got, ow.check_segments(h_a, h_b, threads=8)) == 0
-    # grid vs bits vs brute on the same world (bits allowed up to 4096 OBBs only -> brute here)
+    # grid vs bits vs brute on the same world (bits allowed up to 1024 OBBs only -> brute here)
     gb = epp_b200.World(config, broadphase=epp_b200.BP_BRUTE)
     gb.parse_gates_and_obstacles(g, o)
     gb.set_broadphase(epp_b200.BP_BRUTE)
@@ -604,10 +636,12 @@ def test_gather_segments_and_mindist_logical_ranks(oracle, config):
     # The two ranks' ranges differ in size and may take different block sizes of K2.  CUDA loads a kernel lazily at
     # its first launch and that load waits for running kernels — here the other logical rank's push kernel, which is
     # waiting for this one (only an issue with several ranks inside ONE process): launch every form once beforehand.
-    for block in (256, 512, 1024):
+    for variant, block in ((3, 256), (3, 512), (3, 1024), (2, 0)):
+        epp_b200.set_tuning("segments_variant", variant)
         epp_b200.set_tuning("segments_block", block)
         gw.check_segments_dev(d_a[:4096], d_b[:4096])
     epp_b200.set_tuning("segments_block", 0)
+    epp_b200.set_tuning("segments_variant", 0)
     torch.cuda.synchronize()
     _run_logical_ranks(gathers, seg)
     _run_logical_ranks(gathers, md)
@@ -660,8 +694,9 @@ def test_gather_argument_errors(config, track):
 
 @pytest.mark.parametrize("bp", BPS, ids=BP_IDS)
 def test_segments_smem_record_form_equals_global_record_form(oracle, config, bp):
-    """K2's two forms (records folded into shared memory / records in global memory) and the oracle agree,
-    incl. canPassGate with filling boxes, ragged tails and zero-length segments."""
+    """K2's forms (warp-pipelined with the end points through the cp.async.bulk ring; direct with records folded into
+    shared memory; direct with records in global memory) and the oracle agree, incl. canPassGate with filling boxes,
+    ragged tails, zero-length segments, batches smaller than one chunk and 8 B-aligned batches (loaded by the lanes)."""
     import torch
     g, o, lo, hi = worlds.world_256()
     cfgf = filling_config(config)
@@ -677,11 +712,17 @@ def test_segments_smem_record_form_equals_global_record_form(oracle, config, bp)
         for cpg in (False, True):
             want = ow.check_segments(a, b, cpg, threads=8)
             got = {}
-            for variant, block in ((0, 0), (0, 256), (0, 512), (0, 1024), (1, 0)):   # block: threads per block of the
-                epp_b200.set_tuning("segments_variant", variant)                    # shared-memory form, 0 = by batch size
+            # variant 0 auto, 1 direct + global records, 2 warp-pipelined, 3 direct forms only; block = threads per
+            # block of the direct shared-memory form (0 = by batch size)
+            for variant, block in ((0, 0), (2, 0), (3, 0), (3, 256), (3, 512), (3, 1024), (1, 0)):
+                epp_b200.set_tuning("segments_variant", variant)
                 epp_b200.set_tuning("segments_block", block)
                 try:
                     got[variant, block] = gw.check_segments_dev(d_a, d_b, can_pass_gate=cpg).cpu().numpy().view(np.uint32)
+                    if variant == 2 and n > 64:  # 8 B-aligned end points: the consumers load the chunk themselves
+                        sub = gw.check_segments_dev(d_a.view(-1)[3:].view(-1, 3), d_b.view(-1)[3:].view(-1, 3),
+                                                    can_pass_gate=cpg).cpu().numpy().view(np.uint32)
+                        assert mismatches(sub, ow.check_segments(a[1:], b[1:], cpg, threads=8)) == 0, (n, cpg, "unaligned")
                 finally:
                     epp_b200.set_tuning("segments_variant", 0)
                     epp_b200.set_tuning("segments_block", 0)
@@ -700,3 +741,43 @@ def test_states_warp_form_record_fold_small_batches(oracle, config, bp):
         for cpg in (False, True):
             assert mismatches(gw.check_states(xyz, cpg), ow.check_states(xyz, cpg, threads=8)) == 0, (n, cpg)
         assert mismatches(gw.check_states_mindist(xyz, 0.15), ow.check_states_mindist(xyz, 0.15, threads=8)) == 0, n
+
+
+def test_bits_rows_of_32_words_and_rejection_above(oracle, config):
+    """The bits broad phase summarises a row in ONE 32-bit word, so it holds worlds of up to 1024 OBBs (32-word rows).
+    At 1000 OBBs (summary bit 31 in use) points and segments must equal brute force and the oracle; above 1024 OBBs a
+    request for bits is refused at commit (it used to alias word w >= 32 onto w mod 32 and miss OBBs >= 1024)."""
+    import torch
+    g, o, lo, hi = worlds.lattice_world(160, 200, 60.0, 0x5EED0B17)
+    ow, gw = build_pair(oracle, epp_b200, config, g, o, epp_b200.BP_BITS)
+    assert gw.size() == 1000
+    n = 1 << 16
+    xyz = np.concatenate([worlds.gen_states(21, 0, n, lo, hi), adversarial_points(ow.obbs()[900:], np.random.default_rng(6), 2)])
+    assert mismatches(gw.check_states(xyz, False), ow.check_states(xyz, False, threads=8)) == 0
+    assert gw.active_broadphase() == epp_b200.BP_BITS
+    assert mismatches(gw.check_states_mindist(xyz, 0.1), ow.check_states_mindist(xyz, 0.1, threads=8)) == 0
+    a, b = worlds.gen_segments(22, 0, n, lo, hi, 1.0)
+    aa, ab = adversarial_segments(ow.obbs()[960:], np.random.default_rng(7), lo, hi, per_obb=4)
+    a, b = np.concatenate([a, aa]), np.concatenate([b, ab])
+    assert mismatches(gw.check_segments(a, b, False), ow.check_segments(a, b, False, threads=8)) == 0
+    d = torch.from_numpy(xyz[:n]).cuda()
+    gb = epp_b200.World(config, broadphase=epp_b200.BP_BRUTE)
+    gb.parse_gates_and_obstacles(g, o)
+    gb.set_broadphase(epp_b200.BP_BRUTE)
+    assert torch.equal(gb.check_states_dev(d), gw.check_states_dev(d))
+    # 2000 OBBs: bits refused, auto falls to the grid even when the knob asks for more
+    g2, o2, lo2, hi2 = worlds.lattice_world(320, 400, 80.0, 0x5EED0B18)
+    big = epp_b200.World(config, broadphase=epp_b200.BP_BITS)
+    with pytest.raises(epp_b200.EppError, match="1024"):
+        big.parse_gates_and_obstacles(g2, o2)
+    epp_b200.set_tuning("bits_max_obbs", 4096)
+    try:
+        auto = epp_b200.World(config)
+        auto.parse_gates_and_obstacles(g2, o2)
+        assert auto.size() == 2000 and auto.active_broadphase() == epp_b200.BP_GRID
+        ow2 = oracle.OracleWorld(config)
+        ow2.parse_gates_and_obstacles(g2, o2)
+        xyz2 = worlds.gen_states(23, 0, 1 << 15, lo2, hi2)
+        assert mismatches(auto.check_states(xyz2, False), ow2.check_states(xyz2, False, threads=8)) == 0
+    finally:
+        epp_b200.set_tuning("bits_max_obbs", 1024)
