@@ -921,7 +921,13 @@ def extras_single_gpu(torch, epp_b200, dev):
     t0 = time.perf_counter()
     for i in range(500):
         w3.checkPointValidity([0.1 * (i % 50), 0.0, 1.0], False)
-    out["single_is_valid_latency_us"] = (time.perf_counter() - t0) / 500 * 1e6
+    out["single_is_valid_python_call_us"] = (time.perf_counter() - t0) / 500 * 1e6   # incl. the ctypes binding
+    out["single_is_valid_latency_us"] = w3.single_latency_us(5000)                    # inside the C ABI
+    epp_b200.set_tuning("single_mailbox", 0)
+    try:
+        out["single_is_valid_launch_sync_latency_us"] = w3.single_latency_us(500)       # round-1 form: launch + sync
+    finally:
+        epp_b200.set_tuning("single_mailbox", 1)
     return out
 
 

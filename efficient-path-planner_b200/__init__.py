@@ -87,6 +87,7 @@ SIGNATURES = {
                                   C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
     "epp_mask_summary_dev": (C.c_int, [_vp, C.c_size_t, C.c_uint64, _vp, _vp]),
     "epp_measure_fp64_nofma": (C.c_int, [C.c_int, C.c_int, _vp, _dp, _dp]),
+    "epp_measure_single_latency": (C.c_int, [_vp, C.c_int, _dp]),
     "epp_count_candidates_dev": (C.c_int, [_vp, _vp, _vp, C.c_size_t, _vp, _vp]),
     "epp_gen_states_dev": (C.c_int, [C.c_uint64, C.c_uint64, C.c_size_t, _dp, _dp, _vp, _vp]),
     "epp_gen_segments_dev": (C.c_int, [C.c_uint64, C.c_uint64, C.c_size_t, _dp, _dp, C.c_double,
@@ -429,6 +430,13 @@ class World:
         _chk(lib().epp_check_segments_dev(self._h, a.data_ptr(), b.data_ptr(), n, int(can_pass_gate),
                                           mask.data_ptr(), self._stream()))
         return mask
+
+    def single_latency_us(self, n_calls=2000):
+        """Microseconds per epp_is_valid call, timed inside the library (no ctypes overhead)."""
+        self._sync()
+        us = C.c_double(0.0)
+        _chk(lib().epp_measure_single_latency(self._h, int(n_calls), C.byref(us)))
+        return us.value
 
     def count_candidates_dev(self, a, b=None):
         """(mean broad-phase candidates visited, mean candidates passing the exact stored-AABB test) per unit of a

@@ -5,6 +5,7 @@
 
 #include <algorithm>
 #include <atomic>
+#include <chrono>
 #include <cmath>
 #include <cstring>
 #include <memory>
@@ -74,7 +75,10 @@ Knob g_knobs[] = {
     {"sm_limit", {0}},                   // 0: all SMs; > 0: size grids for this many SMs (several ranks on one GPU in tests)
     {"bits_bins", {0}},                  // 0: by world size
     {"grid_max_cells", {1 << 22}},
-    {"grid_occ_kb", {72}},               // shared-memory budget of the grid's occupancy bitmap
+    {"grid_occ_kb", {72}},
+    {"states_table_copies", {1}},        // worlds of <= 32 OBBs: copies of the bin table in separate bank groups (1, 2, 4, 8, 16); read at commit
+    {"single_mailbox", {1}},             // epp_is_valid / epp_check_motion through the resident mailbox warp (0: launch + sync per call)
+    {"single_mailbox_idle_us", {1000}},  // the mailbox warp leaves after this long without a request               // shared-memory budget of the grid's occupancy bitmap
     {"bits_max_obbs", {1024}},
 };
 
@@ -125,6 +129,17 @@ namespace {
 
 // Per-thread, per-device staging: a stream, pinned host memory and device scratch.  Gives
 // the re-entrancy the reference's concurrent planner threads need without a global lock.
+// Host side of the single-unit mailbox (k_mailbox): one per host thread and device, serving one world epoch at a time.
+struct Mailbox {
+    MailboxSlot *slot = nullptr;          // mapped pinned memory (host pointer == device pointer under UVA)
+    cudaStream_t stream = nullptr;        // the resident warp's own stream
+    std::shared_ptr<DeviceEpoch> epoch;   // keeps the blob the warp reads alive
+    uint32_t seq = 0;
+    bool launched = false;                // a warp was launched and has not been seen to exit
+    void quit();                          // ask the resident warp to leave and wait until it has
+    ~Mailbox();
+};
+
 struct Staging {
     int device = -1;
     cudaStream_t stream = nullptr;
@@ -132,9 +147,11 @@ struct Staging {
     size_t h_cap = 0;
     unsigned char *d = nullptr;
     size_t d_cap = 0;
+    Mailbox mb;
     ~Staging()
     {
         if (device < 0) return;
+        mb.quit();
         // Thread exit may happen after the primary context is gone; ignore errors.
         if (stream) cudaStreamDestroy(stream);
         if (h) cudaFreeHost(h);
@@ -236,7 +253,9 @@ int snapshot(epp_world *w, std::shared_ptr<DeviceEpoch> &ep)
 {
     if (!w) return fail(EPP_ERR_INVALID_ARG, "null world");
     std::lock_guard<std::mutex> lk(w->mu);
-    if (!w->current || w->dirty) return fail(EPP_ERR_NOT_COMMITTED);
+    // Mutations that have not been committed yet are invisible: a check sees the world as of the last commit (another
+    // thread may be between its update and its commit, src/OnlineTrajGenerator.cpp:146 vs :324-340).
+    if (!w->current) return fail(EPP_ERR_NOT_COMMITTED);
     ep = w->current;
     return EPP_OK;
 }
@@ -343,7 +362,107 @@ int check_host(epp_world *w, const double *a, const double *b, size_t n, int kin
     return EPP_OK;
 }
 
-// One unit through mapped pinned memory: a single launch + synchronise, no copies.
+// ---- single units ------------------------------------------------------------------------------------------------
+
+using Clock = std::chrono::steady_clock;
+
+bool mailbox_exited(const MailboxSlot *slot) { return slot->state == kMailboxExited; }
+
+void Mailbox::quit()
+{
+    if (!slot) return;
+    // At thread / process exit the CUDA context may already be gone: then neither the slot nor the stream may be touched.
+    const cudaError_t q = stream ? cudaStreamQuery(stream) : cudaSuccess;
+    if (q != cudaSuccess && q != cudaErrorNotReady) {
+        cudaGetLastError();
+        slot = nullptr;
+        stream = nullptr;
+        launched = false;
+        epoch.reset();
+        return;
+    }
+    if (launched && q == cudaErrorNotReady && !mailbox_exited(slot)) {
+        ++seq;
+        slot->req[0] = (uint64_t)seq | ((uint64_t)kMailboxQuit << 32);
+        std::atomic_thread_fence(std::memory_order_release);
+        slot->req[7] = (uint64_t)seq;
+        std::atomic_thread_fence(std::memory_order_seq_cst);
+        const auto t0 = Clock::now();
+        while (!mailbox_exited(slot) && Clock::now() - t0 < std::chrono::milliseconds(200)) {
+        }
+        if (stream) cudaStreamSynchronize(stream);
+    }
+    launched = false;
+    epoch.reset();
+}
+
+Mailbox::~Mailbox()
+{
+    quit();
+    if (stream) cudaStreamDestroy(stream);
+    if (slot) cudaFreeHost(slot);
+}
+
+// One unit through the resident mailbox warp: no launch and no stream synchronisation per call.
+int check_single_mailbox(Staging *s, const std::shared_ptr<DeviceEpoch> &ep, const double *a, const double *b,
+                         int can_pass_gate, int *valid)
+{
+    Mailbox &mb = s->mb;
+    if (!mb.slot) {
+        EPP_CUDA(cudaHostAlloc((void **)&mb.slot, sizeof(MailboxSlot), cudaHostAllocMapped));
+        std::memset((void *)mb.slot, 0, sizeof(MailboxSlot));
+        EPP_CUDA(cudaStreamCreateWithFlags(&mb.stream, cudaStreamNonBlocking));
+    }
+    if (mb.epoch != ep) { // the world was re-committed (or this is the first call): retire the warp of the old epoch
+        mb.quit();
+        mb.epoch = ep;
+    }
+    MailboxSlot *slot = mb.slot;
+    const uint32_t seq = ++mb.seq;
+    const uint32_t flags = (b ? kMailboxSegment : 0u) | (can_pass_gate ? kMailboxCanPassGate : 0u);
+    uint64_t w[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    std::memcpy(&w[1], a, 24);
+    if (b) std::memcpy(&w[4], b, 24);
+    for (int i = 1; i < 7; ++i) slot->req[i] = w[i];
+    std::atomic_thread_fence(std::memory_order_release); // payload before the sequence numbers (x86: stores stay in order)
+    slot->req[0] = (uint64_t)seq | ((uint64_t)flags << 32);
+    slot->req[7] = (uint64_t)seq;
+    std::atomic_thread_fence(std::memory_order_seq_cst);
+    const uint64_t idle_ns = (uint64_t)std::max(1, knob_value("single_mailbox_idle_us")) * 1000ull;
+    auto launch = [&]() -> int {
+        slot->state = kMailboxRunning;
+        std::atomic_thread_fence(std::memory_order_seq_cst);
+        cudaError_t e = launch_mailbox(ep->view, ep->bp, slot, seq - 1u, idle_ns, mb.stream);
+        if (e != cudaSuccess) return cuda_fail(e, "mailbox launch");
+        mb.launched = true;
+        return EPP_OK;
+    };
+    if (!mb.launched || mailbox_exited(slot)) {
+        int rc = launch();
+        if (rc) return rc;
+    }
+    const auto t0 = Clock::now();
+    uint32_t spins = 0;
+    for (;;) {
+        if (slot->ack[0] == seq) break;
+        if ((++spins & 1023u) == 0u) {
+            if (mailbox_exited(slot) && slot->ack[0] != seq) { // the warp left just before this request: start another
+                int rc = launch();
+                if (rc) return rc;
+            }
+            if (Clock::now() - t0 > std::chrono::seconds(5)) {
+                cudaError_t e = cudaStreamQuery(mb.stream);
+                if (e != cudaSuccess && e != cudaErrorNotReady) return cuda_fail(e, "mailbox kernel");
+                return fail(EPP_ERR_CUDA, "mailbox: no answer from the device within 5 s");
+            }
+        }
+    }
+    std::atomic_thread_fence(std::memory_order_acquire);
+    *valid = (int)(slot->ack[1] & 1u);
+    return EPP_OK;
+}
+
+// One unit through mapped pinned memory: the mailbox warp by default; a single launch + synchronise with the knob off.
 int check_single(epp_world *w, const double *a, const double *b, int can_pass_gate, int *valid)
 {
     std::shared_ptr<DeviceEpoch> ep;
@@ -355,6 +474,7 @@ int check_single(epp_world *w, const double *a, const double *b, int can_pass_ga
     Staging *s;
     rc = get_staging(ep->device, &s);
     if (rc) return rc;
+    if (knob_value("single_mailbox")) return check_single_mailbox(s, ep, a, b, can_pass_gate, valid);
     rc = reserve_host(s, 256);
     if (rc) return rc;
     double *slot = (double *)s->h;
@@ -534,6 +654,19 @@ extern "C" int epp_world_commit(epp_world *w)
         if (nb <= 0) nb = W == 1 ? 256 : (W <= 8 ? 128 : (W <= 32 ? 64 : 32));
         build_bits(aabbs, nb, bits);
     }
+    // W == 1: copies of the `inside` table in separate bank groups for the warp form of K1 (WorldView::rep_B)
+    std::vector<uint32_t> inside_rep;
+    int rep_B = 32;
+    if (bp == EPP_BP_BITS && bits.W == 1) {
+        const int copies = knob_value("states_table_copies");
+        if (copies == 2 || copies == 4 || copies == 8 || copies == 16) {
+            rep_B = 32 / copies;
+            const int words = 3 * bits.nb, rows = (words + rep_B - 1) / rep_B;
+            inside_rep.assign((size_t)rows * 32, 0u);
+            for (int i = 0; i < words; ++i)
+                for (int r = 0; r < copies; ++r) inside_rep[(size_t)(i / rep_B) * 32 + r * rep_B + i % rep_B] = bits.inside[i];
+        }
+    }
     if (bp == EPP_BP_GRID)
         build_grid(aabbs, obbs, knob_value("grid_max_cells"), grid, (long)knob_value("grid_occ_kb") * 1024);
 
@@ -547,7 +680,8 @@ extern "C" int epp_world_commit(epp_world *w)
         {aabbs.data(), aabbs.size() * sizeof(AabbRec), 0},      {obbs.data(), obbs.size() * sizeof(ObbRec), 0},
         {bits.inside.data(), bits.inside.size() * 4, 0},        {bits.min_le.data(), bits.min_le.size() * 4, 0},
         {bits.max_ge.data(), bits.max_ge.size() * 4, 0},        {grid.cell_start.data(), grid.cell_start.size() * 4, 0},
-        {grid.cell_items.data(), grid.cell_items.size() * 4, 0}, {grid.occ.data(), grid.occ.size() * 4, 0}};
+        {grid.cell_items.data(), grid.cell_items.size() * 4, 0}, {grid.occ.data(), grid.occ.size() * 4, 0},
+        {inside_rep.data(), inside_rep.size() * 4, 0}};
     size_t total = 0;
     for (Part &p : parts) {
         p.off = total;
@@ -573,6 +707,8 @@ extern "C" int epp_world_commit(epp_world *w)
     v.W = bits.W;
     v.Ws = bits.Ws;
     v.kb = bits.bins;
+    v.bits_inside_rep = (const uint32_t *)(base + parts[8].off);
+    v.rep_B = rep_B;
     v.zrot = 1;
     for (const ObbRec &o : obbs)
         if (o.rot[2] != 0.0 || o.rot[5] != 0.0 || o.rot[6] != 0.0 || o.rot[7] != 0.0 || o.rot[8] != 1.0) v.zrot = 0;
@@ -632,6 +768,27 @@ extern "C" int epp_check_segments(epp_world *w, const double *a, const double *b
                                   uint32_t *mask)
 {
     return check_host(w, a, b, n, 1, kModeBool, can_pass_gate, 0.0, mask);
+}
+
+// Mean wall time of n back-to-back epp_is_valid calls (microseconds per call), measured inside the library so that no
+// binding overhead is in it: the number an OMPL planner thread sees per StateValidator::isValid.
+extern "C" int epp_measure_single_latency(epp_world *w, int n_calls, double *us_per_call)
+{
+    if (!us_per_call || n_calls <= 0) return fail(EPP_ERR_INVALID_ARG);
+    int valid = 0;
+    double p[3] = {0.0, 0.0, 1.0};
+    for (int i = 0; i < 16; ++i) { // warm-up: staging, first launch of the resident warp
+        int rc = check_single(w, p, nullptr, 0, &valid);
+        if (rc) return rc;
+    }
+    const auto t0 = Clock::now();
+    for (int i = 0; i < n_calls; ++i) {
+        p[0] = 0.01 * (double)(i & 127);
+        int rc = check_single(w, p, nullptr, 0, &valid);
+        if (rc) return rc;
+    }
+    *us_per_call = std::chrono::duration<double, std::micro>(Clock::now() - t0).count() / n_calls;
+    return EPP_OK;
 }
 
 extern "C" int epp_is_valid(epp_world *w, const double p[3], int can_pass_gate, int *valid)

@@ -30,6 +30,10 @@ struct WorldView {
     int W;
     int Ws; // row stride of the bits tables in words (W = 1: 1; else (W + 1) | 1 with a summary word at index W)
     KeyBins kb;
+    // single-word tables (W == 1) replicated across bank groups for the warp form of K1: copy r (= lane % (32 / rep_B))
+    // of word i at ((i / rep_B) * 32 + r * rep_B + i % rep_B); rep_B == 32: not replicated (bits_inside_rep unused)
+    const uint32_t *bits_inside_rep;
+    int rep_B;
     int zrot; // every OBB rotation is a rotation about z (rot[2,5,6,7] == 0, rot[8] == 1)
     // EPP_BP_GRID
     const uint32_t *cell_start;

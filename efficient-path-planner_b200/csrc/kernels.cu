@@ -155,19 +155,36 @@ constexpr int kBpBits1 = 4;
 template <>
 struct PointWorld<kBpBits1> {
     const uint32_t *inside;
+    int lb, bm, roff; // replicated table: log2(banks per copy), banks per copy - 1, first bank of this lane's copy
     __device__ static uint32_t table(const WorldView &wv, bool, const void *&src)
     {
+        if (wv.rep_B < 32) {
+            src = wv.bits_inside_rep;
+            return (uint32_t)((3 * wv.nb + wv.rep_B - 1) / wv.rep_B * 128);
+        }
         src = wv.bits_inside;
         return (uint32_t)(3 * wv.nb * 4);
     }
-    __device__ void bind(const WorldView &, bool) { inside = reinterpret_cast<const uint32_t *>(g_smem); }
+    __device__ void bind(const WorldView &wv, bool)
+    {
+        inside = reinterpret_cast<const uint32_t *>(g_smem);
+        lb = 31 - __clz(wv.rep_B);
+        bm = wv.rep_B - 1;
+        roff = ((threadIdx.x & 31) % (32 >> lb)) << lb;
+    }
+    // Random bins from 32 lanes land ~3.5 deep on some bank; with 8 copies of the table in 8 groups of 4 banks, the 4
+    // lanes that share a copy collide ~1.9 deep (ncu r01_z: 476 k conflict cycles per 1 M-state launch).
+    __device__ __forceinline__ uint32_t look(int i) const
+    {
+        return lb == 5 ? inside[i] : inside[((i >> lb) << 5) + roff + (i & bm)];
+    }
     __device__ __forceinline__ uint32_t candidates(const WorldView &wv, const P3 &p) const
     {
         const int nb = wv.nb;
         const int bx = dev_key_bin(p.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb);
         const int by = dev_key_bin(p.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb);
         const int bz = dev_key_bin(p.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb);
-        return inside[bx] & inside[nb + by] & inside[2 * nb + bz];
+        return look(bx) & look(nb + by) & look(2 * nb + bz);
     }
     template <class F>
     __device__ __forceinline__ bool any(const WorldView &wv, const P3 &p, F test) const
@@ -1540,13 +1557,14 @@ __global__ void __launch_bounds__(kPolyThreads) k_poly_traj(WorldView wv, const 
     const uint32_t Gb = (uint32_t)((n_traj - traj0) < (size_t)G ? (n_traj - traj0) : (size_t)G); // trajectories of this block
     const size_t words_per_traj = max_samples / 32;
     // ring behind the broad-phase table: per round G rows of parked times, G rows of segment numbers, G counts
-    const size_t round_bytes = (size_t)G * kPolyPitch * 10 + (size_t)G * 4;
+    const size_t seg_bytes = ((size_t)G * kPolyPitch * 2 + 7) & ~(size_t)7;
+    const size_t round_bytes = ((size_t)G * kPolyPitch * 8 + seg_bytes + (size_t)G * 4 + 15) & ~(size_t)15;
     auto ring_t = [&](uint32_t slot) { return reinterpret_cast<double *>(g_smem + table_bytes + slot * round_bytes); };
     auto ring_seg = [&](uint32_t slot) {
         return reinterpret_cast<unsigned short *>(g_smem + table_bytes + slot * round_bytes + (size_t)G * kPolyPitch * 8);
     };
     auto ring_cnt = [&](uint32_t slot) {
-        return reinterpret_cast<uint32_t *>(g_smem + table_bytes + slot * round_bytes + (size_t)G * kPolyPitch * 10);
+        return reinterpret_cast<uint32_t *>(g_smem + table_bytes + slot * round_bytes + (size_t)G * kPolyPitch * 8 + seg_bytes);
     };
 
     if (warp == 0) {
@@ -1759,6 +1777,95 @@ __global__ void k_mask_summary(const uint32_t *__restrict__ mask, size_t n_words
     if ((threadIdx.x & 31) == 0) {
         atomicAdd(out, pop);
         atomicXor(out + 1, x);
+    }
+}
+
+// ---- single-unit mailbox: StateValidator::isValid / MotionValidator::checkMotion one call at a time --------------
+//
+// OMPL's planners ask one state or one edge at a time (src/PathPlanner.cpp:106-129).  A kernel launch plus a stream
+// synchronisation per question costs ~23 us; the reference answers in ~0.13 us.  k_mailbox is ONE resident warp per
+// host thread and world epoch that polls a request line in mapped pinned host memory (MailboxSlot, kernels.h): the host
+// writes the unit and bumps a sequence number, the warp evaluates it — lane k takes OBBs k, k + 32, ... with the
+// same per-candidate functions as the batch kernels (grid worlds: the cell list) — and stores (sequence number,
+// verdict) back as one 8-byte store; the host spins on that line.  No launch and no synchronisation per question.
+// The warp leaves when no request has come for idle_ns (so that device-wide synchronisations elsewhere in the
+// process are never held up for longer than that) or on a QUIT request; the host relaunches it on demand.
+template <int BP>
+__global__ void __launch_bounds__(32) k_mailbox(WorldView wv, MailboxSlot *slot, uint32_t last_seq,
+                                                unsigned long long idle_ns)
+{
+    const int lane = threadIdx.x;
+    PointWorld<BP> pw;
+    RayWorld<BP> rw;
+    pw.init(wv, false);
+    rw.init(wv, false);
+    const unsigned long long *req = const_cast<const unsigned long long *>(reinterpret_cast<const volatile unsigned long long *>(slot->req));
+    unsigned long long t_last;
+    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_last));
+    uint32_t polls = 0;
+    bool leaving = false;
+    for (;;) {
+        // one 64-byte read of the request line: lane l < 8 takes 8 bytes of it
+        unsigned long long v = 0ull;
+        if (lane < 8) asm volatile("ld.relaxed.sys.global.u64 %0, [%1];" : "=l"(v) : "l"(req + lane) : "memory");
+        const unsigned long long head = __shfl_sync(0xffffffffu, v, 0), tail = __shfl_sync(0xffffffffu, v, 7);
+        const uint32_t seq_a = (uint32_t)head, flags = (uint32_t)(head >> 32), seq_b = (uint32_t)tail;
+        if (seq_a == last_seq || seq_a != seq_b) { // nothing new (or the two halves of the line are of different age)
+            if (leaving) break;
+            if ((++polls & 15u) == 0u) {
+                unsigned long long t;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
+                if (t - t_last > idle_ns || polls > (1u << 24)) {
+                    // announce, then look once more: a request posted before the announcement is still served
+                    if (lane == 0) {
+                        asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(const_cast<uint32_t *>(&slot->state)), "r"((uint32_t)kMailboxLeaving) : "memory");
+                        __threadfence_system();
+                    }
+                    __syncwarp();
+                    leaving = true;
+                }
+            }
+            continue;
+        }
+        last_seq = seq_a;
+        if (leaving) {
+            leaving = false;
+            if (lane == 0) asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(const_cast<uint32_t *>(&slot->state)), "r"((uint32_t)kMailboxRunning) : "memory");
+        }
+        if (flags & kMailboxQuit) break;
+        const P3 a = {__longlong_as_double((long long)__shfl_sync(0xffffffffu, v, 1)),
+                      __longlong_as_double((long long)__shfl_sync(0xffffffffu, v, 2)),
+                      __longlong_as_double((long long)__shfl_sync(0xffffffffu, v, 3))};
+        const P3 b = {__longlong_as_double((long long)__shfl_sync(0xffffffffu, v, 4)),
+                      __longlong_as_double((long long)__shfl_sync(0xffffffffu, v, 5)),
+                      __longlong_as_double((long long)__shfl_sync(0xffffffffu, v, 6))};
+        const bool cpg = (flags & kMailboxCanPassGate) != 0;
+        bool hit = false;
+        if (flags & kMailboxSegment) {
+            P3 mn, mx;
+            ray_box(a, b, mn, mx);
+            if (BP == EPP_BP_GRID) {
+                if (lane == 0) hit = rw.invalid(wv, a, b, cpg);
+            } else {
+                for (int k = lane; k < wv.M && !hit; k += 32) hit = ray_candidate_invalid(wv.aabb, wv.obb, k, a, b, mn, mx, cpg);
+            }
+        } else {
+            if (BP == EPP_BP_GRID) {
+                if (lane == 0) hit = pw.invalid(wv, a, kModeBool, cpg, 0.0);
+            } else {
+                for (int k = lane; k < wv.M && !hit; k += 32) hit = point_candidate_invalid(wv.aabb, wv.obb, k, a, kModeBool, cpg, 0.0);
+            }
+        }
+        const bool invalid = __any_sync(0xffffffffu, hit);
+        if (lane == 0)
+            asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(const_cast<uint32_t *>(slot->ack)), "r"(seq_a), "r"(invalid ? 0u : 1u) : "memory");
+        asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t_last));
+        polls = 0;
+    }
+    if (lane == 0) {
+        __threadfence_system();
+        asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(const_cast<uint32_t *>(slot->exited)), "r"(last_seq), "r"(1u) : "memory");
+        asm volatile("st.relaxed.sys.global.u32 [%0], %1;" ::"l"(const_cast<uint32_t *>(&slot->state)), "r"((uint32_t)kMailboxExited) : "memory");
     }
 }
 
@@ -1979,12 +2086,13 @@ cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, con
     cudaError_t err = cudaSuccess;
     // Warp-pipelined form: any alignment, any n; worth its prologue from a few thousand states up.
     if ((cfg.states_variant == 3 || (cfg.states_variant == 0 && n >= (size_t)cfg.states_warp_min_n))) {
-        const size_t table_bytes = ((bp == EPP_BP_GRID ? (size_t)wv.occ_bytes : smem) + 127) / 128 * 128;
+        size_t table_bytes = ((bp == EPP_BP_GRID ? (size_t)wv.occ_bytes : smem) + 127) / 128 * 128;
         const int stages = 0; // ring depth comes from the shared-memory budget
         const int S = cfg.states_per_thread == 8 ? 8 : 4;
         const int rec_max = cfg.states_rec_smem_max > 0 ? (cfg.states_rec_smem_max < 992 ? cfg.states_rec_smem_max : 992) : kRecSmemMax;
         bool rs = wv.M <= rec_max && wv.zrot && cfg.states_rec_smem != 0;
         const int wbp = (bp == EPP_BP_BITS && wv.W == 1 && cfg.states_bits1 != 0) ? kBpBits1 : bp;
+        if (wbp == kBpBits1 && wv.rep_B < 32) table_bytes = (size_t)(3 * wv.nb + wv.rep_B - 1) / wv.rep_B * 128;
         bool launched = false;
 #define EPP_LAUNCH_WARP(S_, RS_, GA_)                                                                                 \
     err = launch_states_warp<BP, S_, RS_, GA_>(cfg, wv, d_xyz, n, mode, can_pass_gate, min_distance, in_smem,          \
@@ -2166,10 +2274,11 @@ cudaError_t launch_trajectories(const LaunchCfg &cfg, const WorldView &wv, int b
         // warp-pipelined form (k_states_warp in its trajectory mode): columns 0, 3, 6 arrive by cp.async.bulk
         bool in_smem;
         const size_t smem = point_smem_bytes(wv, bp, in_smem);
-        const size_t table_bytes = ((bp == EPP_BP_GRID ? (size_t)wv.occ_bytes : smem) + 127) / 128 * 128;
+        size_t table_bytes = ((bp == EPP_BP_GRID ? (size_t)wv.occ_bytes : smem) + 127) / 128 * 128;
         const int rec_max = cfg.states_rec_smem_max > 0 ? (cfg.states_rec_smem_max < 992 ? cfg.states_rec_smem_max : 992) : kRecSmemMax;
         bool rs = wv.M <= rec_max && wv.zrot && cfg.states_rec_smem != 0;
         const int wbp = (bp == EPP_BP_BITS && wv.W == 1 && cfg.states_bits1 != 0) ? kBpBits1 : bp;
+        if (wbp == kBpBits1 && wv.rep_B < 32) table_bytes = (size_t)(3 * wv.nb + wv.rep_B - 1) / wv.rep_B * 128;
         TrajArgs ta = {};
         ta.mats = d_mats;
         ta.rows = rows;
@@ -2249,7 +2358,7 @@ cudaError_t launch_poly_trajectories(const LaunchCfg &cfg, const WorldView &wv, 
     G = G > 32 ? 32 : (G < 1 ? 1 : G);
     const unsigned grid = (unsigned)((n_traj + G - 1) / G);
     const size_t table_bytes = (smem + 127) / 128 * 128;
-    const size_t total = table_bytes + (size_t)kPolyRing * ((size_t)G * kPolyPitch * 10 + (size_t)G * 4);
+    const size_t total = table_bytes + (size_t)kPolyRing * ((size_t)G * kPolyPitch * 10 + (size_t)G * 4 + 32);
     // 16-byte coefficient loads need a 16 B-aligned batch (a segment's 3 x 10 coefficients are 240 B)
     const bool n10 = n_coeffs == 10 && (reinterpret_cast<uintptr_t>(d_coeffs) & 15u) == 0;
     EPP_DISPATCH_BP(bp, {
@@ -2268,6 +2377,17 @@ cudaError_t launch_poly_trajectories(const LaunchCfg &cfg, const WorldView &wv, 
                                                                          d_traj_valid);
     g_launches++;
     return cudaGetLastError();
+}
+
+cudaError_t launch_mailbox(const WorldView &wv, int bp, MailboxSlot *slot, uint32_t last_seq, uint64_t idle_ns,
+                           cudaStream_t stream)
+{
+    cudaError_t err = cudaSuccess;
+    if (bp == EPP_BP_GRID) k_mailbox<EPP_BP_GRID><<<1, 32, 0, stream>>>(wv, slot, last_seq, (unsigned long long)idle_ns);
+    else k_mailbox<EPP_BP_BRUTE><<<1, 32, 0, stream>>>(wv, slot, last_seq, (unsigned long long)idle_ns); // all OBBs, 32 at a time
+    err = cudaGetLastError();
+    g_launches++;
+    return err;
 }
 
 cudaError_t launch_count_candidates(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_a, const double *d_b,

@@ -61,6 +61,27 @@ struct GatherView {
     int debug; // profiling only (tuning knob gather_debug): 1 no wait/unpack, 2 no peer stores (wrong results)
 };
 
+// Request / answer lines of the single-unit mailbox (k_mailbox), in mapped pinned host memory.  The request is ONE
+// 64-byte line whose two 32-byte halves each carry the sequence number (the host writes the payload first, then both
+// copies; the device accepts the line when they agree, whatever the order its two halves were read in).
+struct alignas(64) MailboxSlot {
+    // request: [seq | flags << 32][a.x][a.y][a.z] | [b.x][b.y][b.z][seq]
+    volatile uint64_t req[8];
+    // answer: (seq, valid) in one 8-byte store
+    volatile uint32_t ack[2];
+    uint32_t pad0[14];
+    // life cycle of the resident warp
+    volatile uint32_t exited[2]; // (last sequence number seen, 1) once the warp has left
+    volatile uint32_t state;     // kMailboxRunning / Leaving / Exited
+    uint32_t pad1[13];
+};
+static_assert(sizeof(MailboxSlot) == 192, "MailboxSlot layout");
+constexpr uint32_t kMailboxSegment = 1u, kMailboxCanPassGate = 2u, kMailboxQuit = 4u;
+constexpr uint32_t kMailboxIdle = 0u, kMailboxRunning = 1u, kMailboxLeaving = 2u, kMailboxExited = 3u;
+// One resident warp serving `slot` for this world until idle_ns pass without a request or a QUIT request arrives.
+cudaError_t launch_mailbox(const WorldView &wv, int bp, MailboxSlot *slot, uint32_t last_seq, uint64_t idle_ns,
+                           cudaStream_t stream);
+
 cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_xyz, size_t n, int mode,
                           int can_pass_gate, double min_distance, uint32_t *d_mask, cudaStream_t stream,
                           const GatherView *gv = nullptr);

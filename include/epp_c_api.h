@@ -39,7 +39,7 @@ typedef enum {
     EPP_ERR_NO_GEOMETRY = 4, /* unknown gate type / component              src/ConfigParserYAML.cpp:21-37 */
     EPP_ERR_NO_SUCH_OBB = 5, /* std::out_of_range from obbs.at()           src/World.cpp:74,87 */
     EPP_ERR_INVALID_ARG = 6,
-    EPP_ERR_NOT_COMMITTED = 7, /* check issued before epp_world_commit */
+    EPP_ERR_NOT_COMMITTED = 7, /* check issued before the first epp_world_commit */
     EPP_ERR_CUDA = 8,
     EPP_ERR_NO_DEVICE = 9
 } epp_status;
@@ -103,7 +103,8 @@ int epp_world_get_obb(const epp_world *w, int index, epp_obb *out);
 int epp_world_set_broadphase(epp_world *w, epp_broadphase mode);
 /* Publishes the current host world as a new immutable device epoch on the calling
  * thread's current CUDA device (replaces the reference's in-place R-tree mutation,
- * src/World.cpp:57-78).  Must follow any reset/add/update before the next check. */
+ * src/World.cpp:57-78).  Checks see the world as of the LAST commit: reset/add/update stay invisible to
+ * them (also to checks other threads start meanwhile) until the next commit. */
 int epp_world_commit(epp_world *w);
 int epp_world_epoch(const epp_world *w, uint64_t *epoch);
 /* Broad phase actually in use for the committed epoch (an epp_broadphase, never AUTO). */
@@ -258,6 +259,9 @@ int epp_gen_segments_dev(uint64_t seed, uint64_t first, size_t n, const double l
 
 /* Number of kernels this library has launched on the calling process so far. */
 uint64_t epp_kernel_launch_count(void);
+/* Mean wall time (microseconds) of n back-to-back epp_is_valid calls, timed inside the library (no binding overhead):
+ * what one StateValidator::isValid (src/StateValidator.cpp:7-13) costs an OMPL planner thread. */
+int epp_measure_single_latency(epp_world *w, int n_calls, double *us_per_call);
 /* Broad-phase statistics of a device batch against the committed world (d_b NULL: points, else segments):
  * d_visited_hits[0] = candidates the active broad phase visits, [1] = those whose stored AABB passes the
  * reference's exact R-tree predicate (src/World.cpp:83 strict containment / :143 closed intersection).  Feeds the

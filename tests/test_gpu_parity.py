@@ -781,3 +781,115 @@ def test_bits_rows_of_32_words_and_rejection_above(oracle, config):
         assert mismatches(auto.check_states(xyz2, False), ow2.check_states(xyz2, False, threads=8)) == 0
     finally:
         epp_b200.set_tuning("bits_max_obbs", 1024)
+
+
+def test_commit_new_epochs_while_checks_are_in_flight(oracle, config, track):
+    """SURVEY.md §5 race row: the reference rebuilds its World (src/OnlineTrajGenerator.cpp:146) while planner threads
+    may still be querying it (:324-340).  Here a mutator thread moves a gate and commits new epochs as fast as it can
+    while three threads keep checking batches and single units; every answer must be the oracle's answer for ONE of
+    the two worlds (never a mixture, never a crash), and both worlds must be observed."""
+    import threading
+    g, o, lo, hi = track
+    g2 = np.array(g, copy=True)
+    g2[1, 0] += 0.15
+    g2[1, 5] += 0.3
+    gw = epp_b200.World(config)
+    gw.parse_gates_and_obstacles(g, o)
+    want = []
+    xyz = np.concatenate([worlds.gen_states(777, 0, 60000, lo, hi),
+                          np.asarray(g2[1, :3]) + (np.random.default_rng(1).random((4000, 3)) - 0.5) * [1.6, 1.6, 2.0] + [0, 0, 1.0]])
+    a, b = worlds.gen_segments(778, 0, 30000, lo, hi, 1.0)
+    for gg in (g, g2):
+        ow = oracle.OracleWorld(config)
+        ow.parse_gates_and_obstacles(gg, o)
+        want.append((ow.check_states(xyz, False, threads=8), ow.check_segments(a, b, False, threads=8)))
+    assert not np.array_equal(want[0][0], want[1][0])
+    stop = threading.Event()
+    seen, errors = [set(), set(), set()], []
+
+    def checker(tid):
+        try:
+            while not stop.is_set():
+                ms = gw.check_states(xyz, False)
+                me = gw.check_segments(a, b, False)
+                for got, idx in ((ms, 0), (me, 1)):
+                    which = [k for k in (0, 1) if np.array_equal(got, want[k][idx])]
+                    if not which:
+                        errors.append("thread %d: a mask that belongs to neither world" % tid)
+                        return
+                    seen[tid].update(which)
+                for i in range(0, 200, 7):  # single units through the mailbox warp, across epoch changes
+                    one = gw.checkPointValidity(xyz[60000 + i], False)
+                    bits = [bool(want[k][0][(60000 + i) >> 5] >> ((60000 + i) & 31) & 1) for k in (0, 1)]
+                    if one not in bits:
+                        errors.append("thread %d: single answer of neither world" % tid)
+                        return
+        except Exception as ex:  # noqa: BLE001
+            errors.append(repr(ex))
+
+    def mutator():
+        try:
+            k = 0
+            while not stop.is_set():
+                k ^= 1
+                gw.updateGatePosition(1, (g2 if k else g)[1])
+                gw.commit()
+        except Exception as ex:  # noqa: BLE001
+            errors.append("mutator: " + repr(ex))
+
+    ts = [threading.Thread(target=checker, args=(i,)) for i in range(3)] + [threading.Thread(target=mutator)]
+    [t.start() for t in ts]
+    import time
+    time.sleep(3.0)
+    stop.set()
+    [t.join(60) for t in ts]
+    assert not errors, errors[:3]
+    assert set().union(*seen) == {0, 1}
+
+
+def test_single_unit_mailbox_life_cycle(oracle, config, track):
+    """epp_is_valid / epp_check_motion go through a resident warp polling a mapped request line.  It must answer like
+    the batch kernels, leave when idle (so device-wide synchronisations are not held up), come back on the next
+    call, follow the world across commits, and the launch + synchronise form behind the knob must agree."""
+    import time
+    import torch
+    g, o, lo, hi = track
+    ow, gw = build_pair(oracle, epp_b200, config, g, o)
+    xyz = np.concatenate([worlds.gen_states(901, 0, 300, lo, hi), adversarial_points(ow.obbs()[:4], np.random.default_rng(8), 1)])
+    a, b = worlds.gen_segments(902, 0, 300, lo, hi, 1.0)
+    for cpg in (False, True):
+        wp = np.unpackbits(ow.check_states(xyz, cpg).view(np.uint8), bitorder="little")
+        ws = np.unpackbits(ow.check_segments(a, b, cpg).view(np.uint8), bitorder="little")
+        assert [gw.checkPointValidity(p, cpg) for p in xyz] == [bool(v) for v in wp[: len(xyz)]]
+        assert [gw.checkRayValid(p, q, cpg) for p, q in zip(a, b)] == [bool(v) for v in ws[:300]]
+    # idle exit: after 20 ms without a request the warp has left and a device-wide synchronise returns at once
+    time.sleep(0.02)
+    t0 = time.perf_counter()
+    torch.cuda.synchronize()
+    assert time.perf_counter() - t0 < 0.01
+    assert gw.checkPointValidity([0.0, 0.0, 0.4], False) == ow.check_point([0.0, 0.0, 0.4], False)
+    # the world changes between single calls: the next call must see the new epoch
+    p = np.asarray(g[0][:3]) + [0.0, 0.0, 0.3]
+    before = gw.checkPointValidity(p, False)
+    gw.updateGatePosition(0, [g[0][0] + 1.0, g[0][1] + 1.0, 0, 0, 0, g[0][5], g[0][6]])
+    assert gw.checkPointValidity(p, False) is True and before is False
+    # knob off: one launch + synchronise per call, same answers
+    epp_b200.set_tuning("single_mailbox", 0)
+    try:
+        assert gw.checkPointValidity(p, False) is True
+        assert [gw.checkRayValid(p_, q_, False) for p_, q_ in zip(a[:50], b[:50])] == \
+               [gw.checkRayValid(p_, q_, False) for p_, q_ in zip(a[:50], b[:50])]
+    finally:
+        epp_b200.set_tuning("single_mailbox", 1)
+    us = gw.single_latency_us(2000)
+    print("single isValid through the mailbox: %.2f us per call" % us)
+    assert us < 20.0
+    # big world (grid broad phase): lane 0 walks the cell list
+    g5, o5, lo5, hi5 = worlds.world_10k()
+    ow5, gw5 = build_pair(oracle, epp_b200, config, g5, o5)
+    pts = np.concatenate([worlds.gen_states(903, 0, 100, lo5, hi5), adversarial_points(ow5.obbs()[:3], np.random.default_rng(9), 1)])
+    w5 = np.unpackbits(ow5.check_states(pts, False).view(np.uint8), bitorder="little")
+    assert [gw5.checkPointValidity(q, False) for q in pts] == [bool(v) for v in w5[: len(pts)]]
+    a5, b5 = worlds.gen_segments(904, 0, 100, lo5, hi5, 1.0)
+    s5 = np.unpackbits(ow5.check_segments(a5, b5, False).view(np.uint8), bitorder="little")
+    assert [gw5.checkRayValid(p_, q_, False) for p_, q_ in zip(a5, b5)] == [bool(v) for v in s5[:100]]

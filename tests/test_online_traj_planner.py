@@ -127,3 +127,69 @@ def test_prune_waypoints_equals_the_reference_loop(oracle, config):
             idx += 1
         want.append(w[-1])
         assert np.array_equal(pp.pruneWaypoints(w), np.array(want))
+
+
+@pytest.mark.gpu
+def test_call_trace_of_one_solve_replays_bit_for_bit(oracle, config, tmp_path):
+    """record EVERY question one pre_compute_traj asks the world — the states and edges the
+    planner got "invalid" for as well as the ones it kept (src/PathPlanner.cpp:80-158 asks them through
+    StateValidator::isValid / MotionValidator::checkMotion, src/StateValidator.cpp:7-13, src/MotionValidator.cpp:8-17) —
+    and replay the trace through the CPU oracle, the reference's own code where it is built, and, one call at a time,
+    through the single-unit entry points the OMPL virtuals use.  Masks must be equal everywhere."""
+    import time
+    import online_traj_planner as otp
+    t = config["track"]
+    otp.OnlineTrajGenerator.path_segments_folder = str(tmp_path / "path_segments")
+    gen = otp.OnlineTrajGenerator(t["start"], t["goal"], t["gates"], t["obstacles"], config)
+    world = gen.pathPlanner.worldPtr
+    trace = []
+    real_states, real_segments = world.check_states, world.check_segments
+
+    def rec_states(xyz, can_pass_gate=False):
+        m = real_states(xyz, can_pass_gate)
+        trace.append(("states", np.array(xyz, dtype=np.float64, copy=True), None, bool(can_pass_gate), np.array(m, copy=True)))
+        return m
+
+    def rec_segments(a, b, can_pass_gate=False):
+        m = real_segments(a, b, can_pass_gate)
+        trace.append(("segments", np.array(a, dtype=np.float64, copy=True), np.array(b, dtype=np.float64, copy=True),
+                      bool(can_pass_gate), np.array(m, copy=True)))
+        return m
+
+    world.check_states, world.check_segments = rec_states, rec_segments
+    try:
+        gen.pre_compute_traj(0.0)
+    finally:
+        world.check_states, world.check_segments = real_states, real_segments
+    n_states = sum(q[1].shape[0] for q in trace if q[0] == "states")
+    n_edges = sum(q[1].shape[0] for q in trace if q[0] == "segments")
+    assert n_states > 1000 and n_edges > 1000
+
+    checkers = [oracle.OracleWorld(config)]
+    try:
+        import ref_py
+        if ref_py.available():
+            checkers.append(ref_py.RefWorld(config))
+    except ImportError:
+        pass
+    invalid_answers = 0
+    for cw in checkers:
+        cw.parse_gates_and_obstacles(gen.gates, gen.obstacles)
+        for kind, a, b, cpg, got in trace:
+            want = cw.check_states(a, cpg, threads=4) if kind == "states" else cw.check_segments(a, b, cpg, threads=4)
+            assert np.array_equal(np.asarray(got, np.uint32), want), (kind, a.shape, cpg)
+            invalid_answers += a.shape[0] - int(np.unpackbits(want.view(np.uint8)).sum())
+    assert invalid_answers > 0  # the trace holds rejected questions too, not only the kept ones
+
+    # one call at a time through epp_is_valid / epp_check_motion (what OMPL's per-call loop would do): a sample of
+    # the trace, answers equal to the batch's bits; per-call latency printed for the record
+    rng = np.random.default_rng(5)
+    t0, calls = time.perf_counter(), 0
+    for kind, a, b, cpg, got in trace:
+        bits = np.unpackbits(np.asarray(got, np.uint32).view(np.uint8), bitorder="little")
+        for i in rng.choice(a.shape[0], size=min(40, a.shape[0]), replace=False):
+            one = world.checkPointValidity(a[i], cpg) if kind == "states" else world.checkRayValid(a[i], b[i], cpg)
+            assert one == bool(bits[i]), (kind, i)
+            calls += 1
+    print("call trace: %d states + %d edges in %d batches; %d single calls replayed, %.1f us per call (incl. binding)"
+          % (n_states, n_edges, len(trace), calls, (time.perf_counter() - t0) / calls * 1e6))
