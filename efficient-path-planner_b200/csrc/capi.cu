@@ -76,7 +76,10 @@ Knob g_knobs[] = {
     {"bits_bins", {0}},                  // 0: by world size
     {"grid_max_cells", {1 << 22}},
     {"grid_occ_kb", {72}},
+    {"grid_cell_recs", {1}},             // grid: candidates read from records stored in cell order (0: item -> AabbRec -> ObbRec); read at commit
     {"states_table_copies", {1}},        // worlds of <= 32 OBBs: copies of the bin table in separate bank groups (1, 2, 4, 8, 16); read at commit
+    {"bits_cmask", {1}},                 // bits broad phase, W > 1: coarse-cell word masks (0: round-1 summaries); read at commit
+    {"morton_sort", {1}},                // device records along a Morton curve (worlds of > 32 OBBs); read at commit
     {"single_mailbox", {1}},             // epp_is_valid / epp_check_motion through the resident mailbox warp (0: launch + sync per call)
     {"single_mailbox_idle_us", {1000}},  // the mailbox warp leaves after this long without a request               // shared-memory budget of the grid's occupancy bitmap
     {"bits_max_obbs", {1024}},
@@ -637,6 +640,7 @@ extern "C" int epp_world_commit(epp_world *w)
     int rc = w->host.flatten(aabbs, obbs);
     if (rc) return fail(rc);
     const int M = (int)aabbs.size();
+    if (M > 32 && knob_value("morton_sort")) morton_sort(aabbs, obbs); // device order only; the host registry keeps its own
 
     int bp = w->bp_request;
     // A bits row is summarised by ONE 32-bit word (bit w = word w of the row is non-zero) and the ray walk keeps its
@@ -681,7 +685,8 @@ extern "C" int epp_world_commit(epp_world *w)
         {bits.inside.data(), bits.inside.size() * 4, 0},        {bits.min_le.data(), bits.min_le.size() * 4, 0},
         {bits.max_ge.data(), bits.max_ge.size() * 4, 0},        {grid.cell_start.data(), grid.cell_start.size() * 4, 0},
         {grid.cell_items.data(), grid.cell_items.size() * 4, 0}, {grid.occ.data(), grid.occ.size() * 4, 0},
-        {inside_rep.data(), inside_rep.size() * 4, 0}};
+        {inside_rep.data(), inside_rep.size() * 4, 0},
+        {grid.cell_recs.data(), grid.cell_recs.size() * 8, 0}};
     size_t total = 0;
     for (Part &p : parts) {
         p.off = total;
@@ -707,6 +712,11 @@ extern "C" int epp_world_commit(epp_world *w)
     v.W = bits.W;
     v.Ws = bits.Ws;
     v.kb = bits.bins;
+    v.cmask_off = bits.cmask_off;
+    v.cmask_words = knob_value("bits_cmask") ? bits.cmask_words : 0; // 0: per-axis summaries / full row scans (round-1 form)
+    v.cn0 = bits.cn[0];
+    v.cn1 = bits.cn[1];
+    for (int a = 0; a < 3; ++a) v.cshift[a] = bits.cshift[a];
     v.bits_inside_rep = (const uint32_t *)(base + parts[8].off);
     v.rep_B = rep_B;
     v.zrot = 1;
@@ -715,6 +725,7 @@ extern "C" int epp_world_commit(epp_world *w)
     v.cell_start = (const uint32_t *)(base + parts[5].off);
     v.cell_items = (const uint32_t *)(base + parts[6].off);
     v.gbins = grid.bins;
+    v.cell_recs = (grid.cell_recs.empty() || !knob_value("grid_cell_recs")) ? nullptr : (const double *)(base + parts[9].off);
     v.occ = (const uint32_t *)(base + parts[7].off);
     v.occ_bytes = (uint32_t)align_up(grid.occ.size() * 4, 16); // parts are padded to 256 B
     v.occ_n0 = grid.occ_n[0];

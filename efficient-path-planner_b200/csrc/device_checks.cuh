@@ -30,6 +30,9 @@ struct WorldView {
     int W;
     int Ws; // row stride of the bits tables in words (W = 1: 1; else (W + 1) | 1 with a summary word at index W)
     KeyBins kb;
+    // W > 1: coarse cell -> word mask table behind bits_inside (BitsTables::cmask_*); 0 words: absent
+    int cmask_off, cmask_words, cn0, cn1;
+    int cshift[3];
     // single-word tables (W == 1) replicated across bank groups for the warp form of K1: copy r (= lane % (32 / rep_B))
     // of word i at ((i / rep_B) * 32 + r * rep_B + i % rep_B); rep_B == 32: not replicated (bits_inside_rep unused)
     const uint32_t *bits_inside_rep;
@@ -39,6 +42,7 @@ struct WorldView {
     const uint32_t *cell_start;
     const uint32_t *cell_items;
     AxisBins gbins;
+    const double *cell_recs; // GridTables::cell_recs (kCellRec doubles per entry of cell_items); null: not built
     // occupancy bitmap over coarse cells (GridTables::occ): bit (z' * occ_n1 + y') * occ_n0 + x', c' = c >> occ_shift
     const uint32_t *occ;
     uint32_t occ_bytes; // multiple of 16

@@ -82,40 +82,47 @@ struct PointWorld<EPP_BP_BRUTE> {
 };
 
 // Per-axis bin bitmasks: candidates = inside_x[bin(x)] & inside_y[bin(y)] & inside_z[bin(z)].
+// W > 1: the words worth a look come from the coarse-cell table behind the rows (one read: the cell of p names the
+// words that hold an OBB near it; records are Morton-sorted, so that is one word or two).
+__device__ __forceinline__ int bits_words(const WorldView &wv) { return wv.cmask_words ? wv.cmask_off + wv.cmask_words : 3 * wv.nb * wv.Ws; }
+
 template <>
 struct PointWorld<EPP_BP_BITS> {
     const uint32_t *inside;
     __device__ void init(const WorldView &wv, bool)
     {
         uint32_t *dst = reinterpret_cast<uint32_t *>(g_smem);
-        block_copy_words(dst, wv.bits_inside, 3 * wv.nb * wv.Ws);
+        block_copy_words(dst, wv.bits_inside, bits_words(wv));
         __syncthreads();
         inside = dst;
     }
     __device__ static uint32_t table(const WorldView &wv, bool, const void *&src)
     {
         src = wv.bits_inside;
-        return (uint32_t)(3 * wv.nb * wv.Ws * 4);
+        return (uint32_t)(bits_words(wv) * 4);
     }
     __device__ void bind(const WorldView &, bool) { inside = reinterpret_cast<const uint32_t *>(g_smem); }
+    // rows of p's bins and the set of words to look at
+    __device__ __forceinline__ uint32_t rows(const WorldView &wv, const P3 &p, const uint32_t *&tx, const uint32_t *&ty,
+                                             const uint32_t *&tz) const
+    {
+        const int nb = wv.nb, Ws = wv.Ws;
+        const int bx = dev_key_bin(p.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb);
+        const int by = dev_key_bin(p.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb);
+        const int bz = dev_key_bin(p.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb);
+        tx = inside + bx * Ws;
+        ty = inside + (nb + by) * Ws;
+        tz = inside + (2 * nb + bz) * Ws;
+        if (wv.W == 1) return 1u;
+        if (wv.cmask_words)
+            return inside[wv.cmask_off + ((bz >> wv.cshift[2]) * wv.cn1 + (by >> wv.cshift[1])) * wv.cn0 + (bx >> wv.cshift[0])];
+        return tx[wv.W] & ty[wv.W] & tz[wv.W]; // per-axis summaries (word W of a row)
+    }
     template <class F>
     __device__ __forceinline__ bool any(const WorldView &wv, const P3 &p, F test) const
     {
-        const int nb = wv.nb, W = wv.W, Ws = wv.Ws;
-        const uint32_t *tx = inside + dev_key_bin(p.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb) * Ws;
-        const uint32_t *ty = inside + (nb + dev_key_bin(p.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb)) * Ws;
-        const uint32_t *tz = inside + (2 * nb + dev_key_bin(p.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb)) * Ws;
-        if (W == 1) { // one word per row: nothing to converge
-            uint32_t m = tx[0] & ty[0] & tz[0];
-            while (m) {
-                const int k = __ffs(m) - 1;
-                m &= m - 1;
-                if (test(k)) return true;
-            }
-            return false;
-        }
-        // word W of a row summarises which of its words are non-zero: three reads bound the words worth a look
-        uint32_t nz = tx[W] & ty[W] & tz[W];
+        const uint32_t *tx, *ty, *tz;
+        uint32_t nz = rows(wv, p, tx, ty, tz);
         while (nz) {
             const int w = __ffs(nz) - 1;
             nz &= nz - 1;
@@ -130,12 +137,8 @@ struct PointWorld<EPP_BP_BITS> {
     }
     __device__ __forceinline__ bool has_candidates(const WorldView &wv, const P3 &p) const
     {
-        const int nb = wv.nb, W = wv.W, Ws = wv.Ws;
-        const uint32_t *tx = inside + dev_key_bin(p.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb) * Ws;
-        const uint32_t *ty = inside + (nb + dev_key_bin(p.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb)) * Ws;
-        const uint32_t *tz = inside + (2 * nb + dev_key_bin(p.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb)) * Ws;
-        if (W == 1) return (tx[0] & ty[0] & tz[0]) != 0u;
-        uint32_t nz = tx[W] & ty[W] & tz[W]; // summaries (see any())
+        const uint32_t *tx, *ty, *tz;
+        uint32_t nz = rows(wv, p, tx, ty, tz);
         while (nz) {
             const int w = __ffs(nz) - 1;
             nz &= nz - 1;
@@ -203,6 +206,54 @@ struct PointWorld<kBpBits1> {
     }
 };
 
+// ---- records in cell order (GridTables::cell_recs): the whole per-candidate test from one kCellRec-double record.
+// Same arithmetic as rec_hit / ray_rec_invalid below (z-rotation form of src/OBB.cpp:63-91, :10-61; inputs finite).
+
+__device__ __forceinline__ bool cellrec_point_invalid(const double *__restrict__ r, const P3 &p, int mode, bool cpg,
+                                                      double md)
+{
+    const bool in = (p.x > __ldg(r + 0)) & (p.x < __ldg(r + 3)) & (p.y > __ldg(r + 1)) & (p.y < __ldg(r + 4)) &
+                    (p.z > __ldg(r + 2)) & (p.z < __ldg(r + 5));
+    if (!in) return false;
+    const uint32_t flags = (uint32_t)__double_as_longlong(__ldg(r + 17)) & 3u;
+    const bool filling = (flags & kFlagFilling) != 0;
+    if (mode == kModeBool ? (filling && cpg) : filling) return false; // src/World.cpp:92-95, :116-119
+    const double infl = filling ? 0.0 : (mode == kModeBool ? __ldg(r + 16) : md);
+    const double d0 = dsub(p.x, __ldg(r + 6)), d1 = dsub(p.y, __ldg(r + 7)), d2 = dsub(p.z, __ldg(r + 8));
+    const double lx = dadd(dmul(__ldg(r + 9), d0), dmul(__ldg(r + 11), d1));
+    const double ly = dadd(dmul(__ldg(r + 10), d0), dmul(__ldg(r + 12), d1));
+    const double hx = filling ? __ldg(r + 13) : dadd(__ldg(r + 13), infl);
+    const double hy = filling ? __ldg(r + 14) : dadd(__ldg(r + 14), infl);
+    const double hz = filling ? __ldg(r + 15) : dadd(__ldg(r + 15), infl);
+    return (fabs(lx) <= hx) & (fabs(ly) <= hy) & (fabs(d2) <= hz);
+}
+
+__device__ __forceinline__ bool cellrec_ray_invalid(const double *__restrict__ r, const P3 &a, const P3 &b, const P3 &mn,
+                                                    const P3 &mx, bool cpg)
+{
+    if (mx.x < __ldg(r + 0) || mn.x > __ldg(r + 3) || mx.y < __ldg(r + 1) || mn.y > __ldg(r + 4) || mx.z < __ldg(r + 2) ||
+        mn.z > __ldg(r + 5))
+        return false;
+    const uint32_t flags = (uint32_t)__double_as_longlong(__ldg(r + 17)) & 3u;
+    const bool filling = (flags & kFlagFilling) != 0;
+    if (filling && cpg) return false; // src/World.cpp:150-153
+    const double infl = __ldg(r + 16);
+    const double h0 = __ldg(r + 13), h1 = __ldg(r + 14), h2 = __ldg(r + 15);
+    const double e0 = filling ? h0 : dadd(h0, infl), e1 = filling ? h1 : dadd(h1, infl), e2 = filling ? h2 : dadd(h2, infl);
+    const double a0 = dsub(a.x, __ldg(r + 6)), a1 = dsub(a.y, __ldg(r + 7)), a2 = dsub(a.z, __ldg(r + 8));
+    const double b0 = dsub(b.x, __ldg(r + 6)), b1 = dsub(b.y, __ldg(r + 7)), b2 = dsub(b.z, __ldg(r + 8));
+    const double r00 = __ldg(r + 9), r01 = __ldg(r + 10), r10 = __ldg(r + 11), r11 = __ldg(r + 12);
+    const double ax = dadd(dmul(r00, a0), dmul(r10, a1)), ay = dadd(dmul(r01, a0), dmul(r11, a1));
+    const double bx = dadd(dmul(r00, b0), dmul(r10, b1)), by = dadd(dmul(r01, b0), dmul(r11, b1));
+    if (fabs(ax) <= e0 && fabs(ay) <= e1 && fabs(a2) <= e2) return true; // end points first (src/OBB.cpp:13-18)
+    if (fabs(bx) <= e0 && fabs(by) <= e1 && fabs(b2) <= e2) return true;
+    double t_min = 0.0, t_max = 1.0;
+    if (!slab_axis(dsub(bx, ax), ax, dadd(h0, infl), t_min, t_max)) return false; // every type inflated (:28)
+    if (!slab_axis(dsub(by, ay), ay, dadd(h1, infl), t_min, t_max)) return false;
+    if (!slab_axis(dsub(b2, a2), a2, dadd(h2, infl), t_min, t_max)) return false;
+    return 0.0 <= t_min && t_min <= 1.0 && 0.0 <= t_max && t_max <= 1.0;
+}
+
 // Uniform grid: candidates = CSR list of the cell holding p.  The warp-pipelined form first asks an occupancy
 // bitmap over (coarsened) cells that lives in shared memory: in a 10 000-OBB world spread over 400 x 400 m a few
 // per cent of the states are in an occupied cell, the rest never touch global memory for the broad phase (with
@@ -253,9 +304,23 @@ struct PointWorld<EPP_BP_GRID> {
         const size_t b = occ_bit(wv, bx, by, bz);
         return (occ[b >> 5] >> (b & 31)) & 1u;
     }
+    // The cell's candidates from the records stored in cell order: one dependent round trip behind cell_start, two
+    // records in flight at a time (item -> AabbRec -> ObbRec was 3 round trips per candidate, one candidate at a time:
+    // ncu r02_b showed the warps of the 10 000-OBB run waiting on exactly those loads).
     __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &p, int mode, bool cpg, double md) const
     {
-        return any(wv, p, [&](int k) { return point_candidate_invalid(wv.aabb, wv.obb, k, p, mode, cpg, md); });
+        if (!wv.cell_recs) return any(wv, p, [&](int k) { return point_candidate_invalid(wv.aabb, wv.obb, k, p, mode, cpg, md); });
+        uint32_t s, e;
+        cell_range(wv, p, s, e);
+        for (uint32_t j = s; j < e; j += 2) {
+            const double *r0 = wv.cell_recs + (size_t)j * kCellRec;
+            const bool two = j + 1 < e;
+            const double *r1 = two ? r0 + kCellRec : r0;
+            const bool h0 = cellrec_point_invalid(r0, p, mode, cpg, md);
+            const bool h1 = cellrec_point_invalid(r1, p, mode, cpg, md);
+            if (h0 | h1) return true;
+        }
+        return false;
     }
 };
 
@@ -305,26 +370,28 @@ template <>
 struct RayWorld<EPP_BP_BITS> {
     const uint32_t *min_le;
     const uint32_t *max_ge;
+    const uint32_t *cmask;
     __device__ void init(const WorldView &wv, bool)
     {
         const int words = 3 * wv.nb * wv.Ws;
         uint32_t *dst = reinterpret_cast<uint32_t *>(g_smem);
         block_copy_words(dst, wv.bits_min_le, words);
         block_copy_words(dst + words, wv.bits_max_ge, words);
+        block_copy_words(dst + 2 * words, wv.bits_inside + wv.cmask_off, wv.cmask_words);
         __syncthreads();
         min_le = dst;
         max_ge = dst + words;
+        cmask = dst + 2 * words;
     }
     template <typename F>
     __device__ __forceinline__ bool any(const WorldView &wv, const P3 &mn, const P3 &mx, F f) const
     {
         const int nb = wv.nb, W = wv.W, Ws = wv.Ws;
-        const uint32_t *gx = max_ge + dev_key_bin(mn.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb) * Ws;
-        const uint32_t *gy = max_ge + (nb + dev_key_bin(mn.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb)) * Ws;
-        const uint32_t *gz = max_ge + (2 * nb + dev_key_bin(mn.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb)) * Ws;
-        const uint32_t *lx = min_le + dev_key_bin(mx.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb) * Ws;
-        const uint32_t *ly = min_le + (nb + dev_key_bin(mx.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb)) * Ws;
-        const uint32_t *lz = min_le + (2 * nb + dev_key_bin(mx.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb)) * Ws;
+        const int gx_ = dev_key_bin(mn.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb), lx_ = dev_key_bin(mx.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb);
+        const int gy_ = dev_key_bin(mn.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb), ly_ = dev_key_bin(mx.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb);
+        const int gz_ = dev_key_bin(mn.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb), lz_ = dev_key_bin(mx.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb);
+        const uint32_t *gx = max_ge + gx_ * Ws, *gy = max_ge + (nb + gy_) * Ws, *gz = max_ge + (2 * nb + gz_) * Ws;
+        const uint32_t *lx = min_le + lx_ * Ws, *ly = min_le + (nb + ly_) * Ws, *lz = min_le + (2 * nb + lz_) * Ws;
         if (W == 1) {
             uint32_t m = gx[0] & gy[0] & gz[0] & lx[0] & ly[0] & lz[0];
             while (m) {
@@ -334,12 +401,24 @@ struct RayWorld<EPP_BP_BITS> {
             }
             return false;
         }
-        // Pass 1, converged: which words of the candidate set are non-zero at all.  Walking the candidates inside this
-        // loop made the lanes of a warp drift through it separately (ncu: the row AND ran 2.6 x per warp).
+        // Pass 1, converged: which words can hold a candidate at all.  With the coarse-cell table: the OR of the word
+        // masks of the coarse cells under the ray box (a handful of reads); without it: the row AND of every word
+        // (6 rows x W reads — a fifth of K2's instructions on the 256-OBB world, ncu r01_ac).  Walking the candidates
+        // inside this loop made the lanes of a warp drift through it separately.
         uint32_t nz = 0u;
-        for (int w = 0; w < W; ++w)
-            if (gx[w] & gy[w] & gz[w] & lx[w] & ly[w] & lz[w]) nz |= 1u << w;
-        // Pass 2: the few non-zero words again, in order, with the exact tests
+        if (wv.cmask_words) {
+            const int x0 = gx_ >> wv.cshift[0], x1 = lx_ >> wv.cshift[0], y0 = gy_ >> wv.cshift[1], y1 = ly_ >> wv.cshift[1];
+            const int z0 = gz_ >> wv.cshift[2], z1 = lz_ >> wv.cshift[2];
+            for (int z = z0; z <= z1; ++z)
+                for (int y = y0; y <= y1; ++y) {
+                    const uint32_t *row = cmask + (z * wv.cn1 + y) * wv.cn0;
+                    for (int x = x0; x <= x1; ++x) nz |= row[x];
+                }
+        } else {
+            for (int w = 0; w < W; ++w)
+                if (gx[w] & gy[w] & gz[w] & lx[w] & ly[w] & lz[w]) nz |= 1u << w;
+        }
+        // Pass 2: those words, in order, with the exact tests
         while (nz) {
             const int w = __ffs(nz) - 1;
             nz &= nz - 1;
@@ -425,11 +504,35 @@ struct RayWorld<EPP_BP_GRID> {
             }
         return false;
     }
+    // Candidates from the records stored in cell order.  The cells of one (y, z) row under the ray box are consecutive,
+    // so their CSR ranges are too: one pair of cell_start reads per row, then the row's records back to back.  A copy
+    // is evaluated only in the first cell of (ray cells) x (the OBB's cells) — both are in the record.
+    __device__ __forceinline__ bool walk_recs(const WorldView &wv, const P3 &a, const P3 &b, const P3 &mn, const P3 &mx, bool cpg) const
+    {
+        const AxisBins &g = wv.gbins;
+        int x0, x1, y0, y1, z0, z1;
+        cells_of(wv, mn, mx, x0, x1, y0, y1, z0, z1);
+        for (int z = z0; z <= z1; ++z)
+            for (int y = y0; y <= y1; ++y) {
+                const size_t row = ((size_t)z * g.n[1] + y) * g.n[0];
+                const uint32_t s = __ldg(wv.cell_start + row + x0), e = __ldg(wv.cell_start + row + x1 + 1);
+                for (uint32_t j = s; j < e; ++j) {
+                    const double *r = wv.cell_recs + (size_t)j * kCellRec;
+                    const uint64_t own = (uint64_t)__double_as_longlong(__ldg(r + 17)), here = (uint64_t)__double_as_longlong(__ldg(r + 18));
+                    const int kx = (int)((own >> 2) & 0xFFFFF), ky = (int)((own >> 22) & 0xFFFFF), kz = (int)((own >> 42) & 0xFFFFF);
+                    const int cx = (int)(here & 0xFFFFF), cy = (int)((here >> 20) & 0xFFFFF), cz = (int)((here >> 40) & 0xFFFFF);
+                    if (cx != (kx > x0 ? kx : x0) || cy != (ky > y0 ? ky : y0) || cz != (kz > z0 ? kz : z0)) continue;
+                    if (cellrec_ray_invalid(r, a, b, mn, mx, cpg)) return true;
+                }
+            }
+        return false;
+    }
     __device__ __forceinline__ bool invalid(const WorldView &wv, const P3 &a, const P3 &b, bool cpg) const
     {
         P3 mn, mx;
         ray_box(a, b, mn, mx);
         if (!has_candidates_t<true>(wv, mn, mx)) return false; // direct form: the bitmap is read from global memory
+        if (wv.cell_recs) return walk_recs(wv, a, b, mn, mx, cpg);
         return any(wv, mn, mx, [&](int k) -> bool { return ray_candidate_invalid(wv.aabb, wv.obb, k, a, b, mn, mx, cpg); });
     }
 };
@@ -745,10 +848,15 @@ __device__ __forceinline__ uint32_t warp_states_step(const PointWorld<BP> &world
             const int unit = queue[q];
             const P3 p = SOA ? P3{pts[unit], pts[S * 32 + unit], pts[2 * S * 32 + unit]}
                              : P3{pts[3 * unit], pts[3 * unit + 1], pts[3 * unit + 2]};
-            const bool hit = world.any(wv, p, [&](int k) -> bool {
-                if (RS) return rec_hit(rec + k * kRecDoubles, p);
-                return point_candidate_invalid(wv.aabb, wv.obb, k, p, mode, cpg, md);
-            });
+            bool hit;
+            if constexpr (BP == EPP_BP_GRID) {
+                hit = world.invalid(wv, p, mode, cpg, md); // records in cell order when the world has them
+            } else {
+                hit = world.any(wv, p, [&](int k) -> bool {
+                    if (RS) return rec_hit(rec + k * kRecDoubles, p);
+                    return point_candidate_invalid(wv.aabb, wv.obb, k, p, mode, cpg, md);
+                });
+            }
             if (hit) atomicOr(&inv[unit >> 5], 1u << (unit & 31));
         }
         __syncwarp();
@@ -787,7 +895,7 @@ struct TrajArgs {
 
 // Block = 1 producer warp + up to 31 consumer warps, one block per SM by default.  Block b owns words
 // [b*wpb + min(b, rem), +wpb + (b < rem)) (the host passes wpb = words / blocks and rem = words % blocks, so no
-// thread divides) and cuts them into chunks of S words.  Chunks flow through a block-wide ring of 2^log2_slots
+// thread divides) and cuts them into chunks of S words.  Chunks flow through a block-wide ring of n_slots (<= 64)
 // shared-memory slots:
 //   producer   lane l issues chunks l, l+32, ... in order (cp.async.bulk, `full` barrier of the slot), waiting
 //              on the slot's `empty` barrier once the ring has wrapped;
@@ -812,7 +920,7 @@ __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
 template <int BP, int S, bool RS, bool GA, bool TR = false>
 __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const double *__restrict__ xyz, size_t n, int mode,
                                                       int can_pass_gate, double min_distance, int aabb_in_smem,
-                                                      int log2_slots, uint32_t table_bytes, uint32_t rec_bytes,
+                                                      uint32_t n_slots, uint32_t table_bytes, uint32_t rec_bytes,
                                                       uint32_t wpb, uint32_t rem, uint32_t *__restrict__ mask,
                                                       const __grid_constant__ GatherView gv, uint32_t ga_group,
                                                       const __grid_constant__ TrajArgs ta)
@@ -828,7 +936,7 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
     const uint32_t consumers = (blockDim.x >> 5) - 1u;
     const bool cpg = can_pass_gate != 0;
     constexpr uint32_t kSlotBytes = S * kWordBytes;
-    const uint32_t slots = 1u << log2_slots, slot_mask = slots - 1u;
+    const uint32_t slots = n_slots;
     // shared memory: [broad-phase table][records][ring][per consumer: byte queue (S*32) | invalid words (32 B)]
     double *rec = reinterpret_cast<double *>(g_smem + table_bytes);
     unsigned char *ring = g_smem + table_bytes + rec_bytes;
@@ -924,13 +1032,12 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
 
     if (warp == 0) {
         // ---- producer
-        // Waves of min(32, slots) chunks: a slot is armed by one lane per wave, in program order, so a lane
-        // never waits on a phase of `empty` that lies more than one behind the barrier's current phase.
-        const uint32_t wave = slots < 32u ? slots : 32u;
-        for (uint32_t base = 0; base < chunks; base += wave) {
-            const uint32_t i = base + (uint32_t)lane;
-            if ((uint32_t)lane >= wave || i >= chunks) continue;
-            const uint32_t slot = i & slot_mask, round = i >> log2_slots;
+        // Lane l owns ring slots l and l + 32 and arms them round after round, in program order, so a lane never
+        // waits on a phase of `empty` that lies more than one behind the barrier's current phase (any slot count).
+        for (uint32_t round = 0; round * slots + (uint32_t)lane < chunks; ++round)
+        for (uint32_t slot = (uint32_t)lane; slot < slots; slot += 32u) {
+            const uint32_t i = round * slots + slot;
+            if (i >= chunks) break;
             if (round > 0) mbar_wait(&s_empty[slot], (round - 1u) & 1u);
             const int units = chunk_units(i);
             if (by_tma(units)) {
@@ -999,7 +1106,7 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
         if (lane == 0) i = atomicAdd(&s_next, 1u);
         i = __shfl_sync(0xffffffffu, i, 0);
         if (i >= chunks) break;
-        const uint32_t slot = i & slot_mask, round = i >> log2_slots;
+        const uint32_t round = i / slots, slot = i - round * slots;
         const int units = chunk_units(i);
         double *pts = reinterpret_cast<double *>(ring + slot * kSlotBytes);
         // A parity wait is only meaningful while the barrier is in phase `round` or `round + 1`.  Chunk numbers
@@ -1308,23 +1415,23 @@ __global__ void __launch_bounds__(1024, 1) k_segments_warp(WorldView wv, const d
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     if (warp == 0) {
-        // ---- producer: waves of min(32, slots) chunks; slots is <= 32 or a multiple of 32 (launcher), so a slot is
-        // always armed by the same lane, in program order
-        const uint32_t wave = slots < 32u ? slots : 32u;
-        for (uint32_t base = 0; base < chunks; base += wave) {
-            const uint32_t i = base + (uint32_t)lane;
-            if ((uint32_t)lane >= wave || i >= chunks) continue;
-            const uint32_t slot = i % slots, round = i / slots;
-            if (round > 0) mbar_wait(&s_empty[slot], (round - 1u) & 1u);
-            const int units = chunk_units(i);
-            if (by_tma(units)) {
-                unsigned char *dst = ring + slot * kSegSlotBytes;
-                const size_t off = (size_t)(b0 + i * S) * 96;
-                mbar_expect_tx(&s_full[slot], (uint32_t)units * 48u);
-                bulk_g2s(dst, pa + off, (uint32_t)units * 24u, &s_full[slot]);
-                bulk_g2s(dst + S * kWordBytes, pb + off, (uint32_t)units * 24u, &s_full[slot]);
-            } else {
-                mbar_arrive(&s_full[slot]);
+        // ---- producer: lane l owns ring slots l and l + 32 and arms them round after round, in program order (a
+        // parity wait on `empty` is only meaningful one phase behind the barrier, so a slot never changes hands)
+        for (uint32_t round = 0; round * slots + (uint32_t)lane < chunks; ++round) {
+            for (uint32_t slot = (uint32_t)lane; slot < slots; slot += 32u) {
+                const uint32_t i = round * slots + slot;
+                if (i >= chunks) break;
+                if (round > 0) mbar_wait(&s_empty[slot], (round - 1u) & 1u);
+                const int units = chunk_units(i);
+                if (by_tma(units)) {
+                    unsigned char *dst = ring + slot * kSegSlotBytes;
+                    const size_t off = (size_t)(b0 + i * S) * 96;
+                    mbar_expect_tx(&s_full[slot], (uint32_t)units * 48u);
+                    bulk_g2s(dst, pa + off, (uint32_t)units * 24u, &s_full[slot]);
+                    bulk_g2s(dst + S * kWordBytes, pb + off, (uint32_t)units * 24u, &s_full[slot]);
+                } else {
+                    mbar_arrive(&s_full[slot]);
+                }
             }
         }
         return;
@@ -1394,9 +1501,10 @@ __global__ void __launch_bounds__(1024, 1) k_segments_warp(WorldView wv, const d
                     const P3 b = {B[3 * unit], B[3 * unit + 1], B[3 * unit + 2]};
                     P3 mn, mx;
                     ray_box(a, b, mn, mx);
-                    const bool hit = world.any(wv, mn, mx, [&](int k) -> bool {
-                        return ray_candidate_invalid(wv.aabb, wv.obb, k, a, b, mn, mx, cpg);
-                    });
+                    const bool hit = wv.cell_recs ? world.walk_recs(wv, a, b, mn, mx, cpg)
+                                                  : world.any(wv, mn, mx, [&](int k) -> bool {
+                                                        return ray_candidate_invalid(wv.aabb, wv.obb, k, a, b, mn, mx, cpg);
+                                                    });
                     if (hit) atomicOr(&inv[unit >> 5], 1u << (unit & 31));
                 }
                 __syncwarp();
@@ -1652,11 +1760,12 @@ __global__ void __launch_bounds__(kPolyThreads) k_poly_traj(WorldView wv, const 
     }
 
     // ---- consumers
+    const uint32_t gb_magic = Gb > 1u ? (uint32_t)(0x100000000ull / Gb) + ((0x100000000ull % Gb) ? 1u : 0u) : 0u;
     for (;;) {
         uint32_t i = 0;
         if (lane == 0) i = atomicAdd(&s_next, 1u);
         i = __shfl_sync(0xffffffffu, i, 0);
-        const uint32_t round = i / Gb, j = i - round * Gb;
+        const uint32_t round = Gb == 1u ? i : __umulhi(i, gb_magic), j = i - round * Gb; // i / Gb (exact for i < 2^27)
         bool gone = false;
         for (;;) { // wait for the round, or learn that it will never come
             uint32_t p, t;
@@ -1667,6 +1776,7 @@ __global__ void __launch_bounds__(kPolyThreads) k_poly_traj(WorldView wv, const 
                 gone = true;
                 break;
             }
+            __nanosleep(200); // a spinning consumer takes issue slots from the producer it is waiting for (ncu r02_b: 37 %)
         }
         if (gone) break;
         const uint32_t slot = round % kPolyRing;
@@ -1916,7 +2026,7 @@ __global__ void __launch_bounds__(kBlock) k_count_candidates(WorldView wv, const
 size_t point_smem_bytes(const WorldView &wv, int bp, bool &aabb_in_smem)
 {
     aabb_in_smem = false;
-    if (bp == EPP_BP_BITS) return (size_t)3 * wv.nb * wv.Ws * 4;
+    if (bp == EPP_BP_BITS) return (size_t)(wv.cmask_words ? wv.cmask_off + wv.cmask_words : 3 * wv.nb * wv.Ws) * 4;
     if (bp == EPP_BP_BRUTE && wv.M <= 2048) {
         aabb_in_smem = true;
         return (size_t)wv.M * sizeof(AabbRec);
@@ -1927,7 +2037,7 @@ size_t point_smem_bytes(const WorldView &wv, int bp, bool &aabb_in_smem)
 size_t ray_smem_bytes(const WorldView &wv, int bp, bool &aabb_in_smem)
 {
     aabb_in_smem = false;
-    if (bp == EPP_BP_BITS) return (size_t)6 * wv.nb * wv.Ws * 4;
+    if (bp == EPP_BP_BITS) return ((size_t)6 * wv.nb * wv.Ws + wv.cmask_words) * 4;
     if (bp == EPP_BP_BRUTE && wv.M <= 2048) {
         aabb_in_smem = true;
         return (size_t)wv.M * sizeof(AabbRec);
@@ -2020,18 +2130,17 @@ cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const 
     const size_t ga_bytes = ga_group ? (size_t)kGaStageWords * 4 + (kGaStageWords / S) * 4 : 0;
     const size_t fixed = table_bytes + rec_bytes + cons * warp_bytes + ga_bytes;
     if (fixed + 2 * slot_bytes > budget) return cudaSuccess;
-    int log2_slots = 1;
-    while (log2_slots < 6 && fixed + (slot_bytes << (log2_slots + 1)) <= budget &&
-           ((size_t)1 << log2_slots) < chunks_per_block)
-        ++log2_slots;
-    if (cfg.states_warp_log2_slots > 0 && cfg.states_warp_log2_slots < log2_slots) log2_slots = cfg.states_warp_log2_slots;
+    size_t slots = (budget - fixed) / slot_bytes;
+    slots = slots > (size_t)kMaxSlots ? (size_t)kMaxSlots : slots;
+    if (slots > chunks_per_block) slots = chunks_per_block < 2 ? 2 : chunks_per_block;
+    if (cfg.states_warp_log2_slots > 0 && ((size_t)1 << cfg.states_warp_log2_slots) < slots) slots = (size_t)1 << cfg.states_warp_log2_slots;
     // A consumer that takes chunk i waits on phase (i / slots) of the slot's `full` barrier; that is only
     // well defined if chunk i - slots has been consumed, which in-order hand-out guarantees iff slots >= consumers.
-    if (cons > (1 << log2_slots)) cons = 1 << log2_slots;
+    if ((size_t)cons > slots) cons = (int)slots;
     // records are folded by one consumer thread each: a batch too small for M consumer threads per block takes
     // the records from global memory instead (the caller retries with RS = false)
     if (RS && cons * 32 < wv.M) return cudaSuccess;
-    const size_t smem = fixed + (slot_bytes << log2_slots);
+    const size_t smem = fixed + slot_bytes * slots;
     // ownership is handed out in words for state batches and in whole chunks for trajectory matrices
     const size_t own_units = TR ? chunks_total : words;
     cudaError_t err = cudaFuncSetAttribute(k_states_warp<BP, S, RS, GA, TR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -2047,7 +2156,7 @@ cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const 
     lc.attrs = attr;
     lc.numAttrs = cfg.states_pdl ? 1 : 0;
     err = cudaLaunchKernelEx(&lc, k_states_warp<BP, S, RS, GA, TR>, wv, d_xyz, n, mode | (cfg.states_debug << 8),
-                             can_pass_gate, min_distance, in_smem ? 1 : 0, log2_slots, (uint32_t)table_bytes,
+                             can_pass_gate, min_distance, in_smem ? 1 : 0, (uint32_t)slots, (uint32_t)table_bytes,
                              (uint32_t)rec_bytes, (uint32_t)(own_units / grid), (uint32_t)(own_units % grid), d_mask, gv,
                              ga_group, ta);
     if (err != cudaSuccess) return err;
@@ -2161,8 +2270,7 @@ cudaError_t launch_segments_warp(const LaunchCfg &cfg, const WorldView &wv, cons
     size_t slots = (budget - fixed) / kSegSlotBytes;
     if (slots > chunks_per_block) slots = chunks_per_block < 2 ? 2 : chunks_per_block;
     if (cfg.segments_warp_slots > 0 && (size_t)cfg.segments_warp_slots < slots) slots = cfg.segments_warp_slots;
-    // a slot must always be armed by the same producer lane: <= 32 slots, or a multiple of 32
-    slots = slots >= (size_t)kSegMaxSlots ? (size_t)kSegMaxSlots : (slots > 32 ? 32 : slots);
+    slots = slots >= (size_t)kSegMaxSlots ? (size_t)kSegMaxSlots : slots;
     if (slots < 2) slots = 2;
     if ((size_t)cons > slots) cons = (int)slots; // in-order hand-out needs slots >= consumers (see k_states_warp)
     const size_t smem = fixed + slots * kSegSlotBytes;
@@ -2353,7 +2461,7 @@ cudaError_t launch_poly_trajectories(const LaunchCfg &cfg, const WorldView &wv, 
     int G = cfg.poly_traj_per_warp;
     if (G <= 0) {
         G = 32;
-        while (G > 4 && n_traj / (size_t)G < (size_t)cfg.sm_count * 6) G >>= 1;
+        while (G > 4 && (n_traj + G - 1) / (size_t)G < (size_t)cfg.sm_count * 4) G >>= 1;
     }
     G = G > 32 ? 32 : (G < 1 ? 1 : G);
     const unsigned grid = (unsigned)((n_traj + G - 1) / G);

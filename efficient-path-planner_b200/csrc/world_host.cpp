@@ -362,6 +362,68 @@ void build_bits(const std::vector<AabbRec> &aabbs, int bins_per_axis, BitsTables
                     if ((*t)[row * out.Ws + w]) summary |= 1u << w;
                 (*t)[row * out.Ws + out.W] = summary;
             }
+    // coarse cell -> word mask (W > 1 only), appended to `inside`
+    out.cmask_off = out.cmask_words = 0;
+    if (out.W > 1) {
+        for (int a = 0; a < 3; ++a) {
+            const int target = a == 2 ? 4 : 32; // the planner's worlds are flat
+            out.cshift[a] = 0;
+            while (((out.nb - 1) >> out.cshift[a]) + 1 > target + 1) ++out.cshift[a];
+            out.cn[a] = ((out.nb - 1) >> out.cshift[a]) + 1;
+        }
+        out.cmask_off = static_cast<int>((words + 3) / 4 * 4);
+        out.cmask_words = out.cn[0] * out.cn[1] * out.cn[2];
+        out.inside.resize(static_cast<size_t>(out.cmask_off) + out.cmask_words + 4, 0u);
+        uint32_t *cm = out.inside.data() + out.cmask_off;
+        for (int k = 0; k < M; ++k) {
+            int c0[3], c1[3];
+            for (int a = 0; a < 3; ++a) {
+                c0[a] = host_key_bin(aabbs[k].mn[a], out.bins.off[a], out.bins.h0[a], out.bins.shift[a], out.nb) >> out.cshift[a];
+                c1[a] = host_key_bin(aabbs[k].mx[a], out.bins.off[a], out.bins.h0[a], out.bins.shift[a], out.nb) >> out.cshift[a];
+            }
+            for (int z = c0[2]; z <= c1[2]; ++z)
+                for (int y = c0[1]; y <= c1[1]; ++y)
+                    for (int x = c0[0]; x <= c1[0]; ++x)
+                        cm[(static_cast<size_t>(z) * out.cn[1] + y) * out.cn[0] + x] |= 1u << (k >> 5);
+        }
+    }
+}
+
+void morton_sort(std::vector<AabbRec> &aabbs, std::vector<ObbRec> &obbs)
+{
+    const size_t M = aabbs.size();
+    if (M < 2) return;
+    double lo[3], hi[3];
+    world_extent(aabbs, lo, hi);
+    auto spread = [](uint32_t v) { // 16 bits -> every second bit
+        uint64_t x = v & 0xffffu;
+        x = (x | (x << 8)) & 0x00ff00ffull;
+        x = (x | (x << 4)) & 0x0f0f0f0full;
+        x = (x | (x << 2)) & 0x33333333ull;
+        x = (x | (x << 1)) & 0x55555555ull;
+        return x;
+    };
+    std::vector<std::pair<uint64_t, uint32_t>> key(M);
+    for (size_t k = 0; k < M; ++k) {
+        uint32_t q[2];
+        for (int a = 0; a < 2; ++a) {
+            const double span = hi[a] - lo[a];
+            double u = span > 0.0 ? (0.5 * (aabbs[k].mn[a] + aabbs[k].mx[a]) - lo[a]) / span : 0.0;
+            if (!(u >= 0.0)) u = 0.0;
+            if (u > 1.0) u = 1.0;
+            q[a] = static_cast<uint32_t>(u * 65535.0);
+        }
+        key[k] = {spread(q[0]) | (spread(q[1]) << 1), static_cast<uint32_t>(k)};
+    }
+    std::stable_sort(key.begin(), key.end());
+    std::vector<AabbRec> a2(M);
+    std::vector<ObbRec> o2(M);
+    for (size_t k = 0; k < M; ++k) {
+        a2[k] = aabbs[key[k].second];
+        o2[k] = obbs[key[k].second];
+    }
+    aabbs.swap(a2);
+    obbs.swap(o2);
 }
 
 void build_grid(const std::vector<AabbRec> &aabbs, std::vector<ObbRec> &obbs, long max_cells,
@@ -424,6 +486,42 @@ void build_grid(const std::vector<AabbRec> &aabbs, std::vector<ObbRec> &obbs, lo
             for (int y = b0[3 * k + 1]; y <= b1[3 * k + 1]; ++y)
                 for (int x = b0[3 * k]; x <= b1[3 * k]; ++x)
                     out.cell_items[cursor[cell_id(x, y, z)]++] = static_cast<uint32_t>(k);
+
+    // Records in cell order (only meaningful when every rotation is about z and cells fit 20 bits per axis)
+    out.cell_recs.clear();
+    bool zrot = n[0] < (1 << 20) && n[1] < (1 << 20) && n[2] < (1 << 20);
+    for (size_t k = 0; k < M && zrot; ++k) {
+        const double *r = obbs[k].rot;
+        if (r[2] != 0.0 || r[5] != 0.0 || r[6] != 0.0 || r[7] != 0.0 || r[8] != 1.0) zrot = false;
+    }
+    if (zrot) {
+        out.cell_recs.assign(out.cell_items.size() * static_cast<size_t>(kCellRec), 0.0);
+        for (int z = 0; z < n[2]; ++z)
+            for (int y = 0; y < n[1]; ++y)
+                for (int x = 0; x < n[0]; ++x) {
+                    const size_t c = cell_id(x, y, z);
+                    for (uint32_t j = out.cell_start[c]; j < out.cell_start[c + 1]; ++j) {
+                        const size_t k = out.cell_items[j];
+                        double *rec = out.cell_recs.data() + static_cast<size_t>(j) * kCellRec;
+                        for (int a = 0; a < 3; ++a) {
+                            rec[a] = aabbs[k].mn[a];
+                            rec[3 + a] = aabbs[k].mx[a];
+                            rec[6 + a] = obbs[k].center[a];
+                            rec[13 + a] = obbs[k].half[a];
+                        }
+                        rec[9] = obbs[k].rot[0];
+                        rec[10] = obbs[k].rot[1];
+                        rec[11] = obbs[k].rot[3];
+                        rec[12] = obbs[k].rot[4];
+                        rec[16] = obbs[k].inflate;
+                        const uint64_t own = static_cast<uint64_t>(obbs[k].flags & 3u) | (static_cast<uint64_t>(b0[3 * k]) << 2) |
+                                             (static_cast<uint64_t>(b0[3 * k + 1]) << 22) | (static_cast<uint64_t>(b0[3 * k + 2]) << 42);
+                        const uint64_t here = static_cast<uint64_t>(x) | (static_cast<uint64_t>(y) << 20) | (static_cast<uint64_t>(z) << 40);
+                        std::memcpy(rec + 17, &own, 8);
+                        std::memcpy(rec + 18, &here, 8);
+                    }
+                }
+    }
 
     // Occupancy bitmap over coarsened cells: fold z first (worlds of this planner are flat: 400 x 400 x 4 m), then
     // x and y together, until the map fits its shared-memory budget.

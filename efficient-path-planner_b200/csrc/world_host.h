@@ -34,6 +34,7 @@ struct ObbRec {
 static_assert(sizeof(AabbRec) == 48, "AabbRec layout");
 static_assert(sizeof(ObbRec) == 144, "ObbRec layout");
 
+constexpr int kCellRec = 19;
 constexpr uint32_t kFlagFilling = 1u;
 constexpr uint32_t kFlagGate = 2u;
 
@@ -67,6 +68,14 @@ struct BitsTables {
     int W = 0;  // 32-bit words per bin = ceil(M / 32)
     int Ws = 0; // row stride in words: 1 for W = 1, else (W + 1) | 1 — W words, a summary word at index W, odd stride
     KeyBins bins{};
+    // W > 1: coarse 3-D cells (coarse bin = bin >> cshift) -> which WORDS hold an OBB whose bin range overlaps the cell;
+    // appended to `inside` at word offset cmask_off (a multiple of 4) so that one copy brings both on chip.  A query
+    // ORs the masks of the coarse cells it covers and looks at those words only (records are Morton-sorted at commit,
+    // so the OBBs of a word are neighbours and a cell names one or two words).
+    int cmask_off = 0;
+    int cmask_words = 0;
+    int cn[3] = {1, 1, 1};
+    int cshift[3] = {0, 0, 0};
     std::vector<uint32_t> inside; // k set iff bin(min_k) <= b <= bin(max_k)
     std::vector<uint32_t> min_le; // k set iff bin(min_k) <= b
     std::vector<uint32_t> max_ge; // k set iff bin(max_k) >= b
@@ -77,6 +86,12 @@ struct GridTables {
     AxisBins bins{};
     std::vector<uint32_t> cell_start; // ncell + 1
     std::vector<uint32_t> cell_items;
+    // Records in CELL order (z-rotated worlds): kCellRec doubles per entry of cell_items, so that a query reads a cell's
+    // candidates from consecutive memory right behind the cell_start lookup instead of chasing item -> AabbRec -> ObbRec:
+    // [0..5] stored AABB, [6..8] centre, [9..12] R(0,0) R(0,1) R(1,0) R(1,1), [13..15] half sizes, [16] inflate,
+    // [17] bits: flags (2) | min cell of the OBB's AABB x, y, z (20 bits each, from bit 2), [18] bits: the cell this
+    // copy is listed in, x, y, z (20 bits each).
+    std::vector<double> cell_recs;
     // Occupancy bitmap: one bit per COARSE cell (fine cell index >> occ_shift per axis), set iff any fine cell
     // under it has an item.  Sized to live in shared memory (occ_budget_bytes): a unit whose coarse cells are
     // all clear has no candidate and never touches cell_start / cell_items.
@@ -141,6 +156,10 @@ void obb_aabb(const HostObb &o, double inflate, double mn[3], double mx[3]);
 
 // Broad-phase construction over flattened records.
 void build_bits(const std::vector<AabbRec> &aabbs, int bins_per_axis, BitsTables &out);
+// Reorders the records along a Morton curve over the stored-AABB centres (x, y): neighbours in space become
+// neighbours in index.  Results are order-independent (any hit invalidates), the broad phases get spatially coherent
+// words / cell lists.
+void morton_sort(std::vector<AabbRec> &aabbs, std::vector<ObbRec> &obbs);
 void build_grid(const std::vector<AabbRec> &aabbs, std::vector<ObbRec> &obbs, long max_cells,
                 GridTables &out, long occ_budget_bytes = 72 * 1024);
 
