@@ -8,6 +8,7 @@
 #include <chrono>
 #include <cmath>
 #include <cstring>
+#include <limits>
 #include <memory>
 #include <mutex>
 #include <new>
@@ -78,6 +79,9 @@ Knob g_knobs[] = {
     {"grid_occ_kb", {72}},
     {"grid_cell_recs", {1}},             // grid: candidates read from records stored in cell order (0: item -> AabbRec -> ObbRec); read at commit
     {"states_table_copies", {1}},        // worlds of <= 32 OBBs: copies of the bin table in separate bank groups (1, 2, 4, 8, 16); read at commit
+    {"bits_range_d", {5}},               // bits broad phase, rays: (first bin, span) rows for boxes spanning < d bins on x and y (0: cumulative rows only); read at commit
+    {"states_skip_dense_z", {1}},        // worlds of <= 32 OBBs: phase 1 of K1 skips the z rows when they are more than half full; read at commit
+    {"segments_recs_at_commit", {1}},    // K2: folded records for both canPassGate values built at commit (0: folded per block); read at commit
     {"bits_cmask", {1}},                 // bits broad phase, W > 1: coarse-cell word masks (0: round-1 summaries); read at commit
     {"morton_sort", {1}},                // device records along a Morton curve (worlds of > 32 OBBs); read at commit
     {"single_mailbox", {1}},             // epp_is_valid / epp_check_motion through the resident mailbox warp (0: launch + sync per call)
@@ -656,7 +660,7 @@ extern "C" int epp_world_commit(epp_world *w)
         int nb = knob_value("bits_bins");
         const int W = std::max(1, (M + 31) / 32);
         if (nb <= 0) nb = W == 1 ? 256 : (W <= 8 ? 128 : (W <= 32 ? 64 : 32));
-        build_bits(aabbs, nb, bits);
+        build_bits(aabbs, nb, bits, knob_value("bits_range_d"));
     }
     // W == 1: copies of the `inside` table in separate bank groups for the warp form of K1 (WorldView::rep_B)
     std::vector<uint32_t> inside_rep;
@@ -674,6 +678,37 @@ extern "C" int epp_world_commit(epp_world *w)
     if (bp == EPP_BP_GRID)
         build_grid(aabbs, obbs, knob_value("grid_max_cells"), grid, (long)knob_value("grid_occ_kb") * 1024);
 
+    // K2's per-call record fold (kernels.cu fold_ray_records) depends on the call only through canPassGate: both
+    // variants are built here once per epoch so the kernel can take them with one bulk copy.
+    std::vector<double> ray_recs;
+    {
+        bool zr = M > 0 && M <= 256;
+        for (const ObbRec &o : obbs)
+            if (o.rot[2] != 0.0 || o.rot[5] != 0.0 || o.rot[6] != 0.0 || o.rot[7] != 0.0 || o.rot[8] != 1.0) zr = false;
+        if (zr && knob_value("segments_recs_at_commit")) {
+            ray_recs.assign((size_t)2 * M * 21 + 2, 0.0);
+            for (int cpg = 0; cpg < 2; ++cpg)
+                for (int k = 0; k < M; ++k) {
+                    double *r = ray_recs.data() + ((size_t)cpg * M + k) * 21;
+                    const bool filling = (obbs[k].flags & kFlagFilling) != 0;
+                    for (int d = 0; d < 3; ++d) {
+                        r[d] = aabbs[k].mn[d];
+                        r[3 + d] = aabbs[k].mx[d];
+                        r[6 + d] = obbs[k].center[d];
+                        const double h = obbs[k].half[d];
+                        const double hi = h + obbs[k].inflate;
+                        r[13 + d] = filling ? h : hi;
+                        r[16 + d] = hi;
+                    }
+                    if (filling && cpg) r[0] = std::numeric_limits<double>::infinity();
+                    r[9] = obbs[k].rot[0];
+                    r[10] = obbs[k].rot[1];
+                    r[11] = obbs[k].rot[3];
+                    r[12] = obbs[k].rot[4];
+                }
+        }
+    }
+
     // One blob: [aabb][obb][bits inside|min_le|max_ge][cell_start][cell_items], 256 B aligned parts.
     struct Part {
         const void *src;
@@ -686,7 +721,9 @@ extern "C" int epp_world_commit(epp_world *w)
         {bits.max_ge.data(), bits.max_ge.size() * 4, 0},        {grid.cell_start.data(), grid.cell_start.size() * 4, 0},
         {grid.cell_items.data(), grid.cell_items.size() * 4, 0}, {grid.occ.data(), grid.occ.size() * 4, 0},
         {inside_rep.data(), inside_rep.size() * 4, 0},
-        {grid.cell_recs.data(), grid.cell_recs.size() * 8, 0}};
+        {grid.cell_recs.data(), grid.cell_recs.size() * 8, 0},
+        {bits.range.data(), bits.range.size() * 4, 0},
+        {ray_recs.data(), ray_recs.size() * 8, 0}};
     size_t total = 0;
     for (Part &p : parts) {
         p.off = total;
@@ -708,6 +745,9 @@ extern "C" int epp_world_commit(epp_world *w)
     v.bits_inside = (const uint32_t *)(base + parts[2].off);
     v.bits_min_le = (const uint32_t *)(base + parts[3].off);
     v.bits_max_ge = (const uint32_t *)(base + parts[4].off);
+    v.ray_recs = ray_recs.empty() ? nullptr : (const double *)(base + parts[11].off);
+    v.bits_range = (const uint32_t *)(base + parts[10].off);
+    v.range_d = bits.range.empty() ? 0 : bits.range_d;
     v.nb = bits.nb;
     v.W = bits.W;
     v.Ws = bits.Ws;
@@ -719,6 +759,13 @@ extern "C" int epp_world_commit(epp_world *w)
     for (int a = 0; a < 3; ++a) v.cshift[a] = bits.cshift[a];
     v.bits_inside_rep = (const uint32_t *)(base + parts[8].off);
     v.rep_B = rep_B;
+    // z rows that are mostly full do not pay for their lookups in phase 1 of the warp form (see PointWorld<kBpBits1>)
+    v.skip_axis = -1;
+    if (bp == EPP_BP_BITS && bits.W == 1 && M > 0 && knob_value("states_skip_dense_z")) {
+        size_t set = 0;
+        for (int b = 0; b < bits.nb; ++b) set += (size_t)__builtin_popcount(bits.inside[(size_t)2 * bits.nb + b]);
+        if ((double)set > 0.5 * (double)bits.nb * (double)M) v.skip_axis = 2;
+    }
     v.zrot = 1;
     for (const ObbRec &o : obbs)
         if (o.rot[2] != 0.0 || o.rot[5] != 0.0 || o.rot[6] != 0.0 || o.rot[7] != 0.0 || o.rot[8] != 1.0) v.zrot = 0;

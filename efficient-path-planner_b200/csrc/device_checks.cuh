@@ -26,6 +26,11 @@ struct WorldView {
     const uint32_t *bits_inside;
     const uint32_t *bits_min_le;
     const uint32_t *bits_max_ge;
+    // worlds of <= 256 z-rotated OBBs: K2's folded 21-double records (kernels.cu kRayRec) for canPassGate = false and,
+    // M records further, for canPassGate = true, built at commit; null: the kernels fold them per block
+    const double *ray_recs;
+    const uint32_t *bits_range; // BitsTables::range ((first bin, span) rows of x and y); range_d == 0: absent
+    int range_d;
     int nb;
     int W;
     int Ws; // row stride of the bits tables in words (W = 1: 1; else (W + 1) | 1 with a summary word at index W)
@@ -37,6 +42,7 @@ struct WorldView {
     // of word i at ((i / rep_B) * 32 + r * rep_B + i % rep_B); rep_B == 32: not replicated (bits_inside_rep unused)
     const uint32_t *bits_inside_rep;
     int rep_B;
+    int skip_axis; // W == 1, warp form of K1: axis left out of phase 1's "any candidate?" question (-1: none); see capi.cu
     int zrot; // every OBB rotation is a rotation about z (rot[2,5,6,7] == 0, rot[8] == 1)
     // EPP_BP_GRID
     const uint32_t *cell_start;

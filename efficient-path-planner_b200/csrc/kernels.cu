@@ -200,8 +200,17 @@ struct PointWorld<kBpBits1> {
         }
         return false;
     }
+    // Phase 1 only asks WHETHER a state has candidates.  An axis whose rows are nearly full (z on the race track:
+    // every box stands on the floor) filters almost nothing but costs a third of the lookups; leaving it out queues a
+    // few more states for phase 2, which evaluates up to 32 queued states per round at the same cost.
     __device__ __forceinline__ bool has_candidates(const WorldView &wv, const P3 &p) const
     {
+        if (wv.skip_axis == 2) {
+            const int nb = wv.nb;
+            const int bx = dev_key_bin(p.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb);
+            const int by = dev_key_bin(p.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb);
+            return (look(bx) & look(nb + by)) != 0u;
+        }
         return candidates(wv, p) != 0u;
     }
 };
@@ -324,6 +333,14 @@ struct PointWorld<EPP_BP_GRID> {
     }
 };
 
+// PointWorld<GRID>::invalid as a free function (callable from code that is compiled, but never run, for other BP)
+__device__ __forceinline__ bool world_invalid_grid(const WorldView &wv, const P3 &p, int mode, bool cpg, double md)
+{
+    PointWorld<EPP_BP_GRID> w;
+    w.occ = nullptr;
+    return w.invalid(wv, p, mode, cpg, md);
+}
+
 // ---- segment queries ---------------------------------------------------------------------
 
 template <int BP>
@@ -344,6 +361,7 @@ struct RayWorld<EPP_BP_BRUTE> {
             aabb = reinterpret_cast<const AabbRec *>(g_smem);
         }
     }
+    __device__ void bind(const WorldView &) {}
     template <typename F>
     __device__ __forceinline__ bool any(const WorldView &wv, const P3 &, const P3 &, F f) const
     {
@@ -368,20 +386,33 @@ struct RayWorld<EPP_BP_BRUTE> {
 // starts in one of four banks (ncu: 10.5 M bank-conflict cycles per 1 M segments, 40 % of the kernel's cycles).
 template <>
 struct RayWorld<EPP_BP_BITS> {
-    const uint32_t *min_le;
+    const uint32_t *min_le; // cumulative rows: shared memory when the world has no range rows, else global (rare path)
     const uint32_t *max_ge;
-    const uint32_t *cmask;
+    const uint32_t *range;  // (first bin, span) rows of x and y in shared memory
     __device__ void init(const WorldView &wv, bool)
     {
-        const int words = 3 * wv.nb * wv.Ws;
         uint32_t *dst = reinterpret_cast<uint32_t *>(g_smem);
-        block_copy_words(dst, wv.bits_min_le, words);
-        block_copy_words(dst + words, wv.bits_max_ge, words);
-        block_copy_words(dst + 2 * words, wv.bits_inside + wv.cmask_off, wv.cmask_words);
+        if (wv.range_d > 0) {
+            block_copy_words(dst, wv.bits_range, 2 * wv.nb * wv.range_d * wv.Ws);
+            range = dst;
+            min_le = wv.bits_min_le;
+            max_ge = wv.bits_max_ge;
+        } else {
+            const int words = 3 * wv.nb * wv.Ws;
+            block_copy_words(dst, wv.bits_min_le, words);
+            block_copy_words(dst + words, wv.bits_max_ge, words);
+            range = nullptr;
+            min_le = dst;
+            max_ge = dst + words;
+        }
         __syncthreads();
-        min_le = dst;
-        max_ge = dst + words;
-        cmask = dst + 2 * words;
+    }
+    // the range rows arrived in shared memory by bulk copy (k_segments_warp)
+    __device__ void bind(const WorldView &wv)
+    {
+        range = reinterpret_cast<const uint32_t *>(g_smem);
+        min_le = wv.bits_min_le;
+        max_ge = wv.bits_max_ge;
     }
     template <typename F>
     __device__ __forceinline__ bool any(const WorldView &wv, const P3 &mn, const P3 &mx, F f) const
@@ -389,36 +420,34 @@ struct RayWorld<EPP_BP_BITS> {
         const int nb = wv.nb, W = wv.W, Ws = wv.Ws;
         const int gx_ = dev_key_bin(mn.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb), lx_ = dev_key_bin(mx.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb);
         const int gy_ = dev_key_bin(mn.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb), ly_ = dev_key_bin(mx.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb);
-        const int gz_ = dev_key_bin(mn.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb), lz_ = dev_key_bin(mx.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb);
-        const uint32_t *gx = max_ge + gx_ * Ws, *gy = max_ge + (nb + gy_) * Ws, *gz = max_ge + (2 * nb + gz_) * Ws;
-        const uint32_t *lx = min_le + lx_ * Ws, *ly = min_le + (nb + ly_) * Ws, *lz = min_le + (2 * nb + lz_) * Ws;
-        if (W == 1) {
-            uint32_t m = gx[0] & gy[0] & gz[0] & lx[0] & ly[0] & lz[0];
-            while (m) {
-                const int k = __ffs(m) - 1;
-                m &= m - 1;
-                if (f(k)) return true;
+        const int D = wv.range_d;
+        if (lx_ - gx_ < D && ly_ - gy_ < D) {
+            // One row per axis: the OBBs whose bin range meets [bin(rayMin), bin(rayMax)] on x and on y (z is left to
+            // the exact stored-AABB test every candidate takes anyway).  Two reads name the words, two more per word.
+            const uint32_t *rx = range + ((gx_ * D) + (lx_ - gx_)) * Ws, *ry = range + (((nb + gy_) * D) + (ly_ - gy_)) * Ws;
+            uint32_t nz = W == 1 ? 1u : (rx[W] & ry[W]);
+            while (nz) {
+                const int w = __ffs(nz) - 1;
+                nz &= nz - 1;
+                uint32_t m = rx[w] & ry[w];
+                while (m) {
+                    const int k = (w << 5) + __ffs(m) - 1;
+                    m &= m - 1;
+                    if (f(k)) return true;
+                }
             }
             return false;
         }
-        // Pass 1, converged: which words can hold a candidate at all.  With the coarse-cell table: the OR of the word
-        // masks of the coarse cells under the ray box (a handful of reads); without it: the row AND of every word
-        // (6 rows x W reads — a fifth of K2's instructions on the 256-OBB world, ncu r01_ac).  Walking the candidates
-        // inside this loop made the lanes of a warp drift through it separately.
+        // Boxes spanning many bins (or worlds without range rows): cumulative rows, all three axes.
+        const int gz_ = dev_key_bin(mn.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb), lz_ = dev_key_bin(mx.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb);
+        const uint32_t *gx = max_ge + gx_ * Ws, *gy = max_ge + (nb + gy_) * Ws, *gz = max_ge + (2 * nb + gz_) * Ws;
+        const uint32_t *lx = min_le + lx_ * Ws, *ly = min_le + (nb + ly_) * Ws, *lz = min_le + (2 * nb + lz_) * Ws;
+        // Pass 1, converged: which words of the candidate set are non-zero at all.  Walking the candidates inside this
+        // loop made the lanes of a warp drift through it separately (ncu: the row AND ran 2.6 x per warp).
         uint32_t nz = 0u;
-        if (wv.cmask_words) {
-            const int x0 = gx_ >> wv.cshift[0], x1 = lx_ >> wv.cshift[0], y0 = gy_ >> wv.cshift[1], y1 = ly_ >> wv.cshift[1];
-            const int z0 = gz_ >> wv.cshift[2], z1 = lz_ >> wv.cshift[2];
-            for (int z = z0; z <= z1; ++z)
-                for (int y = y0; y <= y1; ++y) {
-                    const uint32_t *row = cmask + (z * wv.cn1 + y) * wv.cn0;
-                    for (int x = x0; x <= x1; ++x) nz |= row[x];
-                }
-        } else {
-            for (int w = 0; w < W; ++w)
-                if (gx[w] & gy[w] & gz[w] & lx[w] & ly[w] & lz[w]) nz |= 1u << w;
-        }
-        // Pass 2: those words, in order, with the exact tests
+        for (int w = 0; w < W; ++w)
+            if (gx[w] & gy[w] & gz[w] & lx[w] & ly[w] & lz[w]) nz |= 1u << w;
+        // Pass 2: the few non-zero words again, in order, with the exact tests
         while (nz) {
             const int w = __ffs(nz) - 1;
             nz &= nz - 1;
@@ -463,17 +492,25 @@ struct RayWorld<EPP_BP_GRID> {
         x0 >>= wv.occ_shift[0], x1 >>= wv.occ_shift[0];
         y0 >>= wv.occ_shift[1], y1 >>= wv.occ_shift[1];
         z0 >>= wv.occ_shift[2], z1 >>= wv.occ_shift[2];
+        const int len = x1 - x0 + 1;
         for (int z = z0; z <= z1; ++z)
             for (int y = y0; y <= y1; ++y) {
                 size_t s = ((size_t)z * wv.occ_n1 + y) * wv.occ_n0 + x0;
-                int len = x1 - x0 + 1;
-                while (len > 0) {
-                    const int off = (int)(s & 31), take = (32 - off) < len ? (32 - off) : len;
+                if (len <= 32) { // the usual case: the row's bits lie in two consecutive words (the map has slack words)
+                    const uint32_t lo = GLOBAL ? __ldg(occ + (s >> 5)) : occ[s >> 5];
+                    const uint32_t hi = GLOBAL ? __ldg(occ + (s >> 5) + 1) : occ[(s >> 5) + 1];
+                    const uint32_t bits = __funnelshift_r(lo, hi, (uint32_t)(s & 31));
+                    if (bits & (len == 32 ? 0xffffffffu : ((1u << len) - 1u))) return true;
+                    continue;
+                }
+                int left = len;
+                while (left > 0) {
+                    const int off = (int)(s & 31), take = (32 - off) < left ? (32 - off) : left;
                     const uint32_t m = (take == 32 ? 0xffffffffu : ((1u << take) - 1u)) << off;
                     const uint32_t w = GLOBAL ? __ldg(occ + (s >> 5)) : occ[s >> 5];
                     if (w & m) return true;
                     s += take;
-                    len -= take;
+                    left -= take;
                 }
             }
         return false;
@@ -909,6 +946,9 @@ struct TrajArgs {
 // coordinate so they are not queued behind the coordinates.
 constexpr int kMaxWarps = 32;
 constexpr int kMaxSlots = 64;
+// per consumer warp: byte queue (S * 32) + invalid words (32 B); grid worlds: room for the deferred list of up to
+// 31 + S * 32 state indices instead (see k_states_warp)
+__host__ __device__ constexpr uint32_t warp_area_bytes(int bp, int S) { return bp == EPP_BP_GRID ? (32u + S * 32u) * 4u : S * 32u + 32u; }
 constexpr uint32_t kGaStageWords = 1024; // GA: blocks of up to this many mask words send them in groups
 
 __device__ __forceinline__ void mbar_arrive(uint64_t *bar)
@@ -944,7 +984,7 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
     // GA, small blocks of words (ga_group > 0): verdict words are parked here and leave for the peers in groups of
     // ga_group chunks (one 8 * S * ga_group byte run per peer instead of ga_group runs of 8 * S bytes: at 8 ranks the
     // exchange is bound by the NUMBER of NVLink writes, not their bytes); behind them one counter per group.
-    uint32_t *ga_words = reinterpret_cast<uint32_t *>(areas + ((blockDim.x >> 5) - 1u) * (S * 32u + 32u));
+    uint32_t *ga_words = reinterpret_cast<uint32_t *>(areas + ((blockDim.x >> 5) - 1u) * warp_area_bytes(BP, S));
     uint32_t *ga_count = ga_words + kGaStageWords;
     EPP_TRACE_EV(blockIdx.x * consumers + (warp == 0 ? 0 : warp - 1), warp == 0 ? 13 : 14);
 
@@ -1070,9 +1110,29 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
     int tstep = 0;
 #endif
     EPP_TRACE_EV(g, 0);
-    unsigned char *queue = areas + c * (S * 32u + 32u);
+    unsigned char *queue = areas + c * warp_area_bytes(BP, S);
     uint32_t *inv = reinterpret_cast<uint32_t *>(queue + S * 32);
-    if (lane < 8) inv[lane] = 0u;
+    // Grid worlds, plain state batches: phase 2 (the cell's records, dependent global loads) is DEFERRED — states whose
+    // coarse cell is occupied (a few per cent) go on a per-warp list by global index, the chunk's mask words are
+    // written as valid and the ring slot is released; whenever 32 states are waiting each lane takes one (coordinates
+    // re-read from global memory, fresh in L2) and clears the bit of a state that collides.  Per chunk, phase 2 kept a
+    // slot for its whole latency with ~8 of 32 lanes busy.  Not with the fused exchange (words leave for the peers when
+    // the chunk ends) and not for trajectory matrices (the first invalid row is reduced per chunk).
+    constexpr bool DEFER = BP == EPP_BP_GRID && !GA && !TR;
+    uint32_t *defer = reinterpret_cast<uint32_t *>(queue);
+    int fill = 0;
+    const uint32_t lt = (1u << lane) - 1u;
+    auto deferred_round = [&](int first, int count) {
+        __syncwarp();
+        if constexpr (DEFER) if (lane < count) {
+            const uint32_t id = defer[first + lane];
+            const double *gp = xyz + (size_t)id * 3;
+            const P3 p = {__ldg(gp), __ldg(gp + 1), __ldg(gp + 2)};
+            if (world_invalid_grid(wv, p, mode & 0xff, cpg, min_distance)) atomicAnd(mask + (id >> 5), ~(1u << (id & 31)));
+        }
+        __syncwarp();
+    };
+    if (!DEFER && lane < 8) inv[lane] = 0u;
     // fold the call's rules into the records (src/World.cpp:92-97, :116-121; src/OBB.cpp:67-72)
     if (have_rec) {
         double *r = rec + rk * kRecDoubles;
@@ -1143,6 +1203,21 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
             const uint32_t cand = bad ? tr_j * (S * 32) + (uint32_t)lane * 32u + (uint32_t)(__ffs(bad) - 1) : 0xffffffffu;
             const uint32_t first = __reduce_min_sync(0xffffffffu, cand);
             if (lane == 0 && first != 0xffffffffu) atomicMin(ta.first_row + tr_t, (long long)first);
+        } else if constexpr (DEFER) {
+#pragma unroll
+            for (int u = 0; u < S; ++u) {
+                const int unit = u * 32 + lane;
+                bool has = false;
+                if (unit < units) has = world.has_candidates(wv, P3{pts[3 * unit], pts[3 * unit + 1], pts[3 * unit + 2]});
+                const uint32_t bal = __ballot_sync(0xffffffffu, has);
+                if (has) defer[fill + __popc(bal & lt)] = (b0 + i * S) * 32u + (uint32_t)unit;
+                fill += __popc(bal);
+            }
+            if (lane < S && lane * 32 < units) {
+                const int live = units - 32 * lane;
+                mask[b0 + i * S + lane] = live >= 32 ? 0xffffffffu : ((1u << live) - 1u);
+            }
+            __syncwarp();
         } else {
             warp_states_step<BP, S, RS, GA>(world, wv, rec, pts, units, mode, cpg, min_distance, queue, inv,
                                             mask + b0 + i * S, lane, gv, seq, ll_row + b0 + i * S,
@@ -1179,6 +1254,15 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
             mbar_arrive(&s_empty[slot]);
             asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(smem_addr(&s_rounds_done[slot])), "r"(round + 1u) : "memory");
         }
+        if constexpr (DEFER) {
+            while (fill >= 32) {
+                fill -= 32;
+                deferred_round(fill, 32);
+            }
+        }
+    }
+    if constexpr (DEFER) {
+        if (fill > 0) deferred_round(0, fill);
     }
     EPP_TRACE_EV(g, 15);
     if (GA) {
@@ -1252,7 +1336,8 @@ constexpr int kRayRecMax = 256;
 __device__ __forceinline__ bool ray_rec_invalid(const double *__restrict__ r, const P3 &a, const P3 &b, const P3 &mn,
                                                 const P3 &mx)
 {
-    if (mx.x < r[0] || mn.x > r[3] || mx.y < r[1] || mn.y > r[4] || mx.z < r[2] || mn.z > r[5]) return false;
+    // z first: the bits rows only look at x and y, so z is where most candidates leave
+    if (mx.z < r[2] || mn.z > r[5] || mx.x < r[0] || mn.x > r[3] || mx.y < r[1] || mn.y > r[4]) return false;
     const double a0 = dsub(a.x, r[6]), a1 = dsub(a.y, r[7]), a2 = dsub(a.z, r[8]);
     const double b0 = dsub(b.x, r[6]), b1 = dsub(b.y, r[7]), b2 = dsub(b.z, r[8]);
     const double ax = dadd(dmul(r[9], a0), dmul(r[11], a1)), ay = dadd(dmul(r[10], a0), dmul(r[12], a1));
@@ -1353,6 +1438,7 @@ __global__ void __launch_bounds__(TB, TB >= 1024 ? 1 : (TB >= 512 ? 2 : 4)) k_se
 constexpr int kSegS = 2;
 constexpr int kSegSlotBytes = kSegS * 2 * kWordBytes; // both end points of kSegS * 32 segments
 constexpr int kSegMaxSlots = 64;
+constexpr int kSegWarpBytes = 96 * 4; // per consumer warp: deferred list of up to 31 + kSegS * 32 segment indices
 
 template <int BP, bool RS>
 __global__ void __launch_bounds__(1024, 1) k_segments_warp(WorldView wv, const double *__restrict__ pa,
@@ -1388,20 +1474,31 @@ __global__ void __launch_bounds__(1024, 1) k_segments_warp(WorldView wv, const d
     };
     auto by_tma = [&](int units) -> bool { return aligned && (units & 1) == 0; };
 
+    // The broad-phase table and the folded records come by bulk copy (one thread, two instructions): a block-wide
+    // copy loop + record fold behind a barrier was ~3 us of every 30 us launch (ncu r02_e: the copy loop had the most
+    // stall samples of the kernel), and it cannot overlap the previous launch because two blocks do not fit one SM.
     RayWorld<BP> world;
-    if constexpr (BP == EPP_BP_GRID) {
-        if (threadIdx.x == 0) {
-            s_next = 0u;
-            mbar_init(&s_table, 1);
-            mbar_init_fence();
-            mbar_expect_tx(&s_table, wv.occ_bytes);
-            bulk_g2s(g_smem, wv.occ, wv.occ_bytes, &s_table);
-        }
-    } else {
-        if (threadIdx.x == 0) s_next = 0u;
-        world.init(wv, aabb_in_smem != 0); // tables (bits) / stored AABBs (brute) by all threads; ends with a barrier
+    const void *tsrc = nullptr;
+    uint32_t tbytes = 0;
+    if (BP == EPP_BP_GRID) {
+        tsrc = wv.occ;
+        tbytes = wv.occ_bytes;
+    } else if (BP == EPP_BP_BITS && wv.range_d > 0) {
+        tsrc = wv.bits_range;
+        tbytes = (uint32_t)(2 * wv.nb * wv.range_d * wv.Ws * 4 + 15) & ~15u;
     }
-    if (RS) fold_ray_records(wv, rec, cpg);
+    const bool recs_by_tma = RS && wv.ray_recs != nullptr;
+    if (threadIdx.x == 0) {
+        s_next = 0u;
+        mbar_init(&s_table, 1);
+        mbar_init_fence();
+        const uint32_t rbytes = recs_by_tma ? (uint32_t)(wv.M * kRayRec * 8 + 15) & ~15u : 0u;
+        if (tbytes + rbytes) mbar_expect_tx(&s_table, tbytes + rbytes);
+        if (tbytes) bulk_g2s(g_smem, tsrc, tbytes, &s_table);
+        if (rbytes) bulk_g2s(rec, wv.ray_recs + (size_t)(cpg ? 1 : 0) * wv.M * kRayRec, rbytes, &s_table);
+    }
+    if (BP != EPP_BP_GRID && !tbytes) world.init(wv, aabb_in_smem != 0); // brute / bits without range rows: block-wide copy
+    if (RS && !recs_by_tma) fold_ray_records(wv, rec, cpg);
     if (threadIdx.x >= 32) {
         for (uint32_t s = threadIdx.x - 32; s < slots; s += blockDim.x - 32) {
             mbar_init(&s_full[s], 1);
@@ -1439,15 +1536,34 @@ __global__ void __launch_bounds__(1024, 1) k_segments_warp(WorldView wv, const d
 
     // ---- consumers
     const uint32_t c = (uint32_t)warp - 1u;
-    unsigned char *queue = areas + c * (S * 32u + 32u);
-    uint32_t *inv = reinterpret_cast<uint32_t *>(queue + S * 32);
-    if (lane < 8) inv[lane] = 0u;
-    if constexpr (BP == EPP_BP_GRID) {
-        world.bind(wv);
-        mbar_wait(&s_table, 0);
-    }
+    if (tbytes) world.bind(wv);
+    if (tbytes || recs_by_tma) mbar_wait(&s_table, 0);
     __syncwarp();
     const uint32_t lt = (1u << lane) - 1u;
+    // Grid: phase 2 (the walk through the cell lists, a chain of dependent global loads) is DEFERRED.  Segments with an
+    // occupied cell under their box (~1 in 8) are listed by global index; when 32 are waiting, each lane takes one
+    // (end points re-read from global memory: they were streamed through L2 a moment ago) and clears the mask bit of
+    // a segment that collides.  Doing phase 2 per 64-segment chunk kept a ring slot for its whole latency with ~8 of
+    // 32 lanes busy (ncu r02_e: 13.6 active threads per instruction, consumers waiting for slots).
+    uint32_t *defer = reinterpret_cast<uint32_t *>(areas + c * kSegWarpBytes);
+    int fill = 0;
+    auto deferred_round = [&](int first, int count) {
+        __syncwarp();
+        if constexpr (BP == EPP_BP_GRID) if (lane < count) {
+            const uint32_t id = defer[first + lane];
+            const double *ga = pa + (size_t)id * 3, *gb = pb + (size_t)id * 3;
+            const P3 a = {__ldg(ga), __ldg(ga + 1), __ldg(ga + 2)};
+            const P3 b = {__ldg(gb), __ldg(gb + 1), __ldg(gb + 2)};
+            P3 mn, mx;
+            ray_box(a, b, mn, mx);
+            const bool hit = wv.cell_recs ? world.walk_recs(wv, a, b, mn, mx, cpg)
+                                          : world.any(wv, mn, mx, [&](int k) -> bool {
+                                                return ray_candidate_invalid(wv.aabb, wv.obb, k, a, b, mn, mx, cpg);
+                                            });
+            if (hit) atomicAnd(mask + (id >> 5), ~(1u << (id & 31)));
+        }
+        __syncwarp();
+    };
 
     for (;;) {
         uint32_t i = 0;
@@ -1475,8 +1591,8 @@ __global__ void __launch_bounds__(1024, 1) k_segments_warp(WorldView wv, const d
         }
         uint32_t *mo = mask + b0 + i * S;
         if constexpr (BP == EPP_BP_GRID) {
-            // phase 1: which of my segments have an occupied coarse cell under their box
-            int queued = 0;
+            // phase 1: which of my segments have an occupied coarse cell under their box; their global indices go on
+            // the warp's deferred list, the mask words are written as if they were valid, the slot is released
 #pragma unroll
             for (int u = 0; u < S; ++u) {
                 const int unit = u * 32 + lane;
@@ -1489,31 +1605,12 @@ __global__ void __launch_bounds__(1024, 1) k_segments_warp(WorldView wv, const d
                     has = world.has_candidates(wv, mn, mx);
                 }
                 const uint32_t bal = __ballot_sync(0xffffffffu, has);
-                if (has) queue[queued + __popc(bal & lt)] = (unsigned char)unit;
-                queued += __popc(bal);
-            }
-            if (queued != 0) {
-                __syncwarp();
-                // phase 2: one queued segment per lane through the cell lists
-                for (int q = lane; q < queued; q += 32) {
-                    const int unit = queue[q];
-                    const P3 a = {A[3 * unit], A[3 * unit + 1], A[3 * unit + 2]};
-                    const P3 b = {B[3 * unit], B[3 * unit + 1], B[3 * unit + 2]};
-                    P3 mn, mx;
-                    ray_box(a, b, mn, mx);
-                    const bool hit = wv.cell_recs ? world.walk_recs(wv, a, b, mn, mx, cpg)
-                                                  : world.any(wv, mn, mx, [&](int k) -> bool {
-                                                        return ray_candidate_invalid(wv.aabb, wv.obb, k, a, b, mn, mx, cpg);
-                                                    });
-                    if (hit) atomicOr(&inv[unit >> 5], 1u << (unit & 31));
-                }
-                __syncwarp();
+                if (has) defer[fill + __popc(bal & lt)] = (b0 + i * S) * 32u + (uint32_t)unit;
+                fill += __popc(bal);
             }
             if (lane < S && lane * 32 < units) {
                 const int live = units - 32 * lane;
-                const uint32_t active = live >= 32 ? 0xffffffffu : ((1u << live) - 1u);
-                mo[lane] = ~inv[lane] & active;
-                inv[lane] = 0u;
+                mo[lane] = live >= 32 ? 0xffffffffu : ((1u << live) - 1u);
             }
             __syncwarp();
         } else {
@@ -1542,6 +1639,15 @@ __global__ void __launch_bounds__(1024, 1) k_segments_warp(WorldView wv, const d
             mbar_arrive(&s_empty[slot]);
             asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(smem_addr(&s_rounds_done[slot])), "r"(round + 1u) : "memory");
         }
+        if constexpr (BP == EPP_BP_GRID) {
+            while (fill >= 32) { // phase 2 on full rounds only: 32 busy lanes, no ring slot held meanwhile
+                fill -= 32;
+                deferred_round(fill, 32);
+            }
+        }
+    }
+    if constexpr (BP == EPP_BP_GRID) {
+        if (fill > 0) deferred_round(0, fill);
     }
 }
 
@@ -1737,12 +1843,28 @@ __global__ void __launch_bounds__(kPolyThreads) k_poly_traj(WorldView wv, const 
             double *st = ring_t(slot) + lane * kPolyPitch;
             unsigned short *sg = ring_seg(slot) + lane * kPolyPitch;
             int cnt = 0;
+            // The sampler's critical path is compare -> branch -> add per sample, and the producer warp shares its
+            // scheduler with consumers (ncu r02_e: consumers spent a quarter of the kernel waiting for it).  Between two
+            // events (segment change, end of the trajectory: ~9 per 1000 samples) the loop only adds, so: advance()
+            // settles the exact state machine at the current sample, then a run of n samples is emitted with no
+            // compares, n chosen so that NO event can fall inside it — a bound in real arithmetic with a margin that
+            // covers the rounding of up to 2^20 running-sum steps.  Same sequence of rounded adds, same values.
             while (cnt < 32 && advance()) {
-                st[cnt] = tin; // :132
-                sg[cnt] = (unsigned short)seg;
-                ++cnt;
-                tin = dadd(tin, dt); // :138-139
-                acc = dadd(acc, dt);
+                int n = 1;
+                if (dt > 0.0) {
+                    const double room_t = dsub(dsub(seg_T, tin), dmul(1e-9, dadd(fabs(seg_T), 1.0)));
+                    const double room_a = dsub(dsub(t_end, acc), dmul(1e-9, dadd(fabs(t_end), 1.0)));
+                    const double steps = __ddiv_rn(room_t < room_a ? room_t : room_a, dt);
+                    if (steps > 3.0) n = steps > 64.0 ? 32 : (int)steps - 2; // states 1 .. n-1 emit for sure
+                }
+                n = n < 32 - cnt ? n : 32 - cnt;
+                for (int u = 0; u < n; ++u) {
+                    st[cnt + u] = tin; // :132
+                    sg[cnt + u] = (unsigned short)seg;
+                    tin = dadd(tin, dt); // :138-139
+                    acc = dadd(acc, dt);
+                }
+                cnt += n;
             }
             if (have) ring_cnt(slot)[lane] = (uint32_t)cnt;
             emitted_total += (uint32_t)cnt;
@@ -1759,13 +1881,16 @@ __global__ void __launch_bounds__(kPolyThreads) k_poly_traj(WorldView wv, const 
         return;
     }
 
-    // ---- consumers
-    const uint32_t gb_magic = Gb > 1u ? (uint32_t)(0x100000000ull / Gb) + ((0x100000000ull % Gb) ? 1u : 0u) : 0u;
+    // ---- consumers: a work item is one round of TWO trajectories (j0, j0 + 1): their Horner chains are independent,
+    // so a lane has six dependent DMUL/DADD chains in flight instead of three (ncu r02_e: the FP64 pipe was 27 % busy
+    // with the warps waiting on its latency), and the per-item bookkeeping is halved.
+    const uint32_t Hb = (Gb + 1u) >> 1;
+    const uint32_t hb_magic = Hb > 1u ? (uint32_t)(0x100000000ull / Hb) + ((0x100000000ull % Hb) ? 1u : 0u) : 0u;
     for (;;) {
         uint32_t i = 0;
         if (lane == 0) i = atomicAdd(&s_next, 1u);
         i = __shfl_sync(0xffffffffu, i, 0);
-        const uint32_t round = Gb == 1u ? i : __umulhi(i, gb_magic), j = i - round * Gb; // i / Gb (exact for i < 2^27)
+        const uint32_t round = Hb == 1u ? i : __umulhi(i, hb_magic), j0 = (i - round * Hb) * 2u; // i / Hb (exact for i < 2^27)
         bool gone = false;
         for (;;) { // wait for the round, or learn that it will never come
             uint32_t p, t;
@@ -1776,23 +1901,39 @@ __global__ void __launch_bounds__(kPolyThreads) k_poly_traj(WorldView wv, const 
                 gone = true;
                 break;
             }
-            __nanosleep(200); // a spinning consumer takes issue slots from the producer it is waiting for (ncu r02_b: 37 %)
+            __nanosleep(200);
         }
         if (gone) break;
         const uint32_t slot = round % kPolyRing;
-        const int cj = (int)ring_cnt(slot)[j];
-        if (cj != 0) {
-            const size_t tj = traj0 + j;
-            bool valid = false;
-            if (lane < cj) {
-                const double t = ring_t(slot)[j * kPolyPitch + lane];
-                const int sg = ring_seg(slot)[j * kPolyPitch + lane];
-                const double *c = coeffs + ((tj * n_segments + sg) * 3) * (size_t)n_coeffs; // segment.cpp:51-58
-                const P3 p = N10 ? P3{horner10(c, t), horner10(c + 10, t), horner10(c + 20, t)}
-                                 : P3{horner(c, n_coeffs, t), horner(c + n_coeffs, n_coeffs, t),
-                                      horner(c + 2 * n_coeffs, n_coeffs, t)};
-                valid = !world.invalid(wv, p, kModeMinDist, false, min_distance);
+        const bool two = j0 + 1u < Gb;
+        const int cnt0 = (int)ring_cnt(slot)[j0], cnt1 = two ? (int)ring_cnt(slot)[j0 + 1u] : 0;
+        P3 p0 = {0.0, 0.0, 0.0}, p1 = {0.0, 0.0, 0.0};
+        {
+            // both samples' coefficients are requested before either chain starts
+            const size_t tj0 = traj0 + j0, tj1 = tj0 + (two ? 1u : 0u);
+            const uint32_t at0 = j0 * kPolyPitch + lane, at1 = (j0 + (two ? 1u : 0u)) * kPolyPitch + lane;
+            const bool a0 = lane < cnt0, a1 = lane < cnt1;
+            const double t0 = a0 ? ring_t(slot)[at0] : 0.0, t1 = a1 ? ring_t(slot)[at1] : 0.0;
+            const int sg0 = a0 ? ring_seg(slot)[at0] : 0, sg1 = a1 ? ring_seg(slot)[at1] : 0;
+            const double *c0 = coeffs + ((tj0 * n_segments + sg0) * 3) * (size_t)n_coeffs; // segment.cpp:51-58
+            const double *c1 = coeffs + ((tj1 * n_segments + sg1) * 3) * (size_t)n_coeffs;
+            if (N10) {
+                if (a0 | a1) {
+                    p0 = {horner10(c0, t0), horner10(c0 + 10, t0), horner10(c0 + 20, t0)};
+                    p1 = {horner10(c1, t1), horner10(c1 + 10, t1), horner10(c1 + 20, t1)};
+                }
+            } else {
+                if (a0) p0 = {horner(c0, n_coeffs, t0), horner(c0 + n_coeffs, n_coeffs, t0), horner(c0 + 2 * n_coeffs, n_coeffs, t0)};
+                if (a1) p1 = {horner(c1, n_coeffs, t1), horner(c1 + n_coeffs, n_coeffs, t1), horner(c1 + 2 * n_coeffs, n_coeffs, t1)};
             }
+        }
+#pragma unroll
+        for (int k = 0; k < 2; ++k) {
+            const int cj = k ? cnt1 : cnt0;
+            if (cj == 0) continue;
+            const size_t tj = traj0 + j0 + k;
+            bool valid = false;
+            if (lane < cj) valid = !world.invalid(wv, k ? p1 : p0, kModeMinDist, false, min_distance);
             const uint32_t word = __ballot_sync(0xffffffffu, valid);
             if (lane == 0) {
                 if (sample_mask) sample_mask[tj * words_per_traj + round] = word;
@@ -1804,7 +1945,7 @@ __global__ void __launch_bounds__(kPolyThreads) k_poly_traj(WorldView wv, const 
         __syncwarp();
         if (lane == 0) {
             __threadfence_block();
-            atomicAdd(&s_done[slot], 1u);
+            atomicAdd(&s_done[slot], two ? 2u : 1u);
         }
     }
 }
@@ -2037,7 +2178,7 @@ size_t point_smem_bytes(const WorldView &wv, int bp, bool &aabb_in_smem)
 size_t ray_smem_bytes(const WorldView &wv, int bp, bool &aabb_in_smem)
 {
     aabb_in_smem = false;
-    if (bp == EPP_BP_BITS) return ((size_t)6 * wv.nb * wv.Ws + wv.cmask_words) * 4;
+    if (bp == EPP_BP_BITS) return (wv.range_d > 0 ? (size_t)2 * wv.nb * wv.range_d * wv.Ws : (size_t)6 * wv.nb * wv.Ws) * 4;
     if (bp == EPP_BP_BRUTE && wv.M <= 2048) {
         aabb_in_smem = true;
         return (size_t)wv.M * sizeof(AabbRec);
@@ -2051,6 +2192,16 @@ cudaError_t ensure_smem(K kernel, size_t bytes, size_t static_bytes = 0)
 {
     if (bytes + static_bytes <= 40 * 1024) return cudaSuccess;
     return cudaFuncSetAttribute(kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)bytes);
+}
+
+// The coarse-cell word masks pay for kernels that copy the table once per SM (the warp-pipelined point kernels); direct
+// forms copy the table per block (the 22 KB of masks made K3b 20 % slower) and the ray queries loop over coarse cells
+// (K2 10 % slower): those take the view without them.
+WorldView without_cmask(const WorldView &wv)
+{
+    WorldView v = wv;
+    v.cmask_words = 0;
+    return v;
 }
 
 unsigned persistent_grid(const LaunchCfg &cfg, size_t tiles, int blocks_per_sm)
@@ -2107,7 +2258,7 @@ cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const 
     const size_t words = TR ? n_traj * ta.cpt * S : (n + 31) / 32;
     if (words >= 0xfff00000ull) return cudaSuccess;
     const size_t rec_bytes = RS ? ((size_t)wv.M * kRecDoubles * 8 + 127) / 128 * 128 : 0;
-    const size_t warp_bytes = S * 32 + 32, slot_bytes = (size_t)S * kWordBytes;
+    const size_t warp_bytes = warp_area_bytes(BP, S), slot_bytes = (size_t)S * kWordBytes;
     // resident blocks per SM (tuning, default 1) and the shared-memory budget of each
     int bps = cfg.states_warp_blocks_per_sm > 0 ? cfg.states_warp_blocks_per_sm : 1;
     bps = bps > 8 ? 8 : bps;
@@ -2237,10 +2388,12 @@ cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, con
     }
     const size_t tiles = (n + kBlock - 1) / kBlock;
     const unsigned grid = persistent_grid(cfg, tiles, cfg.states_blocks_per_sm);
+    const WorldView wd = without_cmask(wv);
+    const size_t smem_d = point_smem_bytes(wd, bp, in_smem);
     EPP_DISPATCH_BP(bp, {
-        err = ensure_smem(k_states<BP>, smem);
+        err = ensure_smem(k_states<BP>, smem_d);
         if (err == cudaSuccess) {
-            k_states<BP><<<grid, kBlock, smem, stream>>>(wv, d_xyz, n, mode, can_pass_gate, min_distance, in_smem ? 1 : 0, d_mask);
+            k_states<BP><<<grid, kBlock, smem_d, stream>>>(wd, d_xyz, n, mode, can_pass_gate, min_distance, in_smem ? 1 : 0, d_mask);
             err = cudaGetLastError();
         }
     });
@@ -2265,7 +2418,7 @@ cudaError_t launch_segments_warp(const LaunchCfg &cfg, const WorldView &wv, cons
     cons = cons < 1 ? 1 : (cons > kMaxWarps - 1 ? kMaxWarps - 1 : cons);
     if ((size_t)cons > chunks_per_block) cons = (int)chunks_per_block;
     const size_t budget = (size_t)(228 * 1024) - 1024 - 4096;
-    const size_t fixed = table_bytes + rec_bytes + (size_t)cons * (kSegS * 32 + 32);
+    const size_t fixed = table_bytes + rec_bytes + (size_t)cons * kSegWarpBytes;
     if (fixed + 2 * (size_t)kSegSlotBytes > budget) return cudaSuccess;
     size_t slots = (budget - fixed) / kSegSlotBytes;
     if (slots > chunks_per_block) slots = chunks_per_block < 2 ? 2 : chunks_per_block;
@@ -2294,9 +2447,10 @@ cudaError_t launch_segments_warp(const LaunchCfg &cfg, const WorldView &wv, cons
     return cudaGetLastError();
 }
 
-cudaError_t launch_segments(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_a, const double *d_b,
+cudaError_t launch_segments(const LaunchCfg &cfg, const WorldView &wv_in, int bp, const double *d_a, const double *d_b,
                             size_t n, int can_pass_gate, uint32_t *d_mask, cudaStream_t stream, const GatherView *gv)
 {
+    const WorldView wv = without_cmask(wv_in);
     if (n == 0) return gv ? launch_gather_push(cfg, *gv, stream) : cudaSuccess;
     bool in_smem;
     const size_t smem = ray_smem_bytes(wv, bp, in_smem);
@@ -2417,14 +2571,15 @@ cudaError_t launch_trajectories(const LaunchCfg &cfg, const WorldView &wv, int b
     }
     if (rows > 0 && !done) {
         bool in_smem;
-        const size_t smem = point_smem_bytes(wv, bp, in_smem);
+        const WorldView wd = without_cmask(wv);
+        const size_t smem = point_smem_bytes(wd, bp, in_smem);
         const size_t row_tiles = (rows + kBlock - 1) / kBlock;
         if (row_tiles > 65535 || n_traj > 0x7fffffffull) return cudaErrorInvalidValue;
         dim3 grid((unsigned)n_traj, (unsigned)row_tiles);
         EPP_DISPATCH_BP(bp, {
             err = ensure_smem(k_traj_samples<BP>, smem);
             if (err == cudaSuccess) {
-                k_traj_samples<BP><<<grid, kBlock, smem, stream>>>(wv, d_mats, rows, ld, traj_stride, min_distance,
+                k_traj_samples<BP><<<grid, kBlock, smem, stream>>>(wd, d_mats, rows, ld, traj_stride, min_distance,
                                                                    in_smem ? 1 : 0, d_sample_mask, d_first_scratch);
                 err = cudaGetLastError();
             }
@@ -2438,12 +2593,13 @@ cudaError_t launch_trajectories(const LaunchCfg &cfg, const WorldView &wv, int b
     return cudaGetLastError();
 }
 
-cudaError_t launch_poly_trajectories(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_coeffs,
+cudaError_t launch_poly_trajectories(const LaunchCfg &cfg, const WorldView &wv_in, int bp, const double *d_coeffs,
                                      const double *d_durations, const double *d_dt, size_t n_traj, int n_segments,
                                      int n_coeffs, double min_distance, size_t max_samples, uint32_t *d_traj_valid,
                                      uint32_t *d_sample_mask, uint32_t *d_n_samples, int64_t *d_first_invalid,
                                      long long *d_first_scratch, cudaStream_t stream)
 {
+    const WorldView wv = without_cmask(wv_in);
     if (n_traj == 0) return cudaSuccess;
     k_fill_i64<<<(unsigned)((n_traj + 255) / 256), 256, 0, stream>>>((int64_t *)d_first_scratch, n_traj, LLONG_MAX);
     g_launches++;

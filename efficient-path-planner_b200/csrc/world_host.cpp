@@ -324,7 +324,7 @@ void make_key_axis(double lo, double hi, int inner, double &off, int32_t &h0, in
 
 } // namespace
 
-void build_bits(const std::vector<AabbRec> &aabbs, int bins_per_axis, BitsTables &out)
+void build_bits(const std::vector<AabbRec> &aabbs, int bins_per_axis, BitsTables &out, int range_d)
 {
     const int M = static_cast<int>(aabbs.size());
     out.W = std::max(1, (M + 31) / 32);
@@ -362,6 +362,30 @@ void build_bits(const std::vector<AabbRec> &aabbs, int bins_per_axis, BitsTables
                     if ((*t)[row * out.Ws + w]) summary |= 1u << w;
                 (*t)[row * out.Ws + out.W] = summary;
             }
+    // (first bin, span) rows of the x and y axes for ray boxes
+    out.range_d = range_d > 0 ? std::min(range_d, 16) : 0;
+    out.range.clear();
+    if (out.range_d > 0) {
+        const int D = out.range_d;
+        out.range.assign(static_cast<size_t>(2) * out.nb * D * out.Ws + 4, 0u);
+        for (int k = 0; k < M; ++k)
+            for (int a = 0; a < 2; ++a) {
+                const int k0 = host_key_bin(aabbs[k].mn[a], out.bins.off[a], out.bins.h0[a], out.bins.shift[a], out.nb);
+                const int k1 = host_key_bin(aabbs[k].mx[a], out.bins.off[a], out.bins.h0[a], out.bins.shift[a], out.nb);
+                for (int b0 = 0; b0 <= k1 && b0 < out.nb; ++b0)
+                    for (int d = 0; d < D; ++d) {
+                        if (k0 > b0 + d) continue;
+                        out.range[((static_cast<size_t>(a) * out.nb + b0) * D + d) * out.Ws + (k >> 5)] |= 1u << (k & 31);
+                    }
+            }
+        if (out.W > 1)
+            for (size_t row = 0; row < static_cast<size_t>(2) * out.nb * D; ++row) {
+                uint32_t summary = 0u;
+                for (int w = 0; w < out.W; ++w)
+                    if (out.range[row * out.Ws + w]) summary |= 1u << w;
+                out.range[row * out.Ws + out.W] = summary;
+            }
+    }
     // coarse cell -> word mask (W > 1 only), appended to `inside`
     out.cmask_off = out.cmask_words = 0;
     if (out.W > 1) {

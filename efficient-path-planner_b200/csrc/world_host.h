@@ -77,6 +77,12 @@ struct BitsTables {
     int cn[3] = {1, 1, 1};
     int cshift[3] = {0, 0, 0};
     std::vector<uint32_t> inside; // k set iff bin(min_k) <= b <= bin(max_k)
+    // Ray queries: rows indexed by (first bin b0, bin span d < range_d) of the ray box on the x and y axes:
+    // k set iff bin(min_k) <= b0 + d and bin(max_k) >= b0 — what max_ge[b0] & min_le[b0 + d] gives, in ONE row whose
+    // summary word is selective (the cumulative rows' summaries are all ones).  Row of axis a at
+    // ((a * nb + b0) * range_d + d) * Ws.  Boxes spanning more bins take the cumulative rows.
+    int range_d = 0;
+    std::vector<uint32_t> range;
     std::vector<uint32_t> min_le; // k set iff bin(min_k) <= b
     std::vector<uint32_t> max_ge; // k set iff bin(max_k) >= b
 };
@@ -155,7 +161,7 @@ private:
 void obb_aabb(const HostObb &o, double inflate, double mn[3], double mx[3]);
 
 // Broad-phase construction over flattened records.
-void build_bits(const std::vector<AabbRec> &aabbs, int bins_per_axis, BitsTables &out);
+void build_bits(const std::vector<AabbRec> &aabbs, int bins_per_axis, BitsTables &out, int range_d = 5);
 // Reorders the records along a Morton curve over the stored-AABB centres (x, y): neighbours in space become
 // neighbours in index.  Results are order-independent (any hit invalidates), the broad phases get spatially coherent
 // words / cell lists.
