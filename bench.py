@@ -73,6 +73,7 @@ def parse_args():
     ap.add_argument("--no-config5", action="store_true", help="skip the full-size config 5 run under extras")
     ap.add_argument("--c5-steps", type=int, default=5)
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--no-multi", action="store_true", help="one epp_check_states_dev call per step instead of the multi-batch call")
     ap.add_argument("--exchange", default="fused", choices=["fused", "nccl", "none", "none-ipc"],
                     help="N > 1: mask exchange fused into the check kernel (default) or NCCL all-gather")
     ap.add_argument("--tune", action="append", default=[], metavar="KEY=VALUE",
@@ -267,28 +268,42 @@ def run_b200(args):
     launches0 = epp_b200.kernel_launch_count()
     graph = tail_graph = None
     per_step = 1
+    # Single GPU, states: the ring pass goes through epp_check_states_multi_dev (independent batches, one call): from
+    # the second batch on a kernel streams its states while the previous one is in its tail.  --no-multi keeps one
+    # epp_check_states_dev call per step (reported as extras.config2_one_call_per_step_ms as well).
+    pipelined = world == 1 and not segs and not args.no_multi
+    multi_masks = [torch.zeros(words, dtype=torch.int32, device=dev) for _ in range(max(RING, min(K, 64)))] if pipelined else None
     if use_graph:
         # EXACTLY K steps = (K // RING) replays of a graph of one ring pass + one graph of the K % RING steps left
-        def capture(first, count):
+        def capture(first, count, multi=None):
             g_ = torch.cuda.CUDAGraph()
             with torch.cuda.graph(g_):
-                for s_ in range(first, first + count):
-                    step_dev(s_)
+                if multi is None:
+                    multi = pipelined
+                if multi:  # the batched entry point: `count` independent batches in ONE library call
+                    gw.check_states_multi_dev([ring[s_ % RING][0] for s_ in range(first, first + count)],
+                                              [multi_masks[s_ - first] for s_ in range(first, first + count)])
+                else:
+                    for s_ in range(first, first + count):
+                        step_dev(s_)
             g_.replay()  # warm the instantiated graph
             return g_
-        if K >= RING:
+        if K <= 64:   # the whole region as ONE graph (K = 20 under the driver): no second graph launch inside the region
+            tail_graph = capture(0, K)
+            per_step = (epp_b200.kernel_launch_count() - launches0) // K
+            ring_replays = 0
+        else:
             graph = capture(0, RING)
             per_step = (epp_b200.kernel_launch_count() - launches0) // RING
-        if K % RING:
-            l_ = epp_b200.kernel_launch_count()
-            tail_graph = capture((K // RING) * RING, K % RING)
-            per_step = (epp_b200.kernel_launch_count() - l_) // (K % RING)
+            ring_replays = K // RING
+            if K % RING:
+                tail_graph = capture((K // RING) * RING, K % RING)
         torch.cuda.synchronize()
     launches1 = epp_b200.kernel_launch_count()
 
     def timed_region():
         if use_graph:
-            for _ in range(K // RING):
+            for _ in range(ring_replays):
                 graph.replay()
             if tail_graph is not None:
                 tail_graph.replay()
@@ -311,7 +326,13 @@ def run_b200(args):
     gpu_launches = per_step * K if use_graph else direct // REGION_REPS   # launches inside ONE K-step region
     ms_total = sorted(regions)[len(regions) // 2]
     value = world * BATCH * K / (ms_total * 1e-3)
-    pop, xor = epp_b200.mask_summary_dev(gathered[0][rank])
+    one_call_ms = None
+    if pipelined and use_graph and K >= RING:
+        # for the record: the same steps as one epp_check_states_dev call each (kernels strictly one after the other)
+        g1 = capture(0, RING, multi=False)
+        one_call_ms = sorted(timed_events(torch, lambda: [g1.replay() for _ in range(max(K // RING, 1))])
+                             for _ in range(REGION_REPS))[REGION_REPS // 2] / (max(K // RING, 1) * RING)
+    pop, xor = epp_b200.mask_summary_dev(multi_masks[0] if pipelined and use_graph else gathered[0][rank])
     exchange_ok = None
     if world > 1:
         # what the last two steps left in the gathered buffers vs an NCCL all-gather of plain local checks
@@ -394,8 +415,13 @@ def run_b200(args):
                    "world_obbs": gw.size(), "broadphase": epp_b200.BP_NAMES[gw.active_broadphase()],
                    "l2": "inputs rotate over a ring of %d distinct batches (%d MiB) > 126 MB L2" %
                          (RING, RING * in_bytes >> 20),
-                   "launch": ("cuda graphs: %d replays of one ring pass (%d steps) + one graph of %d steps = exactly %d "
-                              "steps per region" % (K // RING, RING, K % RING, K)) if use_graph else "direct launches",
+                   "api": ("epp_check_states_multi_dev: the ring pass is ONE call over %d independent 1M-state batches "
+                           "(one kernel per batch, a batch starts streaming while the previous kernel is in its tail)" % RING)
+                          if (pipelined and use_graph) else "one epp_check_*_dev call per step",
+                   "one_call_per_step_ms": one_call_ms,
+                   "launch": (("one cuda graph of exactly %d steps per region" % K) if K <= 64 else
+                              ("cuda graphs: %d replays of one ring pass (%d steps) + one graph of %d steps = exactly %d "
+                               "steps per region" % (K // RING, RING, K % RING, K))) if use_graph else "direct launches",
                    "timing": "median of %d regions of %d steps, each between barrier + synchronize, max over ranks; "
                              "regions ms: %s" % (REGION_REPS, K, ["%.4f" % r for r in regions]),
                    "sharding": "contiguous index range per rank; every rank ends each step with all ranks' mask words"
@@ -438,6 +464,22 @@ def measure_h2d(torch, dev, mib=256, reps=5):
         return (mib << 20) / (best * 1e-3) / 1e9
     except Exception:
         return None
+
+
+def cpu_rates(fn, n_all, n_one):
+    """checks/s of a CPU checker: all host cores on n_all units (best of 3 passes) and one thread on n_one units."""
+    threads = os.cpu_count() or 1
+    fn(threads, n_all)
+    best = 1e30
+    for _ in range(3):
+        t0 = time.perf_counter()
+        fn(threads, n_all)
+        best = min(best, time.perf_counter() - t0)
+    t0 = time.perf_counter()
+    fn(1, n_one)
+    one = time.perf_counter() - t0
+    return {"all_cores": n_all / best, "cores": threads, "single_thread": n_one / one,
+            "sample": "%d units on all cores (best of 3 passes), %d units on one thread" % (n_all, n_one)}
 
 
 def popcount_words(a):
@@ -722,8 +764,17 @@ def cpu_parity_config5(gw, gs, ge, sb, eb, lo, hi, seed, n_s=1 << 20, n_e=1 << 1
     a, b = oracle_py.gen_segments(seed, eb, n_e, lo, hi, 1.0)
     t0 = time.perf_counter()
     ms = w.check_states(xyz, False, threads=threads)
+    el_s = time.perf_counter() - t0
+    t0 = time.perf_counter()
     me = w.check_segments(a, b, False, threads=threads)
-    el = time.perf_counter() - t0
+    el_e = time.perf_counter() - t0
+    el = el_s + el_e
+    t0 = time.perf_counter()
+    w.check_states(xyz[: n_s // 64], False, threads=1)
+    one_s = (n_s // 64) / (time.perf_counter() - t0)
+    t0 = time.perf_counter()
+    w.check_segments(a[: n_e // 64], b[: n_e // 64], False, threads=1)
+    one_e = (n_e // 64) / (time.perf_counter() - t0)
     got_s = gs[0][: n_s // 32].cpu().numpy().view(np.uint32)
     got_e = ge[0][: n_e // 32].cpu().numpy().view(np.uint32)
     bad = int(np.unpackbits((got_s ^ ms).view(np.uint8)).sum() + np.unpackbits((got_e ^ me).view(np.uint8)).sum())
@@ -731,6 +782,8 @@ def cpu_parity_config5(gw, gs, ge, sb, eb, lo, hi, seed, n_s=1 << 20, n_e=1 << 1
             "sample": "%d states + %d edges with the global indices of rank 0's range head, one pass (%.1f s); "
                       "CPU broad phase = linear scan of the 10 000 stored AABBs (the R-tree stand-in is a list)"
                       % (n_s, n_e, el),
+            "states_all_cores": n_s / el_s, "edges_all_cores": n_e / el_e,
+            "states_single_thread": one_s, "edges_single_thread": one_e,
             "mask_mismatches_vs_gpu": bad}
 
 
@@ -802,6 +855,8 @@ def extras_single_gpu(torch, epp_b200, dev):
     got = w3.check_segments_dev(segs[0][0], segs[0][1]).cpu().numpy().view(np.uint32)
     roofs["config3_segments_256obb"]["mask_mismatches_vs_cpu"] = popcount_words(got ^ want)
     roofs["config3_segments_256obb"]["cpu_kind"] = kind
+    roofs["config3_segments_256obb"]["cpu"] = cpu_rates(
+        lambda th, n: cw.check_segments(h_a[:n], h_b[:n], False, threads=th), BATCH, BATCH // 8)
     pts = [epp_b200.gen_states_dev(worlds.SEED_SEGMENTS, s * BATCH, BATCH, lo, hi, device=dev) for s in range(8)]
     ms = launch_ms(lambda: [w3.check_states_dev(p, mask=m) for p in pts]) / 8
     st = w3.count_candidates_dev(pts[0])
@@ -839,6 +894,20 @@ def extras_single_gpu(torch, epp_b200, dev):
             bad += popcount_words(sm[t_] ^ mk) + (0 if int(ns[t_]) == n_ else 1)
         roofs["config4_fused"]["mask_mismatches_vs_cpu"] = bad
         roofs["config4_fused"]["cpu_kind"] = "port (200 trajectories)"
+        from concurrent.futures import ThreadPoolExecutor
+        ncpu = os.cpu_count() or 1
+
+        def sweep(t_):
+            return ow.check_poly_traj(coeffs[t_], T[t_], dt[t_], 0.1, max_samples=1024)[2]
+        t0 = time.perf_counter()
+        n1 = sum(sweep(t_) for t_ in range(100))
+        one = n1 / (time.perf_counter() - t0)
+        with ThreadPoolExecutor(ncpu) as pool:   # the C call releases the GIL
+            t0 = time.perf_counter()
+            nall = sum(pool.map(sweep, range(2000)))
+            allc = nall / (time.perf_counter() - t0)
+        roofs["config4_fused"]["cpu"] = {"single_thread": one, "all_cores": allc, "cores": ncpu, "kind": "port",
+                                         "sample": "100 / 2000 trajectories (sampler + Horner + world check per sample)"}
     except Exception as ex:
         roofs["config4_fused"]["mask_mismatches_vs_cpu"] = repr(ex)
     del mats, pos
@@ -851,6 +920,12 @@ def extras_single_gpu(torch, epp_b200, dev):
     st = w3.count_candidates_dev(xyz.reshape(-1, 3)[: 1 << 20])
     roofs["config4_presampled"] = roofline_entry("k_states_warp<bits,TR>", n_traj * rows, ms, BYTES_PER_STATE, peak, peak_src,
                                                  state_ops(*st), fp64, stats=st)
+    h_pts = xyz.reshape(-1, 3)[:BATCH].cpu().numpy()
+    want = cw.check_states_mindist(h_pts, 0.1, threads=os.cpu_count() or 1)
+    got = w3.check_states_mindist(h_pts, 0.1)
+    roofs["config4_presampled"]["mask_mismatches_vs_cpu"] = popcount_words(np.asarray(got, np.uint32) ^ want)
+    roofs["config4_presampled"]["cpu"] = cpu_rates(lambda th, n: cw.check_states_mindist(h_pts[:n], 0.1, threads=th),
+                                                   BATCH, BATCH // 8)
     out["config4_presampled_samples_per_s"] = n_traj * rows / (ms * 1e-3)
     del mats, xyz
 

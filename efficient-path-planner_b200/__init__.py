@@ -87,6 +87,7 @@ SIGNATURES = {
                                   C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
     "epp_mask_summary_dev": (C.c_int, [_vp, C.c_size_t, C.c_uint64, _vp, _vp]),
     "epp_measure_fp64_nofma": (C.c_int, [C.c_int, C.c_int, _vp, _dp, _dp]),
+    "epp_check_states_multi_dev": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int, C.c_int, _vp]),
     "epp_measure_single_latency": (C.c_int, [_vp, C.c_int, _dp]),
     "epp_count_candidates_dev": (C.c_int, [_vp, _vp, _vp, C.c_size_t, _vp, _vp]),
     "epp_gen_states_dev": (C.c_int, [C.c_uint64, C.c_uint64, C.c_size_t, _dp, _dp, _vp, _vp]),
@@ -420,6 +421,16 @@ class World:
             _chk(lib().epp_check_states_mindist_dev(self._h, xyz.data_ptr(), n, float(min_distance),
                                                     mask.data_ptr(), self._stream()))
         return mask
+
+    def check_states_multi_dev(self, batches, masks, can_pass_gate=False):
+        """Independent state batches (device tensors) -> their mask tensors, one library call (epp_check_states_multi_dev)."""
+        self._sync()
+        k = len(batches)
+        ptrs = (C.c_void_p * k)(*[b.data_ptr() for b in batches])
+        ns = (C.c_size_t * k)(*[b.numel() // 3 for b in batches])
+        ms = (C.c_void_p * k)(*[m.data_ptr() for m in masks])
+        _chk(lib().epp_check_states_multi_dev(self._h, ptrs, ns, ms, k, int(can_pass_gate), self._stream()))
+        return masks
 
     def check_segments_dev(self, a, b, mask=None, can_pass_gate=False):
         import torch

@@ -69,8 +69,10 @@ Knob g_knobs[] = {
     {"states_rec_smem_max", {0}},        // 0: 256 OBBs
     {"states_bits1", {1}},
     {"states_pdl", {1}},
+    {"states_late_wait", {1}},           // multi-batch calls: batches after the first do not wait for the previous launch before streaming
     {"states_debug", {0}},               // profiling builds only
-    {"poly_traj_per_warp", {0}},         // K3b: trajectories per warp, 0 = by batch size
+    {"poly_traj_per_warp", {0}},
+    {"poly_threads", {256}},             // K3b: threads per block, 256 or 512         // K3b: trajectories per warp, 0 = by batch size
     {"gather_group_chunks", {8}},        // fused exchange: chunks per NVLink run (1: every chunk alone)
     {"gather_debug", {0}},               // profiling only: 1 no wait/unpack, 2 no peer stores
     {"sm_limit", {0}},                   // 0: all SMs; > 0: size grids for this many SMs (several ranks on one GPU in tests)
@@ -293,6 +295,7 @@ LaunchCfg launch_cfg(const DeviceEpoch &ep)
     c.states_pdl = knob_value("states_pdl");
     c.states_debug = knob_value("states_debug");
     c.poly_traj_per_warp = knob_value("poly_traj_per_warp");
+    c.poly_threads = knob_value("poly_threads");
     c.gather_debug = knob_value("gather_debug");
     c.gather_group_chunks = knob_value("gather_group_chunks");
     return c;
@@ -635,6 +638,9 @@ extern "C" int epp_world_active_broadphase(const epp_world *w, int *mode)
 extern "C" int epp_world_commit(epp_world *w)
 {
     if (!w) return fail(EPP_ERR_INVALID_ARG, "null world");
+    // the epoch this commit retires is released AFTER the world's lock (declared first, destroyed last): freeing its
+    // blob synchronises the device and must not stall checks that only want to take a snapshot
+    std::shared_ptr<DeviceEpoch> retired;
     std::lock_guard<std::mutex> lk(w->mu);
 
     int device = 0;
@@ -780,6 +786,7 @@ extern "C" int epp_world_commit(epp_world *w)
     for (int a = 0; a < 3; ++a) v.occ_shift[a] = grid.occ_shift[a];
     ep->bp = bp;
     ep->epoch = ++w->epoch;
+    retired = std::move(w->current);
     w->current = ep; // the previous epoch is released when its last in-flight user drops it
     w->dirty = false;
     return EPP_OK;
@@ -985,6 +992,36 @@ extern "C" int epp_check_states_dev(epp_world *w, const double *d_xyz, size_t n,
     cudaError_t e = launch_states(launch_cfg(*ep), ep->view, ep->bp, d_xyz, n, kModeBool, can_pass_gate, 0.0, d_mask,
                                   (cudaStream_t)stream);
     return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
+}
+
+// Several INDEPENDENT batches in one call (the planner's sample batches): launched back to back on `stream`; from the
+// second on, a batch does not wait for the previous one before it starts streaming its states (programmatic dependent
+// launch with the wait at the kernel's end).  The caller guarantees what makes that safe: every input buffer is
+// complete before the call, and no buffer of one batch overlaps a mask of another.
+extern "C" int epp_check_states_multi_dev(epp_world *w, const double *const *d_xyz, const size_t *n, uint32_t *const *d_mask,
+                                          int batches, int can_pass_gate, void *stream)
+{
+    std::shared_ptr<DeviceEpoch> ep;
+    int rc = snapshot(w, ep);
+    if (rc) return rc;
+    if (batches < 0 || (batches && (!d_xyz || !n || !d_mask))) return fail(EPP_ERR_INVALID_ARG, "null buffer");
+    for (int i = 0; i < batches; ++i) {
+        if (n[i] && (!d_xyz[i] || !d_mask[i])) return fail(EPP_ERR_INVALID_ARG, "null buffer");
+        for (int j = 0; j < i; ++j) { // masks must not overlap each other or any input
+            const char *mi = (const char *)d_mask[i], *mj = (const char *)d_mask[j];
+            const size_t bi = (n[i] + 31) / 32 * 4, bj = (n[j] + 31) / 32 * 4;
+            if (mi < mj + bj && mj < mi + bi) return fail(EPP_ERR_INVALID_ARG, "masks of two batches overlap");
+        }
+    }
+    LaunchCfg cfg = launch_cfg(*ep);
+    const int want_late = knob_value("states_late_wait");
+    for (int i = 0; i < batches; ++i) {
+        cfg.states_late_wait = (i > 0 && want_late) ? 1 : 0;
+        cudaError_t e = launch_states(cfg, ep->view, ep->bp, d_xyz[i], n[i], kModeBool, can_pass_gate, 0.0, d_mask[i],
+                                      (cudaStream_t)stream);
+        if (e != cudaSuccess) return cuda_fail(e, "kernel launch");
+    }
+    return EPP_OK;
 }
 
 extern "C" int epp_check_states_mindist_dev(epp_world *w, const double *d_xyz, size_t n, double min_distance,

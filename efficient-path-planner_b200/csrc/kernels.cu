@@ -407,6 +407,18 @@ struct RayWorld<EPP_BP_BITS> {
         }
         __syncthreads();
     }
+    // The two range rows of a ray box; false: the box spans too many bins (cumulative rows, any()).
+    __device__ __forceinline__ bool rows(const WorldView &wv, const P3 &mn, const P3 &mx, const uint32_t *&rx,
+                                         const uint32_t *&ry) const
+    {
+        const int nb = wv.nb, Ws = wv.Ws, D = wv.range_d;
+        const int gx_ = dev_key_bin(mn.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb), lx_ = dev_key_bin(mx.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb);
+        const int gy_ = dev_key_bin(mn.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb), ly_ = dev_key_bin(mx.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb);
+        if (!(lx_ - gx_ < D && ly_ - gy_ < D)) return false;
+        rx = range + ((gx_ * D) + (lx_ - gx_)) * Ws;
+        ry = range + (((nb + gy_) * D) + (ly_ - gy_)) * Ws;
+        return true;
+    }
     // the range rows arrived in shared memory by bulk copy (k_segments_warp)
     __device__ void bind(const WorldView &wv)
     {
@@ -715,6 +727,8 @@ __device__ __forceinline__ uint32_t gather_seq(const GatherView &gv)
 {
     uint32_t v;
     asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(gv.ctl + 1) : "memory");
+    // the read above must be performed before this block is counted: the block that is counted last bumps ctl[1]
+    asm volatile("fence.acq_rel.gpu;" ::: "memory");
     if (atomicAdd(&gv.ctl[0], 1u) == gridDim.x - 1u) {
         gv.ctl[0] = 0u;
         asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(gv.ctl + 1), "r"(v + 1u) : "memory");
@@ -860,7 +874,7 @@ __device__ __forceinline__ uint32_t warp_states_step(const PointWorld<BP> &world
     const uint32_t lt = (1u << lane) - 1u;
     int queued = 0;
 #ifdef EPP_TRACE
-    const int dbg = mode >> 8; // profiling build only (epp_set_tuning states_debug): 1 skips phase 2, 2 also phase 1
+    const int dbg = (mode >> 8) & 0xff; // profiling build only (epp_set_tuning states_debug): 1 skips phase 2, 2 also phase 1
 #else
     constexpr int dbg = 0;
 #endif
@@ -1067,7 +1081,11 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
     // Programmatic dependent launch: everything above touched only this block's shared memory and the
     // immutable world epoch, so it may overlap the tail of the previous kernel in the stream; the batch and
     // the mask may not.  (Without the launch attribute both instructions are no-ops.)
-    asm volatile("griddepcontrol.wait;" ::: "memory");
+    // late_wait (batches of one multi-batch call, known to be independent of each other and complete before the call):
+    // the wait moves to the END of the kernel, so this launch streams its states while the previous one is still in
+    // its tail, and still does not complete before it — ordering against later launches is kept transitively.
+    const bool late_wait = !GA && ((mode >> 16) & 1) != 0;
+    if (!late_wait) asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     if (warp == 0) {
@@ -1264,6 +1282,7 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
     if constexpr (DEFER) {
         if (fill > 0) deferred_round(0, fill);
     }
+    if (late_wait) asm volatile("griddepcontrol.wait;" ::: "memory");
     EPP_TRACE_EV(g, 15);
     if (GA) {
         // Out of states: take this warp's share of the peers' slots.  Block b owns words
@@ -1431,14 +1450,16 @@ __global__ void __launch_bounds__(TB, TB >= 1024 ? 1 : (TB >= 512 ? 2 : 4)) k_se
 // chunks of kSegS words (64 segments); the producer brings a chunk's two end-point runs (2 x 1536 B) into a ring slot
 // with two bulk copies on one mbarrier; consumers take chunk numbers from a shared counter.
 //   bits / brute: every lane evaluates its kSegS segments from shared memory (records folded as in k_segments_rs for
-//                 worlds of <= 256 z-rotated OBBs) — three lanes in four have candidates there, compaction would not pay;
+//                 worlds of <= 256 z-rotated OBBs).  Compacting (segment, OBB) pairs into dense warp-wide steps was
+//                 built twice (round 1; round 2 with survivors deferred across chunks) and was 4 % SLOWER both times:
+//                 lane utilisation rose from 13 to 24 of 32 but the queue bookkeeping cost more than it saved;
 //   grid:         phase 1 asks the occupancy bitmap (shared memory) whether any coarse cell under the ray box is
 //                 occupied and compacts those segments (~1 in 8 in the 10 000-OBB world) into a per-warp queue,
 //                 phase 2 walks their cell lists one queued segment per lane.
 constexpr int kSegS = 2;
 constexpr int kSegSlotBytes = kSegS * 2 * kWordBytes; // both end points of kSegS * 32 segments
 constexpr int kSegMaxSlots = 64;
-constexpr int kSegWarpBytes = 96 * 4; // per consumer warp: deferred list of up to 31 + kSegS * 32 segment indices
+constexpr int kSegWarpBytes = 96 * 4; // per consumer warp: deferred list of up to 31 + kSegS * 32 segment indices (grid)
 
 template <int BP, bool RS>
 __global__ void __launch_bounds__(1024, 1) k_segments_warp(WorldView wv, const double *__restrict__ pa,
@@ -1564,7 +1585,6 @@ __global__ void __launch_bounds__(1024, 1) k_segments_warp(WorldView wv, const d
         }
         __syncwarp();
     };
-
     for (;;) {
         uint32_t i = 0;
         if (lane == 0) i = atomicAdd(&s_next, 1u);
@@ -1744,8 +1764,8 @@ __device__ __forceinline__ double horner10(const double *__restrict__ c, double 
 // sampler and it was a third of all issued instructions (ncu r02_a); with G = 32 there were 313 warps in all.
 // A trajectory with more than max_samples samples is reported INVALID with first row max_samples (the first row that
 // was not checked) unless an earlier row is invalid — never silently valid.
-template <int BP, bool N10>
-__global__ void __launch_bounds__(kPolyThreads) k_poly_traj(WorldView wv, const double *__restrict__ coeffs,
+template <int BP, bool N10, int TB>
+__global__ void __launch_bounds__(TB, TB >= 512 ? 2 : 5) k_poly_traj(WorldView wv, const double *__restrict__ coeffs,
                                                             const double *__restrict__ durations,
                                                             const double *__restrict__ dts, size_t n_traj,
                                                             int n_segments, int n_coeffs, double min_distance,
@@ -2306,7 +2326,8 @@ cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const 
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     lc.attrs = attr;
     lc.numAttrs = cfg.states_pdl ? 1 : 0;
-    err = cudaLaunchKernelEx(&lc, k_states_warp<BP, S, RS, GA, TR>, wv, d_xyz, n, mode | (cfg.states_debug << 8),
+    err = cudaLaunchKernelEx(&lc, k_states_warp<BP, S, RS, GA, TR>, wv, d_xyz, n,
+                             mode | (cfg.states_debug << 8) | ((cfg.states_late_wait && cfg.states_pdl && !GA && !TR) ? (1 << 16) : 0),
                              can_pass_gate, min_distance, in_smem ? 1 : 0, (uint32_t)slots, (uint32_t)table_bytes,
                              (uint32_t)rec_bytes, (uint32_t)(own_units / grid), (uint32_t)(own_units % grid), d_mask, gv,
                              ga_group, ta);
@@ -2626,10 +2647,12 @@ cudaError_t launch_poly_trajectories(const LaunchCfg &cfg, const WorldView &wv_i
     // 16-byte coefficient loads need a 16 B-aligned batch (a segment's 3 x 10 coefficients are 240 B)
     const bool n10 = n_coeffs == 10 && (reinterpret_cast<uintptr_t>(d_coeffs) & 15u) == 0;
     EPP_DISPATCH_BP(bp, {
-        auto kern = n10 ? k_poly_traj<BP, true> : k_poly_traj<BP, false>;
+        const bool big = cfg.poly_threads >= 512;
+        auto kern = big ? (n10 ? k_poly_traj<BP, true, 512> : k_poly_traj<BP, false, 512>)
+                        : (n10 ? k_poly_traj<BP, true, 256> : k_poly_traj<BP, false, 256>);
         err = ensure_smem(kern, total);
         if (err == cudaSuccess) {
-            kern<<<grid, kPolyThreads, total, stream>>>(wv, d_coeffs, d_durations, d_dt, n_traj, n_segments, n_coeffs,
+            kern<<<grid, big ? 512 : 256, total, stream>>>(wv, d_coeffs, d_durations, d_dt, n_traj, n_segments, n_coeffs,
                                                         min_distance, max_samples, in_smem ? 1 : 0, G, (uint32_t)table_bytes,
                                                         d_sample_mask, d_n_samples, d_first_scratch);
             err = cudaGetLastError();

@@ -26,10 +26,12 @@ struct LaunchCfg {
     int states_debug = 0;           // profiling only: 1 skips phase 2 of the warp form, 2 also phase 1 (wrong masks)
     int segments_block = 0;         // k_segments_rs: threads per block (256, 512, 1024; 0 = by batch size)
     int traj_variant = 0;           // pre-sampled trajectories: 0 auto (warp-pipelined form), 1 direct form only
+    int states_late_wait = 0;       // set per launch by the multi-batch entry point: this batch is independent of the previous launch
     int states_pdl = 1;             // warp form: programmatic dependent launch (prologue overlaps the previous kernel's tail)
     int states_bits1 = 1;           // warp form: single-word candidate masks for worlds of <= 32 OBBs
     int states_rec_smem = 1;        // warp-pipelined form: fold the world records into shared memory
     int states_rec_smem_max = 0;    // ... for worlds of up to this many OBBs (0: 256)
+    int poly_threads = 256;         // K3b: threads per block (256: 1 producer + 7 consumer warps; 512: 1 + 15)
     int poly_traj_per_warp = 0;     // K3b: trajectories per warp (0: by batch size)
     int gather_group_chunks = 8;    // fused exchange: chunks whose mask words travel to a peer in one run (1: each chunk alone)
     int gather_debug = 0;           // profiling only, see GatherView::debug

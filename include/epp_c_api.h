@@ -13,6 +13,14 @@
  * VALID (collision free); tail bits of the last word are 0.  A batch of n units needs
  * (n + 31) / 32 uint32 words.
  *
+ * Inputs: coordinates must be finite.  The kernels use the z-rotation structure of every world this API can build
+ * (src/Object.cpp:38-47 rejects roll and pitch): the exact 0 * d terms of the reference's 3-term sums are dropped, which
+ * is bit-identical for finite inputs and undefined for NaN / infinite ones (the reference itself returns garbage there).
+ *
+ * Device-pointer entry points (*_dev) only enqueue work on `stream`; they may be captured into CUDA graphs.  A captured
+ * graph reads the world epoch that was current at capture time: re-capture after epp_world_commit (the retired epoch's
+ * memory is released once no call in flight holds it).
+ *
  * Threading: check calls are re-entrant and may be issued concurrently from several host
  * threads on one world (the reference runs two planner threads on one World,
  * src/OnlineTrajGenerator.cpp:324-340).  World mutation (reset/add/update/commit) must be
@@ -151,6 +159,13 @@ int epp_check_poly_trajectories(epp_world *w, const double *coeffs, const double
 
 int epp_check_states_dev(epp_world *w, const double *d_xyz, size_t n, int can_pass_gate,
                          uint32_t *d_mask, void *stream);
+/* Several INDEPENDENT state batches in one call (the added batched entry point at the size the planner produces:
+ * many sample batches per solve): batch i = n[i] states at d_xyz[i] -> mask words at d_mask[i].  Launched back to
+ * back on `stream`; from the second batch on a kernel starts streaming its states while the previous one is in its
+ * tail.  Contract: all inputs are complete before the call and no batch's mask overlaps another batch's buffers
+ * (overlapping masks are refused). */
+int epp_check_states_multi_dev(epp_world *w, const double *const *d_xyz, const size_t *n, uint32_t *const *d_mask,
+                               int batches, int can_pass_gate, void *stream);
 int epp_check_states_mindist_dev(epp_world *w, const double *d_xyz, size_t n, double min_distance,
                                  uint32_t *d_mask, void *stream);
 int epp_check_segments_dev(epp_world *w, const double *d_a, const double *d_b, size_t n,

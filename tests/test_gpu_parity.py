@@ -893,3 +893,29 @@ def test_single_unit_mailbox_life_cycle(oracle, config, track):
     a5, b5 = worlds.gen_segments(904, 0, 100, lo5, hi5, 1.0)
     s5 = np.unpackbits(ow5.check_segments(a5, b5, False).view(np.uint8), bitorder="little")
     assert [gw5.checkRayValid(p_, q_, False) for p_, q_ in zip(a5, b5)] == [bool(v) for v in s5[:100]]
+
+
+@pytest.mark.parametrize("which", ["track", "w10k"])
+def test_multi_batch_call_equals_single_calls(oracle, config, which):
+    """epp_check_states_multi_dev: independent batches in one call (kernels overlap at their boundaries: from the second
+    batch on the dependency wait sits at the kernel's end).  Every batch's mask must equal the single-call mask and the
+    oracle's, for warp-form and direct-form sizes and ragged tails, run repeatedly; overlapping masks are refused."""
+    import torch
+    g, o, lo, hi = worlds.track_world(config) if which == "track" else worlds.world_10k()
+    ow, gw = build_pair(oracle, epp_b200, config, g, o)
+    sizes = [1 << 20, 300_001, 4096, 100, 1 << 19, 65_537, 1 << 20]
+    batches = [epp_b200.gen_states_dev(4000 + k, 0, n, lo, hi) for k, n in enumerate(sizes)]
+    masks = [torch.zeros((n + 31) // 32, dtype=torch.int32, device="cuda") for n in sizes]
+    singles = [gw.check_states_dev(b) for b in batches]
+    for _ in range(5):
+        for m in masks:
+            m.zero_()
+        gw.check_states_multi_dev(batches, masks)
+        torch.cuda.synchronize()
+        for k in range(len(sizes)):
+            assert torch.equal(masks[k], singles[k]), (which, k)
+    for k in (0, 1, 3):
+        want = ow.check_states(batches[k].cpu().numpy(), False, threads=8)
+        assert mismatches(masks[k].cpu().numpy().view(np.uint32), want) == 0
+    with pytest.raises(epp_b200.EppError, match="overlap"):
+        gw.check_states_multi_dev([batches[2], batches[3]], [masks[2], masks[2]])
