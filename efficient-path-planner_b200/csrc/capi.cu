@@ -69,11 +69,13 @@ Knob g_knobs[] = {
     {"states_rec_smem_max", {0}},        // 0: 256 OBBs
     {"states_bits1", {1}},
     {"states_pdl", {1}},
-    {"states_late_wait", {1}},           // multi-batch calls: batches after the first do not wait for the previous launch before streaming
+    {"states_late_wait", {1}},
+    {"states_multi_blocks_per_sm", {2}},
+    {"states_multi_grid_per_sm", {1}},   // multi-batch calls: blocks per SM in each launch's grid (0: all that are resident) // multi-batch calls: resident blocks per SM (threads per block = 1024 / this)           // multi-batch calls: batches after the first do not wait for the previous launch before streaming
     {"states_debug", {0}},               // profiling builds only
     {"poly_traj_per_warp", {0}},
     {"poly_threads", {256}},             // K3b: threads per block, 256 or 512         // K3b: trajectories per warp, 0 = by batch size
-    {"gather_group_chunks", {8}},        // fused exchange: chunks per NVLink run (1: every chunk alone)
+    {"gather_group_chunks", {9}},        // fused exchange: chunks per NVLink run (1: every chunk alone)
     {"gather_debug", {0}},               // profiling only: 1 no wait/unpack, 2 no peer stores
     {"sm_limit", {0}},                   // 0: all SMs; > 0: size grids for this many SMs (several ranks on one GPU in tests)
     {"bits_bins", {0}},                  // 0: by world size
@@ -1015,6 +1017,8 @@ extern "C" int epp_check_states_multi_dev(epp_world *w, const double *const *d_x
     }
     LaunchCfg cfg = launch_cfg(*ep);
     const int want_late = knob_value("states_late_wait");
+    cfg.states_multi = (want_late && batches > 1) ? std::max(1, std::min(8, knob_value("states_multi_blocks_per_sm"))) : 0;
+    cfg.states_multi_grid = knob_value("states_multi_grid_per_sm");
     for (int i = 0; i < batches; ++i) {
         cfg.states_late_wait = (i > 0 && want_late) ? 1 : 0;
         cudaError_t e = launch_states(cfg, ep->view, ep->bp, d_xyz[i], n[i], kModeBool, can_pass_gate, 0.0, d_mask[i],
@@ -1091,7 +1095,7 @@ extern "C" int epp_check_poly_trajectories_dev(epp_world *w, const double *d_coe
 struct epp_gather {
     int rank = 0, world = 1, device = 0, n_buffers = 1;
     size_t slot_words = 0;
-    // [control words: 256 B][n_buffers x world x slot_words words][staging: 2 x world x (2 + slot_words) pairs]
+    // [control words: 256 B][n_buffers x world x slot_words words][staging: 2 x world x (1 + ceil(slot_words / 3)) quads]
     unsigned char *base = nullptr;
     unsigned char *peer_base[kMaxRanks] = {}; // every rank's allocation in this process's address space
     bool opened[kMaxRanks] = {};              // peer_base[p] came from cudaIpcOpenMemHandle
@@ -1100,7 +1104,8 @@ struct epp_gather {
     size_t buffer_bytes() const { return (size_t)world * slot_words * 4; }
     uint32_t *buffer_of(unsigned char *b, int i) const { return (uint32_t *)(b + 256 + (size_t)i * buffer_bytes()); }
     size_t staging_off() const { return (256 + (size_t)n_buffers * buffer_bytes() + 255) / 256 * 256; }
-    size_t staging_bytes() const { return (size_t)2 * world * (slot_words + 2) * 8; }
+    size_t row_quads() const { return 1 + (slot_words + 2) / 3; }
+    size_t staging_bytes() const { return (size_t)2 * world * row_quads() * 16; }
 };
 
 namespace {
@@ -1114,8 +1119,9 @@ int gather_view(epp_gather *g, int buffer, size_t n, GatherView &gv)
     if (buffer < 0 || buffer >= g->n_buffers) return fail(EPP_ERR_INVALID_ARG, "gather buffer index");
     if ((n + 31) / 32 > g->slot_words) return fail(EPP_ERR_INVALID_ARG, "more units than the gather slot holds");
     for (int p = 0; p < kMaxRanks; ++p)
-        gv.peer_ll[p] = p < g->world ? (uint2 *)(g->peer_base[p] + g->staging_off()) : nullptr;
-    gv.my_ll = (const uint2 *)(g->base + g->staging_off());
+        gv.peer_ll[p] = p < g->world ? (uint4 *)(g->peer_base[p] + g->staging_off()) : nullptr;
+    gv.my_ll = (const uint4 *)(g->base + g->staging_off());
+    gv.row_quads = g->row_quads();
     gv.out = g->buffer_of(g->base, buffer);
     gv.ctl = (uint32_t *)(g->base + kGatherCtlOff);
     gv.slot_words = g->slot_words;

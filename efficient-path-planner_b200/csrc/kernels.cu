@@ -736,34 +736,61 @@ __device__ __forceinline__ uint32_t gather_seq(const GatherView &gv)
     return v + 1u;
 }
 
-// pair index of word 0 of (parity of seq, source rank) in a staging area
+// Exchange units: a QUAD = three mask words + flags in one 16-byte store (layout at ll_store); unit u of a rank's
+// slot holds words 3u .. 3u + 2.  Round 1 sent (word, number) PAIRS: 8 bytes per word over NVLink, 5.3 now; at 8 ranks the exchange is
+// bound by what crosses NVLink.  Staging row of (parity, source) = 1 header quad + ceil(slot_words / 3) data quads.
+
+// quad index of unit 0 of (parity of seq, source rank) in a staging area
 __device__ __forceinline__ uint64_t gather_row(const GatherView &gv, uint32_t seq, int src)
 {
-    return ((uint64_t)(seq & 1u) * (uint64_t)gv.world + (uint64_t)src) * (gv.slot_words + 2u) + 2u;
+    return ((uint64_t)(seq & 1u) * (uint64_t)gv.world + (uint64_t)src) * gv.row_quads + 1u;
 }
 
-__device__ __forceinline__ void ll_store(uint2 *p, uint32_t word, uint32_t seq)
+// A 16-byte vector access is NOT single-copy atomic (PTX treats it as separate element accesses, and a reader polling
+// while the writer's store is in flight did see the flag of a quad whose other half was still stale: a header read
+// that way zeroed one block's share of a peer's slot about once in a hundred first calls).  So each 8-byte HALF of a
+// quad carries the low 16 bits of the sequence number next to 48 data bits, and a quad counts only when both agree:
+//   half 0 = w0 | w1[15:0] << 32 | flag << 48        half 1 = w1[31:16] | w2 << 16 | flag << 48
+// 16 bits suffice: a row is reused every second call, so a stale flag differs by 2 (and a fresh row holds 0, which
+// no call's flag equals before 65536 calls have made every row non-zero).
+__device__ __forceinline__ void ll_store(uint4 *p, uint32_t w0, uint32_t w1, uint32_t w2, uint32_t seq)
 {
-    asm volatile("st.relaxed.sys.global.v2.u32 [%0], {%1, %2};" ::"l"(p), "r"(word), "r"(seq) : "memory");
+    const unsigned long long f = (unsigned long long)(seq & 0xffffu) << 48;
+    const unsigned long long h0 = (unsigned long long)w0 | ((unsigned long long)(w1 & 0xffffu) << 32) | f;
+    const unsigned long long h1 = (unsigned long long)(w1 >> 16) | ((unsigned long long)w2 << 16) | f;
+    asm volatile("st.relaxed.sys.global.v2.u64 [%0], {%1, %2};" ::"l"(p), "l"(h0), "l"(h1) : "memory");
 }
 
-// Wait until the pair carries this call's sequence number (8-byte stores are single-copy atomic, so the word
-// next to it is the word of this call).  Bounded: a time-out is counted and reads as 0.
-__device__ __forceinline__ uint32_t ll_wait(const uint2 *p, uint32_t seq, const GatherView &gv, bool &dead)
+// Returns the quad as (w0, w1, w2, ok): ok = 1 iff both halves carry this call's flag.
+__device__ __forceinline__ uint4 ll_load(const uint4 *p, uint32_t seq)
 {
-    uint32_t w, f, spins = 0;
+    unsigned long long h0, h1;
+    asm volatile("ld.relaxed.sys.global.v2.u64 {%0, %1}, [%2];" : "=l"(h0), "=l"(h1) : "l"(p) : "memory");
+    const uint32_t f = seq & 0xffffu;
+    uint4 q;
+    q.x = (uint32_t)h0;
+    q.y = (uint32_t)((h0 >> 32) & 0xffffu) | ((uint32_t)(h1 & 0xffffu) << 16);
+    q.z = (uint32_t)(h1 >> 16);
+    q.w = ((uint32_t)(h0 >> 48) == f && (uint32_t)(h1 >> 48) == f) ? 1u : 0u;
+    return q;
+}
+
+// Wait until both halves of the quad carry this call's flag.  Bounded: a time-out is counted and reads as 0.
+__device__ __forceinline__ uint4 ll_wait(const uint4 *p, uint32_t seq, const GatherView &gv, bool &dead)
+{
+    uint32_t spins = 0;
     unsigned long long t0 = 0, t;
     for (;;) {
-        asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];" : "=r"(w), "=r"(f) : "l"(p) : "memory");
-        if (f == seq) return w;
-        if (dead) return 0u; // this thread has already waited one full time-out in this call
+        const uint4 q = ll_load(p, seq);
+        if (q.w) return q;
+        if (dead) return make_uint4(0u, 0u, 0u, 1u); // this thread has already waited one full time-out in this call
         if ((++spins & 63u) == 0u) {
             asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t));
             if (t0 == 0) t0 = t;
             else if (t - t0 > gv.timeout_ns) {
                 atomicAdd(&gv.ctl[2], 1u);
                 dead = true;
-                return 0u;
+                return make_uint4(0u, 0u, 0u, 1u);
             }
         }
     }
@@ -773,51 +800,52 @@ __device__ __forceinline__ uint32_t ll_wait(const uint2 *p, uint32_t seq, const 
 __device__ __forceinline__ void gather_send_header(const GatherView &gv, uint32_t seq, int lane)
 {
     if (lane < gv.world && lane != gv.rank && !(gv.debug & 2))
-        ll_store(gv.peer_ll[lane] + gather_row(gv, seq, gv.rank) - 2u, (uint32_t)gv.my_words, seq);
+        ll_store(gv.peer_ll[lane] + gather_row(gv, seq, gv.rank) - 1u, (uint32_t)gv.my_words, 0u, 0u, seq);
 }
 
-// How many words each peer sends in this call (its header pair), one lane per peer, into cnt[] (shared memory).
+// How many words each peer sends in this call (its header quad), one lane per peer, into cnt[] (shared memory).
 // One warp per BLOCK does this: thousands of warps polling one address would serialise on its L2 slice.
 __device__ __forceinline__ void gather_read_headers(const GatherView &gv, uint32_t seq, uint32_t *cnt, int lane)
 {
     bool dead = false;
-    if (lane < gv.world && lane != gv.rank) cnt[lane] = ll_wait(gv.my_ll + gather_row(gv, seq, lane) - 2, seq, gv, dead);
+    if (lane < gv.world && lane != gv.rank) cnt[lane] = ll_wait(gv.my_ll + gather_row(gv, seq, lane) - 1u, seq, gv, dead).x;
 }
 
-// A warp unpacks words [u0, u1) of every peer's slot into the local gathered buffer (0 beyond what the peer sends).
-// The pairs of ALL peers for a lane's word are requested before any is examined: one L2 round trip per word
+// A warp unpacks units [u0, u1) of every peer's slot into the local gathered buffer (0 beyond what the peer sends).
+// The quads of ALL peers for a lane's unit are requested before any is examined: one L2 round trip per unit
 // instead of one per peer (7 dependent round trips at 8 ranks were ~2.5 us at the tail of every launch).
 __device__ __forceinline__ void gather_unpack(const GatherView &gv, uint32_t seq, const uint32_t *cnt, uint64_t u0,
                                               uint64_t u1, int lane)
 {
     bool dead = false;
-    const uint64_t row = gv.slot_words + 2u;
-    const uint2 *base = gv.my_ll + (uint64_t)(seq & 1u) * (uint64_t)gv.world * row + 2u;
+    const uint4 *base = gv.my_ll + (uint64_t)(seq & 1u) * (uint64_t)gv.world * gv.row_quads + 1u;
     uint32_t *own = gv.out + (uint64_t)gv.rank * gv.slot_words; // own slot: the check wrote [0, my_words); the rest reads 0
-    for (uint64_t w = (u0 > gv.my_words ? u0 : gv.my_words) + (uint64_t)lane; w < u1; w += 32u) own[w] = 0u;
-    for (uint64_t w = u0 + (uint64_t)lane; w < u1; w += 32u) {
-        uint32_t word[kMaxRanks], flag[kMaxRanks];
+    {
+        const uint64_t w1 = 3u * u1 < gv.slot_words ? 3u * u1 : gv.slot_words;
+        for (uint64_t w = (3u * u0 > gv.my_words ? 3u * u0 : gv.my_words) + (uint64_t)lane; w < w1; w += 32u) own[w] = 0u;
+    }
+    for (uint64_t u = u0 + (uint64_t)lane; u < u1; u += 32u) {
+        uint4 q[kMaxRanks];
 #pragma unroll
         for (int p = 0; p < kMaxRanks; ++p) {
-            word[p] = 0u;
-            flag[p] = seq;
-            if (p < gv.world && p != gv.rank && w < cnt[p])
-                asm volatile("ld.relaxed.sys.global.v2.u32 {%0, %1}, [%2];"
-                             : "=r"(word[p]), "=r"(flag[p])
-                             : "l"(base + (uint64_t)p * row + w)
-                             : "memory");
+            q[p] = make_uint4(0u, 0u, 0u, 1u);
+            if (p < gv.world && p != gv.rank && 3u * u < cnt[p]) q[p] = ll_load(base + (uint64_t)p * gv.row_quads + u, seq);
         }
 #pragma unroll
         for (int p = 0; p < kMaxRanks; ++p) {
             if (p >= gv.world || p == gv.rank) continue;
-            if (flag[p] != seq) word[p] = ll_wait(base + (uint64_t)p * row + w, seq, gv, dead);
-            gv.out[(uint64_t)p * gv.slot_words + w] = word[p];
+            if (!q[p].w) q[p] = ll_wait(base + (uint64_t)p * gv.row_quads + u, seq, gv, dead);
+            uint32_t *dst = gv.out + (uint64_t)p * gv.slot_words + 3u * u;
+            const uint64_t w = 3u * u, c = cnt[p];
+            if (w < gv.slot_words) dst[0] = w < c ? q[p].x : 0u;
+            if (w + 1u < gv.slot_words) dst[1] = w + 1u < c ? q[p].y : 0u;
+            if (w + 2u < gv.slot_words) dst[2] = w + 2u < c ? q[p].z : 0u;
         }
     }
 }
 
 // Generic form: any check kernel wrote this rank's words into its own slot of the local gathered buffer;
-// send them to every peer as (word, sequence number) pairs, then unpack the peers' slots.
+// send them to every peer as quads, then unpack the peers' slots.
 __global__ void __launch_bounds__(256) k_gather_push(const __grid_constant__ GatherView gv)
 {
     __shared__ uint32_t s_seq, s_cnt[kMaxRanks];
@@ -829,17 +857,21 @@ __global__ void __launch_bounds__(256) k_gather_push(const __grid_constant__ Gat
     if (blockIdx.x == 0 && threadIdx.x < 32) gather_send_header(gv, seq, lane);
     const uint32_t *src = gv.out + (uint64_t)gv.rank * gv.slot_words;
     const uint64_t stride = (uint64_t)gridDim.x * blockDim.x, t0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t my_units = (gv.my_words + 2u) / 3u, slot_units = (gv.slot_words + 2u) / 3u;
     if (!(gv.debug & 2))
         for (int p = 0; p < gv.world; ++p) {
             if (p == gv.rank) continue;
-            uint2 *dst = gv.peer_ll[p] + gather_row(gv, seq, gv.rank);
-            for (uint64_t i = t0; i < gv.my_words; i += stride) ll_store(dst + i, src[i], seq);
+            uint4 *dst = gv.peer_ll[p] + gather_row(gv, seq, gv.rank);
+            for (uint64_t i = t0; i < my_units; i += stride) {
+                const uint64_t w = 3u * i;
+                ll_store(dst + i, src[w], w + 1u < gv.my_words ? src[w + 1u] : 0u, w + 2u < gv.my_words ? src[w + 2u] : 0u, seq);
+            }
         }
     // this block's share of the peers' slots, a warp at a time
     const uint64_t warps = (uint64_t)gridDim.x * (blockDim.x >> 5), wid = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
-    const uint64_t per = (gv.slot_words + warps - 1) / warps;
-    const uint64_t u0 = wid * per < gv.slot_words ? wid * per : gv.slot_words;
-    const uint64_t u1 = u0 + per < gv.slot_words ? u0 + per : gv.slot_words;
+    const uint64_t per = (slot_units + warps - 1) / warps;
+    const uint64_t u0 = wid * per < slot_units ? wid * per : slot_units;
+    const uint64_t u1 = u0 + per < slot_units ? u0 + per : slot_units;
     if (!(gv.debug & 1)) {
         if (threadIdx.x < 32) gather_read_headers(gv, seq, s_cnt, lane);
         __syncthreads();
@@ -920,12 +952,7 @@ __device__ __forceinline__ uint32_t warp_states_step(const PointWorld<BP> &world
         const uint32_t verdict = ~inv[lane] & active;
         bad = inv[lane] & active;
         if (mask_out) mask_out[lane] = verdict;
-        if (GA && stage_words) {
-            stage_words[lane] = verdict; // sent with its group (k_states_warp)
-        } else if (GA && !(gv.debug & 2)) { // the same word, with this call's number, into every peer's row of this rank
-            for (int p = 0; p < gv.world; ++p)
-                if (p != gv.rank) ll_store(gv.peer_ll[p] + ll_word0 + lane, verdict, seq);
-        }
+        if (GA && stage_words) stage_words[lane] = verdict; // sent with its group (k_states_warp)
         inv[lane] = 0u;
     }
     __syncwarp();
@@ -977,7 +1004,7 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
                                                       uint32_t n_slots, uint32_t table_bytes, uint32_t rec_bytes,
                                                       uint32_t wpb, uint32_t rem, uint32_t *__restrict__ mask,
                                                       const __grid_constant__ GatherView gv, uint32_t ga_group,
-                                                      const __grid_constant__ TrajArgs ta)
+                                                      const __grid_constant__ TrajArgs ta, uint32_t gran)
 {
     static_assert(!(TR && GA), "the trajectory form has no fused exchange");
     __shared__ uint32_t s_seq, s_hdr, s_cnt[kMaxRanks]; // GA: call number; header state (0 none, 1 claimed, 2 read)
@@ -1002,10 +1029,12 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
     uint32_t *ga_count = ga_words + kGaStageWords;
     EPP_TRACE_EV(blockIdx.x * consumers + (warp == 0 ? 0 : warp - 1), warp == 0 ? 13 : 14);
 
-    const uint32_t b0 = blockIdx.x * wpb + (blockIdx.x < rem ? blockIdx.x : rem);
-    const uint32_t b1 = b0 + wpb + (blockIdx.x < rem ? 1u : 0u);
-    const uint32_t chunks = TR ? (b1 - b0) : (b1 - b0 + S - 1) / S;
+    // ownership in units of `gran` words (1; 12 with the fused exchange: whole chunks AND whole 3-word exchange units)
     const uint32_t words_total = (uint32_t)((n + 31) / 32);
+    const uint32_t b0 = (blockIdx.x * wpb + (blockIdx.x < rem ? blockIdx.x : rem)) * gran;
+    uint32_t b1 = b0 + (wpb + (blockIdx.x < rem ? 1u : 0u)) * gran;
+    if (!TR && b1 > words_total) b1 = words_total;
+    const uint32_t chunks = TR ? (b1 - b0) : (b1 - b0 + S - 1) / S;
     const bool aligned = TR ? ta.aligned != 0 : (reinterpret_cast<uintptr_t>(xyz) & 15u) == 0;
     // TR: trajectory and first row of chunk i of this block
     auto traj_of = [&](uint32_t i, uint32_t &t, uint32_t &j) {
@@ -1253,13 +1282,15 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
             old = __shfl_sync(0xffffffffu, old, 0);
             if (old + 1u == g_chunks && !(gv.debug & 2)) {
                 __threadfence_block();
+                // the group's words as quads: b0 and the group's first word are multiples of 12, so unit = word / 3
                 const uint32_t w0 = g0 * S;
                 const uint32_t w1 = (w0 + g_chunks * S) < (b1 - b0) ? (w0 + g_chunks * S) : (b1 - b0);
+                const volatile uint32_t *gw = ga_words;
                 for (int p = 0; p < gv.world; ++p) {
                     if (p == gv.rank) continue;
-                    uint2 *dst = gv.peer_ll[p] + ll_row + b0;
-                    for (uint32_t w = w0 + (uint32_t)lane; w < w1; w += 32u)
-                        ll_store(dst + w, *(volatile uint32_t *)&ga_words[w], seq);
+                    uint4 *dst = gv.peer_ll[p] + ll_row + (b0 + w0) / 3u;
+                    for (uint32_t w = w0 + 3u * (uint32_t)lane; w < w1; w += 96u)
+                        ll_store(dst + (w - w0) / 3u, gw[w], w + 1u < w1 ? gw[w + 1u] : 0u, w + 2u < w1 ? gw[w + 2u] : 0u, seq);
                 }
             }
         }
@@ -1285,12 +1316,13 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
     if (late_wait) asm volatile("griddepcontrol.wait;" ::: "memory");
     EPP_TRACE_EV(g, 15);
     if (GA) {
-        // Out of states: take this warp's share of the peers' slots.  Block b owns words
-        // [b, b + 1) * slot_words / blocks of every peer's slot, its consumer warps split that range.
-        const uint64_t per_b = (gv.slot_words + gridDim.x - 1) / gridDim.x;
+        // Out of states: take this warp's share of the peers' slots.  Block b owns units
+        // [b, b + 1) * slot_units / blocks of every peer's slot, its consumer warps split that range.
+        const uint64_t slot_units = (gv.slot_words + 2u) / 3u; // exchange units (quads) per slot
+        const uint64_t per_b = (slot_units + gridDim.x - 1) / gridDim.x;
         const uint64_t per_w = (per_b + consumers - 1) / consumers;
         uint64_t e = ((uint64_t)blockIdx.x + 1u) * per_b;
-        e = e < gv.slot_words ? e : gv.slot_words;
+        e = e < slot_units ? e : slot_units;
         uint64_t u0 = (uint64_t)blockIdx.x * per_b + (uint64_t)c * per_w;
         u0 = u0 < e ? u0 : e;
         const uint64_t u1 = u0 + per_w < e ? u0 + per_w : e;
@@ -2263,6 +2295,8 @@ extern "C" int epp_debug_trace_copy(unsigned long long *host, size_t n, int clea
     default: { constexpr int BP = EPP_BP_GRID; __VA_ARGS__; } break;             \
     }
 
+cudaError_t launch_gather_push_impl(const LaunchCfg &cfg, const GatherView &gv, cudaStream_t stream);
+
 // TR: the units are the rows of ta's matrices (n = trajectories * rows is only used for the size checks).
 template <int BP, int S, bool RS, bool GA, bool TR = false>
 cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const double *d_xyz, size_t n, int mode,
@@ -2281,23 +2315,54 @@ cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const 
     const size_t warp_bytes = warp_area_bytes(BP, S), slot_bytes = (size_t)S * kWordBytes;
     // resident blocks per SM (tuning, default 1) and the shared-memory budget of each
     int bps = cfg.states_warp_blocks_per_sm > 0 ? cfg.states_warp_blocks_per_sm : 1;
+    int threads = cfg.states_warp_threads;
+    // Batches of a multi-batch call overlap (late dependency wait): that only works if a block of the next launch
+    // fits next to a block of this one, so they run as blocks of 512 threads with half the ring each, ONE per SM in
+    // the grid and room for the next launch's block beside it: two launches share every SM, one in its ramp or tail
+    // while the other streams (1 M states on the track: 6.8 us per batch; 7.4 with both of a launch's blocks on the
+    // SM; 8.2 with one 1024-thread block; single launches are ~8 % slower in this shape, so only multi-batch calls use it).
+    if (cfg.states_multi > 0 && !GA && !TR && bps == 1 && threads == 1024) {
+        bps = cfg.states_multi;
+        threads = 1024 / bps;
+    }
     bps = bps > 8 ? 8 : bps;
-    int cons = (cfg.states_warp_threads > 0 ? cfg.states_warp_threads / 32 : kMaxWarps) - 1;
+    int cons = (threads > 0 ? threads / 32 : kMaxWarps) - 1;
     cons = cons < 1 ? 1 : (cons > kMaxWarps - 1 ? kMaxWarps - 1 : cons);
     // the kernel is compiled for one 1024-thread block per SM (up to 64 registers per thread): several
     // resident blocks share that budget
     if ((cons + 1) * 32 * bps > 1024) cons = 1024 / (32 * bps) - 1;
     cons = cons < 1 ? 1 : cons;
     const size_t chunks_total = (words + S - 1) / S;
-    const size_t blocks_cap = (size_t)cfg.sm_count * bps;
-    const size_t grid = chunks_total < blocks_cap ? chunks_total : blocks_cap;
-    const size_t chunks_per_block = (chunks_total + grid - 1) / grid;
+    // multi-batch launches may put FEWER blocks into the grid than fit (states_multi_grid): the blocks of the next
+    // launch then run next to this launch's blocks for its whole duration, not only in its tail
+    const int gps = (cfg.states_multi > 0 && cfg.states_multi_grid > 0 && cfg.states_multi_grid < bps) ? cfg.states_multi_grid : bps;
+    const size_t blocks_cap = (size_t)cfg.sm_count * gps;
+    // ownership is handed out in words for state batches (12-word units with the fused exchange: whole chunks and whole
+    // 3-word exchange units) and in whole chunks for trajectory matrices
+    const size_t gran = GA ? 12 : 1;
+    const size_t own_units = TR ? chunks_total : (words + gran - 1) / gran;
+    size_t grid = chunks_total < blocks_cap ? chunks_total : blocks_cap;
+    if (grid > own_units) grid = own_units;
+    const size_t words_per_block = ((own_units + grid - 1) / grid) * (TR ? S : gran);
+    const size_t chunks_per_block = (words_per_block + S - 1) / S;
     if ((size_t)cons > chunks_per_block) cons = (int)chunks_per_block;
     const size_t budget = (size_t)(228 * 1024) / bps - 1024 - 4096; // 1 KB reserved per block + static + slack
-    // GA: group staging when a block's words fit it (small batches, where the exchange is the cost that matters)
-    const size_t words_per_block = (words + grid - 1) / grid + S;
+    // GA: a block parks its verdict words and sends them in groups of whole exchange units; batches whose blocks own
+    // more words than the parking area holds (> 4.8 M states per rank) take the plain kernel + the push kernel
     uint32_t ga_group = 0;
-    if (GA && cfg.gather_group_chunks > 1 && words_per_block <= kGaStageWords) ga_group = (uint32_t)cfg.gather_group_chunks;
+    if (GA) {
+        ga_group = (uint32_t)(cfg.gather_group_chunks / 3 * 3);
+        ga_group = ga_group < 3u ? 3u : ga_group;
+        if (words_per_block > kGaStageWords) {
+            if constexpr (GA) {
+                const GatherView none = {};
+                cudaError_t e2 = launch_states_warp<BP, S, RS, false, false>(cfg, wv, d_xyz, n, mode, can_pass_gate, min_distance,
+                                                                            in_smem, table_bytes, stages, d_mask, stream, launched, none);
+                if (e2 != cudaSuccess || !launched) return e2;
+                return launch_gather_push_impl(cfg, gv, stream);
+            }
+        }
+    }
     const size_t ga_bytes = ga_group ? (size_t)kGaStageWords * 4 + (kGaStageWords / S) * 4 : 0;
     const size_t fixed = table_bytes + rec_bytes + cons * warp_bytes + ga_bytes;
     if (fixed + 2 * slot_bytes > budget) return cudaSuccess;
@@ -2312,8 +2377,6 @@ cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const 
     // the records from global memory instead (the caller retries with RS = false)
     if (RS && cons * 32 < wv.M) return cudaSuccess;
     const size_t smem = fixed + slot_bytes * slots;
-    // ownership is handed out in words for state batches and in whole chunks for trajectory matrices
-    const size_t own_units = TR ? chunks_total : words;
     cudaError_t err = cudaFuncSetAttribute(k_states_warp<BP, S, RS, GA, TR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (err != cudaSuccess) return err;
     cudaLaunchConfig_t lc = {};
@@ -2330,13 +2393,18 @@ cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const 
                              mode | (cfg.states_debug << 8) | ((cfg.states_late_wait && cfg.states_pdl && !GA && !TR) ? (1 << 16) : 0),
                              can_pass_gate, min_distance, in_smem ? 1 : 0, (uint32_t)slots, (uint32_t)table_bytes,
                              (uint32_t)rec_bytes, (uint32_t)(own_units / grid), (uint32_t)(own_units % grid), d_mask, gv,
-                             ga_group, ta);
+                             ga_group, ta, (uint32_t)gran);
     if (err != cudaSuccess) return err;
     launched = true;
     return cudaGetLastError();
 }
 
 cudaError_t launch_gather_push(const LaunchCfg &cfg, const GatherView &gv, cudaStream_t stream)
+{
+    return launch_gather_push_impl(cfg, gv, stream);
+}
+
+cudaError_t launch_gather_push_impl(const LaunchCfg &cfg, const GatherView &gv, cudaStream_t stream)
 {
     size_t blocks = (gv.slot_words / 4 + 255) / 256;
     const size_t cap = (size_t)cfg.sm_count * 4;

@@ -26,6 +26,8 @@ struct LaunchCfg {
     int states_debug = 0;           // profiling only: 1 skips phase 2 of the warp form, 2 also phase 1 (wrong masks)
     int segments_block = 0;         // k_segments_rs: threads per block (256, 512, 1024; 0 = by batch size)
     int traj_variant = 0;           // pre-sampled trajectories: 0 auto (warp-pipelined form), 1 direct form only
+    int states_multi = 0;           // set by the multi-batch entry point: resident blocks per SM for its launches (0: not a multi-batch launch)
+    int states_multi_grid = 0;      // multi-batch launches: blocks per SM in the GRID (0: as many as are resident)
     int states_late_wait = 0;       // set per launch by the multi-batch entry point: this batch is independent of the previous launch
     int states_pdl = 1;             // warp form: programmatic dependent launch (prologue overlaps the previous kernel's tail)
     int states_bits1 = 1;           // warp form: single-word candidate masks for worlds of <= 32 OBBs
@@ -48,12 +50,14 @@ extern std::atomic<uint64_t> g_launches;
 // staging pairs until they carry this call's sequence number and writes the words into the local gathered
 // buffer.  When the kernel has ended, the local gathered buffer holds the words of all ranks: an all-gather
 // with no collective launch, overlapped with the checks chunk by chunk.
-// Staging: 2 parities (sequence number & 1) x world source ranks x (2 + slot_words) pairs; pair 0 of a row
-// is the header (number of words the source sends in this call, sequence number).
+// Staging: 2 parities (sequence number & 1) x world source ranks x (1 + ceil(slot_words / 3)) QUADS of 16 bytes
+// (three mask words + a 16-bit call flag in each 8-byte half); quad 0 of a row is the header (number of words the
+// source sends).
 constexpr int kMaxRanks = 8;
 struct GatherView {
-    uint2 *peer_ll[kMaxRanks]; // rank p's staging area in this process's address space
-    const uint2 *my_ll;        // this rank's staging area
+    uint4 *peer_ll[kMaxRanks]; // rank p's staging area in this process's address space
+    const uint4 *my_ll;        // this rank's staging area
+    uint64_t row_quads;        // quads per staging row: 1 header + ceil(slot_words / 3)
     uint32_t *out;             // this rank's gathered buffer of this call (world x slot_words words)
     uint32_t *ctl;             // local: [0] blocks done, [1] calls completed (sequence number), [2] wait time-outs
     uint64_t slot_words;
