@@ -544,11 +544,14 @@ def config5_measure(args, torch, dist, epp_b200, dev, rank, world, K, W, cpu_par
     exchange = "none (single GPU)"
     if world > 1 and args.exchange == "fused":
         try:
-            gat_s = epp_b200.Gather(rank, world, sw_s, n_buffers=1).connect()
-            gat_e = epp_b200.Gather(rank, world, sw_e, n_buffers=1).connect()
-            gs, ge = gat_s.tensor(0, dev), gat_e.tensor(0, dev)
-            exchange = ("fused: states - peer stores from the check kernel; edges - push kernel behind "
-                        "k_segments; signal/wait on the device, no collective launch")
+            # two buffers, alternating: large slots are written by the peers directly and a peer may be a call ahead
+            gat_s = epp_b200.Gather(rank, world, sw_s, n_buffers=2).connect()
+            gat_e = epp_b200.Gather(rank, world, sw_e, n_buffers=2).connect()
+            gs_b, ge_b = [gat_s.tensor(i, dev) for i in (0, 1)], [gat_e.tensor(i, dev) for i in (0, 1)]
+            gs, ge = gs_b[0], ge_b[0]
+            exchange = ("device-side, no collective launch: slots of >= 65536 mask words are copied straight into the "
+                        "peers' gathered buffers behind the check kernel (k_gather_bulk: 16-byte NVLink stores, system "
+                        "fence, one header per peer); smaller slots travel as flagged quads (k_gather_push)")
         except epp_b200.EppError as ex:
             gat_s = gat_e = None
             exchange = "nccl all-gather (fused exchange unavailable: %s)" % ex
@@ -559,10 +562,14 @@ def config5_measure(args, torch, dist, epp_b200, dev, rank, world, K, W, cpu_par
             exchange = "nccl all-gather, in place"
     torch.cuda.synchronize()
 
+    calls = [0]
+
     def step():
         if gat_s is not None:
-            gat_s.check_states(gw, d_xyz, 0)
-            gat_e.check_segments(gw, d_a, d_b, 0)
+            b_ = calls[0] & 1
+            calls[0] += 1
+            gat_s.check_states(gw, d_xyz, b_)
+            gat_e.check_segments(gw, d_a, d_b, b_)
             return
         if se > sb:
             gw.check_states_dev(d_xyz, mask=gs[rank][:ws])
@@ -593,6 +600,7 @@ def config5_measure(args, torch, dist, epp_b200, dev, rank, world, K, W, cpu_par
 
     timeouts = 0
     if gat_s is not None:
+        gs, ge = gs_b[(calls[0] - 1) & 1], ge_b[(calls[0] - 1) & 1]   # what the last step left
         timeouts = gat_s.status()[1] + gat_e.status()[1]
         if timeouts:
             raise SystemExit("bench: %d gather waits timed out" % timeouts)
@@ -675,7 +683,7 @@ def config5_measure(args, torch, dist, epp_b200, dev, rank, world, K, W, cpu_par
         out["cpu_baseline"] = cpu_parity_config5(gw, gs, ge, sb, eb, lo, hi, seed)
     del d_xyz, d_a, d_b, gs, ge, tmp_s, tmp_e
     if gat_s is not None:
-        del gat_s, gat_e
+        del gat_s, gat_e, gs_b, ge_b
     torch.cuda.empty_cache()
     return out
 

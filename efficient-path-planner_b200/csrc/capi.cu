@@ -76,6 +76,7 @@ Knob g_knobs[] = {
     {"poly_traj_per_warp", {0}},
     {"poly_threads", {256}},             // K3b: threads per block, 256 or 512         // K3b: trajectories per warp, 0 = by batch size
     {"gather_group_chunks", {9}},        // fused exchange: chunks per NVLink run (1: every chunk alone)
+    {"gather_bulk_min_words", {65536}},  // exchange: slots from this many words up are copied straight into the peers' buffers (0: never)
     {"gather_debug", {0}},               // profiling only: 1 no wait/unpack, 2 no peer stores
     {"sm_limit", {0}},                   // 0: all SMs; > 0: size grids for this many SMs (several ranks on one GPU in tests)
     {"bits_bins", {0}},                  // 0: by world size
@@ -300,6 +301,7 @@ LaunchCfg launch_cfg(const DeviceEpoch &ep)
     c.poly_threads = knob_value("poly_threads");
     c.gather_debug = knob_value("gather_debug");
     c.gather_group_chunks = knob_value("gather_group_chunks");
+    c.gather_bulk_min_words = knob_value("gather_bulk_min_words");
     return c;
 }
 
@@ -1100,6 +1102,7 @@ struct epp_gather {
     unsigned char *peer_base[kMaxRanks] = {}; // every rank's allocation in this process's address space
     bool opened[kMaxRanks] = {};              // peer_base[p] came from cudaIpcOpenMemHandle
     bool connected = false;
+    int last_buffer = -1;                     // buffer of the previous gathering call
     uint64_t timeout_ns = 2000000000ull;
     size_t buffer_bytes() const { return (size_t)world * slot_words * 4; }
     uint32_t *buffer_of(unsigned char *b, int i) const { return (uint32_t *)(b + 256 + (size_t)i * buffer_bytes()); }
@@ -1122,6 +1125,16 @@ int gather_view(epp_gather *g, int buffer, size_t n, GatherView &gv)
         gv.peer_ll[p] = p < g->world ? (uint4 *)(g->peer_base[p] + g->staging_off()) : nullptr;
     gv.my_ll = (const uint4 *)(g->base + g->staging_off());
     gv.row_quads = g->row_quads();
+    for (int p = 0; p < kMaxRanks; ++p) gv.peer_out[p] = p < g->world ? g->buffer_of(g->peer_base[p], buffer) : nullptr;
+    // Large slots are copied straight into the peers' gathered buffers (k_gather_bulk): a peer may be one call ahead,
+    // so the buffer of the previous call must not be the target of this one.
+    const int bulk_min = knob_value("gather_bulk_min_words");
+    if (g->world > 1 && bulk_min > 0 && g->slot_words >= (size_t)bulk_min) {
+        if (g->n_buffers < 2 || buffer == g->last_buffer)
+            return fail(EPP_ERR_INVALID_ARG, "gather slots of this size are written by the peers directly: use n_buffers >= 2 "
+                                             "and a different buffer than the previous call");
+    }
+    g->last_buffer = buffer;
     gv.out = g->buffer_of(g->base, buffer);
     gv.ctl = (uint32_t *)(g->base + kGatherCtlOff);
     gv.slot_words = g->slot_words;

@@ -726,9 +726,9 @@ __global__ void k_trace_base(uint32_t base) { g_trace_base = base; }
 __device__ __forceinline__ uint32_t gather_seq(const GatherView &gv)
 {
     uint32_t v;
-    asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(gv.ctl + 1) : "memory");
-    // the read above must be performed before this block is counted: the block that is counted last bumps ctl[1]
-    asm volatile("fence.acq_rel.gpu;" ::: "memory");
+    // an ACQUIRE load: it is performed before the atomic below counts this block (the block that is counted last
+    // bumps ctl[1]; a full fence here cost 3 us per launch)
+    asm volatile("ld.acquire.gpu.global.u32 %0, [%1];" : "=r"(v) : "l"(gv.ctl + 1) : "memory");
     if (atomicAdd(&gv.ctl[0], 1u) == gridDim.x - 1u) {
         gv.ctl[0] = 0u;
         asm volatile("st.relaxed.gpu.global.u32 [%0], %1;" ::"l"(gv.ctl + 1), "r"(v + 1u) : "memory");
@@ -876,6 +876,55 @@ __global__ void __launch_bounds__(256) k_gather_push(const __grid_constant__ Gat
         if (threadIdx.x < 32) gather_read_headers(gv, seq, s_cnt, lane);
         __syncthreads();
         gather_unpack(gv, seq, s_cnt, u0, u1, lane);
+    }
+}
+
+// Bulk form of the exchange for LARGE slots (config 5: 3.9 M mask words per rank at 8 ranks).  Flags in the data make
+// a 9 us step cheap but cost a third more NVLink bytes, a staging area and an unpack pass; for megabytes the plain
+// way wins: every block copies its share of the rank's slot straight into slot `rank` of every peer's gathered buffer
+// (16-byte stores, 4 bytes per word on the wire, nothing to unpack), makes its stores visible system-wide and is
+// counted; the block that is counted last tells the peers (their header quad) and waits for theirs.  When the kernel
+// has ended, every peer's slot is in place.  Peers write into the gathered buffer itself, so consecutive calls must
+// alternate buffers (checked on the host).  8 ranks, 1 B states: 0.2 ms instead of 0.7 ms behind the check kernel.
+__global__ void __launch_bounds__(256) k_gather_bulk(const __grid_constant__ GatherView gv)
+{
+    __shared__ uint32_t s_seq, s_last, s_cnt[kMaxRanks];
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    if (threadIdx.x == 0) s_seq = gather_seq(gv);
+    __syncthreads();
+    const uint32_t seq = s_seq;
+    uint32_t *own = gv.out + (uint64_t)gv.rank * gv.slot_words;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x, t0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t n4 = gv.slot_words / 4; // slot_words is a multiple of 4 (epp_gather_create)
+    for (uint64_t i = t0; i < n4; i += stride) {
+        const uint64_t w = 4u * i;
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (w + 3u < gv.my_words) {
+            v = *reinterpret_cast<const uint4 *>(own + w);
+        } else {
+            if (w < gv.my_words) v.x = own[w];
+            if (w + 1u < gv.my_words) v.y = own[w + 1u];
+            if (w + 2u < gv.my_words) v.z = own[w + 2u];
+            *reinterpret_cast<uint4 *>(own + w) = v; // words beyond this rank's units read 0 everywhere
+        }
+        if (!(gv.debug & 2))
+            for (int p = 0; p < gv.world; ++p)
+                if (p != gv.rank)
+                    asm volatile("st.relaxed.sys.global.v4.u32 [%0], {%1, %2, %3, %4};" ::"l"(gv.peer_out[p] + (uint64_t)gv.rank * gv.slot_words + w),
+                                 "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+    }
+    __threadfence_system();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(&gv.ctl[3], 1u) == gridDim.x - 1u ? 1u : 0u;
+    __syncthreads();
+    if (!s_last) return;
+    if (threadIdx.x == 0) gv.ctl[3] = 0u;
+    __threadfence_system();
+    const int lane = threadIdx.x & 31;
+    if (threadIdx.x < 32) {
+        gather_send_header(gv, seq, lane);
+        if (!(gv.debug & 1)) gather_read_headers(gv, seq, s_cnt, lane);
+        __threadfence_system();
     }
 }
 
@@ -2296,6 +2345,7 @@ extern "C" int epp_debug_trace_copy(unsigned long long *host, size_t n, int clea
     }
 
 cudaError_t launch_gather_push_impl(const LaunchCfg &cfg, const GatherView &gv, cudaStream_t stream);
+bool gather_is_bulk(const LaunchCfg &cfg, const GatherView &gv);
 
 // TR: the units are the rows of ta's matrices (n = trajectories * rows is only used for the size checks).
 template <int BP, int S, bool RS, bool GA, bool TR = false>
@@ -2353,7 +2403,7 @@ cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const 
     if (GA) {
         ga_group = (uint32_t)(cfg.gather_group_chunks / 3 * 3);
         ga_group = ga_group < 3u ? 3u : ga_group;
-        if (words_per_block > kGaStageWords) {
+        if (words_per_block > kGaStageWords || gather_is_bulk(cfg, gv)) { // every rank must take the same form: decided by the slot size
             if constexpr (GA) {
                 const GatherView none = {};
                 cudaError_t e2 = launch_states_warp<BP, S, RS, false, false>(cfg, wv, d_xyz, n, mode, can_pass_gate, min_distance,
@@ -2404,8 +2454,21 @@ cudaError_t launch_gather_push(const LaunchCfg &cfg, const GatherView &gv, cudaS
     return launch_gather_push_impl(cfg, gv, stream);
 }
 
+bool gather_is_bulk(const LaunchCfg &cfg, const GatherView &gv)
+{
+    return gv.world > 1 && cfg.gather_bulk_min_words > 0 && gv.slot_words >= (uint64_t)cfg.gather_bulk_min_words;
+}
+
 cudaError_t launch_gather_push_impl(const LaunchCfg &cfg, const GatherView &gv, cudaStream_t stream)
 {
+    if (gather_is_bulk(cfg, gv)) {
+        size_t nb = (gv.slot_words / 4 + 255) / 256;
+        const size_t capb = (size_t)cfg.sm_count * 8;
+        nb = nb < 1 ? 1 : (nb > capb ? capb : nb);
+        k_gather_bulk<<<(unsigned)nb, 256, 0, stream>>>(gv);
+        g_launches++;
+        return cudaGetLastError();
+    }
     size_t blocks = (gv.slot_words / 4 + 255) / 256;
     const size_t cap = (size_t)cfg.sm_count * 4;
     blocks = blocks < 1 ? 1 : (blocks > cap ? cap : blocks);

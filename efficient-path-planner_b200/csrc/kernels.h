@@ -36,6 +36,7 @@ struct LaunchCfg {
     int poly_threads = 256;         // K3b: threads per block (256: 1 producer + 7 consumer warps; 512: 1 + 15)
     int poly_traj_per_warp = 0;     // K3b: trajectories per warp (0: by batch size)
     int gather_group_chunks = 8;    // fused exchange: chunks whose mask words travel to a peer in one run (1: each chunk alone)
+    int gather_bulk_min_words = 65536; // slots from this size up: the slot is copied straight into the peers' gathered buffers
     int gather_debug = 0;           // profiling only, see GatherView::debug
     int states_per_thread = 0;      // warp form: mask words (32 states) per chunk and warp step, 4 (default) or 8
 };
@@ -59,7 +60,8 @@ struct GatherView {
     const uint4 *my_ll;        // this rank's staging area
     uint64_t row_quads;        // quads per staging row: 1 header + ceil(slot_words / 3)
     uint32_t *out;             // this rank's gathered buffer of this call (world x slot_words words)
-    uint32_t *ctl;             // local: [0] blocks done, [1] calls completed (sequence number), [2] wait time-outs
+    uint32_t *peer_out[kMaxRanks]; // the peers' gathered buffers of this call (bulk form: written directly)
+    uint32_t *ctl;             // local: [0] blocks done, [1] calls completed (sequence number), [2] wait time-outs, [3] bulk form: blocks that have stored
     uint64_t slot_words;
     uint64_t my_words;         // words this rank sends in this call
     uint64_t timeout_ns;       // bound on every wait (a peer that never calls must not hang the GPU)

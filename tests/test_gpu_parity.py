@@ -919,3 +919,56 @@ def test_multi_batch_call_equals_single_calls(oracle, config, which):
         assert mismatches(masks[k].cpu().numpy().view(np.uint32), want) == 0
     with pytest.raises(epp_b200.EppError, match="overlap"):
         gw.check_states_multi_dev([batches[2], batches[3]], [masks[2], masks[2]])
+
+
+def test_gather_bulk_form_logical_ranks(oracle, config, track):
+    """Large slots take the bulk form of the exchange (the slot is copied straight into the peers' gathered buffers,
+    fence, header): here forced for a small batch through the knob, 3 logical ranks on one GPU, states and segments,
+    repeated calls over two alternating buffers; reusing the previous call's buffer is refused."""
+    import torch
+    from epp_b200 import sharding
+    g, o, lo, hi = track
+    ow, gw = build_pair(oracle, epp_b200, config, g, o)
+    world_size, n = 3, 200_003
+    xyz = worlds.gen_states(worlds.SEED_STATES, 31, n, lo, hi)
+    a, b = worlds.gen_segments(worlds.SEED_SEGMENTS, 32, n, lo, hi, 1.0)
+    want_s, want_e = ow.check_states(xyz, threads=8), ow.check_segments(a, b, threads=8)
+    d_xyz, d_a, d_b = (torch.from_numpy(x).cuda() for x in (xyz, a, b))
+    sw = sharding.slot_words(n, world_size)
+    epp_b200.set_tuning("gather_bulk_min_words", 1024)
+    try:
+        gathers = [epp_b200.Gather(r, world_size, sw, n_buffers=2) for r in range(world_size)]
+        epp_b200.Gather.connect_local(gathers)
+        for variant in ((3, 256), (2, 0)):   # launch every kernel form once before ranks wait for each other
+            epp_b200.set_tuning("segments_variant", variant[0])
+            epp_b200.set_tuning("segments_block", variant[1])
+            gw.check_segments_dev(d_a[:40000], d_b[:40000])
+        epp_b200.set_tuning("segments_variant", 0)
+        epp_b200.set_tuning("segments_block", 0)
+        gw.check_states_dev(d_xyz[:70000])
+        torch.cuda.synchronize()
+        for call in range(4):
+            buf = call & 1
+            for gth in gathers:
+                gth.tensor(buf).fill_(-1)
+            torch.cuda.synchronize()
+            seg = call >= 2
+
+            def issue(r, gth):
+                lo_, hi_ = epp_b200.shard_range(n, r, world_size, 1024)
+                if seg:
+                    gth.check_segments(gw, d_a[lo_:hi_], d_b[lo_:hi_], buf)
+                else:
+                    gth.check_states(gw, d_xyz[lo_:hi_], buf)
+
+            _run_logical_ranks(gathers, issue)
+            for r, gth in enumerate(gathers):
+                assert mismatches(sharding.assemble(gth.tensor(buf), n), want_e if seg else want_s) == 0, (r, call)
+        with pytest.raises(epp_b200.EppError, match="different buffer"):
+            gathers[0].check_states(gw, d_xyz[:1024], 1)   # the previous call used buffer 1
+        for gth in gathers:
+            assert gth.status()[1] == 0
+    finally:
+        epp_b200.set_tuning("gather_bulk_min_words", 65536)
+        epp_b200.set_tuning("segments_variant", 0)
+        epp_b200.set_tuning("segments_block", 0)
