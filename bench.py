@@ -861,6 +861,7 @@ def extras_single_gpu(torch, epp_b200, dev):
     h_a, h_b = segs[0][0].cpu().numpy(), segs[0][1].cpu().numpy()
     want = cw.check_segments(h_a, h_b, False, threads=os.cpu_count() or 1)
     got = w3.check_segments_dev(segs[0][0], segs[0][1]).cpu().numpy().view(np.uint32)
+    roofs["config3_segments_256obb"]["traffic"] = load_traffic("config3_segments_256obb")
     roofs["config3_segments_256obb"]["mask_mismatches_vs_cpu"] = popcount_words(got ^ want)
     roofs["config3_segments_256obb"]["cpu_kind"] = kind
     roofs["config3_segments_256obb"]["cpu"] = cpu_rates(
@@ -889,6 +890,7 @@ def extras_single_gpu(torch, epp_b200, dev):
     # 54 Horner operations + 2 adds of the sampler per sample, then the state check
     roofs["config4_fused"] = roofline_entry("k_poly_traj<bits>", samples, ms, 8 * 31 * 8 / 1000.0 + 0.125, peak, peak_src,
                                             56.0 + state_ops(*st), fp64, stats=st)
+    roofs["config4_fused"]["traffic"] = load_traffic("config4_fused")
     out["config4_fused_samples_per_s"] = samples / (ms * 1e-3)
     # mismatches of the fused sweep vs the CPU reference on the first 200 trajectories
     bad = 0
@@ -948,12 +950,14 @@ def extras_single_gpu(torch, epp_b200, dev):
     st = w5.count_candidates_dev(pts[: 1 << 22])
     roofs["config5_states_16M"] = roofline_entry("k_states_warp<grid>", n5, ms, BYTES_PER_STATE, peak, peak_src,
                                                  state_ops(*st), fp64, stats=st)
+    roofs["config5_states_16M"]["traffic"] = load_traffic("config5_states_16M")
     out["config5_states_10k_obb_checks_per_s"] = n5 / (ms * 1e-3)
     a, b = epp_b200.gen_segments_dev(worlds.SEED_CLUTTER, 0, n5 // 4, lo, hi, 1.0, device=dev)
     ms = launch_ms(lambda: w5.check_segments_dev(a, b, mask=m5))
     st = w5.count_candidates_dev(a[: 1 << 20], b[: 1 << 20])
     roofs["config5_edges_4M"] = roofline_entry("k_segments_warp<grid>", n5 // 4, ms, BYTES_PER_SEGMENT, peak, peak_src,
                                                segment_ops(*st), fp64, stats=st)
+    roofs["config5_edges_4M"]["traffic"] = load_traffic("config5_edges_4M")
     out["config5_segments_10k_obb_checks_per_s"] = n5 // 4 / (ms * 1e-3)
     out["config5_broadphase"] = epp_b200.BP_NAMES[w5.active_broadphase()]
     del pts, a, b, m5

@@ -88,6 +88,8 @@ SIGNATURES = {
     "epp_mask_summary_dev": (C.c_int, [_vp, C.c_size_t, C.c_uint64, _vp, _vp]),
     "epp_measure_fp64_nofma": (C.c_int, [C.c_int, C.c_int, _vp, _dp, _dp]),
     "epp_check_states_multi_dev": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int, C.c_int, _vp]),
+    "epp_gather_set_deferred": (C.c_int, [_vp, C.c_int]),
+    "epp_gather_flush": (C.c_int, [_vp, _vp]),
     "epp_measure_single_latency": (C.c_int, [_vp, C.c_int, _dp]),
     "epp_count_candidates_dev": (C.c_int, [_vp, _vp, _vp, C.c_size_t, _vp, _vp]),
     "epp_gen_states_dev": (C.c_int, [C.c_uint64, C.c_uint64, C.c_size_t, _dp, _dp, _vp, _vp]),
@@ -551,6 +553,16 @@ class Gather:
 
     def set_timeout_ms(self, ms):
         _chk(lib().epp_gather_set_timeout_ms(self._h, int(ms)))
+
+    def set_deferred(self, on=True):
+        """Deferred form: a call unpacks the peers' words of the previous call; tensor(b) of call s is complete after
+        call s + 1 or flush() (include/epp_c_api.h)."""
+        _chk(lib().epp_gather_set_deferred(self._h, int(bool(on))))
+        return self
+
+    def flush(self):
+        import torch
+        _chk(lib().epp_gather_flush(self._h, torch.cuda.current_stream().cuda_stream))
 
     def status(self):
         calls, timeouts = C.c_uint64(0), C.c_uint64(0)

@@ -1103,11 +1103,13 @@ struct epp_gather {
     bool opened[kMaxRanks] = {};              // peer_base[p] came from cudaIpcOpenMemHandle
     bool connected = false;
     int last_buffer = -1;                     // buffer of the previous gathering call
+    bool deferred = false;                    // deferred form (epp_gather_set_deferred)
+    uint32_t *prev_out = nullptr;             // deferred form: the previous call's gathered buffer, still to be completed
     uint64_t timeout_ns = 2000000000ull;
     size_t buffer_bytes() const { return (size_t)world * slot_words * 4; }
     uint32_t *buffer_of(unsigned char *b, int i) const { return (uint32_t *)(b + 256 + (size_t)i * buffer_bytes()); }
     size_t staging_off() const { return (256 + (size_t)n_buffers * buffer_bytes() + 255) / 256 * 256; }
-    size_t row_quads() const { return 1 + (slot_words + 2) / 3; }
+    size_t row_quads() const { return 2 + (slot_words + 2) / 3; }
     size_t staging_bytes() const { return (size_t)2 * world * row_quads() * 16; }
 };
 
@@ -1136,6 +1138,10 @@ int gather_view(epp_gather *g, int buffer, size_t n, GatherView &gv)
     }
     g->last_buffer = buffer;
     gv.out = g->buffer_of(g->base, buffer);
+    const bool bulk = g->world > 1 && bulk_min > 0 && g->slot_words >= (size_t)bulk_min;
+    gv.deferred = (g->deferred && g->world > 1 && !bulk) ? 1 : 0;
+    gv.prev_out = gv.deferred ? g->prev_out : nullptr;
+    if (gv.deferred) g->prev_out = gv.out;
     gv.ctl = (uint32_t *)(g->base + kGatherCtlOff);
     gv.slot_words = g->slot_words;
     gv.my_words = (n + 31) / 32;
@@ -1253,6 +1259,34 @@ extern "C" int epp_gather_set_timeout_ms(epp_gather *g, unsigned ms)
     if (!g) return fail(EPP_ERR_INVALID_ARG, "null gather");
     g->timeout_ns = (uint64_t)ms * 1000000ull;
     return EPP_OK;
+}
+
+extern "C" int epp_gather_set_deferred(epp_gather *g, int on)
+{
+    if (!g) return fail(EPP_ERR_INVALID_ARG, "null gather");
+    if (g->prev_out) return fail(EPP_ERR_INVALID_ARG, "flush the gather before changing its mode");
+    g->deferred = on != 0;
+    return EPP_OK;
+}
+
+extern "C" int epp_gather_flush(epp_gather *g, void *stream)
+{
+    if (!g) return fail(EPP_ERR_INVALID_ARG, "null gather");
+    if (!g->connected) return fail(EPP_ERR_INVALID_ARG, "gather is not connected to its peers");
+    if (!g->deferred || !g->prev_out) return EPP_OK; // nothing outstanding
+    GatherView gv;
+    int rc = gather_view(g, g->last_buffer, 0, gv);
+    if (rc) return rc;
+    g->prev_out = nullptr; // gather_view has just set it to this buffer again
+    int device = 0, sms = 148;
+    EPP_CUDA(cudaGetDevice(&device));
+    EPP_CUDA(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+    LaunchCfg cfg;
+    cfg.sm_count = sms;
+    const int sm_limit = knob_value("sm_limit");
+    if (sm_limit > 0 && sm_limit < cfg.sm_count) cfg.sm_count = sm_limit;
+    cudaError_t e = launch_gather_deferred(cfg, gv, 1, (cudaStream_t)stream);
+    return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
 }
 
 extern "C" int epp_gather_status(epp_gather *g, uint64_t *calls, uint64_t *timeouts)

@@ -737,13 +737,13 @@ __device__ __forceinline__ uint32_t gather_seq(const GatherView &gv)
 }
 
 // Exchange units: a QUAD = three mask words + flags in one 16-byte store (layout at ll_store); unit u of a rank's
-// slot holds words 3u .. 3u + 2.  Round 1 sent (word, number) PAIRS: 8 bytes per word over NVLink, 5.3 now; at 8 ranks the exchange is
-// bound by what crosses NVLink.  Staging row of (parity, source) = 1 header quad + ceil(slot_words / 3) data quads.
+// slot holds words 3u .. 3u + 2.  Round 1 sent (word, number) PAIRS: 8 bytes per word over NVLink, 5.3 now.
+// Staging row of (parity, source) = header quad + acknowledgement quad (deferred form) + ceil(slot_words / 3) data quads.
 
 // quad index of unit 0 of (parity of seq, source rank) in a staging area
 __device__ __forceinline__ uint64_t gather_row(const GatherView &gv, uint32_t seq, int src)
 {
-    return ((uint64_t)(seq & 1u) * (uint64_t)gv.world + (uint64_t)src) * gv.row_quads + 1u;
+    return ((uint64_t)(seq & 1u) * (uint64_t)gv.world + (uint64_t)src) * gv.row_quads + 2u;
 }
 
 // A 16-byte vector access is NOT single-copy atomic (PTX treats it as separate element accesses, and a reader polling
@@ -800,7 +800,7 @@ __device__ __forceinline__ uint4 ll_wait(const uint4 *p, uint32_t seq, const Gat
 __device__ __forceinline__ void gather_send_header(const GatherView &gv, uint32_t seq, int lane)
 {
     if (lane < gv.world && lane != gv.rank && !(gv.debug & 2))
-        ll_store(gv.peer_ll[lane] + gather_row(gv, seq, gv.rank) - 1u, (uint32_t)gv.my_words, 0u, 0u, seq);
+        ll_store(gv.peer_ll[lane] + gather_row(gv, seq, gv.rank) - 2u, (uint32_t)gv.my_words, 0u, 0u, seq);
 }
 
 // How many words each peer sends in this call (its header quad), one lane per peer, into cnt[] (shared memory).
@@ -808,19 +808,20 @@ __device__ __forceinline__ void gather_send_header(const GatherView &gv, uint32_
 __device__ __forceinline__ void gather_read_headers(const GatherView &gv, uint32_t seq, uint32_t *cnt, int lane)
 {
     bool dead = false;
-    if (lane < gv.world && lane != gv.rank) cnt[lane] = ll_wait(gv.my_ll + gather_row(gv, seq, lane) - 1u, seq, gv, dead).x;
+    if (lane < gv.world && lane != gv.rank) cnt[lane] = ll_wait(gv.my_ll + gather_row(gv, seq, lane) - 2u, seq, gv, dead).x;
 }
 
 // A warp unpacks units [u0, u1) of every peer's slot into the local gathered buffer (0 beyond what the peer sends).
 // The quads of ALL peers for a lane's unit are requested before any is examined: one L2 round trip per unit
 // instead of one per peer (7 dependent round trips at 8 ranks were ~2.5 us at the tail of every launch).
 __device__ __forceinline__ void gather_unpack(const GatherView &gv, uint32_t seq, const uint32_t *cnt, uint64_t u0,
-                                              uint64_t u1, int lane)
+                                              uint64_t u1, int lane, uint32_t *out = nullptr, bool zero_own_tail = true)
 {
     bool dead = false;
-    const uint4 *base = gv.my_ll + (uint64_t)(seq & 1u) * (uint64_t)gv.world * gv.row_quads + 1u;
-    uint32_t *own = gv.out + (uint64_t)gv.rank * gv.slot_words; // own slot: the check wrote [0, my_words); the rest reads 0
-    {
+    if (!out) out = gv.out;
+    const uint4 *base = gv.my_ll + (uint64_t)(seq & 1u) * (uint64_t)gv.world * gv.row_quads + 2u;
+    uint32_t *own = out + (uint64_t)gv.rank * gv.slot_words; // own slot: the check wrote [0, my_words); the rest reads 0
+    if (zero_own_tail) {
         const uint64_t w1 = 3u * u1 < gv.slot_words ? 3u * u1 : gv.slot_words;
         for (uint64_t w = (3u * u0 > gv.my_words ? 3u * u0 : gv.my_words) + (uint64_t)lane; w < w1; w += 32u) own[w] = 0u;
     }
@@ -835,7 +836,7 @@ __device__ __forceinline__ void gather_unpack(const GatherView &gv, uint32_t seq
         for (int p = 0; p < kMaxRanks; ++p) {
             if (p >= gv.world || p == gv.rank) continue;
             if (!q[p].w) q[p] = ll_wait(base + (uint64_t)p * gv.row_quads + u, seq, gv, dead);
-            uint32_t *dst = gv.out + (uint64_t)p * gv.slot_words + 3u * u;
+            uint32_t *dst = out + (uint64_t)p * gv.slot_words + 3u * u;
             const uint64_t w = 3u * u, c = cnt[p];
             if (w < gv.slot_words) dst[0] = w < c ? q[p].x : 0u;
             if (w + 1u < gv.slot_words) dst[1] = w + 1u < c ? q[p].y : 0u;
@@ -877,6 +878,69 @@ __global__ void __launch_bounds__(256) k_gather_push(const __grid_constant__ Gat
         __syncthreads();
         gather_unpack(gv, seq, s_cnt, u0, u1, lane);
     }
+}
+
+// Deferred form of the exchange for SMALL steps (1 M states per rank: a 9 us check).  In the forms above a call ends
+// only when the peers' words of THIS call have arrived: every step is a barrier across the ranks plus one NVLink
+// latency, with the GPU idle meanwhile (8 ranks: 15.7 us per step around an 8.5 us check).  Here call s sends its
+// words and unpacks the peers' words of call s - 1, which arrived a step ago: nothing waits.  Buffer s - 1 is complete
+// when call s has ended; epp_gather_flush completes the last one.  A rank may run ahead of a peer by a step, so before
+// it overwrites the rows of call s - 2 it needs the peers' ACKNOWLEDGEMENT that they have unpacked them (one quad per
+// peer, stored by the block that finishes the unpack last).  flush = 1: no sends, unpack the last call.
+__global__ void __launch_bounds__(256) k_gather_deferred(const __grid_constant__ GatherView gv, int flush)
+{
+    __shared__ uint32_t s_seq, s_last, s_cnt[kMaxRanks];
+    asm volatile("griddepcontrol.wait;" ::: "memory");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
+    if (threadIdx.x == 0) {
+        if (flush) asm volatile("ld.relaxed.gpu.global.u32 %0, [%1];" : "=r"(s_seq) : "l"(gv.ctl + 1) : "memory");
+        else s_seq = gather_seq(gv);
+    }
+    __syncthreads();
+    const uint32_t seq = s_seq; // flush: the number of the last call
+    const int lane = threadIdx.x & 31;
+    const uint64_t stride = (uint64_t)gridDim.x * blockDim.x, t0 = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const uint64_t my_units = (gv.my_words + 2u) / 3u, slot_units = (gv.slot_words + 2u) / 3u;
+    if (!flush) {
+        uint32_t *own = gv.out + (uint64_t)gv.rank * gv.slot_words;
+        for (uint64_t w = gv.my_words + t0; w < gv.slot_words; w += stride) own[w] = 0u; // beyond this rank's units
+        // the rows of this parity still hold call seq - 2 until every peer has said it is done with them
+        if (seq > 2u && threadIdx.x < 32 && lane < gv.world && lane != gv.rank) {
+            bool dead = false;
+            ll_wait(gv.my_ll + gather_row(gv, seq, lane) - 1u, seq - 2u, gv, dead);
+        }
+        __syncthreads();
+        if (blockIdx.x == 0 && threadIdx.x < 32) gather_send_header(gv, seq, lane);
+        const uint32_t *src = gv.out + (uint64_t)gv.rank * gv.slot_words;
+        for (int p = 0; p < gv.world; ++p) {
+            if (p == gv.rank) continue;
+            uint4 *dst = gv.peer_ll[p] + gather_row(gv, seq, gv.rank);
+            for (uint64_t i = t0; i < my_units; i += stride) {
+                const uint64_t w = 3u * i;
+                ll_store(dst + i, src[w], w + 1u < gv.my_words ? src[w + 1u] : 0u, w + 2u < gv.my_words ? src[w + 2u] : 0u, seq);
+            }
+        }
+    }
+    // unpack: call seq - 1 into the previous call's buffer (flush: call seq into its own)
+    const uint32_t useq = flush ? seq : seq - 1u;
+    uint32_t *uout = flush ? gv.out : gv.prev_out;
+    if (useq == 0u || !uout) return;
+    const uint64_t warps = (uint64_t)gridDim.x * (blockDim.x >> 5), wid = (uint64_t)blockIdx.x * (blockDim.x >> 5) + (threadIdx.x >> 5);
+    const uint64_t per = (slot_units + warps - 1) / warps;
+    const uint64_t u0 = wid * per < slot_units ? wid * per : slot_units;
+    const uint64_t u1 = u0 + per < slot_units ? u0 + per : slot_units;
+    if (threadIdx.x < 32) gather_read_headers(gv, useq, s_cnt, lane);
+    __syncthreads();
+    gather_unpack(gv, useq, s_cnt, u0, u1, lane, uout, false);
+    // the block that finishes last tells every peer that its rows of call useq may be overwritten
+    __threadfence();
+    __syncthreads();
+    if (threadIdx.x == 0) s_last = atomicAdd(&gv.ctl[3], 1u) == gridDim.x - 1u ? 1u : 0u;
+    __syncthreads();
+    if (!s_last) return;
+    if (threadIdx.x == 0) gv.ctl[3] = 0u;
+    if (threadIdx.x < 32 && lane < gv.world && lane != gv.rank)
+        ll_store(gv.peer_ll[lane] + gather_row(gv, useq, gv.rank) - 1u, useq, 0u, 0u, useq);
 }
 
 // Bulk form of the exchange for LARGE slots (config 5: 3.9 M mask words per rank at 8 ranks).  Flags in the data make
@@ -2403,7 +2467,7 @@ cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const 
     if (GA) {
         ga_group = (uint32_t)(cfg.gather_group_chunks / 3 * 3);
         ga_group = ga_group < 3u ? 3u : ga_group;
-        if (words_per_block > kGaStageWords || gather_is_bulk(cfg, gv)) { // every rank must take the same form: decided by the slot size
+        if (words_per_block > kGaStageWords || gather_is_bulk(cfg, gv) || gv.deferred) { // every rank must take the same form: decided by the slot size and the gather's mode
             if constexpr (GA) {
                 const GatherView none = {};
                 cudaError_t e2 = launch_states_warp<BP, S, RS, false, false>(cfg, wv, d_xyz, n, mode, can_pass_gate, min_distance,
@@ -2459,6 +2523,25 @@ bool gather_is_bulk(const LaunchCfg &cfg, const GatherView &gv)
     return gv.world > 1 && cfg.gather_bulk_min_words > 0 && gv.slot_words >= (uint64_t)cfg.gather_bulk_min_words;
 }
 
+cudaError_t launch_gather_deferred(const LaunchCfg &cfg, const GatherView &gv, int flush, cudaStream_t stream)
+{
+    size_t blocks = (gv.slot_words / 4 + 255) / 256;
+    const size_t cap = (size_t)cfg.sm_count * 2;
+    blocks = blocks < 1 ? 1 : (blocks > cap ? cap : blocks);
+    cudaLaunchConfig_t lc = {};
+    lc.gridDim = dim3((unsigned)blocks);
+    lc.blockDim = dim3(256);
+    lc.stream = stream;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    lc.attrs = attr;
+    lc.numAttrs = 1;
+    cudaError_t err = cudaLaunchKernelEx(&lc, k_gather_deferred, gv, flush);
+    g_launches++;
+    return err != cudaSuccess ? err : cudaGetLastError();
+}
+
 cudaError_t launch_gather_push_impl(const LaunchCfg &cfg, const GatherView &gv, cudaStream_t stream)
 {
     if (gather_is_bulk(cfg, gv)) {
@@ -2469,6 +2552,7 @@ cudaError_t launch_gather_push_impl(const LaunchCfg &cfg, const GatherView &gv, 
         g_launches++;
         return cudaGetLastError();
     }
+    if (gv.deferred) return launch_gather_deferred(cfg, gv, 0, stream);
     size_t blocks = (gv.slot_words / 4 + 255) / 256;
     const size_t cap = (size_t)cfg.sm_count * 4;
     blocks = blocks < 1 ? 1 : (blocks > cap ? cap : blocks);

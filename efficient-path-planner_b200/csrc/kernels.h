@@ -58,7 +58,7 @@ constexpr int kMaxRanks = 8;
 struct GatherView {
     uint4 *peer_ll[kMaxRanks]; // rank p's staging area in this process's address space
     const uint4 *my_ll;        // this rank's staging area
-    uint64_t row_quads;        // quads per staging row: 1 header + ceil(slot_words / 3)
+    uint64_t row_quads;        // quads per staging row: header + acknowledgement + ceil(slot_words / 3)
     uint32_t *out;             // this rank's gathered buffer of this call (world x slot_words words)
     uint32_t *peer_out[kMaxRanks]; // the peers' gathered buffers of this call (bulk form: written directly)
     uint32_t *ctl;             // local: [0] blocks done, [1] calls completed (sequence number), [2] wait time-outs, [3] bulk form: blocks that have stored
@@ -67,6 +67,8 @@ struct GatherView {
     uint64_t timeout_ns;       // bound on every wait (a peer that never calls must not hang the GPU)
     int world, rank;
     int debug; // profiling only (tuning knob gather_debug): 1 no wait/unpack, 2 no peer stores (wrong results)
+    int deferred;       // deferred form: this call unpacks the PREVIOUS call's words (k_gather_deferred)
+    uint32_t *prev_out; // ... into that call's gathered buffer (null: nothing to unpack)
 };
 
 // Request / answer lines of the single-unit mailbox (k_mailbox), in mapped pinned host memory.  The request is ONE
@@ -98,6 +100,8 @@ cudaError_t launch_segments(const LaunchCfg &cfg, const WorldView &wv, int bp, c
                             const GatherView *gv = nullptr);
 // Send words [0, gv.my_words) of this rank's slot of the local gathered buffer to every peer, unpack theirs.
 cudaError_t launch_gather_push(const LaunchCfg &cfg, const GatherView &gv, cudaStream_t stream);
+// Deferred form: flush = 0 sends this call's words and unpacks the previous call's, flush = 1 only unpacks the last call's.
+cudaError_t launch_gather_deferred(const LaunchCfg &cfg, const GatherView &gv, int flush, cudaStream_t stream);
 cudaError_t launch_trajectories(const LaunchCfg &cfg, const WorldView &wv, int bp, const double *d_mats, size_t n_traj,
                                 size_t rows, size_t ld, size_t traj_stride, double min_distance, uint32_t *d_traj_valid,
                                 uint32_t *d_sample_mask, int64_t *d_first_invalid, long long *d_first_scratch,

@@ -251,6 +251,13 @@ int epp_gather_connect_local(epp_gather *const *all, int world_size);
 /* Device pointer of gathered buffer `buffer` (world_size x slot_words words, rank-major). */
 int epp_gather_buffer(epp_gather *g, int buffer, uint32_t **d_words);
 int epp_gather_set_timeout_ms(epp_gather *g, unsigned ms);
+/* Deferred form, for steps so short that waiting for the peers dominates (1 M states per rank: a 9 us check inside a
+ * 15 us step at 8 ranks): with it on, a gathering call sends its words and unpacks the peers' words of the PREVIOUS
+ * call, which arrived a step ago, so nothing waits.  Buffer b of call s is complete (all ranks' words) once call
+ * s + 1 or epp_gather_flush has completed in stream order; until then it holds this rank's own slot only.  Consecutive
+ * calls must use different buffers (n_buffers >= 2).  Slots large enough for the bulk form ignore the setting. */
+int epp_gather_set_deferred(epp_gather *g, int on);
+int epp_gather_flush(epp_gather *g, void *stream);
 /* Calls completed so far on this rank and how many of their waits timed out (synchronises the device). */
 int epp_gather_status(epp_gather *g, uint64_t *calls, uint64_t *timeouts);
 

@@ -972,3 +972,40 @@ def test_gather_bulk_form_logical_ranks(oracle, config, track):
         epp_b200.set_tuning("gather_bulk_min_words", 65536)
         epp_b200.set_tuning("segments_variant", 0)
         epp_b200.set_tuning("segments_block", 0)
+
+
+@pytest.mark.parametrize("world_size", [2, 3])
+def test_gather_deferred_form_logical_ranks(oracle, config, track, world_size):
+    """Deferred exchange: call s sends its words and unpacks the peers' words of call s - 1; buffer s - 1 is complete
+    after call s, the last one after flush().  Different data per call (so a stale row would show), ranks issued in
+    varying order, 7 calls over two alternating buffers (rows are reused from call 3 on: the acknowledgements gate it)."""
+    import torch
+    from epp_b200 import sharding
+    g, o, lo, hi = track
+    ow, gw = build_pair(oracle, epp_b200, config, g, o)
+    n = 150_001
+    sw = sharding.slot_words(n, world_size)
+    gathers = [epp_b200.Gather(r, world_size, sw, n_buffers=2).set_deferred(True) for r in range(world_size)]
+    epp_b200.Gather.connect_local(gathers)
+    batches, wants = [], []
+    for call in range(7):
+        xyz = worlds.gen_states(5000 + call, 0, n, lo, hi)
+        batches.append(torch.from_numpy(xyz).cuda())
+        wants.append(ow.check_states(xyz, threads=8))
+    gw.check_states_dev(batches[0])
+    torch.cuda.synchronize()
+    for call in range(7):
+        buf = call & 1
+        def issue(r, gth):
+            b, e = epp_b200.shard_range(n, r, world_size, 1024)
+            gth.check_states(gw, batches[call][b:e], buf)
+        order = gathers if call % 2 == 0 else gathers[::-1]
+        _run_logical_ranks(order, lambda r_, gth: issue(gth.rank, gth))
+        if call >= 1:   # the previous call's buffer is complete now
+            for gth in gathers:
+                assert mismatches(sharding.assemble(gth.tensor((call - 1) & 1), n), wants[call - 1]) == 0, (gth.rank, call)
+    _run_logical_ranks(gathers, lambda r_, gth: gth.flush())
+    for gth in gathers:
+        assert mismatches(sharding.assemble(gth.tensor(6 & 1), n), wants[6]) == 0
+        calls, timeouts = gth.status()
+        assert calls == 7 and timeouts == 0
