@@ -76,6 +76,9 @@ def parse_args():
     ap.add_argument("--no-multi", action="store_true", help="one epp_check_states_dev call per step instead of the multi-batch call")
     ap.add_argument("--exchange", default="fused", choices=["fused", "nccl", "none", "none-ipc"],
                     help="N > 1: mask exchange fused into the check kernel (default) or NCCL all-gather")
+    ap.add_argument("--exchange-form", default="immediate", choices=["deferred", "immediate"],
+                    help="N > 1, fused exchange: a step unpacks the peers' words of itself (default) or of the previous step "
+                         "(epp_gather_set_deferred; measured slower at 2 ranks: 14.2 vs 12.3 us per step)")
     ap.add_argument("--tune", action="append", default=[], metavar="KEY=VALUE",
                     help="epp_set_tuning knob (profiling sweeps; the default run sets none)")
     ap.add_argument("--no-verify", action="store_true", help="profiling sweeps with gather_debug only")
@@ -219,6 +222,7 @@ def run_b200(args):
     # (epp_gather) — no collective launch per step.  --exchange nccl keeps the older form
     # (kernel writes row r locally, in-place NCCL all-gather behind it) for comparison.
     gather = None
+    deferred = False
     exchange = "none (single GPU)"
     ipc_probe = None
     if world > 1 and args.exchange == "none-ipc":  # profiling only: plain kernels writing into IPC-exported memory
@@ -227,8 +231,15 @@ def run_b200(args):
         try:
             gather = epp_b200.Gather(rank, world, words, n_buffers=2).connect()
             gathered = [gather.tensor(0, dev), gather.tensor(1, dev)]
-            exchange = ("fused: every mask word goes to every peer as a (word, call number) pair straight from "
-                        "the check kernel; its warps unpack the peers' pairs; no collective launch")
+            deferred = args.exchange_form == "deferred" and args.steps % 2 == 0
+            if deferred:
+                gather.set_deferred(True)
+                exchange = ("deferred: step s sends its mask words to every peer as flagged 16-byte quads over NVLink and "
+                            "unpacks the peers' words of step s - 1 (arrived a step ago: nothing waits); acknowledgements "
+                            "gate the reuse of staging rows; a flush completes the last step; no collective launch")
+            else:
+                exchange = ("fused: every mask word goes to every peer in flagged 16-byte quads straight from the check "
+                            "kernel; its warps unpack the peers' quads of the SAME step; no collective launch")
         except epp_b200.EppError as ex:  # CUDA IPC not permitted on this box: say so, use NCCL
             gather = None
             exchange = "nccl all-gather (fused exchange unavailable: %s)" % ex
@@ -262,7 +273,7 @@ def run_b200(args):
 
     # ---- value: device-resident inputs ------------------------------------------------------
     use_graph = (world == 1 or gather is not None or args.exchange.startswith("none")) and not args.no_graph
-    for s in range(max(W, 3)):
+    for s in range((max(W, 3) + 1) // 2 * 2):   # an even number: the two gathered buffers keep alternating into the graphs
         step_dev(s)
     torch.cuda.synchronize()
     launches0 = epp_b200.kernel_launch_count()
@@ -334,6 +345,9 @@ def run_b200(args):
                              for _ in range(REGION_REPS))[REGION_REPS // 2] / (max(K // RING, 1) * RING)
     pop, xor = epp_b200.mask_summary_dev(multi_masks[0] if pipelined and use_graph else gathered[0][rank])
     exchange_ok = None
+    if deferred:
+        gather.flush()   # completes the last step's buffer (every earlier one was completed by the step after it)
+        torch.cuda.synchronize()
     if world > 1:
         # what the last two steps left in the gathered buffers vs an NCCL all-gather of plain local checks
         exchange_ok = True

@@ -1120,7 +1120,7 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
                                                       const __grid_constant__ TrajArgs ta, uint32_t gran)
 {
     static_assert(!(TR && GA), "the trajectory form has no fused exchange");
-    __shared__ uint32_t s_seq, s_hdr, s_cnt[kMaxRanks]; // GA: call number; header state (0 none, 1 claimed, 2 read)
+    __shared__ uint32_t s_seq, s_hdr, s_unpacked, s_cnt[kMaxRanks]; // GA: call number; header state (0 none, 1 claimed, 2 read); warps done unpacking
     __shared__ __align__(8) uint64_t s_full[kMaxSlots];
     __shared__ __align__(8) uint64_t s_empty[kMaxSlots];
     __shared__ __align__(8) uint64_t s_table;
@@ -1187,6 +1187,7 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
     if (threadIdx.x == 0) {
         s_next = 0u;
         s_hdr = 0u;
+        s_unpacked = 0u;
         mbar_init(&s_table, 1);
         mbar_init_fence();
         const void *tsrc;
@@ -1265,6 +1266,16 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
     uint32_t seq = 0;
     uint64_t ll_row = 0;
     if (GA && threadIdx.x == 32) s_seq = (gv.debug & 4) ? 1u : gather_seq(gv); // one read per block, published by the barrier below
+    if (GA && gv.deferred && c == 0) {
+        // deferred form: the rows of this parity hold call seq - 2 until every peer has acknowledged unpacking them (it
+        // did so a step ago unless it lags); one warp per block checks, the barrier below holds the others back
+        __syncwarp();
+        const uint32_t sq = *(volatile uint32_t *)&s_seq;
+        if (sq > 2u && lane < gv.world && lane != gv.rank) {
+            bool dead = false;
+            ll_wait(gv.my_ll + gather_row(gv, sq, lane) - 1u, sq - 2u, gv, dead);
+        }
+    }
 #ifdef EPP_TRACE
     const uint32_t g = blockIdx.x * consumers + c;
     int tstep = 0;
@@ -1439,20 +1450,42 @@ __global__ void __launch_bounds__(1024, 1) k_states_warp(WorldView wv, const dou
         uint64_t u0 = (uint64_t)blockIdx.x * per_b + (uint64_t)c * per_w;
         u0 = u0 < e ? u0 : e;
         const uint64_t u1 = u0 + per_w < e ? u0 + per_w : e;
-        if (!(gv.debug & 1)) {
+        // Deferred form (epp_gather_set_deferred): the peers' words of THIS call are not waited for; the words of the
+        // previous call, which arrived a step ago, are unpacked into that call's buffer instead.
+        const uint32_t useq = gv.deferred ? seq - 1u : seq;
+        uint32_t *uout = gv.deferred ? gv.prev_out : gv.out;
+        if (gv.deferred) { // own slot beyond this rank's units reads 0 (the immediate form does it inside the unpack)
+            uint32_t *own = gv.out + (uint64_t)gv.rank * gv.slot_words;
+            const uint64_t w1 = 3u * u1 < gv.slot_words ? 3u * u1 : gv.slot_words;
+            for (uint64_t w = (3u * u0 > gv.my_words ? 3u * u0 : gv.my_words) + (uint64_t)lane; w < w1; w += 32u) own[w] = 0u;
+        }
+        if (!(gv.debug & 1) && useq != 0u && uout != nullptr) {
             // the first warp of the block to get here reads the peers' headers for all of them
             uint32_t st = 0;
             if (lane == 0) st = atomicCAS(&s_hdr, 0u, 1u);
             st = __shfl_sync(0xffffffffu, st, 0);
             if (st == 0u) {
-                gather_read_headers(gv, seq, s_cnt, lane);
+                gather_read_headers(gv, useq, s_cnt, lane);
                 __syncwarp();
                 if (lane == 0) asm volatile("st.release.cta.shared.u32 [%0], 2;" ::"r"(smem_addr(&s_hdr)) : "memory");
             } else {
                 while (st != 2u) asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(st) : "r"(smem_addr(&s_hdr)) : "memory");
             }
             __syncwarp();
-            gather_unpack(gv, seq, s_cnt, u0, u1, lane);
+            gather_unpack(gv, useq, s_cnt, u0, u1, lane, uout, !gv.deferred);
+            if (gv.deferred) {
+                // the warp that finishes last tells every peer that its rows of call useq may be overwritten
+                // (counted per block in shared memory first: thousands of atomics on one word serialise in L2)
+                __threadfence();
+                uint32_t last = 0;
+                if (lane == 0 && atomicAdd(&s_unpacked, 1u) == consumers - 1u) last = atomicAdd(&gv.ctl[3], 1u) == gridDim.x - 1u ? 1u : 0u;
+                last = __shfl_sync(0xffffffffu, last, 0);
+                if (last) {
+                    if (lane == 0) gv.ctl[3] = 0u;
+                    if (lane < gv.world && lane != gv.rank)
+                        ll_store(gv.peer_ll[lane] + gather_row(gv, useq, gv.rank) - 1u, useq, 0u, 0u, useq);
+                }
+            }
         }
     }
 }
@@ -2467,7 +2500,7 @@ cudaError_t launch_states_warp(const LaunchCfg &cfg, const WorldView &wv, const 
     if (GA) {
         ga_group = (uint32_t)(cfg.gather_group_chunks / 3 * 3);
         ga_group = ga_group < 3u ? 3u : ga_group;
-        if (words_per_block > kGaStageWords || gather_is_bulk(cfg, gv) || gv.deferred) { // every rank must take the same form: decided by the slot size and the gather's mode
+        if (words_per_block > kGaStageWords || gather_is_bulk(cfg, gv)) { // every rank must take the same form: decided by the slot size
             if constexpr (GA) {
                 const GatherView none = {};
                 cudaError_t e2 = launch_states_warp<BP, S, RS, false, false>(cfg, wv, d_xyz, n, mode, can_pass_gate, min_distance,
