@@ -83,9 +83,7 @@ Knob g_knobs[] = {
     {"grid_max_cells", {1 << 22}},
     {"grid_occ_kb", {72}},
     {"grid_cell_recs", {1}},             // grid: candidates read from records stored in cell order (0: item -> AabbRec -> ObbRec); read at commit
-    {"states_table_copies", {1}},        // worlds of <= 32 OBBs: copies of the bin table in separate bank groups (1, 2, 4, 8, 16); read at commit
     {"bits_range_d", {5}},               // bits broad phase, rays: (first bin, span) rows for boxes spanning < d bins on x and y (0: cumulative rows only); read at commit
-    {"states_skip_dense_z", {1}},        // worlds of <= 32 OBBs: phase 1 of K1 skips the z rows when they are more than half full; read at commit
     {"segments_recs_at_commit", {1}},    // K2: folded records for both canPassGate values built at commit (0: folded per block); read at commit
     {"bits_cmask", {1}},                 // bits broad phase, W > 1: coarse-cell word masks (0: round-1 summaries); read at commit
     {"morton_sort", {1}},                // device records along a Morton curve (worlds of > 32 OBBs); read at commit
@@ -672,19 +670,6 @@ extern "C" int epp_world_commit(epp_world *w)
         if (nb <= 0) nb = W == 1 ? 256 : (W <= 8 ? 128 : (W <= 32 ? 64 : 32));
         build_bits(aabbs, nb, bits, knob_value("bits_range_d"));
     }
-    // W == 1: copies of the `inside` table in separate bank groups for the warp form of K1 (WorldView::rep_B)
-    std::vector<uint32_t> inside_rep;
-    int rep_B = 32;
-    if (bp == EPP_BP_BITS && bits.W == 1) {
-        const int copies = knob_value("states_table_copies");
-        if (copies == 2 || copies == 4 || copies == 8 || copies == 16) {
-            rep_B = 32 / copies;
-            const int words = 3 * bits.nb, rows = (words + rep_B - 1) / rep_B;
-            inside_rep.assign((size_t)rows * 32, 0u);
-            for (int i = 0; i < words; ++i)
-                for (int r = 0; r < copies; ++r) inside_rep[(size_t)(i / rep_B) * 32 + r * rep_B + i % rep_B] = bits.inside[i];
-        }
-    }
     if (bp == EPP_BP_GRID)
         build_grid(aabbs, obbs, knob_value("grid_max_cells"), grid, (long)knob_value("grid_occ_kb") * 1024);
 
@@ -730,7 +715,7 @@ extern "C" int epp_world_commit(epp_world *w)
         {bits.inside.data(), bits.inside.size() * 4, 0},        {bits.min_le.data(), bits.min_le.size() * 4, 0},
         {bits.max_ge.data(), bits.max_ge.size() * 4, 0},        {grid.cell_start.data(), grid.cell_start.size() * 4, 0},
         {grid.cell_items.data(), grid.cell_items.size() * 4, 0}, {grid.occ.data(), grid.occ.size() * 4, 0},
-        {inside_rep.data(), inside_rep.size() * 4, 0},
+        {nullptr, 0, 0}, // (slot kept: the parts below are addressed by index)
         {grid.cell_recs.data(), grid.cell_recs.size() * 8, 0},
         {bits.range.data(), bits.range.size() * 4, 0},
         {ray_recs.data(), ray_recs.size() * 8, 0}};
@@ -767,15 +752,6 @@ extern "C" int epp_world_commit(epp_world *w)
     v.cn0 = bits.cn[0];
     v.cn1 = bits.cn[1];
     for (int a = 0; a < 3; ++a) v.cshift[a] = bits.cshift[a];
-    v.bits_inside_rep = (const uint32_t *)(base + parts[8].off);
-    v.rep_B = rep_B;
-    // z rows that are mostly full do not pay for their lookups in phase 1 of the warp form (see PointWorld<kBpBits1>)
-    v.skip_axis = -1;
-    if (bp == EPP_BP_BITS && bits.W == 1 && M > 0 && knob_value("states_skip_dense_z")) {
-        size_t set = 0;
-        for (int b = 0; b < bits.nb; ++b) set += (size_t)__builtin_popcount(bits.inside[(size_t)2 * bits.nb + b]);
-        if ((double)set > 0.5 * (double)bits.nb * (double)M) v.skip_axis = 2;
-    }
     v.zrot = 1;
     for (const ObbRec &o : obbs)
         if (o.rot[2] != 0.0 || o.rot[5] != 0.0 || o.rot[6] != 0.0 || o.rot[7] != 0.0 || o.rot[8] != 1.0) v.zrot = 0;

@@ -38,11 +38,6 @@ struct WorldView {
     // W > 1: coarse cell -> word mask table behind bits_inside (BitsTables::cmask_*); 0 words: absent
     int cmask_off, cmask_words, cn0, cn1;
     int cshift[3];
-    // single-word tables (W == 1) replicated across bank groups for the warp form of K1: copy r (= lane % (32 / rep_B))
-    // of word i at ((i / rep_B) * 32 + r * rep_B + i % rep_B); rep_B == 32: not replicated (bits_inside_rep unused)
-    const uint32_t *bits_inside_rep;
-    int rep_B;
-    int skip_axis; // W == 1, warp form of K1: axis left out of phase 1's "any candidate?" question (-1: none); see capi.cu
     int zrot; // every OBB rotation is a rotation about z (rot[2,5,6,7] == 0, rot[8] == 1)
     // EPP_BP_GRID
     const uint32_t *cell_start;

@@ -158,36 +158,22 @@ constexpr int kBpBits1 = 4;
 template <>
 struct PointWorld<kBpBits1> {
     const uint32_t *inside;
-    int lb, bm, roff; // replicated table: log2(banks per copy), banks per copy - 1, first bank of this lane's copy
     __device__ static uint32_t table(const WorldView &wv, bool, const void *&src)
     {
-        if (wv.rep_B < 32) {
-            src = wv.bits_inside_rep;
-            return (uint32_t)((3 * wv.nb + wv.rep_B - 1) / wv.rep_B * 128);
-        }
         src = wv.bits_inside;
         return (uint32_t)(3 * wv.nb * 4);
     }
-    __device__ void bind(const WorldView &wv, bool)
-    {
-        inside = reinterpret_cast<const uint32_t *>(g_smem);
-        lb = 31 - __clz(wv.rep_B);
-        bm = wv.rep_B - 1;
-        roff = ((threadIdx.x & 31) % (32 >> lb)) << lb;
-    }
-    // Random bins from 32 lanes land ~3.5 deep on some bank; with 8 copies of the table in 8 groups of 4 banks, the 4
-    // lanes that share a copy collide ~1.9 deep (ncu r01_z: 476 k conflict cycles per 1 M-state launch).
-    __device__ __forceinline__ uint32_t look(int i) const
-    {
-        return lb == 5 ? inside[i] : inside[((i >> lb) << 5) + roff + (i & bm)];
-    }
+    __device__ void bind(const WorldView &, bool) { inside = reinterpret_cast<const uint32_t *>(g_smem); }
+    // Tried and dropped (round 2, profiles/r02_c_ab.log, r02_e): 8 copies of the table in separate bank groups (16 M
+    // states: 109 instead of 92 us — the address arithmetic costs more than the ~3.5-deep bank conflicts of 32 random
+    // bins) and leaving the nearly full z rows out of phase 1 (no change).
     __device__ __forceinline__ uint32_t candidates(const WorldView &wv, const P3 &p) const
     {
         const int nb = wv.nb;
         const int bx = dev_key_bin(p.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb);
         const int by = dev_key_bin(p.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb);
         const int bz = dev_key_bin(p.z, wv.kb.off[2], wv.kb.h0[2], wv.kb.shift[2], nb);
-        return look(bx) & look(nb + by) & look(2 * nb + bz);
+        return inside[bx] & inside[nb + by] & inside[2 * nb + bz];
     }
     template <class F>
     __device__ __forceinline__ bool any(const WorldView &wv, const P3 &p, F test) const
@@ -200,17 +186,8 @@ struct PointWorld<kBpBits1> {
         }
         return false;
     }
-    // Phase 1 only asks WHETHER a state has candidates.  An axis whose rows are nearly full (z on the race track:
-    // every box stands on the floor) filters almost nothing but costs a third of the lookups; leaving it out queues a
-    // few more states for phase 2, which evaluates up to 32 queued states per round at the same cost.
     __device__ __forceinline__ bool has_candidates(const WorldView &wv, const P3 &p) const
     {
-        if (wv.skip_axis == 2) {
-            const int nb = wv.nb;
-            const int bx = dev_key_bin(p.x, wv.kb.off[0], wv.kb.h0[0], wv.kb.shift[0], nb);
-            const int by = dev_key_bin(p.y, wv.kb.off[1], wv.kb.h0[1], wv.kb.shift[1], nb);
-            return (look(bx) & look(nb + by)) != 0u;
-        }
         return candidates(wv, p) != 0u;
     }
 };
@@ -2621,7 +2598,6 @@ cudaError_t launch_states(const LaunchCfg &cfg, const WorldView &wv, int bp, con
         const int rec_max = cfg.states_rec_smem_max > 0 ? (cfg.states_rec_smem_max < 992 ? cfg.states_rec_smem_max : 992) : kRecSmemMax;
         bool rs = wv.M <= rec_max && wv.zrot && cfg.states_rec_smem != 0;
         const int wbp = (bp == EPP_BP_BITS && wv.W == 1 && cfg.states_bits1 != 0) ? kBpBits1 : bp;
-        if (wbp == kBpBits1 && wv.rep_B < 32) table_bytes = (size_t)(3 * wv.nb + wv.rep_B - 1) / wv.rep_B * 128;
         bool launched = false;
 #define EPP_LAUNCH_WARP(S_, RS_, GA_)                                                                                 \
     err = launch_states_warp<BP, S_, RS_, GA_>(cfg, wv, d_xyz, n, mode, can_pass_gate, min_distance, in_smem,          \
@@ -2809,7 +2785,6 @@ cudaError_t launch_trajectories(const LaunchCfg &cfg, const WorldView &wv, int b
         const int rec_max = cfg.states_rec_smem_max > 0 ? (cfg.states_rec_smem_max < 992 ? cfg.states_rec_smem_max : 992) : kRecSmemMax;
         bool rs = wv.M <= rec_max && wv.zrot && cfg.states_rec_smem != 0;
         const int wbp = (bp == EPP_BP_BITS && wv.W == 1 && cfg.states_bits1 != 0) ? kBpBits1 : bp;
-        if (wbp == kBpBits1 && wv.rep_B < 32) table_bytes = (size_t)(3 * wv.nb + wv.rep_B - 1) / wv.rep_B * 128;
         TrajArgs ta = {};
         ta.mats = d_mats;
         ta.rows = rows;
