@@ -998,7 +998,7 @@ extern "C" int epp_check_states_multi_dev(epp_world *w, const double *const *d_x
     cfg.states_multi = (want_late && batches > 1) ? std::max(1, std::min(8, knob_value("states_multi_blocks_per_sm"))) : 0;
     cfg.states_multi_grid = knob_value("states_multi_grid_per_sm");
     for (int i = 0; i < batches; ++i) {
-        cfg.states_late_wait = (i > 0 && want_late) ? 1 : 0;
+        cfg.states_late_wait = (i > 0 && want_late && n[i - 1] > 0) ? 1 : 0; // only behind a launch of this very call
         cudaError_t e = launch_states(cfg, ep->view, ep->bp, d_xyz[i], n[i], kModeBool, can_pass_gate, 0.0, d_mask[i],
                                       (cudaStream_t)stream);
         if (e != cudaSuccess) return cuda_fail(e, "kernel launch");
