@@ -133,6 +133,11 @@ def lib():
             fn.restype = res
             fn.argtypes = args
         _lib = L
+        # EPP_TUNE="knob=value,knob=value": tuning knobs for a whole process (A/B runs of the test suite and of bench.py)
+        for item in filter(None, os.environ.get("EPP_TUNE", "").split(",")):
+            key, _, value = item.partition("=")
+            if L.epp_set_tuning(key.strip().encode(), int(value)) != 0:
+                raise EppError(-1, "EPP_TUNE: unknown knob %r" % key)
     return _lib
 
 

@@ -74,6 +74,9 @@ Knob g_knobs[] = {
     {"states_multi_grid_per_sm", {1}},   // multi-batch calls: blocks per SM in each launch's grid (0: all that are resident) // multi-batch calls: resident blocks per SM (threads per block = 1024 / this)           // multi-batch calls: batches after the first do not wait for the previous launch before streaming
     {"states_debug", {0}},               // profiling builds only
     {"poly_traj_per_warp", {0}},
+    {"poly_balance", {0}},               // K3b: 1 = trajectories per block chosen to balance the SMs
+    {"poly_ring", {4}},                  // K3b: rounds of parked samples per block (2 .. 8)
+    {"poly_wait", {0}},                  // K3b: 1 = consumers sleep on the round's barrier, 0 = nanosleep poll
     {"poly_threads", {256}},             // K3b: threads per block, 256 or 512         // K3b: trajectories per warp, 0 = by batch size
     {"gather_group_chunks", {9}},        // fused exchange: chunks per NVLink run (1: every chunk alone)
     {"gather_bulk_min_words", {65536}},  // exchange: slots from this many words up are copied straight into the peers' buffers (0: never)
@@ -297,6 +300,9 @@ LaunchCfg launch_cfg(const DeviceEpoch &ep)
     c.states_debug = knob_value("states_debug");
     c.poly_traj_per_warp = knob_value("poly_traj_per_warp");
     c.poly_threads = knob_value("poly_threads");
+    c.poly_balance = knob_value("poly_balance");
+    c.poly_ring = knob_value("poly_ring");
+    c.poly_wait = knob_value("poly_wait");
     c.gather_debug = knob_value("gather_debug");
     c.gather_group_chunks = knob_value("gather_group_chunks");
     c.gather_bulk_min_words = knob_value("gather_bulk_min_words");

@@ -1880,7 +1880,8 @@ __global__ void k_traj_finalize(long long *first_row, int64_t *first_out, size_t
 // ---- K3b: fused polynomial sweep --------------------------------------------------------------
 
 constexpr int kPolyThreads = 256;  // 1 producer warp + 7 consumer warps
-constexpr int kPolyRing = 4;       // rounds of parked samples per block
+constexpr int kPolyRingMax = 8;    // rounds of parked samples per block: at most (LaunchCfg::poly_ring, default 4)
+constexpr int kPolyBars = 16;      // "round published" barriers, indexed by round % 16 (more than the consumers' spread)
 constexpr int kPolyPitch = 33;     // odd pitch: conflict-free column writes and row reads
 
 // Polynomial::evaluate(t, 0) (polynomial.h:136-150): Horner from the top coefficient.
@@ -1912,7 +1913,7 @@ __device__ __forceinline__ double horner10(const double *__restrict__ c, double 
 
 // A block owns G <= 32 trajectories.  Its PRODUCER warp runs the reference's sequential sampler
 // (trajectory.cpp:121-140: running sums tin += dt, acc += dt — k * dt would change bits), lane l on trajectory l, 32
-// samples per trajectory and round, and parks (segment, time in segment) in a ring of kPolyRing rounds in shared memory.
+// samples per trajectory and round, and parks (segment, time in segment) in a ring of `ring` rounds in shared memory.
 // The CONSUMER warps take (round, trajectory) items from a shared counter and evaluate the 32 parked samples of the
 // item, one per lane (3 Horner chains + the world check), into one mask word.  Round 1 had the sampler and the
 // evaluation in the same warp: with the G = 2 trajectories per warp that filled the GPU, 2 of 32 lanes worked in the
@@ -1925,18 +1926,20 @@ __global__ void __launch_bounds__(TB, TB >= 512 ? 2 : 5) k_poly_traj(WorldView w
                                                             const double *__restrict__ dts, size_t n_traj,
                                                             int n_segments, int n_coeffs, double min_distance,
                                                             size_t max_samples, int aabb_in_smem, int G,
-                                                            uint32_t table_bytes,
+                                                            uint32_t table_bytes, int ring, int sleep_wait,
                                                             uint32_t *__restrict__ sample_mask,
                                                             uint32_t *__restrict__ n_samples_out,
                                                             long long *__restrict__ first_row)
 {
-    __shared__ uint32_t s_next, s_produced, s_total, s_done[kPolyRing];
+    __shared__ uint32_t s_next, s_produced, s_total, s_done[kPolyRingMax];
+    __shared__ uint64_t s_pub[kPolyBars];
     PointWorld<BP> world;
     if (threadIdx.x == 0) {
         s_next = 0u;
         s_produced = 0u;
         s_total = 0xffffffffu;
-        for (int r = 0; r < kPolyRing; ++r) s_done[r] = 0u;
+        for (int r = 0; r < kPolyRingMax; ++r) s_done[r] = 0u;
+        for (int r = 0; r < kPolyBars; ++r) mbar_init(&s_pub[r], 1);
     }
     world.init(wv, aabb_in_smem != 0);
     __syncthreads();
@@ -2007,13 +2010,15 @@ __global__ void __launch_bounds__(TB, TB >= 512 ? 2 : 5) k_poly_traj(WorldView w
         };
         uint32_t round = 0;
         for (; round < (uint32_t)words_per_traj; ++round) {
-            const uint32_t slot = round % kPolyRing;
-            if (round >= (uint32_t)kPolyRing) { // all Gb items of the slot's previous round have been evaluated
-                const uint32_t need = Gb * (round / kPolyRing);
-                uint32_t d;
-                do {
+            const uint32_t slot = round % (uint32_t)ring;
+            if (round >= (uint32_t)ring) { // all Gb items of the slot's previous round have been evaluated
+                const uint32_t need = Gb * (round / (uint32_t)ring);
+                for (;;) {
+                    uint32_t d;
                     asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(d) : "r"(smem_addr(&s_done[slot])) : "memory");
-                } while (d < need);
+                    if (d >= need) break;
+                    if (sleep_wait) __nanosleep(100); // the ring is full: nothing is waiting for this warp
+                }
             }
             double *st = ring_t(slot) + lane * kPolyPitch;
             unsigned short *sg = ring_seg(slot) + lane * kPolyPitch;
@@ -2045,10 +2050,16 @@ __global__ void __launch_bounds__(TB, TB >= 512 ? 2 : 5) k_poly_traj(WorldView w
             emitted_total += (uint32_t)cnt;
             if (__ballot_sync(0xffffffffu, cnt > 0) == 0u) break; // every trajectory of the block has ended
             __syncwarp();
-            if (lane == 0)
+            if (lane == 0) {
                 asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(smem_addr(&s_produced)), "r"(round + 1u) : "memory");
+                if (sleep_wait) mbar_arrive(&s_pub[round % kPolyBars]); // wakes the consumers that sleep on this round
+            }
         }
-        if (lane == 0) asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(smem_addr(&s_total)), "r"(round) : "memory");
+        if (lane == 0) {
+            asm volatile("st.release.cta.shared.u32 [%0], %1;" ::"r"(smem_addr(&s_total)), "r"(round) : "memory");
+            if (sleep_wait)
+                for (int b = 0; b < kPolyBars; ++b) mbar_arrive(&s_pub[b]); // and those that sleep on rounds that will not come
+        }
         if (have) {
             if (advance()) atomicMin(first_row + my, (long long)max_samples); // truncated: rows beyond max_samples unchecked
             if (n_samples_out) n_samples_out[my] = emitted_total;
@@ -2067,7 +2078,11 @@ __global__ void __launch_bounds__(TB, TB >= 512 ? 2 : 5) k_poly_traj(WorldView w
         i = __shfl_sync(0xffffffffu, i, 0);
         const uint32_t round = Hb == 1u ? i : __umulhi(i, hb_magic), j0 = (i - round * Hb) * 2u; // i / Hb (exact for i < 2^27)
         bool gone = false;
-        for (;;) { // wait for the round, or learn that it will never come
+        // Wait for the round, or learn that it will never come.  s_produced / s_total decide; the barrier of the round
+        // is only where the warp SLEEPS meanwhile (ncu r02_z: with a 200 ns nanosleep poll the waiting consumers were
+        // 32 % of all issued instructions, on the schedulers the producer they wait for needs).  A try_wait that
+        // returns early (time limit, or a barrier already two phases on) just polls again.
+        for (;;) {
             uint32_t p, t;
             asm volatile("ld.acquire.cta.shared.u32 %0, [%1];" : "=r"(p) : "r"(smem_addr(&s_produced)) : "memory");
             if (p > round) break;
@@ -2076,10 +2091,11 @@ __global__ void __launch_bounds__(TB, TB >= 512 ? 2 : 5) k_poly_traj(WorldView w
                 gone = true;
                 break;
             }
-            __nanosleep(200);
+            if (sleep_wait) (void)mbar_try_wait(&s_pub[round % kPolyBars], (round / kPolyBars) & 1u);
+            else __nanosleep(200);
         }
         if (gone) break;
-        const uint32_t slot = round % kPolyRing;
+        const uint32_t slot = round % (uint32_t)ring;
         const bool two = j0 + 1u < Gb;
         const int cnt0 = (int)ring_cnt(slot)[j0], cnt1 = two ? (int)ring_cnt(slot)[j0 + 1u] : 0;
         P3 p0 = {0.0, 0.0, 0.0}, p1 = {0.0, 0.0, 0.0};
@@ -2856,17 +2872,36 @@ cudaError_t launch_poly_trajectories(const LaunchCfg &cfg, const WorldView &wv_i
     }
     bool in_smem;
     const size_t smem = point_smem_bytes(wv, bp, in_smem);
-    // trajectories per block (= lanes of its producer warp that work): 32 for big batches, fewer while the batch would
-    // leave SMs without blocks (the sampler is latency-bound, so idle producer lanes cost nothing but their warp)
+    // Trajectories per block (= lanes of its producer warp that work): 32 for big batches, fewer while the batch would
+    // leave SMs without blocks (the sampler is latency-bound, so idle producer lanes cost nothing but their warp).
+    // poly_balance: all trajectories of a batch cost about the same, blocks go to the SMs round-robin and (up to 5 per
+    // SM) are all resident at once, so the kernel ends when the SM with the most blocks does: choose the G that
+    // minimises ceil(blocks / SMs) * G.  10 000 trajectories as 625 blocks of 16 put 5 blocks on some SMs and 4 on the
+    // others (ncu r02_z: sm__cycles_active.avg 278 k of 328 k elapsed); 715 blocks of 14 bring the busiest SM from 80
+    // trajectories to 70 (the mean is 67.6).
     int G = cfg.poly_traj_per_warp;
-    if (G <= 0) {
+    if (G <= 0 && cfg.poly_balance) {
+        const size_t sms = (size_t)(cfg.sm_count > 0 ? cfg.sm_count : 148);
+        if (n_traj <= 12 * sms) {
+            G = (int)((n_traj + sms - 1) / sms);
+            G = (G + 1) & ~1; // pairs of trajectories are the consumers' work items
+        } else {
+            size_t best = ~(size_t)0;
+            for (int g = 32; g >= 12; g -= 2) {
+                const size_t blocks = (n_traj + g - 1) / (size_t)g;
+                const size_t load = (blocks + sms - 1) / sms * (size_t)g;
+                if (load < best) best = load, G = g; // ties: the larger G (fewer blocks)
+            }
+        }
+    } else if (G <= 0) {
         G = 32;
         while (G > 4 && (n_traj + G - 1) / (size_t)G < (size_t)cfg.sm_count * 4) G >>= 1;
     }
     G = G > 32 ? 32 : (G < 1 ? 1 : G);
+    const int ring = cfg.poly_ring < 2 ? 2 : (cfg.poly_ring > kPolyRingMax ? kPolyRingMax : cfg.poly_ring);
     const unsigned grid = (unsigned)((n_traj + G - 1) / G);
     const size_t table_bytes = (smem + 127) / 128 * 128;
-    const size_t total = table_bytes + (size_t)kPolyRing * ((size_t)G * kPolyPitch * 10 + (size_t)G * 4 + 32);
+    const size_t total = table_bytes + (size_t)ring * ((size_t)G * kPolyPitch * 10 + (size_t)G * 4 + 32);
     // 16-byte coefficient loads need a 16 B-aligned batch (a segment's 3 x 10 coefficients are 240 B)
     const bool n10 = n_coeffs == 10 && (reinterpret_cast<uintptr_t>(d_coeffs) & 15u) == 0;
     EPP_DISPATCH_BP(bp, {
@@ -2877,7 +2912,7 @@ cudaError_t launch_poly_trajectories(const LaunchCfg &cfg, const WorldView &wv_i
         if (err == cudaSuccess) {
             kern<<<grid, big ? 512 : 256, total, stream>>>(wv, d_coeffs, d_durations, d_dt, n_traj, n_segments, n_coeffs,
                                                         min_distance, max_samples, in_smem ? 1 : 0, G, (uint32_t)table_bytes,
-                                                        d_sample_mask, d_n_samples, d_first_scratch);
+                                                        ring, cfg.poly_wait ? 1 : 0, d_sample_mask, d_n_samples, d_first_scratch);
             err = cudaGetLastError();
         }
     });
