@@ -83,6 +83,8 @@ SIGNATURES = {
                                              C.c_size_t, C.c_int, C.c_double, _vp, _vp, _vp, _vp]),
     "epp_check_poly_trajectories_dev": (C.c_int, [_vp, _vp, _vp, _vp, C.c_size_t, C.c_int, C.c_int,
                                                   C.c_double, C.c_size_t, _vp, _vp, _vp, _vp, _vp]),
+    "epp_check_poly_trajectories_static_dev": (C.c_int, [_vp, _vp, _vp, _vp, C.c_size_t, C.c_int, C.c_int,
+                                                         C.c_double, C.c_size_t, _vp, _vp, _vp, _vp, _vp]),
     "epp_shard_range": (C.c_int, [C.c_size_t, C.c_int, C.c_int, C.c_size_t,
                                   C.POINTER(C.c_size_t), C.POINTER(C.c_size_t)]),
     "epp_mask_summary_dev": (C.c_int, [_vp, C.c_size_t, C.c_uint64, _vp, _vp]),
@@ -501,6 +503,24 @@ class World:
                                                    smask.data_ptr() if want_samples else None,
                                                    ns.data_ptr(), first.data_ptr(), self._stream()))
         return valid, smask, ns, first
+
+    def check_poly_trajectories_static_dev(self, coeffs, durations, dt, min_distance, max_samples, valid, smask=None,
+                                           ns=None, first=None):
+        """Allocation-free form (include/epp_c_api.h epp_check_poly_trajectories_static_dev; no counterpart in the
+        reference): every buffer is the caller's, the kernels' per-trajectory scratch is a static device array of
+        STATIC_MAX_TRAJECTORIES words inside the library.  `max_samples` must be a multiple of 32; `valid` is
+        mask_words(n_traj) int32, `smask` (n_traj, max_samples / 32) int32, `ns` n_traj int32, `first` n_traj int64
+        (the last three optional).  Calls that overlap on the GPU race on the scratch array."""
+        if self._dirty:
+            raise EppError(7, "commit() the world first: this entry point allocates nothing, a commit does")
+        n_traj, K, _, N = coeffs.shape
+        _chk(lib().epp_check_poly_trajectories_static_dev(
+            self._h, coeffs.data_ptr(), durations.data_ptr(), dt.data_ptr(), n_traj, K, N, float(min_distance),
+            int(max_samples), valid.data_ptr(), None if smask is None else smask.data_ptr(),
+            None if ns is None else ns.data_ptr(), None if first is None else first.data_ptr(), self._stream()))
+
+
+STATIC_MAX_TRAJECTORIES = 65536  # EPP_STATIC_MAX_TRAJECTORIES
 
 
 class _DevWords:

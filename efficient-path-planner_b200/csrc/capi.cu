@@ -1488,3 +1488,73 @@ extern "C" int epp_gen_segments_dev(uint64_t seed, uint64_t first, size_t n, con
     cudaError_t e = launch_gen_segments(seed, first, n, lo, hi, max_len, d_a, d_b, (cudaStream_t)stream);
     return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
 }
+
+// ---- allocation-free variant of the fused polynomial sweep ------------------------------------------------
+//
+// No counterpart in the reference: added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+//
+// K3b keeps one "first invalid row" word per trajectory that its blocks lower with atomicMin and a last kernel turns
+// into the validity bits.  epp_check_poly_trajectories_dev takes that word array from the caller (d_first_invalid is
+// required there); here it lives in a file-scope device array of EPP_STATIC_MAX_TRAJECTORIES words (512 KiB, held by
+// every GPU that loads the library until the process exits), so the caller passes inputs and outputs only and
+// d_first_invalid becomes optional.  The array is shared by every call and keeps the last call's contents: the launch
+// sequence refills the words it uses with LLONG_MAX first (k_fill_i64), and calls that overlap on the GPU (two
+// streams, two threads) race on it — serialise them or use the caller-scratch entry point.
+//
+// g_static_first_row is a host-side stand-in in this file's host code, not a device address: the address the
+// kernels get comes from cudaGetSymbolAddress, asked once per device with that device current.
+static __device__ __align__(256) long long g_static_first_row[EPP_STATIC_MAX_TRAJECTORIES];
+
+namespace {
+constexpr int kStaticMaxDevices = 64;
+std::mutex g_static_mu;
+long long *g_static_ptr[kStaticMaxDevices] = {};
+
+// Device address of g_static_first_row on the CURRENT device (which the caller has made `device`).
+int static_first_row(int device, long long **out)
+{
+    if (device < 0 || device >= kStaticMaxDevices) return fail(EPP_ERR_INVALID_ARG, "device ordinal beyond 63");
+    std::lock_guard<std::mutex> lk(g_static_mu);
+    if (!g_static_ptr[device]) {
+        void *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress(&p, g_static_first_row);
+        if (e != cudaSuccess) return cuda_fail(e, "cudaGetSymbolAddress(g_static_first_row)");
+        if (!p) return fail(EPP_ERR_CUDA, "cudaGetSymbolAddress returned a null address");
+        g_static_ptr[device] = static_cast<long long *>(p);
+    }
+    *out = g_static_ptr[device];
+    return EPP_OK;
+}
+} // namespace
+
+extern "C" int epp_check_poly_trajectories_static_dev(epp_world *w, const double *d_coeffs, const double *d_durations,
+                                                      const double *d_dt, size_t n_traj, int n_segments, int n_coeffs,
+                                                      double min_distance, size_t max_samples, uint32_t *d_traj_valid,
+                                                      uint32_t *d_sample_mask, uint32_t *d_n_samples,
+                                                      int64_t *d_first_invalid, void *stream)
+{
+    std::shared_ptr<DeviceEpoch> ep;
+    int rc = snapshot(w, ep);
+    if (rc) return rc;
+    if (n_traj > (size_t)EPP_STATIC_MAX_TRAJECTORIES)
+        return fail(EPP_ERR_INVALID_ARG, "n_traj = " + std::to_string(n_traj) + " exceeds EPP_STATIC_MAX_TRAJECTORIES = " +
+                                             std::to_string(EPP_STATIC_MAX_TRAJECTORIES) +
+                                             " (the static scratch array); split the batch or use epp_check_poly_trajectories_dev");
+    if (n_traj == 0) return EPP_OK;
+    if (!d_coeffs || !d_durations || !d_dt || !d_traj_valid || n_segments <= 0 || n_segments > 65535 || n_coeffs <= 0 ||
+        max_samples == 0 || max_samples % 32)
+        return fail(EPP_ERR_INVALID_ARG, "polynomial trajectory batch shape");
+    int device = -1;
+    EPP_CUDA(cudaGetDevice(&device));
+    if (device != ep->device)
+        return fail(EPP_ERR_INVALID_ARG, "the current device is not the one the world was committed on");
+    long long *scratch = nullptr;
+    rc = static_first_row(device, &scratch);
+    if (rc) return rc;
+    cudaError_t e = launch_poly_trajectories(launch_cfg(*ep), ep->view, ep->bp, d_coeffs, d_durations, d_dt, n_traj,
+                                             n_segments, n_coeffs, min_distance, max_samples, d_traj_valid,
+                                             d_sample_mask, d_n_samples, d_first_invalid /* nullable */, scratch,
+                                             (cudaStream_t)stream);
+    return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
+}

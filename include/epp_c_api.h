@@ -181,6 +181,26 @@ int epp_check_poly_trajectories_dev(epp_world *w, const double *d_coeffs, const 
                                     double min_distance, size_t max_samples, uint32_t *d_traj_valid,
                                     uint32_t *d_sample_mask, uint32_t *d_n_samples,
                                     int64_t *d_first_invalid, void *stream);
+/* Allocation-free variant of epp_check_poly_trajectories_dev.  It has NO counterpart in the reference: it was added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid it).  Same arguments, same results bit for bit, except that
+ * d_first_invalid may be NULL: the per-trajectory "first invalid row" words the kernels work on (which the entry
+ * point above takes from the caller's d_first_invalid) live in a static device array of
+ * EPP_STATIC_MAX_TRAJECTORIES int64 words inside the library (512 KiB on every GPU that loads it, until exit).
+ *  - n_traj > EPP_STATIC_MAX_TRAJECTORIES returns EPP_ERR_INVALID_ARG (epp_last_error names the limit); nothing is
+ *    launched.  Split the batch or use the entry point above.
+ *  - The call makes no cudaMalloc / cudaFree and calls no allocating library routine; the world must already be
+ *    committed (epp_world_commit allocates, this does not) on the CURRENT device, else EPP_ERR_NOT_COMMITTED /
+ *    EPP_ERR_INVALID_ARG.
+ *  - Every call shares the array, which keeps the last call's contents; the words a call uses are reset on its
+ *    stream before its kernels read them.  Calls that OVERLAP on the GPU (different streams or threads) race on
+ *    it: serialise them. */
+#define EPP_STATIC_MAX_TRAJECTORIES 65536
+int epp_check_poly_trajectories_static_dev(epp_world *w, const double *d_coeffs, const double *d_durations,
+                                           const double *d_dt, size_t n_traj, int n_segments, int n_coeffs,
+                                           double min_distance, size_t max_samples, uint32_t *d_traj_valid,
+                                           uint32_t *d_sample_mask, uint32_t *d_n_samples,
+                                           int64_t *d_first_invalid /* nullable */, void *stream);
 
 /* ---- Min-snap trajectory generation, batched --------------------------
  *
