@@ -74,7 +74,7 @@ Knob g_knobs[] = {
     {"states_multi_grid_per_sm", {1}},   // multi-batch calls: blocks per SM in each launch's grid (0: all that are resident) // multi-batch calls: resident blocks per SM (threads per block = 1024 / this)           // multi-batch calls: batches after the first do not wait for the previous launch before streaming
     {"states_debug", {0}},               // profiling builds only
     {"poly_traj_per_warp", {0}},
-    {"poly_balance", {0}},               // K3b: 1 = trajectories per block chosen to balance the SMs
+    {"poly_balance", {1}},               // K3b: trajectories per block of big batches chosen to balance the SMs (0: round-2 halving rule)
     {"poly_ring", {4}},                  // K3b: rounds of parked samples per block (2 .. 8)
     {"poly_wait", {0}},                  // K3b: 1 = consumers sleep on the round's barrier, 0 = nanosleep poll
     {"poly_threads", {256}},             // K3b: threads per block, 256 or 512         // K3b: trajectories per warp, 0 = by batch size

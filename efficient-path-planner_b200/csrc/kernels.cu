@@ -2872,30 +2872,28 @@ cudaError_t launch_poly_trajectories(const LaunchCfg &cfg, const WorldView &wv_i
     }
     bool in_smem;
     const size_t smem = point_smem_bytes(wv, bp, in_smem);
-    // Trajectories per block (= lanes of its producer warp that work): 32 for big batches, fewer while the batch would
-    // leave SMs without blocks (the sampler is latency-bound, so idle producer lanes cost nothing but their warp).
-    // poly_balance: all trajectories of a batch cost about the same, blocks go to the SMs round-robin and (up to 5 per
-    // SM) are all resident at once, so the kernel ends when the SM with the most blocks does: choose the G that
-    // minimises ceil(blocks / SMs) * G.  10 000 trajectories as 625 blocks of 16 put 5 blocks on some SMs and 4 on the
-    // others (ncu r02_z: sm__cycles_active.avg 278 k of 328 k elapsed); 715 blocks of 14 bring the busiest SM from 80
-    // trajectories to 70 (the mean is 67.6).
+    // Trajectories per block (= lanes of its producer warp that work).  Up to 5 blocks (40 warps) are resident per SM and
+    // the sweep is latency-bound, so what matters first is that every SM holds its 5 blocks, then that the blocks split
+    // evenly over the SMs.
+    //  - Batches that fill all 5 x SMs block slots with G >= 12 (poly_balance, default): all trajectories of a batch cost
+    //    about the same and blocks go to the SMs round-robin, so G minimises ceil(blocks / SMs) * G.  Measured
+    //    (profiles/r02_fin_ab_poly.log): 10 000 trajectories 176 -> 169 us (715 blocks of 14 instead of 625 of 16, which
+    //    put 5 blocks on some SMs and 4 on the others); 40 000 trajectories 841 -> 579 us (2500 blocks of 16 instead of
+    //    1250 of 32: G = 28 .. 32 leaves each SM with 2 - 3 fat blocks, half the warps).
+    //  - Smaller batches: G halves from 32 while there are fewer than 4 blocks per SM (2000 trajectories: G = 4, 88 us;
+    //    the balanced G = 14 would leave one block per SM: 94 us).
     int G = cfg.poly_traj_per_warp;
-    if (G <= 0 && cfg.poly_balance) {
-        const size_t sms = (size_t)(cfg.sm_count > 0 ? cfg.sm_count : 148);
-        if (n_traj <= 12 * sms) {
-            G = (int)((n_traj + sms - 1) / sms);
-            G = (G + 1) & ~1; // pairs of trajectories are the consumers' work items
-        } else {
-            size_t best = ~(size_t)0;
-            for (int g = 32; g >= 12; g -= 2) {
-                const size_t blocks = (n_traj + g - 1) / (size_t)g;
-                const size_t load = (blocks + sms - 1) / sms * (size_t)g;
-                if (load < best) best = load, G = g; // ties: the larger G (fewer blocks)
-            }
+    const size_t sms = (size_t)(cfg.sm_count > 0 ? cfg.sm_count : 148);
+    if (G <= 0 && cfg.poly_balance && n_traj >= 12 * 5 * sms) {
+        size_t best = ~(size_t)0;
+        for (int g = 32; g >= 12; g -= 2) {
+            const size_t blocks = (n_traj + g - 1) / (size_t)g;
+            const size_t load = (blocks + sms - 1) / sms * (size_t)g;
+            if (load < best) best = load, G = g;
         }
     } else if (G <= 0) {
         G = 32;
-        while (G > 4 && (n_traj + G - 1) / (size_t)G < (size_t)cfg.sm_count * 4) G >>= 1;
+        while (G > 4 && (n_traj + G - 1) / (size_t)G < sms * 4) G >>= 1;
     }
     G = G > 32 ? 32 : (G < 1 ? 1 : G);
     const int ring = cfg.poly_ring < 2 ? 2 : (cfg.poly_ring > kPolyRingMax ? kPolyRingMax : cfg.poly_ring);
