@@ -340,6 +340,41 @@ def test_polynomial_sweep_truncation_and_block_shapes(oracle, config, track, G):
     assert 0 < truncated < n_traj
 
 
+@pytest.mark.parametrize("G", [0, 4, 14])
+def test_polynomial_sweep_segment_shapes(oracle, config, track, G):
+    """K3b over ordinary segments (~125 rows each), segments of a dozen rows, segments shorter than one sampling step
+    (several segment changes between two rows), with rings of 4 and 2 rounds and consumers that sleep on the round's
+    barrier (knob poly_wait) or poll."""
+    g, o, lo, hi = track
+    ow, gw = build_pair(oracle, epp_b200, config, g, o)
+    cases = []
+    cases.append(worlds.rest_to_rest_trajectories(70, 8, lo, hi, seed=901, n_samples=1000))
+    cases.append(worlds.rest_to_rest_trajectories(40, 24, lo, hi, seed=902, n_samples=300))
+    coeffs, T, dt = worlds.rest_to_rest_trajectories(50, 12, lo, hi, seed=903, n_samples=600)
+    rng = np.random.default_rng(903)
+    T = T * np.where(rng.random(T.shape) < 0.4, 0.004, 1.0)  # 40 % of the segments last less than a sampling step
+    cases.append((coeffs, np.ascontiguousarray(T), T.sum(axis=1) / 599.0))
+    for ring in (4, 2):
+        epp_b200.set_tuning("poly_wait", 1 if ring == 2 else 0)
+        epp_b200.set_tuning("poly_traj_per_warp", G)
+        epp_b200.set_tuning("poly_ring", ring)
+        try:
+            got = [gw.check_poly_trajectories(c, T, dt, 0.15, max_samples=1024) for c, T, dt in cases]
+        finally:
+            epp_b200.set_tuning("poly_wait", 0)
+            epp_b200.set_tuning("poly_traj_per_warp", 0)
+            epp_b200.set_tuning("poly_ring", 4)
+        for (c, T, dt), (valid, smask, cnt, first) in zip(cases, got):
+            rows = rows_valid = 0
+            for t in range(c.shape[0]):
+                ok, m, n, f = ow.check_poly_traj(c[t], T[t], dt[t], 0.15, max_samples=1024)
+                assert cnt[t] == n and np.array_equal(smask[t], m) and first[t] == f, (ring, t)
+                assert bool(valid[t >> 5] >> (t & 31) & 1) is ok
+                rows += n
+                rows_valid += int(np.unpackbits(np.asarray(m, np.uint32).view(np.uint8)).sum())
+            assert 0 < rows_valid < rows  # both verdicts occur among the rows
+
+
 def test_device_buffers_and_generators(oracle, config, track):
     """_dev entry points on torch buffers + on-device generators bit-identical to the host twins."""
     import torch
