@@ -75,7 +75,8 @@ Knob g_knobs[] = {
     {"states_debug", {0}},               // profiling builds only
     {"poly_traj_per_warp", {0}},
     {"poly_balance", {1}},               // K3b: trajectories per block of big batches chosen to balance the SMs (0: round-2 halving rule)
-    {"poly_ring", {4}},                  // K3b: rounds of parked samples per block (2 .. 8)
+    {"poly_ring", {0}},                  // K3b: rounds of parked samples per block (2 .. 8; 0 = by variant)
+    {"poly_blocks_per_sm", {0}},         // K3b, 256-thread blocks: 5 (48 registers per thread), 4 (64 registers), 0 = by batch size
     {"poly_wait", {0}},                  // K3b: 1 = consumers sleep on the round's barrier, 0 = nanosleep poll
     {"poly_threads", {256}},             // K3b: threads per block, 256 or 512         // K3b: trajectories per warp, 0 = by batch size
     {"gather_group_chunks", {9}},        // fused exchange: chunks per NVLink run (1: every chunk alone)
@@ -303,6 +304,7 @@ LaunchCfg launch_cfg(const DeviceEpoch &ep)
     c.poly_balance = knob_value("poly_balance");
     c.poly_ring = knob_value("poly_ring");
     c.poly_wait = knob_value("poly_wait");
+    c.poly_blocks_per_sm = knob_value("poly_blocks_per_sm");
     c.gather_debug = knob_value("gather_debug");
     c.gather_group_chunks = knob_value("gather_group_chunks");
     c.gather_bulk_min_words = knob_value("gather_bulk_min_words");

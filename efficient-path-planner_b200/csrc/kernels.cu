@@ -1920,8 +1920,8 @@ __device__ __forceinline__ double horner10(const double *__restrict__ c, double 
 // sampler and it was a third of all issued instructions (ncu r02_a); with G = 32 there were 313 warps in all.
 // A trajectory with more than max_samples samples is reported INVALID with first row max_samples (the first row that
 // was not checked) unless an earlier row is invalid — never silently valid.
-template <int BP, bool N10, int TB>
-__global__ void __launch_bounds__(TB, TB >= 512 ? 2 : 5) k_poly_traj(WorldView wv, const double *__restrict__ coeffs,
+template <int BP, bool N10, int TB, int MB = (TB >= 512 ? 2 : 5)>
+__global__ void __launch_bounds__(TB, MB) k_poly_traj(WorldView wv, const double *__restrict__ coeffs,
                                                             const double *__restrict__ durations,
                                                             const double *__restrict__ dts, size_t n_traj,
                                                             int n_segments, int n_coeffs, double min_distance,
@@ -2872,40 +2872,45 @@ cudaError_t launch_poly_trajectories(const LaunchCfg &cfg, const WorldView &wv_i
     }
     bool in_smem;
     const size_t smem = point_smem_bytes(wv, bp, in_smem);
-    // Trajectories per block (= lanes of its producer warp that work).  Up to 5 blocks (40 warps) are resident per SM and
-    // the sweep is latency-bound, so what matters first is that every SM holds its 5 blocks, then that the blocks split
-    // evenly over the SMs.
-    //  - Batches that fill all 5 x SMs block slots with G >= 12 (poly_balance, default): all trajectories of a batch cost
-    //    about the same and blocks go to the SMs round-robin, so G minimises ceil(blocks / SMs) * G.  Measured
-    //    (profiles/r02_fin_ab_poly.log): 10 000 trajectories 176 -> 169 us (715 blocks of 14 instead of 625 of 16, which
-    //    put 5 blocks on some SMs and 4 on the others); 40 000 trajectories 841 -> 579 us (2500 blocks of 16 instead of
-    //    1250 of 32: G = 28 .. 32 leaves each SM with 2 - 3 fat blocks, half the warps).
-    //  - Smaller batches: G halves from 32 while there are fewer than 4 blocks per SM (2000 trajectories: G = 4, 88 us;
-    //    the balanced G = 14 would leave one block per SM: 94 us).
+    // Trajectories per block G (= lanes of its producer warp that work), threads' registers and ring depth.  The sweep is
+    // latency-bound: what matters first is that every SM holds as many blocks as fit, then that blocks split evenly
+    // over the SMs, and a block's 7 consumer warps keep up with its producer only up to G ~ 18.  Measured on 10 000 /
+    // 20 000 / 40 000 / 2 000 trajectories of ~1000 rows (profiles/r02_fin_ab_poly.log, r02_wide_ab_poly.log):
+    //  - one wave of 4 x SMs blocks of 64-register threads (no spills; 5 x SMs of 48-register threads otherwise) with a
+    //    ring of 6 rounds while that needs G <= 18: 10 000 trajectories 176 us (625 blocks of 16, the round-2 rule: 5
+    //    blocks on some SMs, 4 on others) -> 169 us (715 of 14) -> 158 us (556 of 18, 64 registers, ring 6);
+    //  - else blocks of 16 in several waves: 40 000 trajectories 841 us (1250 blocks of 32) -> 579 us; 20 000: 304 us
+    //    (one wave of 715 blocks of 28: 505 us; 64-register threads: 333 us);
+    //  - batches that cannot fill the SMs with G >= 12: G halves from 32 while there are fewer than 4 blocks per SM
+    //    (2000 trajectories: G = 4, 88 us; G = 14 would leave one block per SM: 94 us).
     int G = cfg.poly_traj_per_warp;
     const size_t sms = (size_t)(cfg.sm_count > 0 ? cfg.sm_count : 148);
-    if (G <= 0 && cfg.poly_balance && n_traj >= 12 * 5 * sms) {
-        size_t best = ~(size_t)0;
-        for (int g = 32; g >= 12; g -= 2) {
-            const size_t blocks = (n_traj + g - 1) / (size_t)g;
-            const size_t load = (blocks + sms - 1) / sms * (size_t)g;
-            if (load < best) best = load, G = g;
-        }
+    const bool big = cfg.poly_threads >= 512;
+    bool wide = !big && cfg.poly_blocks_per_sm == 4; // 64 registers per thread, 4 resident blocks
+    const bool wide_auto = !big && cfg.poly_blocks_per_sm == 0;
+    bool one_wave = false;
+    if (G <= 0 && cfg.poly_balance && n_traj >= 12 * 4 * sms) {
+        if (wide_auto) wide = n_traj <= 18 * 4 * sms;
+        const size_t resident = (size_t)(big ? 2 : (wide ? 4 : 5)) * sms;
+        one_wave = n_traj <= 18 * resident;
+        G = one_wave ? (int)((n_traj + resident - 1) / resident) : 16;
+        G = (G + 1) & ~1; // pairs of trajectories are the consumers' work items
     } else if (G <= 0) {
         G = 32;
         while (G > 4 && (n_traj + G - 1) / (size_t)G < sms * 4) G >>= 1;
     }
     G = G > 32 ? 32 : (G < 1 ? 1 : G);
-    const int ring = cfg.poly_ring < 2 ? 2 : (cfg.poly_ring > kPolyRingMax ? kPolyRingMax : cfg.poly_ring);
+    int ring = cfg.poly_ring > 0 ? cfg.poly_ring : (wide && one_wave ? 6 : 4);
+    ring = ring < 2 ? 2 : (ring > kPolyRingMax ? kPolyRingMax : ring);
     const unsigned grid = (unsigned)((n_traj + G - 1) / G);
     const size_t table_bytes = (smem + 127) / 128 * 128;
     const size_t total = table_bytes + (size_t)ring * ((size_t)G * kPolyPitch * 10 + (size_t)G * 4 + 32);
     // 16-byte coefficient loads need a 16 B-aligned batch (a segment's 3 x 10 coefficients are 240 B)
     const bool n10 = n_coeffs == 10 && (reinterpret_cast<uintptr_t>(d_coeffs) & 15u) == 0;
     EPP_DISPATCH_BP(bp, {
-        const bool big = cfg.poly_threads >= 512;
-        auto kern = big ? (n10 ? k_poly_traj<BP, true, 512> : k_poly_traj<BP, false, 512>)
-                        : (n10 ? k_poly_traj<BP, true, 256> : k_poly_traj<BP, false, 256>);
+        auto kern = big    ? (n10 ? k_poly_traj<BP, true, 512> : k_poly_traj<BP, false, 512>)
+                    : wide ? (n10 ? k_poly_traj<BP, true, 256, 4> : k_poly_traj<BP, false, 256, 4>)
+                           : (n10 ? k_poly_traj<BP, true, 256> : k_poly_traj<BP, false, 256>);
         err = ensure_smem(kern, total);
         if (err == cudaSuccess) {
             kern<<<grid, big ? 512 : 256, total, stream>>>(wv, d_coeffs, d_durations, d_dt, n_traj, n_segments, n_coeffs,

@@ -363,7 +363,7 @@ def test_polynomial_sweep_segment_shapes(oracle, config, track, G):
         finally:
             epp_b200.set_tuning("poly_wait", 0)
             epp_b200.set_tuning("poly_traj_per_warp", 0)
-            epp_b200.set_tuning("poly_ring", 4)
+            epp_b200.set_tuning("poly_ring", 0)
         for (c, T, dt), (valid, smask, cnt, first) in zip(cases, got):
             rows = rows_valid = 0
             for t in range(c.shape[0]):
