@@ -865,11 +865,17 @@ def extras_single_gpu(torch, epp_b200, dev):
     w3.parse_gates_and_obstacles(g, o)
     segs = [epp_b200.gen_segments_dev(worlds.SEED_SEGMENTS, s * BATCH, BATCH, lo, hi, 1.0, device=dev) for s in range(4)]
     m = torch.empty(BATCH // 32, dtype=torch.int32, device=dev)
-    ms = launch_ms(lambda: [w3.check_segments_dev(a, b, mask=m) for a, b in segs]) / 4
+    ms_single = launch_ms(lambda: [w3.check_segments_dev(a, b, mask=m) for a, b in segs]) / 4
+    # the figure of record goes through epp_check_segments_multi_dev like config 2's step: 8 independent batches (the
+    # ring twice, a mask each) in ONE call, so a batch streams while the previous one is in its tail
+    m8 = [torch.empty(BATCH // 32, dtype=torch.int32, device=dev) for _ in range(8)]
+    ms = launch_ms(lambda: w3.check_segments_multi_dev(segs + segs, m8)) / 8
     st = w3.count_candidates_dev(segs[0][0], segs[0][1])
     roofs["config3_segments_256obb"] = roofline_entry("k_segments_warp<bits>", BATCH, ms, BYTES_PER_SEGMENT, peak, peak_src,
                                                       segment_ops(*st), fp64, stats=st)
     out["config3_segments_256obb_checks_per_s"] = BATCH / (ms * 1e-3)
+    roofs["config3_segments_256obb"]["one_call_per_batch_ms"] = ms_single
+    roofs["config3_segments_256obb"]["api"] = "epp_check_segments_multi_dev: 8 independent 1M-segment batches per call"
     # mismatch count of config 3's first batch vs the CPU reference
     kind, cw, _ = cpu_world("segments")
     h_a, h_b = segs[0][0].cpu().numpy(), segs[0][1].cpu().numpy()

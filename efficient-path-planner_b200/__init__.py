@@ -90,6 +90,7 @@ SIGNATURES = {
     "epp_mask_summary_dev": (C.c_int, [_vp, C.c_size_t, C.c_uint64, _vp, _vp]),
     "epp_measure_fp64_nofma": (C.c_int, [C.c_int, C.c_int, _vp, _dp, _dp]),
     "epp_check_states_multi_dev": (C.c_int, [_vp, _vp, _vp, _vp, C.c_int, C.c_int, _vp]),
+    "epp_check_segments_multi_dev": (C.c_int, [_vp, _vp, _vp, _vp, _vp, C.c_int, C.c_int, _vp]),
     "epp_gather_set_deferred": (C.c_int, [_vp, C.c_int]),
     "epp_gather_flush": (C.c_int, [_vp, _vp]),
     "epp_measure_single_latency": (C.c_int, [_vp, C.c_int, _dp]),
@@ -450,6 +451,18 @@ class World:
         _chk(lib().epp_check_segments_dev(self._h, a.data_ptr(), b.data_ptr(), n, int(can_pass_gate),
                                           mask.data_ptr(), self._stream()))
         return mask
+
+    def check_segments_multi_dev(self, batches, masks, can_pass_gate=False):
+        """Independent segment batches [(a, b), ...] (device tensors) -> their mask tensors, one library call
+        (epp_check_segments_multi_dev)."""
+        self._sync()
+        k = len(batches)
+        pa = (C.c_void_p * k)(*[a.data_ptr() for a, _ in batches])
+        pb = (C.c_void_p * k)(*[b.data_ptr() for _, b in batches])
+        ns = (C.c_size_t * k)(*[a.numel() // 3 for a, _ in batches])
+        ms = (C.c_void_p * k)(*[m.data_ptr() for m in masks])
+        _chk(lib().epp_check_segments_multi_dev(self._h, pa, pb, ns, ms, k, int(can_pass_gate), self._stream()))
+        return masks
 
     def single_latency_us(self, n_calls=2000):
         """Microseconds per epp_is_valid call, timed inside the library (no ctypes overhead)."""

@@ -71,6 +71,7 @@ Knob g_knobs[] = {
     {"states_pdl", {1}},
     {"states_late_wait", {1}},
     {"states_multi_blocks_per_sm", {2}},
+    {"segments_multi_blocks_per_sm", {2}}, // multi-batch segment calls: resident blocks per SM (threads per block = 1024 / this; 1: one 1024-thread block)
     {"states_multi_grid_per_sm", {1}},   // multi-batch calls: blocks per SM in each launch's grid (0: all that are resident) // multi-batch calls: resident blocks per SM (threads per block = 1024 / this)           // multi-batch calls: batches after the first do not wait for the previous launch before streaming
     {"states_debug", {0}},               // profiling builds only
     {"poly_traj_per_warp", {0}},
@@ -1036,6 +1037,34 @@ extern "C" int epp_check_segments_dev(epp_world *w, const double *d_a, const dou
     cudaError_t e = launch_segments(launch_cfg(*ep), ep->view, ep->bp, d_a, d_b, n, can_pass_gate, d_mask,
                                     (cudaStream_t)stream);
     return e == cudaSuccess ? EPP_OK : cuda_fail(e, "kernel launch");
+}
+
+extern "C" int epp_check_segments_multi_dev(epp_world *w, const double *const *d_a, const double *const *d_b,
+                                            const size_t *n, uint32_t *const *d_mask, int batches, int can_pass_gate,
+                                            void *stream)
+{
+    std::shared_ptr<DeviceEpoch> ep;
+    int rc = snapshot(w, ep);
+    if (rc) return rc;
+    if (batches < 0 || (batches && (!d_a || !d_b || !n || !d_mask))) return fail(EPP_ERR_INVALID_ARG, "null buffer");
+    for (int i = 0; i < batches; ++i) {
+        if (n[i] && (!d_a[i] || !d_b[i] || !d_mask[i])) return fail(EPP_ERR_INVALID_ARG, "null buffer");
+        for (int j = 0; j < i; ++j) { // masks must not overlap each other
+            const char *mi = (const char *)d_mask[i], *mj = (const char *)d_mask[j];
+            const size_t bi = (n[i] + 31) / 32 * 4, bj = (n[j] + 31) / 32 * 4;
+            if (mi < mj + bj && mj < mi + bi) return fail(EPP_ERR_INVALID_ARG, "masks of two batches overlap");
+        }
+    }
+    LaunchCfg cfg = launch_cfg(*ep);
+    const int want_late = knob_value("states_late_wait");
+    cfg.segments_multi = (want_late && batches > 1) ? std::max(1, std::min(4, knob_value("segments_multi_blocks_per_sm"))) : 0;
+    for (int i = 0; i < batches; ++i) {
+        cfg.segments_late_wait = (i > 0 && want_late && n[i - 1] > 0) ? 1 : 0; // only behind a launch of this very call
+        cudaError_t e = launch_segments(cfg, ep->view, ep->bp, d_a[i], d_b[i], n[i], can_pass_gate, d_mask[i],
+                                        (cudaStream_t)stream);
+        if (e != cudaSuccess) return cuda_fail(e, "kernel launch");
+    }
+    return EPP_OK;
 }
 
 extern "C" int epp_check_trajectories_dev(epp_world *w, const double *d_col_major, size_t n_traj, size_t rows,

@@ -1621,7 +1621,7 @@ __global__ void __launch_bounds__(1024, 1) k_segments_warp(WorldView wv, const d
                                                           const double *__restrict__ pb, size_t n, int can_pass_gate,
                                                           int aabb_in_smem, uint32_t slots, uint32_t table_bytes,
                                                           uint32_t rec_bytes, uint32_t wpb, uint32_t rem,
-                                                          uint32_t *__restrict__ mask)
+                                                          int late_wait, uint32_t *__restrict__ mask)
 {
     constexpr int S = kSegS;
     __shared__ __align__(8) uint64_t s_full[kSegMaxSlots];
@@ -1684,7 +1684,9 @@ __global__ void __launch_bounds__(1024, 1) k_segments_warp(WorldView wv, const d
         if (threadIdx.x - 32 < slots) mbar_init_fence();
     }
     __syncthreads();
-    asm volatile("griddepcontrol.wait;" ::: "memory");
+    // late_wait: batches of one multi-batch call (independent of each other, inputs complete before the call) — the
+    // dependency wait moves to the END of the kernel, see k_states_warp
+    if (!late_wait) asm volatile("griddepcontrol.wait;" ::: "memory");
     asm volatile("griddepcontrol.launch_dependents;" ::: "memory");
 
     if (warp == 0) {
@@ -1824,6 +1826,7 @@ __global__ void __launch_bounds__(1024, 1) k_segments_warp(WorldView wv, const d
     if constexpr (BP == EPP_BP_GRID) {
         if (fill > 0) deferred_round(0, fill);
     }
+    if (late_wait) asm volatile("griddepcontrol.wait;" ::: "memory");
 }
 
 // ---- K3a: pre-sampled trajectory matrices ----------------------------------------------------
@@ -2675,10 +2678,17 @@ cudaError_t launch_segments_warp(const LaunchCfg &cfg, const WorldView &wv, cons
     const size_t chunks_total = (words + kSegS - 1) / kSegS;
     const size_t grid = chunks_total < (size_t)cfg.sm_count ? chunks_total : (size_t)cfg.sm_count;
     const size_t chunks_per_block = (chunks_total + grid - 1) / grid;
-    int cons = (cfg.segments_warp_threads > 0 ? cfg.segments_warp_threads / 32 : kMaxWarps) - 1;
+    // Batches of a multi-batch call overlap (late dependency wait).  Grid worlds: a block of the next launch fits beside
+    // a block of this one — blocks of 1024 / segments_multi threads with that share of the shared memory, one per SM in
+    // the grid, as k_states_warp does (4 M edges, 10 000 OBBs: 107 -> 91 us per batch).  Bits / brute worlds keep the
+    // 1024-thread block: their table and folded records take 65 KB of every block, so half an SM leaves 13 ring slots
+    // and 13 consumer warps (1 M segments, 256 OBBs: 42 us per batch against 22.7); with the late wait alone the next
+    // launch's block starts on an SM the moment this launch's block leaves it: 21.2 us (profiles/r02_segmulti_ab.log).
+    const int bps = (BP == EPP_BP_GRID && cfg.segments_multi > 1) ? (cfg.segments_multi > 4 ? 4 : cfg.segments_multi) : 1;
+    int cons = (bps > 1 ? 1024 / bps / 32 : (cfg.segments_warp_threads > 0 ? cfg.segments_warp_threads / 32 : kMaxWarps)) - 1;
     cons = cons < 1 ? 1 : (cons > kMaxWarps - 1 ? kMaxWarps - 1 : cons);
     if ((size_t)cons > chunks_per_block) cons = (int)chunks_per_block;
-    const size_t budget = (size_t)(228 * 1024) - 1024 - 4096;
+    const size_t budget = (size_t)(228 * 1024) / bps - 1024 - 4096;
     const size_t fixed = table_bytes + rec_bytes + (size_t)cons * kSegWarpBytes;
     if (fixed + 2 * (size_t)kSegSlotBytes > budget) return cudaSuccess;
     size_t slots = (budget - fixed) / kSegSlotBytes;
@@ -2702,7 +2712,7 @@ cudaError_t launch_segments_warp(const LaunchCfg &cfg, const WorldView &wv, cons
     lc.numAttrs = cfg.states_pdl ? 1 : 0;
     err = cudaLaunchKernelEx(&lc, k_segments_warp<BP, RS>, wv, d_a, d_b, n, can_pass_gate, in_smem ? 1 : 0, (uint32_t)slots,
                              (uint32_t)table_bytes, (uint32_t)rec_bytes, (uint32_t)(words / grid), (uint32_t)(words % grid),
-                             d_mask);
+                             (cfg.segments_late_wait && cfg.states_pdl) ? 1 : 0, d_mask);
     if (err != cudaSuccess) return err;
     launched = true;
     return cudaGetLastError();

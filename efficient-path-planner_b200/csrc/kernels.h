@@ -33,6 +33,8 @@ struct LaunchCfg {
     int states_bits1 = 1;           // warp form: single-word candidate masks for worlds of <= 32 OBBs
     int states_rec_smem = 1;        // warp-pipelined form: fold the world records into shared memory
     int states_rec_smem_max = 0;    // ... for worlds of up to this many OBBs (0: 256)
+    int segments_multi = 0;         // K2 warp form, set per launch by the multi-batch entry point: resident blocks per SM (0 / 1: one 1024-thread block)
+    int segments_late_wait = 0;     // K2 warp form, set per launch: this batch does not wait for the previous launch before streaming
     int poly_threads = 256;         // K3b: threads per block (256: 1 producer + 7 consumer warps; 512: 1 + 15)
     int poly_traj_per_warp = 0;     // K3b: trajectories per block (0: by batch size)
     int poly_balance = 1;           // K3b: 1 = trajectories per block chosen to balance the SMs (see launch_poly_trajectories)

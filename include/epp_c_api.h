@@ -170,6 +170,13 @@ int epp_check_states_mindist_dev(epp_world *w, const double *d_xyz, size_t n, do
                                  uint32_t *d_mask, void *stream);
 int epp_check_segments_dev(epp_world *w, const double *d_a, const double *d_b, size_t n,
                            int can_pass_gate, uint32_t *d_mask, void *stream);
+/* `batches` independent segment batches in one call (the edge counterpart of epp_check_states_multi_dev: a planner's
+ * batched MotionValidator::checkMotion, src/MotionValidator.cpp:9-17 -> World::checkRayValid, src/World.cpp:130-163).
+ * Same results as `batches` calls of epp_check_segments_dev; because the library knows the batches are independent
+ * and their inputs complete, a batch streams its end points while the previous one is still in its tail.  The masks
+ * must not overlap each other (EPP_ERR_INVALID_ARG); n[i] may be 0. */
+int epp_check_segments_multi_dev(epp_world *w, const double *const *d_a, const double *const *d_b, const size_t *n,
+                                 uint32_t *const *d_mask, int batches, int can_pass_gate, void *stream);
 /* d_first_invalid (nullable) is int64 per trajectory; d_traj_valid words must be zeroed by
  * the callee (they are). */
 int epp_check_trajectories_dev(epp_world *w, const double *d_col_major, size_t n_traj, size_t rows,

@@ -956,6 +956,37 @@ def test_multi_batch_call_equals_single_calls(oracle, config, which):
         gw.check_states_multi_dev([batches[2], batches[3]], [masks[2], masks[2]])
 
 
+@pytest.mark.parametrize("which", ["track", "w256", "w10k"])
+def test_multi_batch_segment_call_equals_single_calls(oracle, config, which):
+    """epp_check_segments_multi_dev: independent segment batches in one call (half-SM blocks, dependency wait at the
+    kernel's end from the second batch on).  Every batch's mask must equal the single-call mask and the oracle's — brute,
+    bits and grid worlds, warp-form and direct-form sizes, ragged tails, both canPassGate values, run repeatedly;
+    overlapping masks are refused."""
+    import torch
+    g, o, lo, hi = {"track": lambda: worlds.track_world(config), "w256": worlds.world_256, "w10k": worlds.world_10k}[which]()
+    ow, gw = build_pair(oracle, epp_b200, config, g, o)
+    sizes = [1 << 20, 300_001, 4096, 100, 0, 1 << 19, 65_537, 1 << 20]
+    batches = [epp_b200.gen_segments_dev(5000 + k, 0, max(n, 1), lo, hi, 1.0) for k, n in enumerate(sizes)]
+    batches = [(a[:n].contiguous(), b[:n].contiguous()) for (a, b), n in zip(batches, sizes)]  # one of them is empty
+    masks = [torch.zeros(max((n + 31) // 32, 1), dtype=torch.int32, device="cuda") for n in sizes]
+    for cpg in (False, True):
+        singles = [gw.check_segments_dev(a, b, can_pass_gate=cpg) if n else None for (a, b), n in zip(batches, sizes)]
+        for _ in range(4):
+            for m in masks:
+                m.zero_()
+            gw.check_segments_multi_dev(batches, masks, can_pass_gate=cpg)
+            torch.cuda.synchronize()
+            for k, n in enumerate(sizes):
+                if n:
+                    assert torch.equal(masks[k][: (n + 31) // 32], singles[k]), (which, cpg, k)
+        for k in (1, 3, 6):
+            a, b = batches[k]
+            want = ow.check_segments(a.cpu().numpy().reshape(-1, 3), b.cpu().numpy().reshape(-1, 3), cpg, threads=8)
+            assert mismatches(masks[k].cpu().numpy().view(np.uint32)[: want.size], want) == 0
+    with pytest.raises(epp_b200.EppError, match="overlap"):
+        gw.check_segments_multi_dev([batches[2], batches[3]], [masks[2], masks[2]])
+
+
 def test_gather_bulk_form_logical_ranks(oracle, config, track):
     """Large slots take the bulk form of the exchange (the slot is copied straight into the peers' gathered buffers,
     fence, header): here forced for a small batch through the knob, 3 logical ranks on one GPU, states and segments,
