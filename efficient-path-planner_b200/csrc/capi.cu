@@ -52,49 +52,49 @@ struct Knob {
 };
 Knob g_knobs[] = {
     {"states_blocks_per_sm", {8}},       // direct form of K1: persistent blocks per SM
-    {"segments_blocks_per_sm", {4}},
+    {"segments_blocks_per_sm", {4}},     // direct forms of K2: persistent blocks per SM
     {"segments_variant", {0}},           // 0: auto, 1: direct form with records in global memory, 2: warp-pipelined, 3: direct forms only
-    {"segments_warp_min_n", {32768}},
-    {"segments_warp_threads", {1024}},
-    {"segments_warp_slots", {0}},
+    {"segments_warp_min_n", {32768}},    // K2: batches from this size up take the warp-pipelined form
+    {"segments_warp_threads", {1024}},   // K2 warp form: threads per block (1 producer warp + consumers)
+    {"segments_warp_slots", {0}},        // K2 warp form: ring slots (0: all that fit, up to 64)
     {"segments_block", {0}},             // k_segments_rs threads per block: 256, 512, 1024; 0 = by batch size
     {"traj_variant", {0}},               // pre-sampled trajectories: 0 auto (warp-pipelined), 1 direct form only
     {"states_variant", {0}},             // 0: auto, 1: direct, 3: warp-pipelined
     {"states_per_thread", {0}},          // warp form: mask words per chunk (4 default, 8)
-    {"states_warp_blocks_per_sm", {1}},
-    {"states_warp_threads", {1024}},
-    {"states_warp_log2_slots", {0}},
-    {"states_warp_min_n", {4096}},
-    {"states_rec_smem", {1}},
+    {"states_warp_blocks_per_sm", {1}},  // K1 warp form: resident blocks per SM
+    {"states_warp_threads", {1024}},     // K1 warp form: threads per block (1 producer warp + consumers)
+    {"states_warp_log2_slots", {0}},     // K1 warp form: ring slots (0: all that fit)
+    {"states_warp_min_n", {4096}},       // K1: batches from this size up take the warp-pipelined form
+    {"states_rec_smem", {1}},            // K1 warp form: folded OBB records in shared memory for small worlds
     {"states_rec_smem_max", {0}},        // 0: 256 OBBs
-    {"states_bits1", {1}},
-    {"states_pdl", {1}},
-    {"states_late_wait", {1}},
-    {"states_multi_blocks_per_sm", {2}},
+    {"states_bits1", {1}},               // worlds of <= 32 OBBs: one-word bin rows (PointWorld<kBpBits1>)
+    {"states_pdl", {1}},                 // programmatic dependent launch for the warp forms of K1 / K2
+    {"states_late_wait", {1}},           // multi-batch calls: batches after the first do not wait for the previous launch before streaming
+    {"states_multi_blocks_per_sm", {2}}, // multi-batch state calls: resident blocks per SM (threads per block = 1024 / this)
     {"segments_multi_blocks_per_sm", {2}}, // multi-batch segment calls: resident blocks per SM (threads per block = 1024 / this; 1: one 1024-thread block)
-    {"states_multi_grid_per_sm", {1}},   // multi-batch calls: blocks per SM in each launch's grid (0: all that are resident) // multi-batch calls: resident blocks per SM (threads per block = 1024 / this)           // multi-batch calls: batches after the first do not wait for the previous launch before streaming
+    {"states_multi_grid_per_sm", {1}},   // multi-batch calls: blocks per SM in each launch's grid (0: all that are resident)
     {"states_debug", {0}},               // profiling builds only
-    {"poly_traj_per_warp", {0}},
+    {"poly_traj_per_warp", {0}},         // K3b: trajectories per block, 0 = by batch size
     {"poly_balance", {1}},               // K3b: trajectories per block of big batches chosen to balance the SMs (0: round-2 halving rule)
     {"poly_ring", {0}},                  // K3b: rounds of parked samples per block (2 .. 8; 0 = by variant)
     {"poly_blocks_per_sm", {0}},         // K3b, 256-thread blocks: 5 (48 registers per thread), 4 (64 registers), 0 = by batch size
     {"poly_wait", {0}},                  // K3b: 1 = consumers sleep on the round's barrier, 0 = nanosleep poll
-    {"poly_threads", {256}},             // K3b: threads per block, 256 or 512         // K3b: trajectories per warp, 0 = by batch size
+    {"poly_threads", {256}},             // K3b: threads per block, 256 or 512
     {"gather_group_chunks", {9}},        // fused exchange: chunks per NVLink run (1: every chunk alone)
     {"gather_bulk_min_words", {65536}},  // exchange: slots from this many words up are copied straight into the peers' buffers (0: never)
     {"gather_debug", {0}},               // profiling only: 1 no wait/unpack, 2 no peer stores
     {"sm_limit", {0}},                   // 0: all SMs; > 0: size grids for this many SMs (several ranks on one GPU in tests)
     {"bits_bins", {0}},                  // 0: by world size
-    {"grid_max_cells", {1 << 22}},
-    {"grid_occ_kb", {72}},
+    {"grid_max_cells", {1 << 22}},       // grid broad phase: upper bound on cells; read at commit
+    {"grid_occ_kb", {72}},               // shared-memory budget of the grid's occupancy bitmap; read at commit
     {"grid_cell_recs", {1}},             // grid: candidates read from records stored in cell order (0: item -> AabbRec -> ObbRec); read at commit
     {"bits_range_d", {5}},               // bits broad phase, rays: (first bin, span) rows for boxes spanning < d bins on x and y (0: cumulative rows only); read at commit
     {"segments_recs_at_commit", {1}},    // K2: folded records for both canPassGate values built at commit (0: folded per block); read at commit
     {"bits_cmask", {1}},                 // bits broad phase, W > 1: coarse-cell word masks (0: round-1 summaries); read at commit
     {"morton_sort", {1}},                // device records along a Morton curve (worlds of > 32 OBBs); read at commit
     {"single_mailbox", {1}},             // epp_is_valid / epp_check_motion through the resident mailbox warp (0: launch + sync per call)
-    {"single_mailbox_idle_us", {1000}},  // the mailbox warp leaves after this long without a request               // shared-memory budget of the grid's occupancy bitmap
-    {"bits_max_obbs", {1024}},
+    {"single_mailbox_idle_us", {1000}},  // the mailbox warp leaves after this long without a request
+    {"bits_max_obbs", {1024}},           // worlds above this many OBBs take the grid (auto) / are refused for EPP_BP_BITS; at most 1024
 };
 
 std::atomic<int> *knob(const char *name)
