@@ -343,8 +343,8 @@ def test_polynomial_sweep_truncation_and_block_shapes(oracle, config, track, G):
 @pytest.mark.parametrize("G", [0, 4, 14])
 def test_polynomial_sweep_segment_shapes(oracle, config, track, G):
     """K3b over ordinary segments (~125 rows each), segments of a dozen rows, segments shorter than one sampling step
-    (several segment changes between two rows), with rings of 4 and 2 rounds and consumers that sleep on the round's
-    barrier (knob poly_wait) or poll."""
+    (several segment changes between two rows), with rings of 4 and 2 rounds, consumers that sleep on the round's
+    barrier (knob poly_wait) or poll, and both register shapes of the kernel (knob poly_blocks_per_sm)."""
     g, o, lo, hi = track
     ow, gw = build_pair(oracle, epp_b200, config, g, o)
     cases = []
@@ -356,12 +356,14 @@ def test_polynomial_sweep_segment_shapes(oracle, config, track, G):
     cases.append((coeffs, np.ascontiguousarray(T), T.sum(axis=1) / 599.0))
     for ring in (4, 2):
         epp_b200.set_tuning("poly_wait", 1 if ring == 2 else 0)
+        epp_b200.set_tuning("poly_blocks_per_sm", 4 if ring == 2 else 5)  # 64-register / 48-register threads
         epp_b200.set_tuning("poly_traj_per_warp", G)
         epp_b200.set_tuning("poly_ring", ring)
         try:
             got = [gw.check_poly_trajectories(c, T, dt, 0.15, max_samples=1024) for c, T, dt in cases]
         finally:
             epp_b200.set_tuning("poly_wait", 0)
+            epp_b200.set_tuning("poly_blocks_per_sm", 0)
             epp_b200.set_tuning("poly_traj_per_warp", 0)
             epp_b200.set_tuning("poly_ring", 0)
         for (c, T, dt), (valid, smask, cnt, first) in zip(cases, got):
@@ -373,6 +375,36 @@ def test_polynomial_sweep_segment_shapes(oracle, config, track, G):
                 rows += n
                 rows_valid += int(np.unpackbits(np.asarray(m, np.uint32).view(np.uint8)).sum())
             assert 0 < rows_valid < rows  # both verdicts occur among the rows
+
+
+def test_polynomial_sweep_launch_shapes_agree(oracle, config):
+    """A batch large enough for the launcher's batch-size rules (one wave of 64-register blocks by default; 48-register
+    blocks; the halving rule; several waves of 16): every shape gives the same words, and the oracle's on a sample."""
+    g, o, lo, hi = worlds.world_256()
+    ow, gw = build_pair(oracle, epp_b200, config, g, o)
+    n_traj = 7400
+    coeffs, T, dt = worlds.rest_to_rest_trajectories(n_traj, 4, lo, hi, seed=911, n_samples=96, max_hop=3.0)
+    shapes = [{}, {"poly_blocks_per_sm": 5}, {"poly_balance": 0}, {"poly_traj_per_warp": 16, "poly_ring": 3}]
+    results = []
+    for knobs in shapes:
+        for k, v in knobs.items():
+            epp_b200.set_tuning(k, v)
+        try:
+            results.append(gw.check_poly_trajectories(coeffs, T, dt, 0.1, max_samples=128))
+        finally:
+            for k in knobs:
+                epp_b200.set_tuning(k, {"poly_balance": 1}.get(k, 0))
+    for r in results[1:]:
+        for got, want in zip(r, results[0]):
+            assert np.array_equal(got, want)
+    valid, smask, ns, first = results[0]
+    n_valid = 0
+    for t in range(0, n_traj, 37):
+        ok, m, n, f = ow.check_poly_traj(coeffs[t], T[t], dt[t], 0.1, max_samples=128)
+        assert ns[t] == n and np.array_equal(smask[t], m) and first[t] == f
+        assert bool(valid[t >> 5] >> (t & 31) & 1) is ok
+        n_valid += ok
+    assert 0 < n_valid < len(range(0, n_traj, 37))
 
 
 def test_device_buffers_and_generators(oracle, config, track):
