@@ -77,9 +77,9 @@ Knob g_knobs[] = {
     {"poly_traj_per_warp", {0}},         // K3b: trajectories per block, 0 = by batch size
     {"poly_balance", {1}},               // K3b: trajectories per block of big batches chosen to balance the SMs (0: round-2 halving rule)
     {"poly_ring", {0}},                  // K3b: rounds of parked samples per block (2 .. 8; 0 = by variant)
-    {"poly_blocks_per_sm", {0}},         // K3b, 256-thread blocks: 5 (48 registers per thread), 4 (64 registers), 0 = by batch size
+    {"poly_blocks_per_sm", {0}},         // K3b: 4 = 256-thread blocks of 64-register threads, 5 = never those, 0 = by batch size
     {"poly_wait", {0}},                  // K3b: 1 = consumers sleep on the round's barrier, 0 = nanosleep poll
-    {"poly_threads", {256}},             // K3b: threads per block, 256 or 512
+    {"poly_threads", {0}},               // K3b: threads per block: 0 = by batch size; 256 (48 registers, 5 per SM), 224, 192, 512
     {"gather_group_chunks", {9}},        // fused exchange: chunks per NVLink run (1: every chunk alone)
     {"gather_bulk_min_words", {65536}},  // exchange: slots from this many words up are copied straight into the peers' buffers (0: never)
     {"gather_debug", {0}},               // profiling only: 1 no wait/unpack, 2 no peer stores

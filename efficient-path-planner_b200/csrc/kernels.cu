@@ -2895,13 +2895,21 @@ cudaError_t launch_poly_trajectories(const LaunchCfg &cfg, const WorldView &wv_i
     //    (2000 trajectories: G = 4, 88 us; G = 14 would leave one block per SM: 94 us).
     int G = cfg.poly_traj_per_warp;
     const size_t sms = (size_t)(cfg.sm_count > 0 ? cfg.sm_count : 148);
+    // Block shapes (threads x resident blocks per SM, registers per thread): 256 x 4, 63 registers ("wide": batches that
+    // run as one wave); 224 x 5, 56 registers (1 producer + 6 consumer warps; everything else by default: no spills,
+    // where 256 x 5 at 48 registers reloads spilled loop constants in every work item — 40 000 trajectories 578 -> 515 us,
+    // 20 000: 306 -> 290, 2 000: 90 -> 86; 10 000 as one wave: 168 against the wide shape's 160;
+    // profiles/r02_slim_ab.log); on request (knob poly_threads) 192 x 6 at 56 registers (40 000: 509 us, 20 000: 296),
+    // 256 x 5 at 48 and 512 x 2.
     const bool big = cfg.poly_threads >= 512;
-    bool wide = !big && cfg.poly_blocks_per_sm == 4; // 64 registers per thread, 4 resident blocks
-    const bool wide_auto = !big && cfg.poly_blocks_per_sm == 0;
+    const bool legacy = cfg.poly_threads == 256; // 256 x 5, 48 registers
+    int slim = (cfg.poly_threads == 224 || cfg.poly_threads == 192) ? cfg.poly_threads : 0;
+    bool wide = !big && !slim && cfg.poly_blocks_per_sm == 4; // 64 registers per thread, 4 resident blocks
+    const bool wide_auto = !big && !slim && !legacy && cfg.poly_blocks_per_sm == 0;
     bool one_wave = false;
     if (G <= 0 && cfg.poly_balance && n_traj >= 12 * 4 * sms) {
         if (wide_auto) wide = n_traj <= 18 * 4 * sms;
-        const size_t resident = (size_t)(big ? 2 : (wide ? 4 : 5)) * sms;
+        const size_t resident = (size_t)(big ? 2 : (slim == 192 ? 6 : (wide ? 4 : 5))) * sms;
         one_wave = n_traj <= 18 * resident;
         G = one_wave ? (int)((n_traj + resident - 1) / resident) : 16;
         G = (G + 1) & ~1; // pairs of trajectories are the consumers' work items
@@ -2910,6 +2918,7 @@ cudaError_t launch_poly_trajectories(const LaunchCfg &cfg, const WorldView &wv_i
         while (G > 4 && (n_traj + G - 1) / (size_t)G < sms * 4) G >>= 1;
     }
     G = G > 32 ? 32 : (G < 1 ? 1 : G);
+    if (!big && !wide && !legacy && !slim) slim = 224;
     int ring = cfg.poly_ring > 0 ? cfg.poly_ring : (wide && one_wave ? 6 : 4);
     ring = ring < 2 ? 2 : (ring > kPolyRingMax ? kPolyRingMax : ring);
     const unsigned grid = (unsigned)((n_traj + G - 1) / G);
@@ -2921,9 +2930,11 @@ cudaError_t launch_poly_trajectories(const LaunchCfg &cfg, const WorldView &wv_i
         auto kern = big    ? (n10 ? k_poly_traj<BP, true, 512> : k_poly_traj<BP, false, 512>)
                     : wide ? (n10 ? k_poly_traj<BP, true, 256, 4> : k_poly_traj<BP, false, 256, 4>)
                            : (n10 ? k_poly_traj<BP, true, 256> : k_poly_traj<BP, false, 256>);
+        if (slim == 224) kern = n10 ? k_poly_traj<BP, true, 224, 5> : k_poly_traj<BP, false, 224, 5>;
+        if (slim == 192) kern = n10 ? k_poly_traj<BP, true, 192, 6> : k_poly_traj<BP, false, 192, 6>;
         err = ensure_smem(kern, total);
         if (err == cudaSuccess) {
-            kern<<<grid, big ? 512 : 256, total, stream>>>(wv, d_coeffs, d_durations, d_dt, n_traj, n_segments, n_coeffs,
+            kern<<<grid, big ? 512 : (slim ? slim : 256), total, stream>>>(wv, d_coeffs, d_durations, d_dt, n_traj, n_segments, n_coeffs,
                                                         min_distance, max_samples, in_smem ? 1 : 0, G, (uint32_t)table_bytes,
                                                         ring, cfg.poly_wait ? 1 : 0, d_sample_mask, d_n_samples, d_first_scratch);
             err = cudaGetLastError();

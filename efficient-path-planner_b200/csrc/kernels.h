@@ -35,11 +35,11 @@ struct LaunchCfg {
     int states_rec_smem_max = 0;    // ... for worlds of up to this many OBBs (0: 256)
     int segments_multi = 0;         // K2 warp form, set per launch by the multi-batch entry point: resident blocks per SM (0 / 1: one 1024-thread block)
     int segments_late_wait = 0;     // K2 warp form, set per launch: this batch does not wait for the previous launch before streaming
-    int poly_threads = 256;         // K3b: threads per block (256: 1 producer + 7 consumer warps; 512: 1 + 15)
+    int poly_threads = 0;           // K3b: threads per block (0: by batch size, 256 x 4 or 224 x 5 per SM; 256 / 224 / 192 / 512 force a shape)
     int poly_traj_per_warp = 0;     // K3b: trajectories per block (0: by batch size)
     int poly_balance = 1;           // K3b: 1 = trajectories per block chosen to balance the SMs (see launch_poly_trajectories)
     int poly_ring = 0;              // K3b: rounds of parked samples per block (2 .. 8; 0 = 4, or 6 with 64-register threads)
-    int poly_blocks_per_sm = 0;     // K3b, 256-thread blocks: 5 resident blocks of 48-register threads, 4 of 64, 0 = by batch size
+    int poly_blocks_per_sm = 0;     // K3b: 4 = 256-thread blocks of 64-register threads (4 resident), 5 = never those, 0 = by batch size
     int poly_wait = 0;              // K3b: consumers sleep on the round's barrier (1) or poll with nanosleep (0)
     int gather_group_chunks = 8;    // fused exchange: chunks whose mask words travel to a peer in one run (1: each chunk alone)
     int gather_bulk_min_words = 65536; // slots from this size up: the slot is copied straight into the peers' gathered buffers

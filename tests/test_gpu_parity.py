@@ -356,7 +356,8 @@ def test_polynomial_sweep_segment_shapes(oracle, config, track, G):
     cases.append((coeffs, np.ascontiguousarray(T), T.sum(axis=1) / 599.0))
     for ring in (4, 2):
         epp_b200.set_tuning("poly_wait", 1 if ring == 2 else 0)
-        epp_b200.set_tuning("poly_blocks_per_sm", 4 if ring == 2 else 5)  # 64-register / 48-register threads
+        epp_b200.set_tuning("poly_blocks_per_sm", 4 if ring == 2 else 5)  # 256 x 4 (64 registers) / the other shapes
+        epp_b200.set_tuning("poly_threads", {0: 0, 4: 256, 14: 192}[G] if ring == 4 else 0)  # 224 x 5, 256 x 5, 192 x 6
         epp_b200.set_tuning("poly_traj_per_warp", G)
         epp_b200.set_tuning("poly_ring", ring)
         try:
@@ -364,6 +365,7 @@ def test_polynomial_sweep_segment_shapes(oracle, config, track, G):
         finally:
             epp_b200.set_tuning("poly_wait", 0)
             epp_b200.set_tuning("poly_blocks_per_sm", 0)
+            epp_b200.set_tuning("poly_threads", 0)
             epp_b200.set_tuning("poly_traj_per_warp", 0)
             epp_b200.set_tuning("poly_ring", 0)
         for (c, T, dt), (valid, smask, cnt, first) in zip(cases, got):
@@ -378,13 +380,15 @@ def test_polynomial_sweep_segment_shapes(oracle, config, track, G):
 
 
 def test_polynomial_sweep_launch_shapes_agree(oracle, config):
-    """A batch large enough for the launcher's batch-size rules (one wave of 64-register blocks by default; 48-register
-    blocks; the halving rule; several waves of 16): every shape gives the same words, and the oracle's on a sample."""
+    """A batch large enough for the launcher's batch-size rules (one wave of 256 x 4 blocks of 64-register threads by
+    default; 224 x 5; 256 x 5 at 48 registers; 192 x 6; 512 x 2; the halving rule; several waves of 16): every shape
+    gives the same words, and the oracle's on a sample."""
     g, o, lo, hi = worlds.world_256()
     ow, gw = build_pair(oracle, epp_b200, config, g, o)
     n_traj = 7400
     coeffs, T, dt = worlds.rest_to_rest_trajectories(n_traj, 4, lo, hi, seed=911, n_samples=96, max_hop=3.0)
-    shapes = [{}, {"poly_blocks_per_sm": 5}, {"poly_balance": 0}, {"poly_traj_per_warp": 16, "poly_ring": 3}]
+    shapes = [{}, {"poly_blocks_per_sm": 5}, {"poly_threads": 256}, {"poly_threads": 192}, {"poly_threads": 512},
+              {"poly_balance": 0}, {"poly_traj_per_warp": 16, "poly_ring": 3}]
     results = []
     for knobs in shapes:
         for k, v in knobs.items():
