@@ -37,6 +37,26 @@ def test_header_symbols_are_exported():
     assert set(epp_b200.SIGNATURES) == declared
 
 
+def test_header_constants_match_the_binding():
+    """Limits the header states are the ones the Python layer repeats."""
+    text = open(os.path.join(ROOT, "include", "epp_c_api.h")).read()
+    m = re.search(r"#define\s+EPP_STATIC_MAX_TRAJECTORIES\s+(\d+)", text)
+    assert m and int(m.group(1)) == epp_b200.STATIC_MAX_TRAJECTORIES
+
+
+def test_epp_tune_environment_sets_knobs():
+    """EPP_TUNE="knob=value,..." is applied when the library is loaded; an unknown knob is an error, not ignored."""
+    import subprocess
+    import sys
+    code = "import sys; sys.path.insert(0, %r); import epp_b200; print(epp_b200.get_tuning('poly_ring'), epp_b200.get_tuning('poly_wait'))" % ROOT
+    env = dict(os.environ, EPP_TUNE="poly_ring=3, poly_wait=1")
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True)
+    assert out.returncode == 0 and out.stdout.split() == ["3", "1"], out.stderr
+    env = dict(os.environ, EPP_TUNE="no_such_knob=1")
+    out = subprocess.run([sys.executable, "-c", code], env=env, capture_output=True, text=True)
+    assert out.returncode != 0 and "no_such_knob" in out.stderr
+
+
 @pytest.mark.parametrize("which", ["track", "w256", "w10k"])
 def test_world_records_match_oracle_bit_for_bit(oracle, config, which):
     if which == "track":
